@@ -1,0 +1,518 @@
+// gemm_sm100.cu — persistent, warp-specialised bf16 GEMM on tcgen05 tensor cores (sm_100a).
+//
+// Replaces the cuBLAS GEMMs the reference reaches through torch.nn.Linear in
+// transformers' BertSelfAttention / BertSelfOutput / BertIntermediate / BertOutput
+// (site-packages/transformers/models/bert/modeling_bert.py:179-181,294-298,339-342,352-356)
+// and their autograd backward (reference trainer.py:197-204).
+//
+// CTA = 256 threads, one CTA per SM, static round-robin tile schedule:
+//   warp 0 (1 thread)  TMA producer: 4-stage ring of {A 128x64, B 256x64} bf16 tiles, 128B swizzle
+//   warp 1 (1 thread)  MMA issuer  : tcgen05.mma cta_group::1 kind::f16, M=128 N=256 K=16, fp32 in TMEM
+//   warp 2             TMEM allocator (512 columns = two 128x256 fp32 accumulators, double-buffered)
+//   warps 4-7          epilogue    : tcgen05.ld -> registers -> fused op -> swizzled smem -> TMA store
+// Operands may be K-major or MN-major (instruction-descriptor major bits + smem descriptor
+// strides), so forward, dgrad and wgrad all read the tensors in the layout PyTorch gives them.
+#include "gemm_sm100.cuh"
+
+#include <cstdarg>
+#include <cstdio>
+#include <mutex>
+
+namespace bqa {
+
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_N = 256;
+constexpr int BLOCK_K = 64;
+constexpr int STAGES = 4;
+constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KiB
+constexpr int B_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;  // 32 KiB
+constexpr int C_STAGE_BYTES = BLOCK_M * 128;          // 128 rows x 128 B (64 bf16 or 32 fp32)
+constexpr int SMEM_BARRIER_BYTES = 256;
+constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + 2 * C_STAGE_BYTES + SMEM_BARRIER_BYTES;
+constexpr int SMEM_ALLOC = SMEM_BYTES + 1024;  // slack for manual 1024-byte alignment
+constexpr int TMEM_COLS = 512;
+constexpr int NUM_THREADS = 256;
+constexpr int EPI_THREADS = 128;
+
+static_assert(SMEM_ALLOC <= 232448, "exceeds the 227 KiB per-CTA shared memory limit");
+
+template <int A_MN, int B_MN, int EPI>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
+            const GemmArgs args) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + STAGES * A_STAGE_BYTES;
+  uint8_t* sC = sB + STAGES * B_STAGE_BYTES;
+  uint64_t* bar_full = reinterpret_cast<uint64_t*>(sC + 2 * C_STAGE_BYTES);
+  uint64_t* bar_empty = bar_full + STAGES;
+  uint64_t* bar_tfull = bar_empty + STAGES;
+  uint64_t* bar_tempty = bar_tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmC);
+    if (EPI == EPI_GELU_FWD) tma_prefetch_desc(&tmC2);
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&bar_full[i], 1);
+      mbar_init(&bar_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bar_tfull[i], 1);
+      mbar_init(&bar_tempty[i], EPI_THREADS);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int tiles_mn = args.m_tiles * args.n_tiles;
+  const int num_tiles = tiles_mn * args.k_splits;
+
+  if (warp == 0 && lane == 0) {
+    // ------------------------------ TMA producer ------------------------------
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int split = tile / tiles_mn;
+      const int mn = tile - split * tiles_mn;
+      const int m0 = (mn / args.n_tiles) * BLOCK_M;
+      const int n0 = (mn % args.n_tiles) * BLOCK_N;
+      const int kb0 = split * args.kb_per_split;
+      const int kb1 = min(kb0 + args.kb_per_split, args.kb_total);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&bar_empty[stage], phase ^ 1u);
+        mbar_arrive_expect_tx(&bar_full[stage], A_STAGE_BYTES + B_STAGE_BYTES);
+        const int k0 = kb * BLOCK_K;
+        uint8_t* a_dst = sA + stage * A_STAGE_BYTES;
+        uint8_t* b_dst = sB + stage * B_STAGE_BYTES;
+        if (A_MN) {
+#pragma unroll
+          for (int i = 0; i < BLOCK_M / 64; ++i)
+            tma_load_2d(a_dst + i * (BLOCK_K * 128), &tmA, m0 + i * 64, k0, &bar_full[stage]);
+        } else {
+          tma_load_2d(a_dst, &tmA, k0, m0, &bar_full[stage]);
+        }
+        if (B_MN) {
+#pragma unroll
+          for (int i = 0; i < BLOCK_N / 64; ++i)
+            tma_load_2d(b_dst + i * (BLOCK_K * 128), &tmB, n0 + i * 64, k0, &bar_full[stage]);
+        } else {
+          tma_load_2d(b_dst, &tmB, k0, n0, &bar_full[stage]);
+        }
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ------------------------------ MMA issuer ------------------------------
+    constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BLOCK_N, A_MN, B_MN);
+    int stage = 0;
+    uint32_t phase = 0;
+    uint32_t it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int split = tile / tiles_mn;
+      const int kb0 = split * args.kb_per_split;
+      const int kb1 = min(kb0 + args.kb_per_split, args.kb_total);
+      const uint32_t as = it & 1u;
+      const uint32_t aphase = (it >> 1) & 1u;
+      mbar_wait(&bar_tempty[as], aphase ^ 1u);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&bar_full[stage], phase);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(sA + stage * A_STAGE_BYTES);
+        const uint32_t b_addr = smem_u32(sB + stage * B_STAGE_BYTES);
+#pragma unroll
+        for (int k = 0; k < BLOCK_K / 16; ++k) {
+          const uint64_t adesc = A_MN ? umma_desc_mnmajor(a_addr + k * 2048, BLOCK_K * 128)
+                                      : umma_desc_kmajor(a_addr + k * 32);
+          const uint64_t bdesc = B_MN ? umma_desc_mnmajor(b_addr + k * 2048, BLOCK_K * 128)
+                                      : umma_desc_kmajor(b_addr + k * 32);
+          umma_bf16(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&bar_empty[stage]);
+        if (kb == kb1 - 1) umma_commit(&bar_tfull[as]);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------ epilogue ------------------------------
+    const int ew = warp - 4;          // == warp % 4: the TMEM lane quarter this warp may read
+    const int row = ew * 32 + lane;   // accumulator row owned by this thread
+    const bool leader = (threadIdx.x == NUM_THREADS - EPI_THREADS);
+    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(ew * 32) << 16);
+    constexpr int CHUNK_COLS = (EPI == EPI_F32_ADD) ? 32 : 64;
+    constexpr int NCHUNK = BLOCK_N / CHUNK_COLS;
+    uint32_t it = 0;
+    uint32_t nstore = 0;  // staging-buffer ring position (EPI with a single output)
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int split = tile / tiles_mn;
+      const int mn = tile - split * tiles_mn;
+      const int m0 = (mn / args.n_tiles) * BLOCK_M;
+      const int n0 = (mn % args.n_tiles) * BLOCK_N;
+      const uint32_t as = it & 1u;
+      const uint32_t aphase = (it >> 1) & 1u;
+      mbar_wait(&bar_tfull[as], aphase);
+      tc_fence_after();
+      const int m = m0 + row;
+      const bool row_ok = m < args.M;
+#pragma unroll 1
+      for (int c = 0; c < NCHUNK; ++c) {
+        uint8_t* stage0;
+        uint8_t* stage1 = nullptr;
+        if (EPI == EPI_GELU_FWD) {
+          if (leader) tma_wait_group_read<0>();
+          stage0 = sC;
+          stage1 = sC + C_STAGE_BYTES;
+        } else {
+          if (leader) tma_wait_group_read<1>();
+          stage0 = sC + (nstore & 1u) * C_STAGE_BYTES;
+          ++nstore;
+        }
+        named_bar_sync(1, EPI_THREADS);
+#pragma unroll
+        for (int half = 0; half < CHUNK_COLS / 32; ++half) {
+          uint32_t v[32];
+          tmem_ld_32x32(lane_base + as * BLOCK_N + c * CHUNK_COLS + half * 32, v);
+          tmem_wait_ld();
+          if (c == NCHUNK - 1 && half == CHUNK_COLS / 32 - 1) {
+            // accumulator fully drained into registers: hand the TMEM stage back to the MMA warp
+            tc_fence_before();
+            mbar_arrive(&bar_tempty[as]);
+          }
+          const int n = n0 + c * CHUNK_COLS + half * 32;
+          float f[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+
+          if (EPI == EPI_F32_ADD) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              float4 o = make_float4(f[4 * q], f[4 * q + 1], f[4 * q + 2], f[4 * q + 3]);
+              *reinterpret_cast<float4*>(stage0 + row * 128 + ((q ^ (row & 7)) << 4)) = o;
+            }
+          } else {
+            if (EPI != EPI_GELU_BWD && args.bias != nullptr && n < args.N) {
+              const float4* bp = reinterpret_cast<const float4*>(args.bias + n);
+#pragma unroll
+              for (int q = 0; q < 8; ++q) {
+                const float4 b = __ldg(bp + q);
+                f[4 * q] += b.x;
+                f[4 * q + 1] += b.y;
+                f[4 * q + 2] += b.z;
+                f[4 * q + 3] += b.w;
+              }
+            }
+            if (EPI == EPI_LINEAR) {
+              if (args.drop.thresh != 0u) {
+                const uint32_t base_idx = static_cast<uint32_t>(m) * static_cast<uint32_t>(args.N) +
+                                          static_cast<uint32_t>(n);
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                  f[i] = drop_keep(args.drop, base_idx + i) ? f[i] * args.drop.scale : 0.0f;
+              }
+              if (args.residual != nullptr && row_ok && n < args.N) {
+                const uint4* rp =
+                    reinterpret_cast<const uint4*>(args.residual + static_cast<size_t>(m) * args.ld_res + n);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  const uint4 r = __ldg(rp + q);
+                  const float2 r0 = unpack_bf16x2(r.x), r1 = unpack_bf16x2(r.y);
+                  const float2 r2 = unpack_bf16x2(r.z), r3 = unpack_bf16x2(r.w);
+                  f[8 * q] += r0.x;
+                  f[8 * q + 1] += r0.y;
+                  f[8 * q + 2] += r1.x;
+                  f[8 * q + 3] += r1.y;
+                  f[8 * q + 4] += r2.x;
+                  f[8 * q + 5] += r2.y;
+                  f[8 * q + 6] += r3.x;
+                  f[8 * q + 7] += r3.y;
+                }
+              }
+            }
+            if (EPI == EPI_GELU_BWD) {
+              if (row_ok && n < args.N) {
+                const uint4* up =
+                    reinterpret_cast<const uint4*>(args.aux + static_cast<size_t>(m) * args.ld_aux + n);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  const uint4 r = __ldg(up + q);
+                  const float2 u0 = unpack_bf16x2(r.x), u1 = unpack_bf16x2(r.y);
+                  const float2 u2 = unpack_bf16x2(r.z), u3 = unpack_bf16x2(r.w);
+                  f[8 * q] *= gelu_erf_grad(u0.x);
+                  f[8 * q + 1] *= gelu_erf_grad(u0.y);
+                  f[8 * q + 2] *= gelu_erf_grad(u1.x);
+                  f[8 * q + 3] *= gelu_erf_grad(u1.y);
+                  f[8 * q + 4] *= gelu_erf_grad(u2.x);
+                  f[8 * q + 5] *= gelu_erf_grad(u2.y);
+                  f[8 * q + 6] *= gelu_erf_grad(u3.x);
+                  f[8 * q + 7] *= gelu_erf_grad(u3.y);
+                }
+              }
+            }
+            // bf16 pack: 32 values = 4 x 16 B, swizzled like the TMA store expects (SWIZZLE_128B)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              uint4 o;
+              o.x = pack_bf16x2(f[8 * q], f[8 * q + 1]);
+              o.y = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
+              o.z = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]);
+              o.w = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
+              const int j = half * 4 + q;
+              *reinterpret_cast<uint4*>(stage0 + row * 128 + ((j ^ (row & 7)) << 4)) = o;
+            }
+            if (EPI == EPI_GELU_FWD) {
+              // the reference applies GELU to the bf16-rounded pre-activation under autocast;
+              // here it is applied to the fp32 value, which is the more accurate of the two.
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                uint4 o;
+                o.x = pack_bf16x2(gelu_erf(f[8 * q]), gelu_erf(f[8 * q + 1]));
+                o.y = pack_bf16x2(gelu_erf(f[8 * q + 2]), gelu_erf(f[8 * q + 3]));
+                o.z = pack_bf16x2(gelu_erf(f[8 * q + 4]), gelu_erf(f[8 * q + 5]));
+                o.w = pack_bf16x2(gelu_erf(f[8 * q + 6]), gelu_erf(f[8 * q + 7]));
+                const int j = half * 4 + q;
+                *reinterpret_cast<uint4*>(stage1 + row * 128 + ((j ^ (row & 7)) << 4)) = o;
+              }
+            }
+          }
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(1, EPI_THREADS);
+        if (leader) {
+          const int nc = n0 + c * CHUNK_COLS;
+          if (nc < args.N) {
+            if (EPI == EPI_F32_ADD) {
+              tma_reduce_add_2d(&tmC, stage0, nc, m0);
+            } else {
+              tma_store_2d(&tmC, stage0, nc, m0);
+              if (EPI == EPI_GELU_FWD) tma_store_2d(&tmC2, stage1, nc, m0);
+            }
+          }
+          tma_commit_group();
+        }
+      }
+    }
+    if (leader) tma_wait_group<0>();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+template <int A_MN, int B_MN, int EPI>
+int launch_variant(const GemmPlan& plan, cudaStream_t stream) {
+  static bool configured = false;  // per-process; the attribute is per-device but all devices share the value
+  auto kfn = gemm_kernel<A_MN, B_MN, EPI>;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_ALLOC);
+    if (e != cudaSuccess) {
+      set_error("gemm: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+      return 1;
+    }
+    configured = true;
+  }
+  kfn<<<plan.grid, NUM_THREADS, SMEM_ALLOC, stream>>>(plan.tmA, plan.tmB, plan.tmC, plan.tmC2, plan.args);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("gemm: launch failed: %s", cudaGetErrorString(e));
+    return 1;
+  }
+  return 0;
+}
+
+}  // namespace
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+const char* last_error() { return g_err; }
+
+int encode_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t cols, uint64_t rows,
+                   uint64_t ld_elems, uint32_t box_cols, uint32_t box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (fn == nullptr) {
+    set_error("cuTensorMapEncodeTiled is unavailable (no CUDA driver?)");
+    return 1;
+  }
+  if ((reinterpret_cast<uintptr_t>(base) & 15u) != 0 || ((ld_elems * elem_bytes) & 15u) != 0) {
+    set_error("tensor map: base/stride must be 16-byte aligned (base=%p ld=%llu)", base,
+              (unsigned long long)ld_elems);
+    return 1;
+  }
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld_elems * static_cast<uint64_t>(elem_bytes)};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                  const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(2d) failed: CUresult %d (cols=%llu rows=%llu ld=%llu box=%ux%u)", (int)r,
+              (unsigned long long)cols, (unsigned long long)rows, (unsigned long long)ld_elems, box_cols,
+              box_rows);
+    return 1;
+  }
+  return 0;
+}
+
+int encode_tmap_3d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t d0, uint64_t d1, uint64_t d2,
+                   uint64_t stride1_elems, uint64_t stride2_elems, uint32_t b0, uint32_t b1, uint32_t b2) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (fn == nullptr) {
+    set_error("cuTensorMapEncodeTiled is unavailable (no CUDA driver?)");
+    return 1;
+  }
+  cuuint64_t dims[3] = {d0, d1, d2};
+  cuuint64_t strides[2] = {stride1_elems * static_cast<uint64_t>(elem_bytes),
+                           stride2_elems * static_cast<uint64_t>(elem_bytes)};
+  cuuint32_t box[3] = {b0, b1, b2};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(out, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3,
+                  const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(3d) failed: CUresult %d", (int)r);
+    return 1;
+  }
+  return 0;
+}
+
+int gemm_plan(GemmPlan* plan, const GemmProblem& p, int num_sms) {
+  if (p.M <= 0 || p.N <= 0 || p.K <= 0) {
+    set_error("gemm: empty problem %dx%dx%d", p.M, p.N, p.K);
+    return 1;
+  }
+  if ((p.N % 64) != 0) {
+    set_error("gemm: N=%d must be a multiple of 64", p.N);
+    return 1;
+  }
+  if (p.k_splits > 1 && p.epilogue != EPI_F32_ADD) {
+    set_error("gemm: split-K needs the fp32 reduce-add epilogue");
+    return 1;
+  }
+  const int a_mn = p.a_mn_major ? 1 : 0, b_mn = p.b_mn_major ? 1 : 0;
+  int rc = 0;
+  if (a_mn)
+    rc |= encode_tmap_2d(&plan->tmA, p.A, 2, p.M, p.K, p.lda, 64, BLOCK_K);
+  else
+    rc |= encode_tmap_2d(&plan->tmA, p.A, 2, p.K, p.M, p.lda, BLOCK_K, BLOCK_M);
+  if (b_mn)
+    rc |= encode_tmap_2d(&plan->tmB, p.B, 2, p.N, p.K, p.ldb, 64, BLOCK_K);
+  else
+    rc |= encode_tmap_2d(&plan->tmB, p.B, 2, p.K, p.N, p.ldb, BLOCK_K, BLOCK_N);
+  if (p.epilogue == EPI_F32_ADD)
+    rc |= encode_tmap_2d(&plan->tmC, p.C, 4, p.N, p.M, p.ldc, 32, BLOCK_M);
+  else
+    rc |= encode_tmap_2d(&plan->tmC, p.C, 2, p.N, p.M, p.ldc, 64, BLOCK_M);
+  if (p.epilogue == EPI_GELU_FWD) {
+    if (p.C2 == nullptr) {
+      set_error("gemm: EPI_GELU_FWD needs a second output");
+      return 1;
+    }
+    rc |= encode_tmap_2d(&plan->tmC2, p.C2, 2, p.N, p.M, p.ldc, 64, BLOCK_M);
+  } else {
+    plan->tmC2 = plan->tmC;
+  }
+  if (rc) return 1;
+
+  GemmArgs& a = plan->args;
+  a.M = p.M;
+  a.N = p.N;
+  a.K = p.K;
+  a.m_tiles = (p.M + BLOCK_M - 1) / BLOCK_M;
+  a.n_tiles = (p.N + BLOCK_N - 1) / BLOCK_N;
+  a.kb_total = (p.K + BLOCK_K - 1) / BLOCK_K;
+  int splits = p.k_splits < 1 ? 1 : p.k_splits;
+  if (splits > a.kb_total) splits = a.kb_total;
+  a.kb_per_split = (a.kb_total + splits - 1) / splits;
+  a.k_splits = (a.kb_total + a.kb_per_split - 1) / a.kb_per_split;
+  a.bias = p.bias;
+  a.residual = reinterpret_cast<const bf16*>(p.residual);
+  a.ld_res = p.ld_res;
+  a.aux = reinterpret_cast<const bf16*>(p.aux);
+  a.ld_aux = p.ld_aux;
+  a.drop = p.drop;
+  if (p.epilogue == EPI_GELU_BWD && p.aux == nullptr) {
+    set_error("gemm: EPI_GELU_BWD needs aux");
+    return 1;
+  }
+  plan->variant = a_mn | (b_mn << 1) | (p.epilogue << 2);
+  const long tiles = static_cast<long>(a.m_tiles) * a.n_tiles * a.k_splits;
+  plan->grid = static_cast<int>(tiles < num_sms ? tiles : num_sms);
+  return 0;
+}
+
+int gemm_launch(const GemmPlan& plan, cudaStream_t stream) {
+  switch (plan.variant) {
+    case 0 | (0 << 1) | (EPI_LINEAR << 2):
+      return launch_variant<0, 0, EPI_LINEAR>(plan, stream);
+    case 0 | (0 << 1) | (EPI_GELU_FWD << 2):
+      return launch_variant<0, 0, EPI_GELU_FWD>(plan, stream);
+    case 0 | (1 << 1) | (EPI_LINEAR << 2):
+      return launch_variant<0, 1, EPI_LINEAR>(plan, stream);
+    case 0 | (1 << 1) | (EPI_GELU_BWD << 2):
+      return launch_variant<0, 1, EPI_GELU_BWD>(plan, stream);
+    case 1 | (1 << 1) | (EPI_F32_ADD << 2):
+      return launch_variant<1, 1, EPI_F32_ADD>(plan, stream);
+    case 0 | (0 << 1) | (EPI_F32_ADD << 2):
+      return launch_variant<0, 0, EPI_F32_ADD>(plan, stream);
+    default:
+      set_error("gemm: unsupported variant a_mn=%d b_mn=%d epilogue=%d", plan.variant & 1, (plan.variant >> 1) & 1,
+                plan.variant >> 2);
+      return 1;
+  }
+}
+
+}  // namespace bqa
