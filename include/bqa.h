@@ -11,14 +11,17 @@
  * Each entry point cites the reference lines it replaces.
  *
  * Conventions: every function returns 0 on success, non-zero on failure with a message in
- * bqa_last_error() (thread-local).  All `void*` tensor arguments are DEVICE pointers unless
- * the name starts with `host_`.  `stream` is a cudaStream_t passed as void*.  The library
- * never takes ownership of caller memory and has no CPU fallback: without a usable CUDA
- * device every compute entry point fails.
+ * bqa_last_error() (thread-local).  All pointer arguments are DEVICE pointers unless the
+ * parameter is a struct passed by the host or its name starts with `host_`.  `stream` is a
+ * cudaStream_t passed as void*.  The library never takes ownership of caller memory, keeps
+ * bound pointers only between bqa_bind() and bqa_destroy(), allocates no device memory of
+ * its own, and has no CPU fallback: without a usable CUDA device every compute entry point
+ * fails.  One handle is driven by one host thread at a time.
  */
 #ifndef BQA_H_
 #define BQA_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #if defined(__GNUC__)
@@ -73,6 +76,138 @@ typedef struct bqa_gemm_desc {
 } bqa_gemm_desc;
 
 BQA_API int bqa_gemm_bf16(const bqa_gemm_desc* desc, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Fused self-attention (head dim 64, S <= 512).  Replaces BertSelfAttention's
+ * softmax(QK^T/8 + mask) -> dropout -> PV (modeling_bert.py:115-140,168-207) and its backward.
+ *   qkv  [B*S][3H] bf16 (Q | K | V slabs), ctx [B*S][H] bf16, lse2 [B][A][S] fp32
+ *   key_mask [B][S] uint8 (1 = attend) or NULL
+ *   backward: dctx [B*S][H] bf16 in, dqkv [B*S][3H] bf16 out, dsum [B][A][S] fp32 scratch
+ * ------------------------------------------------------------------------------------ */
+BQA_API int bqa_attention_forward(const void* qkv, void* ctx, float* lse2, const uint8_t* key_mask, int32_t B,
+                                  int32_t S, int32_t A, float dropout_p, uint64_t drop_seed, uint32_t drop_site,
+                                  void* stream);
+BQA_API int bqa_attention_backward(const void* qkv, const void* ctx, const float* lse2, const void* dctx,
+                                   void* dqkv, float* dsum, const uint8_t* key_mask, int32_t B, int32_t S,
+                                   int32_t A, float dropout_p, uint64_t drop_seed, uint32_t drop_site,
+                                   void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Row kernels (HBM-bound).  LayerNorm(eps) over H of bf16 rows with fp32 affine parameters
+ * (modeling_bert.py:111,297,355) and its backward; column sums for bias gradients.
+ * ------------------------------------------------------------------------------------ */
+BQA_API int bqa_layernorm_forward(const void* z, const float* gamma, const float* beta, void* y, int32_t T,
+                                  int32_t H, float eps, void* stream);
+/* dz_masked/dbias may be NULL.  dgamma/dbeta/dbias are accumulated into (+=). */
+BQA_API int bqa_layernorm_backward(const void* dy, const void* z, const float* gamma, void* dz, void* dz_masked,
+                                   float* dgamma, float* dbeta, float* dbias, int32_t T, int32_t H, float eps,
+                                   float drop_in_p, uint32_t drop_in_site, float drop_out_p,
+                                   uint32_t drop_out_site, uint64_t drop_seed, void* stream);
+BQA_API int bqa_colsum_bf16(const void* X, int32_t ld, float* out, int32_t T, int32_t N, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Optimizer: global-norm clip + HF AdamW(correct_bias=False) over flat fp32 buffers.
+ * Replaces torch.nn.utils.clip_grad_norm_ (trainer.py:221-225) and transformers.AdamW.step
+ * as constructed in modules/init.py:125-138 (two param groups, decoupled decay after the
+ * update, eps 1e-6, no bias correction) plus optimizer.zero_grad() (trainer.py:287).
+ * ------------------------------------------------------------------------------------ */
+typedef struct bqa_adamw_chunk { /* one run of elements of one parameter tensor */
+  uint64_t begin, end;           /* element range in the flat buffers, multiples of 4      */
+  float weight_decay;
+  int32_t group; /* index into the per-call lr[] array                                     */
+} bqa_adamw_chunk;
+
+/* *sumsq (device double) += sum(g[0..n)^2).  scratch: >= bqa_sumsq_scratch_floats() floats. */
+BQA_API int bqa_sumsq_scratch_floats(void);
+BQA_API int bqa_grad_sumsq(const float* g, uint64_t n, double* sumsq, float* scratch, void* stream);
+/* chunks: DEVICE array.  host_lr: HOST array of n_groups (<= 8) learning rates.
+ * max_grad_norm <= 0 disables clipping.  p_bf16 may be NULL.  zero_grad != 0 clears g. */
+BQA_API int bqa_clip_adamw(float* p, float* g, float* m, float* v, void* p_bf16, const bqa_adamw_chunk* chunks,
+                           int32_t n_chunks, const double* sumsq, float max_grad_norm, const float* host_lr,
+                           int32_t n_groups, float beta1, float beta2, float eps, int32_t zero_grad,
+                           void* stream);
+BQA_API int bqa_f32_to_bf16(const float* src, void* dst, uint64_t n, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Span decoding (modules/model/inference/predictor.py:114-120): per row, first-index arg max
+ * and max of the start and end logits, arg max / max probability of softmax(cls), and
+ * score = max_start + max_end - (start[0] + end[0]).
+ * ------------------------------------------------------------------------------------ */
+BQA_API int bqa_decode(const float* start, const float* end, const float* cls, int64_t* start_idx,
+                       int64_t* end_idx, int64_t* cls_idx, float* start_max, float* end_max, float* cls_prob,
+                       float* score, int32_t B, int32_t S, int32_t C, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * The model step.  Replaces BertForQuestionAnswering.forward (model.py:43-73 and, behind
+ * it, transformers BertModel.forward), WeightedLoss.__call__ (loss.py:78-100) and
+ * loss.backward() (trainer.py:197-204).
+ * ------------------------------------------------------------------------------------ */
+typedef struct bqa_config {
+  int32_t num_layers, hidden, heads, intermediate;
+  int32_t vocab, max_pos, type_vocab, num_labels;
+  float ln_eps, hidden_dropout, attn_dropout;
+} bqa_config;
+
+/* Element offsets of every parameter tensor inside the flat buffers (fp32 master, fp32
+ * gradient, bf16 shadow all share it).  Tensors are 128-element aligned; Q/K/V weights
+ * (and biases) of a layer are adjacent so that they form one [3H,H] matrix.  Order:
+ * embeddings, layer 0 .. L-1, pooler, heads — gradients become final in reverse order. */
+typedef struct bqa_layout {
+  int64_t word_emb, pos_emb, type_emb, emb_ln_g, emb_ln_b;
+  int64_t layer0, layer_stride;
+  int64_t qkv_w, qkv_b, ao_w, ao_b, ln1_g, ln1_b, i_w, i_b, o_w, o_b, ln2_g, ln2_b; /* within a layer */
+  int64_t pool_w, pool_b, span_w, span_b, cls_w, cls_b, regs_w, regs_b, rege_w, rege_b;
+  int64_t total; /* elements, multiple of 128 */
+} bqa_layout;
+
+typedef struct bqa_handle bqa_handle;
+
+BQA_API int bqa_param_layout(const bqa_config* cfg, bqa_layout* out);
+BQA_API int bqa_workspace_bytes(const bqa_config* cfg, int32_t B, int32_t S, int32_t training, uint64_t* out);
+BQA_API int bqa_create(const bqa_config* cfg, bqa_handle** out);
+BQA_API int bqa_destroy(bqa_handle* h);
+/* params/grads fp32 [total], params_bf16 bf16 [total]; grads may be NULL for inference.
+ * workspace: >= bqa_workspace_bytes for the largest (B, S, training) that will be used. */
+BQA_API int bqa_bind(bqa_handle* h, float* params, float* grads, void* params_bf16, void* workspace,
+                     uint64_t workspace_bytes);
+
+/* input_ids/token_type_ids int64 [B][S] (token_type_ids may be NULL = zeros), attention_mask
+ * uint8/bool [B][S] or NULL (= all ones), as produced by collate_fun
+ * (modules/model/dataset/split_dataset.py:480-520).  Outputs fp32: start/end [B][S],
+ * cls [B][num_labels], reg_start/reg_end [B] (after the sigmoid).  training != 0 applies
+ * dropout (streams derived from seed and step) and keeps activations for bqa_backward. */
+BQA_API int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_type_ids,
+                        const uint8_t* attention_mask, int32_t B, int32_t S, int32_t training, uint64_t seed,
+                        uint64_t step, float* start, float* end, float* cls, float* reg_start, float* reg_end,
+                        void* stream);
+
+enum bqa_cls_loss { BQA_CLS_SMOOTH = 0, BQA_CLS_CE = 1 };
+typedef struct bqa_loss_config {
+  float w_start, w_end, w_start_reg, w_end_reg, w_cls; /* init.py:19-38                       */
+  int32_t cls_loss;                                    /* params.loss: 'smooth' | 'ce'        */
+  float smooth_alpha;
+  const float* cls_weight; /* DEVICE [num_labels] fp32 or NULL (loss='ce' label weights)       */
+  float loss_scale;        /* 1 / batch_split (trainer.py:198); scales gradients only          */
+} bqa_loss_config;
+
+/* Loss of the last bqa_forward outputs against labels (int64 / fp32 [B]).  losses: DEVICE
+ * fp32[6] = {start_class, end_class, start_reg, end_reg, cls, total} in the key order of
+ * init_losses.  with_grad != 0 also stores d(total * loss_scale)/d(outputs) for bqa_backward. */
+BQA_API int bqa_loss(bqa_handle* h, const float* start, const float* end, const float* cls,
+                     const float* reg_start, const float* reg_end, const int64_t* y_start, const int64_t* y_end,
+                     const int64_t* y_cls, const float* y_reg_start, const float* y_reg_end,
+                     const bqa_loss_config* lc, int32_t with_grad, float* losses, void* stream);
+/* Alternative to bqa_loss(with_grad): supply d(loss)/d(outputs) computed elsewhere (autograd). */
+BQA_API int bqa_set_output_grads(bqa_handle* h, const float* d_start, const float* d_end, const float* d_cls,
+                                 const float* d_reg_start, const float* d_reg_end, void* stream);
+/* Backward phases: 0 = heads + pooler, 1..L = encoder layers L-1..0, L+1 = embeddings.
+ * Runs phases [first, last]; gradients are ACCUMULATED into the bound gradient buffer.  After
+ * phase k every parameter at or beyond the flat offset bqa_phase_grad_begin(k) is final. */
+BQA_API int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* stream);
+BQA_API int bqa_num_backward_phases(const bqa_handle* h);
+BQA_API int64_t bqa_phase_grad_begin(const bqa_handle* h, int32_t phase);
+/* Number of kernels launched by this handle since creation (bench.py's gpu_launches). */
+BQA_API int64_t bqa_launch_count(const bqa_handle* h);
 
 #ifdef __cplusplus
 }

@@ -5,3 +5,4 @@ The directory name carries a hyphen (it is fixed by the project layout), so impo
 ``__graft_entry__.load_package()`` which registers it as ``bqa_b200``.
 """
 from . import _lib  # noqa: F401  (fails loudly if libbqa.so has not been built)
+from . import engine  # noqa: F401,E402

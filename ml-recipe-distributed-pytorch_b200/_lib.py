@@ -9,24 +9,88 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbqa.so")
+ABI_VERSION = 1
 
 EPI_LINEAR, EPI_GELU_FWD, EPI_GELU_BWD, EPI_F32_ADD = 0, 1, 2, 3
+CLS_SMOOTH, CLS_CE = 0, 1
+
+c_i32, c_i64, c_u32, c_u64, c_f32 = ctypes.c_int32, ctypes.c_int64, ctypes.c_uint32, ctypes.c_uint64, ctypes.c_float
+vp = ctypes.c_void_p
 
 
 class GemmDesc(ctypes.Structure):
     _fields_ = [
-        ("M", ctypes.c_int32), ("N", ctypes.c_int32), ("K", ctypes.c_int32),
-        ("A", ctypes.c_void_p), ("lda", ctypes.c_int32), ("a_mn_major", ctypes.c_int32),
-        ("B", ctypes.c_void_p), ("ldb", ctypes.c_int32), ("b_mn_major", ctypes.c_int32),
-        ("C", ctypes.c_void_p), ("ldc", ctypes.c_int32),
-        ("C2", ctypes.c_void_p), ("epilogue", ctypes.c_int32),
-        ("bias", ctypes.c_void_p),
-        ("residual", ctypes.c_void_p), ("ld_res", ctypes.c_int32),
-        ("aux", ctypes.c_void_p), ("ld_aux", ctypes.c_int32),
-        ("k_splits", ctypes.c_int32),
-        ("dropout_p", ctypes.c_float),
-        ("drop_seed", ctypes.c_uint64), ("drop_site", ctypes.c_uint32),
+        ("M", c_i32), ("N", c_i32), ("K", c_i32),
+        ("A", vp), ("lda", c_i32), ("a_mn_major", c_i32),
+        ("B", vp), ("ldb", c_i32), ("b_mn_major", c_i32),
+        ("C", vp), ("ldc", c_i32),
+        ("C2", vp), ("epilogue", c_i32),
+        ("bias", vp),
+        ("residual", vp), ("ld_res", c_i32),
+        ("aux", vp), ("ld_aux", c_i32),
+        ("k_splits", c_i32),
+        ("dropout_p", c_f32),
+        ("drop_seed", c_u64), ("drop_site", c_u32),
     ]
+
+
+class Config(ctypes.Structure):
+    _fields_ = [("num_layers", c_i32), ("hidden", c_i32), ("heads", c_i32), ("intermediate", c_i32),
+                ("vocab", c_i32), ("max_pos", c_i32), ("type_vocab", c_i32), ("num_labels", c_i32),
+                ("ln_eps", c_f32), ("hidden_dropout", c_f32), ("attn_dropout", c_f32)]
+
+
+LAYOUT_FIELDS = ["word_emb", "pos_emb", "type_emb", "emb_ln_g", "emb_ln_b", "layer0", "layer_stride",
+                 "qkv_w", "qkv_b", "ao_w", "ao_b", "ln1_g", "ln1_b", "i_w", "i_b", "o_w", "o_b", "ln2_g", "ln2_b",
+                 "pool_w", "pool_b", "span_w", "span_b", "cls_w", "cls_b", "regs_w", "regs_b", "rege_w", "rege_b",
+                 "total"]
+
+
+class Layout(ctypes.Structure):
+    _fields_ = [(n, c_i64) for n in LAYOUT_FIELDS]
+
+
+class LossConfig(ctypes.Structure):
+    _fields_ = [("w_start", c_f32), ("w_end", c_f32), ("w_start_reg", c_f32), ("w_end_reg", c_f32),
+                ("w_cls", c_f32), ("cls_loss", c_i32), ("smooth_alpha", c_f32), ("cls_weight", vp),
+                ("loss_scale", c_f32)]
+
+
+class AdamWChunk(ctypes.Structure):
+    _fields_ = [("begin", c_u64), ("end", c_u64), ("weight_decay", c_f32), ("group", c_i32)]
+
+
+# name -> (restype, argtypes); the CPU test-suite checks that every symbol of include/bqa.h is here
+SIGNATURES = {
+    "bqa_last_error": (ctypes.c_char_p, []),
+    "bqa_abi_version": (ctypes.c_int, []),
+    "bqa_gemm_bf16": (ctypes.c_int, [ctypes.POINTER(GemmDesc), vp]),
+    "bqa_attention_forward": (ctypes.c_int, [vp, vp, vp, vp, c_i32, c_i32, c_i32, c_f32, c_u64, c_u32, vp]),
+    "bqa_attention_backward": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, c_i32, c_i32, c_i32, c_f32, c_u64, c_u32,
+                                              vp]),
+    "bqa_layernorm_forward": (ctypes.c_int, [vp, vp, vp, vp, c_i32, c_i32, c_f32, vp]),
+    "bqa_layernorm_backward": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, c_i32, c_i32, c_f32, c_f32, c_u32,
+                                              c_f32, c_u32, c_u64, vp]),
+    "bqa_colsum_bf16": (ctypes.c_int, [vp, c_i32, vp, c_i32, c_i32, vp]),
+    "bqa_sumsq_scratch_floats": (ctypes.c_int, []),
+    "bqa_grad_sumsq": (ctypes.c_int, [vp, c_u64, vp, vp, vp]),
+    "bqa_clip_adamw": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, c_i32, vp, c_f32, ctypes.POINTER(c_f32), c_i32,
+                                      c_f32, c_f32, c_f32, c_i32, vp]),
+    "bqa_f32_to_bf16": (ctypes.c_int, [vp, vp, c_u64, vp]),
+    "bqa_decode": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, c_i32, c_i32, c_i32, vp]),
+    "bqa_param_layout": (ctypes.c_int, [ctypes.POINTER(Config), ctypes.POINTER(Layout)]),
+    "bqa_workspace_bytes": (ctypes.c_int, [ctypes.POINTER(Config), c_i32, c_i32, c_i32, ctypes.POINTER(c_u64)]),
+    "bqa_create": (ctypes.c_int, [ctypes.POINTER(Config), ctypes.POINTER(vp)]),
+    "bqa_destroy": (ctypes.c_int, [vp]),
+    "bqa_bind": (ctypes.c_int, [vp, vp, vp, vp, vp, c_u64]),
+    "bqa_forward": (ctypes.c_int, [vp, vp, vp, vp, c_i32, c_i32, c_i32, c_u64, c_u64, vp, vp, vp, vp, vp, vp]),
+    "bqa_loss": (ctypes.c_int, [vp] + [vp] * 10 + [ctypes.POINTER(LossConfig), c_i32, vp, vp]),
+    "bqa_set_output_grads": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp]),
+    "bqa_backward": (ctypes.c_int, [vp, c_i32, c_i32, vp]),
+    "bqa_num_backward_phases": (ctypes.c_int, [vp]),
+    "bqa_phase_grad_begin": (c_i64, [vp, c_i32]),
+    "bqa_launch_count": (c_i64, [vp]),
+}
 
 
 def _load():
@@ -35,11 +99,12 @@ def _load():
             f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
             "(needs nvcc; there is no fallback implementation)")
     lib = ctypes.CDLL(LIB_PATH)
-    lib.bqa_last_error.restype = ctypes.c_char_p
-    lib.bqa_last_error.argtypes = []
-    lib.bqa_abi_version.restype = ctypes.c_int
-    lib.bqa_gemm_bf16.restype = ctypes.c_int
-    lib.bqa_gemm_bf16.argtypes = [ctypes.POINTER(GemmDesc), ctypes.c_void_p]
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError here = library and binding out of sync
+        fn.restype = res
+        fn.argtypes = args
+    if lib.bqa_abi_version() != ABI_VERSION:
+        raise ImportError(f"{LIB_PATH}: ABI version {lib.bqa_abi_version()} != expected {ABI_VERSION}; rebuild")
     return lib
 
 
@@ -52,13 +117,14 @@ def check(rc, what):
         raise RuntimeError(f"{what} failed: {msg.decode() if msg else 'unknown error'}")
 
 
-def _ptr(t):
-    return None if t is None else ctypes.c_void_p(t.data_ptr())
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL)."""
+    return None if t is None else t.data_ptr()
 
 
 def current_stream_ptr():
     import torch
-    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return torch.cuda.current_stream().cuda_stream
 
 
 def gemm_bf16(A, B, C, *, a_mn_major=False, b_mn_major=False, epilogue=EPI_LINEAR, C2=None, bias=None,

@@ -1,0 +1,672 @@
+// attention_sm100.cu — fused multi-head self-attention for sm_100a (head dim 64, S <= 512).
+//
+// Reference: BertSelfAttention.forward + eager_attention_forward
+// (site-packages/transformers/models/bert/modeling_bert.py:115-140,168-207):
+//   P = softmax(Q K^T / sqrt(d) + mask) ; P = dropout(P) ; ctx = P V
+// and its autograd backward.  The reference materialises the [B,A,S,S] score tensor in HBM
+// several times per layer; here scores live only in tensor memory:
+//
+//   forward  (CTA = one (batch, head, 128-query tile)):
+//     TMA -> smem Q, K, V | tcgen05.mma S = Q K^T into TMEM (128 lanes x S columns, fp32)
+//     | 128 softmax threads, one per query row: row max, exp2, row sum straight out of TMEM
+//     | P (bf16, dropped) -> 128B-swizzled smem | tcgen05.mma O += P V (V is the MN-major operand)
+//     | O / rowsum -> ctx, log-sum-exp -> lse2.
+//   backward = two kernels with the same structure, each recomputing its score tile:
+//     dQ  kernel (CTA = 128-query tile):  S, dP = dO V^T ; dS = P (dP - D) ; dQ += dS K
+//     dKV kernel (CTA = 128-key tile), transposed problem so that rows are keys:
+//                S^T = K Q^T, dP^T = V dO^T ; dV += P^T dO ; dK += dS^T Q
+//   with D = rowsum(dO * O) from a small HBM-bound pre-pass.
+// Dropout decisions are the stateless hash of (batch, head, query, key), identical in all kernels.
+#include "attention_sm100.cuh"
+
+#include "bqa_host.cuh"
+#include "gemm_sm100.cuh"
+#include "kernels.cuh"
+
+namespace bqa {
+
+namespace {
+
+constexpr int CH = 16384;  // bytes of one 128 x 64 bf16 tile
+constexpr int ATT_THREADS = 160;
+constexpr int ROW_THREADS = 128;
+
+struct AttnArgs {
+  int B, S, A, H, nchunk, tmem_cols;
+  float scale, scale_log2;
+  const uint8_t* key_mask;
+  bf16* ctx;
+  float* lse2;
+  float* dsum;
+  bf16* dqkv;
+  DropKey drop;
+};
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// D[128 x N] (+)= A[128 x 64] * B[N x 64]^T, both operands K-major tiles of 128-byte rows
+__device__ __forceinline__ void mma_k64(uint32_t tmem_d, uint32_t a_addr, uint32_t b_addr, uint32_t idesc) {
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    umma_bf16(tmem_d, umma_desc_kmajor(a_addr + k * 32), umma_desc_kmajor(b_addr + k * 32), idesc, k > 0 ? 1u : 0u);
+}
+
+// D[128 x 64] (+)= A[128 x 128] * B[128 x 64]; A = two K-major atoms (CH apart), B = MN-major tile
+__device__ __forceinline__ void mma_k128_mn(uint32_t tmem_d, uint32_t a_addr, uint32_t b_addr, uint32_t idesc,
+                                            bool accumulate_first) {
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    umma_bf16(tmem_d, umma_desc_kmajor(a_addr + (k >> 2) * CH + (k & 3) * 32),
+              umma_desc_mnmajor(b_addr + k * 2048, CH), idesc, (accumulate_first || k > 0) ? 1u : 0u);
+}
+
+// 8 consecutive bf16 of row r, 16-byte chunk c16 (0..15) of a [128 x 128] K-major operand tile
+__device__ __forceinline__ void st_tile16(uint8_t* tile, int r, int c16, const float* f) {
+  uint4 o;
+  o.x = pack_bf16x2(f[0], f[1]);
+  o.y = pack_bf16x2(f[2], f[3]);
+  o.z = pack_bf16x2(f[4], f[5]);
+  o.w = pack_bf16x2(f[6], f[7]);
+  *reinterpret_cast<uint4*>(tile + (c16 >> 3) * CH + r * 128 + (((c16 & 7) ^ (r & 7)) << 4)) = o;
+}
+
+__device__ __forceinline__ void st_row_bf16_32(bf16* dst, const float* f) {
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    uint4 o;
+    o.x = pack_bf16x2(f[8 * q], f[8 * q + 1]);
+    o.y = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
+    o.z = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]);
+    o.w = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
+    *reinterpret_cast<uint4*>(dst + 8 * q) = o;
+  }
+}
+
+__device__ __forceinline__ uint8_t* align1024(uint8_t* p) { return p + ((1024u - (smem_u32(p) & 1023u)) & 1023u); }
+
+// =========================================================================================
+// forward
+// =========================================================================================
+__global__ void __launch_bounds__(ATT_THREADS, 1)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align1024(smem_raw);
+  const int N = a.nchunk;
+  uint8_t* sQ = smem;
+  uint8_t* sK = sQ + CH;
+  uint8_t* sV = sK + N * CH;
+  uint8_t* sP = sV + N * CH;  // 2 buffers x (2 * CH)
+  float* kbias = reinterpret_cast<float*>(sP + 4 * CH);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(kbias + 512);
+  uint64_t* bar_qk = bars + 0;
+  uint64_t* bar_v = bars + 1;
+  uint64_t* bar_s = bars + 2;
+  uint64_t* bar_o = bars + 3;
+  uint64_t* bar_p = bars + 4;      // [2]
+  uint64_t* bar_pfree = bars + 6;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int S = a.S, Sp = N * 128;
+
+  if (tid == ROW_THREADS) {
+    tma_prefetch_desc(&tm_qkv);
+    mbar_init(bar_qk, 1);
+    mbar_init(bar_v, 1);
+    mbar_init(bar_s, 1);
+    mbar_init(bar_o, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bar_p[i], ROW_THREADS);
+      mbar_init(&bar_pfree[i], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 4) {
+    tmem_alloc(tmem_slot, a.tmem_cols);
+    tmem_relinquish();
+  }
+  if (tid < ROW_THREADS) {
+    for (int k = tid; k < Sp; k += ROW_THREADS) {
+      const bool ok = k < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + k] != 0);
+      kbias[k] = ok ? 0.0f : -INFINITY;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (tid == ROW_THREADS) {
+    // ---------------- control thread: TMA loads + MMA issue ----------------
+    mbar_arrive_expect_tx(bar_qk, (1 + N) * CH);
+    tma_load_3d(sQ, &tm_qkv, h * 64, qt * 128, b, bar_qk);
+    for (int c = 0; c < N; ++c) tma_load_3d(sK + c * CH, &tm_qkv, a.H + h * 64, c * 128, b, bar_qk);
+    mbar_arrive_expect_tx(bar_v, N * CH);
+    for (int c = 0; c < N; ++c) tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + h * 64, c * 128, b, bar_v);
+
+    constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
+    constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+    mbar_wait(bar_qk, 0);
+    tc_fence_after();
+    for (int c = 0; c < N; ++c) mma_k64(tmem + c * 128, smem_u32(sQ), smem_u32(sK + c * CH), idesc_s);
+    umma_commit(bar_s);
+    mbar_wait(bar_v, 0);
+    for (int j = 0; j < N; ++j) {
+      mbar_wait(&bar_p[j & 1], (j >> 1) & 1);
+      tc_fence_after();
+      mma_k128_mn(tmem, smem_u32(sP + (j & 1) * 2 * CH), smem_u32(sV + j * CH), idesc_o, j > 0);
+      umma_commit(&bar_pfree[j & 1]);
+    }
+    umma_commit(bar_o);
+  } else if (tid < ROW_THREADS) {
+    // ---------------- softmax threads: one query row each ----------------
+    const int r = tid;
+    const int q = qt * 128 + r;
+    const uint32_t lane_addr = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+    const float sl2 = a.scale_log2;
+    mbar_wait(bar_s, 0);
+    tc_fence_after();
+    float mx = -INFINITY;
+    for (int c = 0; c < Sp / 32; ++c) {
+      uint32_t v[32];
+      tmem_ld_32x32(lane_addr + c * 32, v);
+      tmem_wait_ld();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaf(__uint_as_float(v[i]), sl2, kbias[c * 32 + i]));
+    }
+    if (mx == -INFINITY) mx = 0.0f;
+    float l = 0.0f;
+    const uint32_t drop_base = ((static_cast<uint32_t>(b) * a.A + h) * S + static_cast<uint32_t>(q)) * S;
+    for (int j = 0; j < N; ++j) {
+      uint8_t* tile = sP + (j & 1) * 2 * CH;
+      if (j >= 2) mbar_wait(&bar_pfree[j & 1], ((j >> 1) - 1) & 1);
+#pragma unroll 1
+      for (int c4 = 0; c4 < 4; ++c4) {
+        uint32_t v[32];
+        tmem_ld_32x32(lane_addr + j * 128 + c4 * 32, v);
+        tmem_wait_ld();
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          float p[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int key = j * 128 + c4 * 32 + g * 8 + e;
+            float pv = fast_exp2(fmaf(__uint_as_float(v[g * 8 + e]), sl2, kbias[key]) - mx);
+            l += pv;
+            if (a.drop.thresh != 0u) pv = drop_keep(a.drop, drop_base + key) ? pv * a.drop.scale : 0.0f;
+            p[e] = pv;
+          }
+          st_tile16(tile, r, c4 * 4 + g, p);
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(&bar_p[j & 1]);
+    }
+    mbar_wait(bar_o, 0);
+    tc_fence_after();
+    const float inv = l > 0.0f ? 1.0f / l : 0.0f;
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      uint32_t v[32];
+      tmem_ld_32x32(lane_addr + c * 32, v);
+      tmem_wait_ld();
+      if (q < S) {
+        float f[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * inv;
+        st_row_bf16_32(a.ctx + (static_cast<size_t>(b) * S + q) * a.H + h * 64 + c * 32, f);
+      }
+    }
+    // a row whose keys are all masked has l == 0: store +inf so that the backward recomputes P = 0
+    if (q < S) a.lse2[(static_cast<size_t>(b) * a.A + h) * S + q] = l > 0.0f ? mx + log2f(l) : INFINITY;
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc(tmem, a.tmem_cols);
+  }
+}
+
+// =========================================================================================
+// backward pre-pass: D[b][h][q] = sum_d dO[b,q,h,d] * O[b,q,h,d]
+// =========================================================================================
+__global__ void __launch_bounds__(128)
+attn_dsum_kernel(const bf16* __restrict__ ctx, const bf16* __restrict__ dctx, float* __restrict__ dsum, int B, int S,
+                 int A, int H) {
+  const int lane = threadIdx.x & 31;
+  const int t = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (t >= B * S) return;
+  const int b = t / S, q = t - b * S;
+  for (int vbase = 0; vbase < H / 8; vbase += 32) {
+    const int vi = vbase + lane;  // 16-byte vector index in the row; 8 vectors per head
+    float acc = 0.0f;
+    if (vi < H / 8) {
+      const uint4 o = __ldg(reinterpret_cast<const uint4*>(ctx + static_cast<size_t>(t) * H) + vi);
+      const uint4 d = __ldg(reinterpret_cast<const uint4*>(dctx + static_cast<size_t>(t) * H) + vi);
+      const float2 o0 = unpack_bf16x2(o.x), o1 = unpack_bf16x2(o.y), o2 = unpack_bf16x2(o.z), o3 = unpack_bf16x2(o.w);
+      const float2 d0 = unpack_bf16x2(d.x), d1 = unpack_bf16x2(d.y), d2 = unpack_bf16x2(d.z), d3 = unpack_bf16x2(d.w);
+      acc = o0.x * d0.x + o0.y * d0.y + o1.x * d1.x + o1.y * d1.y + o2.x * d2.x + o2.y * d2.y + o3.x * d3.x +
+            o3.y * d3.y;
+    }
+    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+    if ((lane & 7) == 0 && vi < H / 8) dsum[(static_cast<size_t>(b) * A + vi / 8) * S + q] = acc;
+  }
+}
+
+// =========================================================================================
+// backward, dQ
+// =========================================================================================
+__global__ void __launch_bounds__(ATT_THREADS, 1)
+attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_dctx,
+                   const AttnArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align1024(smem_raw);
+  const int N = a.nchunk;
+  uint8_t* sQ = smem;
+  uint8_t* sdO = sQ + CH;
+  uint8_t* sK = sdO + CH;
+  uint8_t* sV = sK + N * CH;
+  uint8_t* sdS = sV + N * CH;  // 2 * CH
+  float* kbias = reinterpret_cast<float*>(sdS + 2 * CH);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(kbias + 512);
+  uint64_t* bar_ld = bars + 0;
+  uint64_t* bar_s = bars + 1;
+  uint64_t* bar_sfree = bars + 2;
+  uint64_t* bar_ds = bars + 3;
+  uint64_t* bar_dsfree = bars + 4;
+  uint64_t* bar_dq = bars + 5;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 6);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int S = a.S, Sp = N * 128;
+
+  if (tid == ROW_THREADS) {
+    tma_prefetch_desc(&tm_qkv);
+    tma_prefetch_desc(&tm_dctx);
+    mbar_init(bar_ld, 1);
+    mbar_init(bar_s, 1);
+    mbar_init(bar_sfree, ROW_THREADS);
+    mbar_init(bar_ds, ROW_THREADS);
+    mbar_init(bar_dsfree, 1);
+    mbar_init(bar_dq, 1);
+    fence_mbar_init();
+  }
+  if (warp == 4) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  if (tid < ROW_THREADS) {
+    for (int k = tid; k < Sp; k += ROW_THREADS) {
+      const bool ok = k < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + k] != 0);
+      kbias[k] = ok ? 0.0f : -INFINITY;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  constexpr uint32_t COL_S = 0, COL_DP = 128, COL_DQ = 256;
+
+  if (tid == ROW_THREADS) {
+    mbar_arrive_expect_tx(bar_ld, (2 + 2 * N) * CH);
+    tma_load_3d(sQ, &tm_qkv, h * 64, qt * 128, b, bar_ld);
+    tma_load_3d(sdO, &tm_dctx, h * 64, qt * 128, b, bar_ld);
+    for (int c = 0; c < N; ++c) {
+      tma_load_3d(sK + c * CH, &tm_qkv, a.H + h * 64, c * 128, b, bar_ld);
+      tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + h * 64, c * 128, b, bar_ld);
+    }
+    constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
+    constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+    mbar_wait(bar_ld, 0);
+    tc_fence_after();
+    mma_k64(tmem + COL_S, smem_u32(sQ), smem_u32(sK), idesc_s);
+    mma_k64(tmem + COL_DP, smem_u32(sdO), smem_u32(sV), idesc_s);
+    umma_commit(bar_s);
+    for (int j = 0; j < N; ++j) {
+      if (j + 1 < N) {
+        mbar_wait(bar_sfree, j & 1);
+        tc_fence_after();
+        mma_k64(tmem + COL_S, smem_u32(sQ), smem_u32(sK + (j + 1) * CH), idesc_s);
+        mma_k64(tmem + COL_DP, smem_u32(sdO), smem_u32(sV + (j + 1) * CH), idesc_s);
+        umma_commit(bar_s);
+      }
+      mbar_wait(bar_ds, j & 1);
+      tc_fence_after();
+      mma_k128_mn(tmem + COL_DQ, smem_u32(sdS), smem_u32(sK + j * CH), idesc_o, j > 0);
+      umma_commit(bar_dsfree);
+    }
+    umma_commit(bar_dq);
+  } else if (tid < ROW_THREADS) {
+    const int r = tid;
+    const int q = qt * 128 + r;
+    const uint32_t lane_addr = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+    const float sl2 = a.scale_log2;
+    const bool q_ok = q < S;
+    const size_t stat = (static_cast<size_t>(b) * a.A + h) * S + (q_ok ? q : 0);
+    const float lse = q_ok ? a.lse2[stat] : INFINITY;
+    const float dsum = q_ok ? a.dsum[stat] : 0.0f;
+    const uint32_t drop_base = ((static_cast<uint32_t>(b) * a.A + h) * S + static_cast<uint32_t>(q)) * S;
+    for (int j = 0; j < N; ++j) {
+      mbar_wait(bar_s, j & 1);
+      tc_fence_after();
+      if (j >= 1) mbar_wait(bar_dsfree, (j - 1) & 1);
+#pragma unroll 1
+      for (int c4 = 0; c4 < 4; ++c4) {
+        uint32_t vs[32], vd[32];
+        tmem_ld_32x32(lane_addr + COL_S + c4 * 32, vs);
+        tmem_ld_32x32(lane_addr + COL_DP + c4 * 32, vd);
+        tmem_wait_ld();
+        if (c4 == 3) {
+          tc_fence_before();
+          mbar_arrive(bar_sfree);
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          float ds[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int key = j * 128 + c4 * 32 + g * 8 + e;
+            const float p = fast_exp2(fmaf(__uint_as_float(vs[g * 8 + e]), sl2, kbias[key]) - lse);
+            float dp = __uint_as_float(vd[g * 8 + e]);
+            if (a.drop.thresh != 0u) dp = drop_keep(a.drop, drop_base + key) ? dp * a.drop.scale : 0.0f;
+            ds[e] = p * (dp - dsum) * a.scale;
+          }
+          st_tile16(sdS, r, c4 * 4 + g, ds);
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(bar_ds);
+    }
+    mbar_wait(bar_dq, 0);
+    tc_fence_after();
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      uint32_t v[32];
+      tmem_ld_32x32(lane_addr + COL_DQ + c * 32, v);
+      tmem_wait_ld();
+      if (q_ok) {
+        float f[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+        st_row_bf16_32(a.dqkv + (static_cast<size_t>(b) * S + q) * 3 * a.H + h * 64 + c * 32, f);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
+// =========================================================================================
+// backward, dK and dV (rows = keys)
+// =========================================================================================
+__global__ void __launch_bounds__(ATT_THREADS, 1)
+attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_dctx,
+                    const AttnArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align1024(smem_raw);
+  const int N = a.nchunk;
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + CH;
+  uint8_t* sQ = sV + CH;     // 2 stages
+  uint8_t* sdO = sQ + 2 * CH;  // 2 stages
+  uint8_t* sPt = sdO + 2 * CH;   // 2 * CH
+  uint8_t* sdSt = sPt + 2 * CH;  // 2 * CH
+  float* s_lse = reinterpret_cast<float*>(sdSt + 2 * CH);
+  float* s_dsum = s_lse + 512;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_dsum + 512);
+  uint64_t* bar_kv = bars + 0;
+  uint64_t* bar_ld = bars + 1;  // [2]
+  uint64_t* bar_s = bars + 3;
+  uint64_t* bar_sfree = bars + 4;
+  uint64_t* bar_pt = bars + 5;
+  uint64_t* bar_ptfree = bars + 6;
+  uint64_t* bar_out = bars + 7;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int S = a.S, Sp = N * 128;
+
+  if (tid == ROW_THREADS) {
+    tma_prefetch_desc(&tm_qkv);
+    tma_prefetch_desc(&tm_dctx);
+    mbar_init(bar_kv, 1);
+    mbar_init(&bar_ld[0], 1);
+    mbar_init(&bar_ld[1], 1);
+    mbar_init(bar_s, 1);
+    mbar_init(bar_sfree, ROW_THREADS);
+    mbar_init(bar_pt, ROW_THREADS);
+    mbar_init(bar_ptfree, 1);
+    mbar_init(bar_out, 1);
+    fence_mbar_init();
+  }
+  if (warp == 4) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  if (tid < ROW_THREADS) {
+    const size_t stat = (static_cast<size_t>(b) * a.A + h) * S;
+    for (int k = tid; k < Sp; k += ROW_THREADS) {
+      s_lse[k] = k < S ? a.lse2[stat + k] : INFINITY;
+      s_dsum[k] = k < S ? a.dsum[stat + k] : 0.0f;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  constexpr uint32_t COL_S = 0, COL_DP = 128, COL_DV = 256, COL_DK = 320;
+
+  if (tid == ROW_THREADS) {
+    mbar_arrive_expect_tx(bar_kv, 2 * CH);
+    tma_load_3d(sK, &tm_qkv, a.H + h * 64, kt * 128, b, bar_kv);
+    tma_load_3d(sV, &tm_qkv, 2 * a.H + h * 64, kt * 128, b, bar_kv);
+    for (int i = 0; i < 2 && i < N; ++i) {
+      mbar_arrive_expect_tx(&bar_ld[i], 2 * CH);
+      tma_load_3d(sQ + i * CH, &tm_qkv, h * 64, i * 128, b, &bar_ld[i]);
+      tma_load_3d(sdO + i * CH, &tm_dctx, h * 64, i * 128, b, &bar_ld[i]);
+    }
+    constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
+    constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+    mbar_wait(bar_kv, 0);
+    for (int i = 0; i < N; ++i) {
+      const int st = i & 1;
+      mbar_wait(&bar_ld[st], (i >> 1) & 1);
+      if (i > 0) mbar_wait(bar_sfree, (i - 1) & 1);
+      tc_fence_after();
+      mma_k64(tmem + COL_S, smem_u32(sK), smem_u32(sQ + st * CH), idesc_s);
+      mma_k64(tmem + COL_DP, smem_u32(sV), smem_u32(sdO + st * CH), idesc_s);
+      umma_commit(bar_s);
+      mbar_wait(bar_pt, i & 1);
+      tc_fence_after();
+      mma_k128_mn(tmem + COL_DV, smem_u32(sPt), smem_u32(sdO + st * CH), idesc_o, i > 0);
+      mma_k128_mn(tmem + COL_DK, smem_u32(sdSt), smem_u32(sQ + st * CH), idesc_o, i > 0);
+      umma_commit(bar_ptfree);
+      if (i + 2 < N) {
+        // stage `st` is re-filled only after every MMA that reads it has completed
+        mbar_wait(bar_ptfree, i & 1);
+        mbar_arrive_expect_tx(&bar_ld[st], 2 * CH);
+        tma_load_3d(sQ + st * CH, &tm_qkv, h * 64, (i + 2) * 128, b, &bar_ld[st]);
+        tma_load_3d(sdO + st * CH, &tm_dctx, h * 64, (i + 2) * 128, b, &bar_ld[st]);
+      }
+    }
+    umma_commit(bar_out);
+  } else if (tid < ROW_THREADS) {
+    const int r = tid;
+    const int key = kt * 128 + r;
+    const uint32_t lane_addr = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+    const float sl2 = a.scale_log2;
+    const bool key_ok = key < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + key] != 0);
+    const float kb = key_ok ? 0.0f : -INFINITY;
+    const uint32_t drop_base = (static_cast<uint32_t>(b) * a.A + h) * S;
+    for (int i = 0; i < N; ++i) {
+      mbar_wait(bar_s, i & 1);
+      tc_fence_after();
+      if (i >= 1) mbar_wait(bar_ptfree, (i - 1) & 1);
+#pragma unroll 1
+      for (int c4 = 0; c4 < 4; ++c4) {
+        uint32_t vs[32], vd[32];
+        tmem_ld_32x32(lane_addr + COL_S + c4 * 32, vs);
+        tmem_ld_32x32(lane_addr + COL_DP + c4 * 32, vd);
+        tmem_wait_ld();
+        if (c4 == 3) {
+          tc_fence_before();
+          mbar_arrive(bar_sfree);
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          float pt[8], ds[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int q = i * 128 + c4 * 32 + g * 8 + e;
+            const float p = fast_exp2(fmaf(__uint_as_float(vs[g * 8 + e]), sl2, kb) - s_lse[q]);
+            float dp = __uint_as_float(vd[g * 8 + e]);
+            float pd = p;
+            if (a.drop.thresh != 0u) {
+              const bool keep = drop_keep(a.drop, (drop_base + static_cast<uint32_t>(q)) * S + key);
+              pd = keep ? p * a.drop.scale : 0.0f;
+              dp = keep ? dp * a.drop.scale : 0.0f;
+            }
+            pt[e] = pd;
+            ds[e] = p * (dp - s_dsum[q]) * a.scale;
+          }
+          st_tile16(sPt, r, c4 * 4 + g, pt);
+          st_tile16(sdSt, r, c4 * 4 + g, ds);
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(bar_pt);
+    }
+    mbar_wait(bar_out, 0);
+    tc_fence_after();
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      uint32_t v[32];
+      tmem_ld_32x32(lane_addr + COL_DV + c * 32, v);  // c = 0,1: dV ; c = 2,3: dK (COL_DK = COL_DV + 64)
+      tmem_wait_ld();
+      if (key < S) {
+        float f[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+        const int which = c < 2 ? 2 : 1;  // V block is the third H-wide slab of dqkv, K the second
+        st_row_bf16_32(a.dqkv + (static_cast<size_t>(b) * S + key) * 3 * a.H + which * a.H + h * 64 + (c & 1) * 32, f);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
+int fwd_smem_bytes(int n) { return CH * (5 + 2 * n) + 2048 + 256 + 1024; }
+int dq_smem_bytes(int n) { return CH * (4 + 2 * n) + 2048 + 256 + 1024; }
+int dkv_smem_bytes() { return CH * 10 + 4096 + 256 + 1024; }
+
+AttnArgs make_args(const AttnPlan& p, const uint8_t* key_mask, DropKey drop) {
+  AttnArgs a;
+  a.B = p.shape.B;
+  a.S = p.shape.S;
+  a.A = p.shape.A;
+  a.H = p.shape.H;
+  a.nchunk = p.nchunk;
+  a.tmem_cols = p.tmem_cols;
+  a.scale = 0.125f;  // 1 / sqrt(64)
+  a.scale_log2 = 0.125f * 1.4426950408889634f;
+  a.key_mask = key_mask;
+  a.ctx = p.ctx;
+  a.lse2 = p.lse2;
+  a.dsum = p.dsum;
+  a.dqkv = p.dqkv;
+  a.drop = drop;
+  return a;
+}
+
+}  // namespace
+
+int attn_plan(AttnPlan* plan, const AttnShape& s, const void* qkv, void* ctx, float* lse2, const void* dctx,
+              float* dsum, void* dqkv) {
+  if (s.H != s.A * 64) {
+    set_error("attention: head dim must be 64 (H=%d, A=%d)", s.H, s.A);
+    return 1;
+  }
+  if (s.S < 1 || s.S > 512) {
+    set_error("attention: sequence length %d outside [1, 512]", s.S);
+    return 1;
+  }
+  plan->shape = s;
+  plan->nchunk = (s.S + 127) / 128;
+  const int cols = plan->nchunk * 128;
+  plan->tmem_cols = cols <= 128 ? 128 : (cols <= 256 ? 256 : 512);
+  plan->qkv = reinterpret_cast<const bf16*>(qkv);
+  plan->ctx = reinterpret_cast<bf16*>(ctx);
+  plan->lse2 = lse2;
+  plan->dctx = reinterpret_cast<const bf16*>(dctx);
+  plan->dsum = dsum;
+  plan->dqkv = reinterpret_cast<bf16*>(dqkv);
+  const uint64_t H = s.H;
+  if (qkv != nullptr &&
+      encode_tmap_3d(&plan->tm_qkv, qkv, 2, 3 * H, s.S, s.B, 3 * H, static_cast<uint64_t>(s.S) * 3 * H, 64, 128, 1))
+    return 1;
+  if (dctx != nullptr &&
+      encode_tmap_3d(&plan->tm_dctx, dctx, 2, H, s.S, s.B, H, static_cast<uint64_t>(s.S) * H, 64, 128, 1))
+    return 1;
+  return 0;
+}
+
+int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st) {
+  static bool configured = false;
+  if (!configured) {
+    BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        fwd_smem_bytes(4)));
+    configured = true;
+  }
+  const AttnArgs a = make_args(plan, key_mask, drop);
+  dim3 grid(plan.nchunk, plan.shape.A, plan.shape.B);
+  attn_fwd_kernel<<<grid, ATT_THREADS, fwd_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, a);
+  return check_launch("attn_fwd");
+}
+
+int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st) {
+  static bool configured = false;
+  if (!configured) {
+    BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        dq_smem_bytes(4)));
+    BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dkv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        dkv_smem_bytes()));
+    configured = true;
+  }
+  const AttnArgs a = make_args(plan, key_mask, drop);
+  const int T = plan.shape.B * plan.shape.S;
+  attn_dsum_kernel<<<(T + 3) / 4, 128, 0, st>>>(plan.ctx, plan.dctx, plan.dsum, plan.shape.B, plan.shape.S,
+                                               plan.shape.A, plan.shape.H);
+  if (check_launch("attn_dsum")) return 1;
+  dim3 grid(plan.nchunk, plan.shape.A, plan.shape.B);
+  attn_bwd_dq_kernel<<<grid, ATT_THREADS, dq_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_dctx, a);
+  if (check_launch("attn_bwd_dq")) return 1;
+  attn_bwd_dkv_kernel<<<grid, ATT_THREADS, dkv_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_dctx, a);
+  return check_launch("attn_bwd_dkv");
+}
+
+}  // namespace bqa

@@ -1,0 +1,37 @@
+// attention_sm100.cuh — host interface of the fused self-attention kernels (attention_sm100.cu).
+#pragma once
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "bqa_common.cuh"
+
+namespace bqa {
+
+struct AttnShape {
+  int B, S, A, H;  // batch, sequence length (<= 512), heads, hidden (= A * 64)
+};
+
+struct AttnPlan {
+  CUtensorMap tm_qkv;   // [B][S][3H] bf16, box {64,128,1}
+  CUtensorMap tm_dctx;  // [B][S][H]  bf16, box {64,128,1}
+  AttnShape shape;
+  int nchunk;     // ceil(S / 128)
+  int tmem_cols;  // forward allocation (power of two >= 128 * nchunk)
+  const bf16* qkv;
+  bf16* ctx;
+  float* lse2;   // [B][A][S] log2-domain log-sum-exp of the scaled, masked scores
+  const bf16* dctx;
+  float* dsum;   // [B][A][S] rowsum(dO * O)
+  bf16* dqkv;    // [B*S][3H]
+};
+
+// qkv/ctx/dctx/dqkv may be null when only the forward (or only a plan for it) is needed.
+int attn_plan(AttnPlan* plan, const AttnShape& s, const void* qkv, void* ctx, float* lse2, const void* dctx,
+              float* dsum, void* dqkv);
+// key_mask: [B][S] uint8 (1 = attend) or null.  drop.thresh == 0 disables dropout.
+int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st);
+int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st);
+
+}  // namespace bqa

@@ -46,3 +46,102 @@ int bqa_gemm_bf16(const bqa_gemm_desc* d, void* stream) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------
+// standalone operator entry points (unit-testable pieces of the step)
+// ---------------------------------------------------------------------------------------
+#include "attention_sm100.cuh"
+#include "kernels.cuh"
+
+extern "C" {
+
+int bqa_attention_forward(const void* qkv, void* ctx, float* lse2, const uint8_t* key_mask, int32_t B, int32_t S,
+                          int32_t A, float dropout_p, uint64_t drop_seed, uint32_t drop_site, void* stream) {
+  AttnPlan plan;
+  AttnShape s{B, S, A, A * 64};
+  if (attn_plan(&plan, s, qkv, ctx, lse2, nullptr, nullptr, nullptr)) return 1;
+  return attn_forward(plan, key_mask, make_drop_key(drop_seed, drop_site, dropout_p),
+                      reinterpret_cast<cudaStream_t>(stream));
+}
+
+int bqa_attention_backward(const void* qkv, const void* ctx, const float* lse2, const void* dctx, void* dqkv,
+                           float* dsum, const uint8_t* key_mask, int32_t B, int32_t S, int32_t A, float dropout_p,
+                           uint64_t drop_seed, uint32_t drop_site, void* stream) {
+  AttnPlan plan;
+  AttnShape s{B, S, A, A * 64};
+  if (attn_plan(&plan, s, qkv, const_cast<void*>(ctx), const_cast<float*>(lse2), dctx, dsum, dqkv)) return 1;
+  return attn_backward(plan, key_mask, make_drop_key(drop_seed, drop_site, dropout_p),
+                       reinterpret_cast<cudaStream_t>(stream));
+}
+
+int bqa_layernorm_forward(const void* z, const float* gamma, const float* beta, void* y, int32_t T, int32_t H,
+                          float eps, void* stream) {
+  return launch_ln_fwd(reinterpret_cast<const bf16*>(z), gamma, beta, reinterpret_cast<bf16*>(y), T, H, eps,
+                       reinterpret_cast<cudaStream_t>(stream));
+}
+
+int bqa_layernorm_backward(const void* dy, const void* z, const float* gamma, void* dz, void* dz_masked,
+                           float* dgamma, float* dbeta, float* dbias, int32_t T, int32_t H, float eps,
+                           float drop_in_p, uint32_t drop_in_site, float drop_out_p, uint32_t drop_out_site,
+                           uint64_t drop_seed, void* stream) {
+  int sms = 0;
+  if (device_sm_count(&sms)) return 1;
+  return launch_ln_bwd(reinterpret_cast<const bf16*>(dy), reinterpret_cast<const bf16*>(z), gamma,
+                       reinterpret_cast<bf16*>(dz), reinterpret_cast<bf16*>(dz_masked), dgamma, dbeta, dbias, T, H,
+                       eps, make_drop_key(drop_seed, drop_in_site, drop_in_p),
+                       make_drop_key(drop_seed, drop_out_site, drop_out_p), sms,
+                       reinterpret_cast<cudaStream_t>(stream));
+}
+
+int bqa_colsum_bf16(const void* X, int32_t ld, float* out, int32_t T, int32_t N, void* stream) {
+  int sms = 0;
+  if (device_sm_count(&sms)) return 1;
+  return launch_colsum(reinterpret_cast<const bf16*>(X), ld, out, T, N, sms, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int bqa_sumsq_scratch_floats(void) { return sumsq_scratch_floats(256); }
+
+int bqa_grad_sumsq(const float* g, uint64_t n, double* sumsq, float* scratch, void* stream) {
+  int sms = 0;
+  if (device_sm_count(&sms)) return 1;
+  if (sms > 256) sms = 256;
+  return launch_grad_sumsq(g, n, sumsq, scratch, sms, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int bqa_clip_adamw(float* p, float* g, float* m, float* v, void* p_bf16, const bqa_adamw_chunk* chunks,
+                   int32_t n_chunks, const double* sumsq, float max_grad_norm, const float* host_lr,
+                   int32_t n_groups, float beta1, float beta2, float eps, int32_t zero_grad, void* stream) {
+  static_assert(sizeof(bqa_adamw_chunk) == sizeof(AdamWChunk), "chunk layouts must match");
+  if (n_groups < 1 || n_groups > 8 || host_lr == nullptr) {
+    set_error("bqa_clip_adamw: need 1..8 parameter groups");
+    return 1;
+  }
+  if (max_grad_norm > 0.0f && sumsq == nullptr) {
+    set_error("bqa_clip_adamw: clipping needs the sum of squares");
+    return 1;
+  }
+  LrTable t{};
+  for (int i = 0; i < n_groups; ++i) t.lr[i] = host_lr[i];
+  return launch_clip_adamw(p, g, m, v, reinterpret_cast<bf16*>(p_bf16), reinterpret_cast<const AdamWChunk*>(chunks),
+                           n_chunks, sumsq, max_grad_norm, t, beta1, beta2, eps, zero_grad,
+                           reinterpret_cast<cudaStream_t>(stream));
+}
+
+int bqa_f32_to_bf16(const float* src, void* dst, uint64_t n, void* stream) {
+  int sms = 0;
+  if (device_sm_count(&sms)) return 1;
+  return launch_f32_to_bf16(src, reinterpret_cast<bf16*>(dst), n, sms, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int bqa_decode(const float* start, const float* end, const float* cls, int64_t* start_idx, int64_t* end_idx,
+               int64_t* cls_idx, float* start_max, float* end_max, float* cls_prob, float* score, int32_t B,
+               int32_t S, int32_t C, void* stream) {
+  if (B < 1 || S < 1 || C < 1) {
+    set_error("bqa_decode: empty input (B=%d S=%d C=%d)", B, S, C);
+    return 1;
+  }
+  return launch_decode(start, end, cls, start_idx, end_idx, cls_idx, start_max, end_max, cls_prob, score, B, S, C,
+                       reinterpret_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

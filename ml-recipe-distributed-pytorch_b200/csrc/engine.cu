@@ -1,0 +1,644 @@
+// engine.cu — the BERT-QA step as a sequence of launches on one stream: parameter layout,
+// activation workspace, forward, loss, phased backward.  Implements the handle part of
+// include/bqa.h.
+//
+// Reference data flow being replaced (per micro-batch):
+//   Trainer._train                        modules/model/trainer/trainer.py:275-290
+//   -> BertForQuestionAnswering.forward   modules/model/model/model.py:43-73
+//      -> BertModel.forward               site-packages/transformers/models/bert/modeling_bert.py:628
+//   -> WeightedLoss.__call__              modules/model/model/loss.py:78-100
+//   -> loss.backward()                    trainer.py:197-204
+//
+// HBM layout.  Parameters: one flat fp32 master buffer, one fp32 gradient buffer and one bf16
+// shadow (GEMM operands) sharing the offsets of bqa_layout.  Activations: [T = B*S][width]
+// bf16 row-major slabs carved from the caller's workspace; per layer the backward needs
+//   qkv [T,3H] | ctx [T,H] | z1 [T,H] | a [T,H] | u [T,I] | g [T,I] | z2 [T,H] | x_{l+1} [T,H]
+// plus lse2 [B,A,S] fp32; in inference two layer slots are ping-ponged instead of L.
+#include "../../include/bqa.h"
+
+#include <new>
+#include <vector>
+
+#include "attention_sm100.cuh"
+#include "bqa_host.cuh"
+#include "gemm_sm100.cuh"
+#include "kernels.cuh"
+
+using namespace bqa;
+
+namespace {
+
+constexpr int64_t ALIGN_ELEMS = 128;
+inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
+
+int compute_layout(const bqa_config& c, bqa_layout* L) {
+  if (c.num_layers < 1 || c.hidden < 64 || c.hidden % 64 != 0 || c.heads * 64 != c.hidden || c.hidden > 1024 ||
+      c.intermediate % 64 != 0 || c.intermediate < 64 || c.vocab < 1 || c.max_pos < 1 || c.type_vocab < 1 ||
+      c.num_labels < 1 || c.num_labels > 32) {
+    set_error("config: unsupported shape (L=%d H=%d A=%d I=%d V=%d P=%d TV=%d C=%d): need H = 64*A <= 1024, "
+              "H and I multiples of 64",
+              c.num_layers, c.hidden, c.heads, c.intermediate, c.vocab, c.max_pos, c.type_vocab, c.num_labels);
+    return 1;
+  }
+  const int64_t H = c.hidden, I = c.intermediate;
+  int64_t o = 0;
+  auto take = [&](int64_t n) {
+    const int64_t at = o;
+    o = align_up(o + n, ALIGN_ELEMS);
+    return at;
+  };
+  L->word_emb = take(static_cast<int64_t>(c.vocab) * H);
+  L->pos_emb = take(static_cast<int64_t>(c.max_pos) * H);
+  L->type_emb = take(static_cast<int64_t>(c.type_vocab) * H);
+  L->emb_ln_g = take(H);
+  L->emb_ln_b = take(H);
+  L->layer0 = o;
+  const int64_t base = o;
+  L->qkv_w = take(3 * H * H) - base;
+  L->qkv_b = take(3 * H) - base;
+  L->ao_w = take(H * H) - base;
+  L->ao_b = take(H) - base;
+  L->ln1_g = take(H) - base;
+  L->ln1_b = take(H) - base;
+  L->i_w = take(I * H) - base;
+  L->i_b = take(I) - base;
+  L->o_w = take(H * I) - base;
+  L->o_b = take(H) - base;
+  L->ln2_g = take(H) - base;
+  L->ln2_b = take(H) - base;
+  L->layer_stride = o - base;
+  o = base + L->layer_stride * c.num_layers;
+  L->pool_w = take(H * H);
+  L->pool_b = take(H);
+  L->span_w = take(2 * H);
+  L->span_b = take(2);
+  L->cls_w = take(static_cast<int64_t>(c.num_labels) * H);
+  L->cls_b = take(c.num_labels);
+  L->regs_w = take(H);
+  L->regs_b = take(1);
+  L->rege_w = take(H);
+  L->rege_b = take(1);
+  L->total = o;
+  return 0;
+}
+
+// dropout call sites of one step (1 + 3L + 1)
+inline uint32_t site_embed() { return 0; }
+inline uint32_t site_attn(int l) { return 1 + 3 * l; }
+inline uint32_t site_ao(int l) { return 2 + 3 * l; }
+inline uint32_t site_ffn(int l) { return 3 + 3 * l; }
+inline uint32_t site_cls(int L) { return 1 + 3 * L; }
+
+struct Bump {
+  uint8_t* base;
+  uint64_t off = 0;
+  template <typename T>
+  T* take(uint64_t count) {
+    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+    off = (off + count * sizeof(T) + 255) & ~static_cast<uint64_t>(255);
+    return p;
+  }
+};
+
+struct LayerActs {
+  bf16 *qkv, *ctx, *z1, *a, *u, *g, *z2, *x_out;
+  float* lse2;
+};
+
+struct Workspace {
+  bf16 *z0, *x0;
+  std::vector<LayerActs> layer;  // L slots in training, 2 in inference
+  float *pooled, *start, *end, *cls, *reg_s, *reg_e;  // internal copies of the outputs
+  float *d_start, *d_end, *d_cls, *d_reg_s, *d_reg_e;
+  float *loss_rows, *dpre, *dx0;
+  uint8_t* mask;
+  int64_t *ids, *tt;
+  // backward temporaries
+  bf16 *dy0, *dy1, *dres, *dgm, *du, *dctx, *dqkv;
+  float* dsum;
+  int* err_flag;
+  uint64_t bytes;
+};
+
+void carve(Workspace* w, uint8_t* base, const bqa_config& c, int B, int S, bool training) {
+  Bump b{base};
+  const uint64_t T = static_cast<uint64_t>(B) * S, H = c.hidden, I = c.intermediate;
+  w->z0 = b.take<bf16>(T * H);
+  w->x0 = b.take<bf16>(T * H);
+  const int slots = training ? c.num_layers : (c.num_layers < 2 ? c.num_layers : 2);
+  w->layer.resize(slots);
+  for (int i = 0; i < slots; ++i) {
+    LayerActs& a = w->layer[i];
+    a.qkv = b.take<bf16>(T * 3 * H);
+    a.ctx = b.take<bf16>(T * H);
+    a.z1 = b.take<bf16>(T * H);
+    a.a = b.take<bf16>(T * H);
+    a.u = b.take<bf16>(T * I);
+    a.g = b.take<bf16>(T * I);
+    a.z2 = b.take<bf16>(T * H);
+    a.x_out = b.take<bf16>(T * H);
+    a.lse2 = b.take<float>(static_cast<uint64_t>(B) * c.heads * S);
+  }
+  w->pooled = b.take<float>(static_cast<uint64_t>(B) * H);
+  w->start = b.take<float>(T);
+  w->end = b.take<float>(T);
+  w->cls = b.take<float>(static_cast<uint64_t>(B) * c.num_labels);
+  w->reg_s = b.take<float>(B);
+  w->reg_e = b.take<float>(B);
+  w->mask = b.take<uint8_t>(T);
+  w->ids = b.take<int64_t>(T);
+  w->tt = b.take<int64_t>(T);
+  w->err_flag = b.take<int>(1);
+  w->loss_rows = b.take<float>(static_cast<uint64_t>(B) * 5);
+  if (training) {
+    w->d_start = b.take<float>(T);
+    w->d_end = b.take<float>(T);
+    w->d_cls = b.take<float>(static_cast<uint64_t>(B) * c.num_labels);
+    w->d_reg_s = b.take<float>(B);
+    w->d_reg_e = b.take<float>(B);
+    w->dpre = b.take<float>(static_cast<uint64_t>(B) * H);
+    w->dx0 = b.take<float>(static_cast<uint64_t>(B) * H);
+    w->dy0 = b.take<bf16>(T * H);
+    w->dy1 = b.take<bf16>(T * H);
+    w->dres = b.take<bf16>(T * H);
+    w->dgm = b.take<bf16>(T * H);
+    w->du = b.take<bf16>(T * I);
+    w->dctx = b.take<bf16>(T * H);
+    w->dqkv = b.take<bf16>(T * 3 * H);
+    w->dsum = b.take<float>(static_cast<uint64_t>(B) * c.heads * S);
+  } else {
+    w->d_start = w->d_end = w->d_cls = w->d_reg_s = w->d_reg_e = w->dpre = w->dx0 = w->dsum = nullptr;
+    w->dy0 = w->dy1 = w->dres = w->dgm = w->du = w->dctx = w->dqkv = nullptr;
+  }
+  w->bytes = b.off;
+}
+
+struct LayerPlans {
+  GemmPlan qkv, ao, ffn1, ffn2;                   // forward
+  GemmPlan d_ffn2, d_ffn1, d_ao, d_qkv;           // dgrad
+  GemmPlan w_ffn2, w_ffn1, w_ao, w_qkv;           // wgrad
+  AttnPlan attn;
+};
+
+struct Plan {
+  int B = 0, S = 0;
+  bool training = false;
+  Workspace ws;
+  std::vector<LayerPlans> layer;
+};
+
+}  // namespace
+
+struct bqa_handle {
+  bqa_config cfg;
+  bqa_layout lay;
+  int num_sms = 0;
+  float* params = nullptr;
+  float* grads = nullptr;
+  bf16* params_bf16 = nullptr;
+  uint8_t* workspace = nullptr;
+  uint64_t workspace_bytes = 0;
+  Plan plan;
+  bool plan_valid = false;
+  // state of the last forward
+  uint64_t seed = 0, step = 0;
+  bool last_training = false;
+  bool has_mask = false;
+  int64_t launches = 0;
+
+  const float* P(int64_t off) const { return params + off; }
+  float* G(int64_t off) const { return grads + off; }
+  const bf16* W(int64_t off) const { return params_bf16 + off; }
+  int64_t layer_off(int l) const { return lay.layer0 + lay.layer_stride * l; }
+  DropKey key(uint32_t site, float p) const {
+    if (!last_training || p <= 0.0f) return make_drop_key(0, 0, 0.0f);
+    return make_drop_key(seed ^ splitmix64(step + 0x51ed270b9f3a6c1dull), site, p);
+  }
+};
+
+namespace {
+
+int wgrad_splits(int M, int N, int K, int num_sms) {
+  const int tiles = ((M + 127) / 128) * ((N + 255) / 256);
+  const int kb = (K + 63) / 64;
+  int s = (2 * num_sms + tiles - 1) / tiles;
+  const int max_s = kb / 4 > 0 ? kb / 4 : 1;
+  if (s > max_s) s = max_s;
+  return s < 1 ? 1 : s;
+}
+
+int build_plan(bqa_handle* h, int B, int S, bool training) {
+  const bqa_config& c = h->cfg;
+  Plan& p = h->plan;
+  h->plan_valid = false;
+  p.B = B;
+  p.S = S;
+  p.training = training;
+  carve(&p.ws, h->workspace, c, B, S, training);
+  if (p.ws.bytes > h->workspace_bytes) {
+    set_error("workspace too small: need %llu bytes for B=%d S=%d training=%d, bound %llu",
+              (unsigned long long)p.ws.bytes, B, S, (int)training, (unsigned long long)h->workspace_bytes);
+    return 1;
+  }
+  const int T = B * S, H = c.hidden, I = c.intermediate;
+  p.layer.assign(c.num_layers, LayerPlans{});
+  const int slots = static_cast<int>(p.ws.layer.size());
+  for (int l = 0; l < c.num_layers; ++l) {
+    LayerPlans& lp = p.layer[l];
+    const LayerActs& act = p.ws.layer[l % slots];
+    const bf16* x_in = l == 0 ? p.ws.x0 : p.ws.layer[(l - 1) % slots].x_out;
+    const int64_t lo = h->layer_off(l);
+    const bqa_layout& Y = h->lay;
+    auto fwd = [&](GemmPlan* out, const bf16* A, int K, const bf16* Wt, int N, void* C, void* C2, int epi,
+                   const float* bias, const bf16* residual) {
+      GemmProblem g{};
+      g.M = T; g.N = N; g.K = K;
+      g.A = A; g.lda = K; g.a_mn_major = 0;
+      g.B = Wt; g.ldb = K; g.b_mn_major = 0;
+      g.C = C; g.ldc = N; g.C2 = C2;
+      g.epilogue = epi; g.bias = bias;
+      g.residual = residual; g.ld_res = N;
+      g.k_splits = 1;
+      g.drop = make_drop_key(0, 0, 0.0f);
+      return gemm_plan(out, g, h->num_sms);
+    };
+    if (fwd(&lp.qkv, x_in, H, h->W(lo + Y.qkv_w), 3 * H, act.qkv, nullptr, EPI_LINEAR, h->P(lo + Y.qkv_b), nullptr))
+      return 1;
+    if (fwd(&lp.ao, act.ctx, H, h->W(lo + Y.ao_w), H, act.z1, nullptr, EPI_LINEAR, h->P(lo + Y.ao_b), x_in)) return 1;
+    if (fwd(&lp.ffn1, act.a, H, h->W(lo + Y.i_w), I, act.u, act.g, EPI_GELU_FWD, h->P(lo + Y.i_b), nullptr)) return 1;
+    if (fwd(&lp.ffn2, act.g, I, h->W(lo + Y.o_w), H, act.z2, nullptr, EPI_LINEAR, h->P(lo + Y.o_b), act.a)) return 1;
+    AttnShape as{B, S, c.heads, H};
+    if (attn_plan(&lp.attn, as, act.qkv, act.ctx, act.lse2, training ? p.ws.dctx : nullptr, p.ws.dsum,
+                  p.ws.dqkv))
+      return 1;
+    if (!training) continue;
+    // dgrad: dX[T,Kin] = dY[T,Nout] . W[Nout,Kin]   (A K-major, W is the MN-major operand)
+    auto dgrad = [&](GemmPlan* out, const bf16* dY, int Nout, const bf16* Wt, int Kin, void* C, int epi,
+                     const bf16* residual, const bf16* aux) {
+      GemmProblem g{};
+      g.M = T; g.N = Kin; g.K = Nout;
+      g.A = dY; g.lda = Nout; g.a_mn_major = 0;
+      g.B = Wt; g.ldb = Kin; g.b_mn_major = 1;
+      g.C = C; g.ldc = Kin;
+      g.epilogue = epi;
+      g.residual = residual; g.ld_res = Kin;
+      g.aux = aux; g.ld_aux = Kin;
+      g.k_splits = 1;
+      g.drop = make_drop_key(0, 0, 0.0f);
+      return gemm_plan(out, g, h->num_sms);
+    };
+    // wgrad: dW[Nout,Kin] += dY[T,Nout]^T . X[T,Kin]   (both MN-major, fp32 reduce-add, split-K)
+    auto wgrad = [&](GemmPlan* out, const bf16* dY, int Nout, const bf16* X, int Kin, float* dW) {
+      GemmProblem g{};
+      g.M = Nout; g.N = Kin; g.K = T;
+      g.A = dY; g.lda = Nout; g.a_mn_major = 1;
+      g.B = X; g.ldb = Kin; g.b_mn_major = 1;
+      g.C = dW; g.ldc = Kin;
+      g.epilogue = EPI_F32_ADD;
+      g.k_splits = wgrad_splits(Nout, Kin, T, h->num_sms);
+      g.drop = make_drop_key(0, 0, 0.0f);
+      return gemm_plan(out, g, h->num_sms);
+    };
+    Workspace& w = p.ws;
+    bf16* dy_out = (l & 1) ? w.dy1 : w.dy0;  // gradient w.r.t. this layer's input
+    // without hidden dropout the masked gradient IS the residual gradient: read it in place
+    const bf16* dgm = c.hidden_dropout > 0.0f ? w.dgm : w.dres;
+    if (dgrad(&lp.d_ffn2, dgm, H, h->W(lo + Y.o_w), I, w.du, EPI_GELU_BWD, nullptr, act.u)) return 1;
+    if (wgrad(&lp.w_ffn2, dgm, H, act.g, I, h->G(lo + Y.o_w))) return 1;
+    if (dgrad(&lp.d_ffn1, w.du, I, h->W(lo + Y.i_w), H, w.dctx /* da, reuses dctx slab */, EPI_LINEAR, w.dres,
+              nullptr))
+      return 1;
+    if (wgrad(&lp.w_ffn1, w.du, I, act.a, H, h->G(lo + Y.i_w))) return 1;
+    if (dgrad(&lp.d_ao, dgm, H, h->W(lo + Y.ao_w), H, w.dctx, EPI_LINEAR, nullptr, nullptr)) return 1;
+    if (wgrad(&lp.w_ao, dgm, H, act.ctx, H, h->G(lo + Y.ao_w))) return 1;
+    if (dgrad(&lp.d_qkv, w.dqkv, 3 * H, h->W(lo + Y.qkv_w), H, dy_out, EPI_LINEAR, w.dres, nullptr)) return 1;
+    if (wgrad(&lp.w_qkv, w.dqkv, 3 * H, x_in, H, h->G(lo + Y.qkv_w))) return 1;
+  }
+  h->plan_valid = true;
+  return 0;
+}
+
+int launch_gemm(bqa_handle* h, GemmPlan& plan, DropKey drop, cudaStream_t st) {
+  plan.args.drop = drop;
+  h->launches += 1;
+  return gemm_launch(plan, st);
+}
+
+HeadParams head_params(const bqa_handle* h) {
+  const bqa_layout& Y = h->lay;
+  HeadParams hp;
+  hp.pool_w = h->P(Y.pool_w); hp.pool_b = h->P(Y.pool_b);
+  hp.span_w = h->P(Y.span_w); hp.span_b = h->P(Y.span_b);
+  hp.cls_w = h->P(Y.cls_w); hp.cls_b = h->P(Y.cls_b);
+  hp.regs_w = h->P(Y.regs_w); hp.regs_b = h->P(Y.regs_b);
+  hp.rege_w = h->P(Y.rege_w); hp.rege_b = h->P(Y.rege_b);
+  return hp;
+}
+
+HeadGrads head_grads(const bqa_handle* h) {
+  const bqa_layout& Y = h->lay;
+  HeadGrads hg;
+  hg.pool_w = h->G(Y.pool_w); hg.pool_b = h->G(Y.pool_b);
+  hg.span_w = h->G(Y.span_w); hg.span_b = h->G(Y.span_b);
+  hg.cls_w = h->G(Y.cls_w); hg.cls_b = h->G(Y.cls_b);
+  hg.regs_w = h->G(Y.regs_w); hg.regs_b = h->G(Y.regs_b);
+  hg.rege_w = h->G(Y.rege_w); hg.rege_b = h->G(Y.rege_b);
+  return hg;
+}
+
+}  // namespace
+
+extern "C" {
+
+int bqa_param_layout(const bqa_config* cfg, bqa_layout* out) {
+  if (cfg == nullptr || out == nullptr) {
+    set_error("bqa_param_layout: null argument");
+    return 1;
+  }
+  return compute_layout(*cfg, out);
+}
+
+int bqa_workspace_bytes(const bqa_config* cfg, int32_t B, int32_t S, int32_t training, uint64_t* out) {
+  bqa_layout L;
+  if (cfg == nullptr || out == nullptr || compute_layout(*cfg, &L)) return 1;
+  if (B < 1 || S < 1 || S > 512 || S > cfg->max_pos) {
+    set_error("bqa_workspace_bytes: B=%d S=%d out of range (S <= min(512, max_pos=%d))", B, S, cfg->max_pos);
+    return 1;
+  }
+  Workspace w;
+  carve(&w, nullptr, *cfg, B, S, training != 0);
+  *out = w.bytes;
+  return 0;
+}
+
+int bqa_create(const bqa_config* cfg, bqa_handle** out) {
+  if (cfg == nullptr || out == nullptr) {
+    set_error("bqa_create: null argument");
+    return 1;
+  }
+  bqa_layout L;
+  if (compute_layout(*cfg, &L)) return 1;
+  int sms = 0;
+  if (device_sm_count(&sms)) return 1;
+  int dev = 0, major = 0;
+  BQA_CUDA_CHECK(cudaGetDevice(&dev));
+  BQA_CUDA_CHECK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  if (major != 10) {
+    set_error("bqa_create: device compute capability %d.x is not sm_100 (this library has no other code path)", major);
+    return 1;
+  }
+  bqa_handle* h = new (std::nothrow) bqa_handle();
+  if (h == nullptr) {
+    set_error("bqa_create: out of host memory");
+    return 1;
+  }
+  h->cfg = *cfg;
+  h->lay = L;
+  h->num_sms = sms;
+  *out = h;
+  return 0;
+}
+
+int bqa_destroy(bqa_handle* h) {
+  delete h;
+  return 0;
+}
+
+int bqa_bind(bqa_handle* h, float* params, float* grads, void* params_bf16, void* workspace,
+             uint64_t workspace_bytes) {
+  if (h == nullptr || params == nullptr || params_bf16 == nullptr || workspace == nullptr) {
+    set_error("bqa_bind: null argument");
+    return 1;
+  }
+  if ((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads) |
+       reinterpret_cast<uintptr_t>(params_bf16) | reinterpret_cast<uintptr_t>(workspace)) & 255u) {
+    set_error("bqa_bind: buffers must be 256-byte aligned");
+    return 1;
+  }
+  h->params = params;
+  h->grads = grads;
+  h->params_bf16 = reinterpret_cast<bf16*>(params_bf16);
+  h->workspace = reinterpret_cast<uint8_t*>(workspace);
+  h->workspace_bytes = workspace_bytes;
+  h->plan_valid = false;
+  return 0;
+}
+
+int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_type_ids,
+                const uint8_t* attention_mask, int32_t B, int32_t S, int32_t training, uint64_t seed,
+                uint64_t step, float* start, float* end, float* cls, float* reg_start, float* reg_end,
+                void* stream) {
+  if (h == nullptr || h->params == nullptr) {
+    set_error("bqa_forward: handle not bound");
+    return 1;
+  }
+  if (B < 1 || S < 1 || S > 512 || S > h->cfg.max_pos) {
+    set_error("bqa_forward: B=%d S=%d out of range (S <= min(512, max_pos=%d))", B, S, h->cfg.max_pos);
+    return 1;
+  }
+  if (training && h->grads == nullptr) {
+    set_error("bqa_forward: training forward needs a bound gradient buffer");
+    return 1;
+  }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const bool tr = training != 0;
+  if (!h->plan_valid || h->plan.B != B || h->plan.S != S || h->plan.training != tr) {
+    if (build_plan(h, B, S, tr)) return 1;
+  }
+  h->seed = seed;
+  h->step = step;
+  h->last_training = tr;
+  const bqa_config& c = h->cfg;
+  const bqa_layout& Y = h->lay;
+  Workspace& w = h->plan.ws;
+  const int T = B * S, H = c.hidden;
+  const size_t tb = static_cast<size_t>(T);
+
+  // inputs are kept for the backward (embedding scatter, key mask)
+  BQA_CUDA_CHECK(cudaMemcpyAsync(w.ids, input_ids, tb * sizeof(int64_t), cudaMemcpyDeviceToDevice, st));
+  if (token_type_ids != nullptr)
+    BQA_CUDA_CHECK(cudaMemcpyAsync(w.tt, token_type_ids, tb * sizeof(int64_t), cudaMemcpyDeviceToDevice, st));
+  else
+    BQA_CUDA_CHECK(cudaMemsetAsync(w.tt, 0, tb * sizeof(int64_t), st));
+  const uint8_t* mask = nullptr;
+  if (attention_mask != nullptr) {
+    BQA_CUDA_CHECK(cudaMemcpyAsync(w.mask, attention_mask, tb, cudaMemcpyDeviceToDevice, st));
+    mask = w.mask;
+  }
+  h->has_mask = mask != nullptr;
+  BQA_CUDA_CHECK(cudaMemsetAsync(w.err_flag, 0, sizeof(int), st));
+
+  if (launch_embed_ln_fwd(w.ids, w.tt, h->P(Y.word_emb), h->P(Y.pos_emb), h->P(Y.type_emb), h->P(Y.emb_ln_g),
+                          h->P(Y.emb_ln_b), w.z0, w.x0, T, S, H, c.vocab, c.type_vocab, c.ln_eps,
+                          h->key(site_embed(), c.hidden_dropout), w.err_flag, st))
+    return 1;
+  h->launches += 1;
+  const int slots = static_cast<int>(w.layer.size());
+  const DropKey nodrop = make_drop_key(0, 0, 0.0f);
+  for (int l = 0; l < c.num_layers; ++l) {
+    LayerPlans& lp = h->plan.layer[l];
+    const LayerActs& act = w.layer[l % slots];
+    const int64_t lo = h->layer_off(l);
+    if (launch_gemm(h, lp.qkv, nodrop, st)) return 1;
+    if (attn_forward(lp.attn, mask, h->key(site_attn(l), c.attn_dropout), st)) return 1;
+    if (launch_gemm(h, lp.ao, h->key(site_ao(l), c.hidden_dropout), st)) return 1;
+    if (launch_ln_fwd(act.z1, h->P(lo + Y.ln1_g), h->P(lo + Y.ln1_b), act.a, T, H, c.ln_eps, st)) return 1;
+    if (launch_gemm(h, lp.ffn1, nodrop, st)) return 1;
+    if (launch_gemm(h, lp.ffn2, h->key(site_ffn(l), c.hidden_dropout), st)) return 1;
+    if (launch_ln_fwd(act.z2, h->P(lo + Y.ln2_g), h->P(lo + Y.ln2_b), act.x_out, T, H, c.ln_eps, st)) return 1;
+    h->launches += 3;
+  }
+  const bf16* y = w.layer[(c.num_layers - 1) % slots].x_out;
+  const HeadParams hp = head_params(h);
+  if (launch_span_head_fwd(y, hp.span_w, hp.span_b, w.start, w.end, T, H, st)) return 1;
+  if (launch_pooler_heads_fwd(y, hp, w.pooled, w.cls, w.reg_s, w.reg_e, B, S, H, c.num_labels,
+                              h->key(site_cls(c.num_layers), c.hidden_dropout), st))
+    return 1;
+  h->launches += 3;
+  BQA_CUDA_CHECK(cudaMemcpyAsync(start, w.start, tb * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  BQA_CUDA_CHECK(cudaMemcpyAsync(end, w.end, tb * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  BQA_CUDA_CHECK(cudaMemcpyAsync(cls, w.cls, static_cast<size_t>(B) * c.num_labels * sizeof(float),
+                                 cudaMemcpyDeviceToDevice, st));
+  BQA_CUDA_CHECK(cudaMemcpyAsync(reg_start, w.reg_s, static_cast<size_t>(B) * sizeof(float),
+                                 cudaMemcpyDeviceToDevice, st));
+  BQA_CUDA_CHECK(cudaMemcpyAsync(reg_end, w.reg_e, static_cast<size_t>(B) * sizeof(float),
+                                 cudaMemcpyDeviceToDevice, st));
+  return 0;
+}
+
+int bqa_loss(bqa_handle* h, const float* start, const float* end, const float* cls, const float* reg_start,
+             const float* reg_end, const int64_t* y_start, const int64_t* y_end, const int64_t* y_cls,
+             const float* y_reg_start, const float* y_reg_end, const bqa_loss_config* lc, int32_t with_grad,
+             float* losses, void* stream) {
+  if (h == nullptr || !h->plan_valid || lc == nullptr) {
+    set_error("bqa_loss: no forward has been run on this handle");
+    return 1;
+  }
+  if (with_grad && !h->plan.training) {
+    set_error("bqa_loss: gradients requested but the last forward was not a training forward");
+    return 1;
+  }
+  if (lc->cls_loss != BQA_CLS_SMOOTH && lc->cls_loss != BQA_CLS_CE) {
+    set_error("bqa_loss: unsupported class loss %d (focal loss is not implemented)", lc->cls_loss);
+    return 1;
+  }
+  Workspace& w = h->plan.ws;
+  LossConfig k;
+  k.w_start = lc->w_start; k.w_end = lc->w_end;
+  k.w_start_reg = lc->w_start_reg; k.w_end_reg = lc->w_end_reg; k.w_cls = lc->w_cls;
+  k.cls_kind = lc->cls_loss == BQA_CLS_CE ? CLS_LOSS_CE : CLS_LOSS_SMOOTH;
+  k.smooth_alpha = lc->smooth_alpha;
+  k.cls_weight = lc->cls_weight;
+  k.grad_scale = lc->loss_scale;
+  h->launches += 2;
+  return launch_loss_fwd_bwd(start, end, cls, reg_start, reg_end, y_start, y_end, y_cls, y_reg_start, y_reg_end,
+                             w.d_start, w.d_end, w.d_cls, w.d_reg_s, w.d_reg_e, w.loss_rows, losses, h->plan.B,
+                             h->plan.S, h->cfg.num_labels, k, with_grad, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int bqa_set_output_grads(bqa_handle* h, const float* d_start, const float* d_end, const float* d_cls,
+                         const float* d_reg_start, const float* d_reg_end, void* stream) {
+  if (h == nullptr || !h->plan_valid || !h->plan.training) {
+    set_error("bqa_set_output_grads: the last forward was not a training forward");
+    return 1;
+  }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  Workspace& w = h->plan.ws;
+  const size_t T = static_cast<size_t>(h->plan.B) * h->plan.S, B = h->plan.B, C = h->cfg.num_labels;
+  auto put = [&](float* dst, const float* src, size_t n) -> int {
+    if (src != nullptr)
+      BQA_CUDA_CHECK(cudaMemcpyAsync(dst, src, n * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    else
+      BQA_CUDA_CHECK(cudaMemsetAsync(dst, 0, n * sizeof(float), st));
+    return 0;
+  };
+  if (put(w.d_start, d_start, T) || put(w.d_end, d_end, T) || put(w.d_cls, d_cls, B * C) ||
+      put(w.d_reg_s, d_reg_start, B) || put(w.d_reg_e, d_reg_end, B))
+    return 1;
+  return 0;
+}
+
+int bqa_num_backward_phases(const bqa_handle* h) { return h == nullptr ? 0 : h->cfg.num_layers + 2; }
+
+int64_t bqa_phase_grad_begin(const bqa_handle* h, int32_t phase) {
+  if (h == nullptr) return -1;
+  const int L = h->cfg.num_layers;
+  if (phase <= 0) return h->lay.pool_w;
+  if (phase <= L) return h->layer_off(L - phase);
+  return 0;
+}
+
+int64_t bqa_launch_count(const bqa_handle* h) { return h == nullptr ? 0 : h->launches; }
+
+int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* stream) {
+  if (h == nullptr || !h->plan_valid || !h->plan.training || !h->last_training) {
+    set_error("bqa_backward: the last forward was not a training forward");
+    return 1;
+  }
+  const bqa_config& c = h->cfg;
+  const bqa_layout& Y = h->lay;
+  const int L = c.num_layers;
+  if (first_phase < 0 || last_phase > L + 1 || first_phase > last_phase) {
+    set_error("bqa_backward: phase range [%d, %d] outside [0, %d]", first_phase, last_phase, L + 1);
+    return 1;
+  }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  Workspace& w = h->plan.ws;
+  const int B = h->plan.B, S = h->plan.S, T = B * S, H = c.hidden, I = c.intermediate;
+  const DropKey nodrop = make_drop_key(0, 0, 0.0f);
+  const uint8_t* mask = h->has_mask ? w.mask : nullptr;
+
+  for (int phase = first_phase; phase <= last_phase; ++phase) {
+    if (phase == 0) {
+      // gradient of the last hidden states comes out of the heads in slot dy[(L) & 1]
+      bf16* dy = (L & 1) ? w.dy1 : w.dy0;
+      const bf16* y = w.layer[L - 1].x_out;
+      if (launch_heads_bwd(y, w.pooled, w.reg_s, w.reg_e, w.d_start, w.d_end, w.d_cls, w.d_reg_s, w.d_reg_e,
+                           head_params(h), head_grads(h), w.dpre, w.dx0, dy, B, S, H, c.num_labels,
+                           h->key(site_cls(L), c.hidden_dropout), h->num_sms, st))
+        return 1;
+      h->launches += 4;
+    } else if (phase <= L) {
+      const int l = L - phase;
+      LayerPlans& lp = h->plan.layer[l];
+      const LayerActs& act = w.layer[l];
+      const int64_t lo = h->layer_off(l);
+      const bf16* dy_in = ((l + 1) & 1) ? w.dy1 : w.dy0;  // gradient w.r.t. this layer's output
+      const bool hd = c.hidden_dropout > 0.0f;
+      // LN2 backward: dres = d z2 (residual branch), dgm = d (ffn2 GEMM output) = dres * keep-mask
+      if (launch_ln_bwd(dy_in, act.z2, h->P(lo + Y.ln2_g), w.dres, hd ? w.dgm : w.dres, h->G(lo + Y.ln2_g),
+                        h->G(lo + Y.ln2_b), h->G(lo + Y.o_b), T, H, c.ln_eps, nodrop,
+                        h->key(site_ffn(l), c.hidden_dropout), h->num_sms, st))
+        return 1;
+      if (launch_gemm(h, lp.w_ffn2, nodrop, st)) return 1;
+      if (launch_gemm(h, lp.d_ffn2, nodrop, st)) return 1;  // du = (dgm . W2) * gelu'(u)
+      if (launch_colsum(w.du, I, h->G(lo + Y.i_b), T, I, h->num_sms, st)) return 1;
+      if (launch_gemm(h, lp.w_ffn1, nodrop, st)) return 1;
+      if (launch_gemm(h, lp.d_ffn1, nodrop, st)) return 1;  // da = du . W1 + dres   (into the dctx slab)
+      // LN1 backward on da
+      if (launch_ln_bwd(w.dctx, act.z1, h->P(lo + Y.ln1_g), w.dres, hd ? w.dgm : w.dres, h->G(lo + Y.ln1_g),
+                        h->G(lo + Y.ln1_b), h->G(lo + Y.ao_b), T, H, c.ln_eps, nodrop,
+                        h->key(site_ao(l), c.hidden_dropout), h->num_sms, st))
+        return 1;
+      if (launch_gemm(h, lp.w_ao, nodrop, st)) return 1;
+      if (launch_gemm(h, lp.d_ao, nodrop, st)) return 1;  // dctx = dgm . Wo
+      if (attn_backward(lp.attn, mask, h->key(site_attn(l), c.attn_dropout), st)) return 1;
+      if (launch_colsum(w.dqkv, 3 * H, h->G(lo + Y.qkv_b), T, 3 * H, h->num_sms, st)) return 1;
+      if (launch_gemm(h, lp.w_qkv, nodrop, st)) return 1;
+      if (launch_gemm(h, lp.d_qkv, nodrop, st)) return 1;  // dx = dqkv . Wqkv + dres
+      h->launches += 7;
+    } else {
+      // embeddings: x0 = dropout(LN(z0)); dz0 scattered into the three tables
+      const bf16* dy_in = w.dy0;  // layer 0 wrote its input gradient into dy[0 & 1]
+      if (launch_ln_bwd(dy_in, w.z0, h->P(Y.emb_ln_g), w.dres, nullptr, h->G(Y.emb_ln_g), h->G(Y.emb_ln_b), nullptr,
+                        T, H, c.ln_eps, h->key(site_embed(), c.hidden_dropout), nodrop, h->num_sms, st))
+        return 1;
+      if (launch_embed_bwd(w.dres, w.ids, w.tt, h->G(Y.word_emb), h->G(Y.pos_emb), h->G(Y.type_emb), T, S, H, st))
+        return 1;
+      h->launches += 2;
+    }
+  }
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,516 @@
+// heads_loss.cu — pooler, the four QA heads, the weighted multi-task loss (forward and the
+// gradients it sends into the heads), the heads' backward and validate.py-style span decoding.
+//
+// Reference:
+//   BertPooler.forward                site-packages/transformers/models/bert/modeling_bert.py:462-468
+//   heads                             modules/model/model/model.py:30-41,54-65
+//   WeightedLoss / losses             modules/model/model/loss.py:5-38,74-100, modules/init.py:18-40
+//   decode                            modules/model/inference/predictor.py:114-120
+// All of this is < 0.01 % of the step's FLOPs; the kernels are latency/HBM-bound warp-shuffle
+// reductions in fp32 on fp32 master weights (logits stay fp32 so that argmax ties resolve as
+// in the reference: first maximal index).
+#include "kernels.cuh"
+
+namespace bqa {
+
+namespace {
+
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  v = warp_sum(v);
+  __syncthreads();
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float s = 0.0f;
+  for (int w = 0; w < nw; ++w) s += red[w];  // fixed order: deterministic
+  return s;
+}
+
+__device__ __forceinline__ float block_max(float v, float* red) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  v = warp_max(v);
+  __syncthreads();
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float s = red[0];
+  for (int w = 1; w < nw; ++w) s = fmaxf(s, red[w]);
+  return s;
+}
+
+// dot of a bf16 row with an fp32 vector, warp-cooperative; H % 8 == 0
+__device__ __forceinline__ float warp_dot_bf16_f32(const bf16* __restrict__ x, const float* __restrict__ w, int H,
+                                                   int lane) {
+  float acc = 0.0f;
+  for (int c = lane * 8; c < H; c += 256) {
+    const uint4 u = __ldg(reinterpret_cast<const uint4*>(x + c));
+    const float4 w0 = __ldg(reinterpret_cast<const float4*>(w + c));
+    const float4 w1 = __ldg(reinterpret_cast<const float4*>(w + c + 4));
+    const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+    acc += a.x * w0.x + a.y * w0.y + b.x * w0.z + b.y * w0.w + cc.x * w1.x + cc.y * w1.y + d.x * w1.z + d.y * w1.w;
+  }
+  return warp_sum(acc);
+}
+
+// ---------------------------------------------------------------------------------------
+// forward
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+span_head_fwd_kernel(const bf16* __restrict__ y, const float* __restrict__ w, const float* __restrict__ b,
+                     float* __restrict__ start, float* __restrict__ end, int T, int H) {
+  const int lane = threadIdx.x & 31;
+  const int t = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (t >= T) return;
+  const bf16* row = y + static_cast<size_t>(t) * H;
+  const float s = warp_dot_bf16_f32(row, w, H, lane);
+  const float e = warp_dot_bf16_f32(row, w + H, H, lane);
+  if (lane == 0) {
+    start[t] = s + b[0];
+    end[t] = e + b[1];
+  }
+}
+
+// pooled[b][j] = tanh(y[b*S][:] . Wp[j][:] + bp[j]);  grid (ceil(H/32), B), 8 warps x 4 rows
+__global__ void __launch_bounds__(256)
+pooler_fwd_kernel(const bf16* __restrict__ y, const float* __restrict__ Wp, const float* __restrict__ bp,
+                  float* __restrict__ pooled, int S, int H) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int b = blockIdx.y;
+  const bf16* x = y + static_cast<size_t>(b) * S * H;
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int j = blockIdx.x * 32 + warp * 4 + r;
+    if (j < H) {
+      const float v = warp_dot_bf16_f32(x, Wp + static_cast<size_t>(j) * H, H, lane);
+      if (lane == 0) pooled[static_cast<size_t>(b) * H + j] = tanhf(v + bp[j]);
+    }
+  }
+}
+
+// cls[b][c] = dropout(pooled[b]) . Wc[c] + bc[c]; reg = sigmoid(pooled[b] . w + b);  grid B
+__global__ void __launch_bounds__(256)
+heads_fwd_kernel(const float* __restrict__ pooled, HeadParams hp, float* __restrict__ cls, float* __restrict__ reg_s,
+                 float* __restrict__ reg_e, int H, int C, DropKey drop) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int b = blockIdx.x;
+  const float* p = pooled + static_cast<size_t>(b) * H;
+  for (int o = warp; o < C + 2; o += nw) {
+    const float* w = o < C ? hp.cls_w + static_cast<size_t>(o) * H : (o == C ? hp.regs_w : hp.rege_w);
+    float acc = 0.0f;
+    for (int j = lane; j < H; j += 32) {
+      float pv = p[j];
+      if (o < C && drop.thresh != 0u) pv = drop_keep(drop, static_cast<uint32_t>(b) * H + j) ? pv * drop.scale : 0.0f;
+      acc += pv * w[j];
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) {
+      if (o < C) {
+        cls[static_cast<size_t>(b) * C + o] = acc + hp.cls_b[o];
+      } else {
+        const float z = acc + (o == C ? hp.regs_b[0] : hp.rege_b[0]);
+        const float sg = 1.0f / (1.0f + __expf(-z));
+        (o == C ? reg_s : reg_e)[b] = sg;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// loss: one block per batch row writes its five contributions; a 1-block kernel adds them
+// in a fixed order (deterministic) and forms the weighted total.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+loss_rows_kernel(const float* __restrict__ start, const float* __restrict__ end, const float* __restrict__ cls,
+                 const float* __restrict__ reg_s, const float* __restrict__ reg_e, const int64_t* __restrict__ y_start,
+                 const int64_t* __restrict__ y_end, const int64_t* __restrict__ y_cls,
+                 const float* __restrict__ y_reg_s, const float* __restrict__ y_reg_e, float* __restrict__ d_start,
+                 float* __restrict__ d_end, float* __restrict__ d_cls, float* __restrict__ d_reg_s,
+                 float* __restrict__ d_reg_e, float* __restrict__ row_scratch, int B, int S, int C, LossConfig lc,
+                 int with_grad) {
+  __shared__ float red[8];
+  __shared__ float s_cnt[3];
+  const int b = blockIdx.x;
+  // denominators of the three mean-reduced classification losses
+  if (threadIdx.x < 3) {
+    float cnt = 0.0f;
+    for (int i = 0; i < B; ++i) {
+      if (threadIdx.x == 0) cnt += (y_start[i] != -1) ? 1.0f : 0.0f;
+      if (threadIdx.x == 1) cnt += (y_end[i] != -1) ? 1.0f : 0.0f;
+      if (threadIdx.x == 2) {
+        const long long yc = y_cls[i];
+        if (yc != -100) cnt += (lc.cls_kind == CLS_LOSS_CE && lc.cls_weight != nullptr && yc >= 0 && yc < C)
+                                   ? lc.cls_weight[yc]
+                                   : 1.0f;
+      }
+    }
+    s_cnt[threadIdx.x] = cnt;
+  }
+  __syncthreads();
+
+  // ---- start / end : CrossEntropyLoss(ignore_index=-1) over the S positions (init.py:34-35)
+  for (int which = 0; which < 2; ++which) {
+    const float* logit = (which == 0 ? start : end) + static_cast<size_t>(b) * S;
+    float* dl = (which == 0 ? d_start : d_end) + static_cast<size_t>(b) * S;
+    const long long y = (which == 0 ? y_start : y_end)[b];
+    const float w = which == 0 ? lc.w_start : lc.w_end;
+    const float nvalid = s_cnt[which];
+    float mx = -INFINITY;
+    for (int s = threadIdx.x; s < S; s += blockDim.x) mx = fmaxf(mx, logit[s]);
+    mx = block_max(mx, red);
+    float se = 0.0f;
+    for (int s = threadIdx.x; s < S; s += blockDim.x) se += __expf(logit[s] - mx);
+    se = block_sum(se, red);
+    const float lse = mx + __logf(se);
+    const bool valid = (y != -1);
+    if (threadIdx.x == 0) {
+      float l = 0.0f;
+      if (valid && y >= 0 && y < S) l = (lse - logit[y]) / nvalid;
+      if (nvalid == 0.0f) l = __int_as_float(0x7fc00000);  // torch: mean over zero targets is NaN
+      row_scratch[b * 5 + which] = l;
+    }
+    if (with_grad) {
+      const float gs = valid ? w * lc.grad_scale / nvalid : 0.0f;
+      for (int s = threadIdx.x; s < S; s += blockDim.x) {
+        const float p = __expf(logit[s] - lse);
+        dl[s] = gs * (p - ((valid && s == y) ? 1.0f : 0.0f));
+      }
+    }
+  }
+
+  // ---- regressions : MSELoss on the sigmoid outputs (init.py:36-37)
+  if (threadIdx.x == 0) {
+    for (int which = 0; which < 2; ++which) {
+      const float sg = (which == 0 ? reg_s : reg_e)[b];
+      const float t = (which == 0 ? y_reg_s : y_reg_e)[b];
+      const float w = which == 0 ? lc.w_start_reg : lc.w_end_reg;
+      const float d = sg - t;
+      row_scratch[b * 5 + 2 + which] = d * d / static_cast<float>(B);
+      if (with_grad) (which == 0 ? d_reg_s : d_reg_e)[b] = w * lc.grad_scale * 2.0f * d / static_cast<float>(B);
+    }
+    // ---- answer-type class loss (init.py:22-31)
+    const float* z = cls + static_cast<size_t>(b) * C;
+    float mx = -INFINITY;
+    for (int c = 0; c < C; ++c) mx = fmaxf(mx, z[c]);
+    float se = 0.0f;
+    for (int c = 0; c < C; ++c) se += __expf(z[c] - mx);
+    const float lse = mx + __logf(se);
+    const long long y = y_cls[b];
+    float l = 0.0f;
+    if (lc.cls_kind == CLS_LOSS_SMOOTH && lc.smooth_alpha > 0.0f) {
+      // LabelSmoothingLossWithLogits (loss.py:5-38): KLDivLoss(batchmean) against
+      // fill = alpha / (C - 1) everywhere, 1 - alpha at the label
+      const float fill = lc.smooth_alpha / static_cast<float>(C - 1);
+      const float conf = 1.0f - lc.smooth_alpha;
+      float tsum = 0.0f;
+      for (int c = 0; c < C; ++c) {
+        const float t = (c == y) ? conf : fill;
+        tsum += t;
+        if (t > 0.0f) l += t * (__logf(t) - (z[c] - lse));
+      }
+      l /= static_cast<float>(B);
+      if (with_grad)
+        for (int c = 0; c < C; ++c) {
+          const float t = (c == y) ? conf : fill;
+          d_cls[static_cast<size_t>(b) * C + c] =
+              lc.w_cls * lc.grad_scale * (__expf(z[c] - lse) * tsum - t) / static_cast<float>(B);
+        }
+    } else {
+      // nn.CrossEntropyLoss(weight) / NLLLoss(ignore_index=-100): weighted mean over valid rows
+      const bool valid = (y != -100) && y >= 0 && y < C;
+      const float wy = (valid && lc.cls_kind == CLS_LOSS_CE && lc.cls_weight != nullptr) ? lc.cls_weight[y] : 1.0f;
+      const float den = s_cnt[2];
+      if (valid) l = wy * (lse - z[y]) / den;
+      if (den == 0.0f) l = __int_as_float(0x7fc00000);
+      if (with_grad)
+        for (int c = 0; c < C; ++c)
+          d_cls[static_cast<size_t>(b) * C + c] =
+              valid ? lc.w_cls * lc.grad_scale * wy * (__expf(z[c] - lse) - (c == y ? 1.0f : 0.0f)) / den : 0.0f;
+    }
+    row_scratch[b * 5 + 4] = l;
+  }
+}
+
+__global__ void loss_finalize_kernel(const float* __restrict__ row_scratch, float* __restrict__ losses, int B,
+                                     LossConfig lc) {
+  if (threadIdx.x < 5) {
+    float s = 0.0f;
+    for (int b = 0; b < B; ++b) s += row_scratch[b * 5 + threadIdx.x];
+    losses[threadIdx.x] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    // same accumulation order as WeightedLoss.__call__ (loss.py:83-96): dict order of init_losses
+    float total = 0.0f;
+    total += lc.w_start * losses[0];
+    total += lc.w_end * losses[1];
+    total += lc.w_start_reg * losses[2];
+    total += lc.w_end_reg * losses[3];
+    total += lc.w_cls * losses[4];
+    losses[5] = total;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// backward of the heads
+// ---------------------------------------------------------------------------------------
+// grid B: dpre[b][j] = (dcls . Wc[:,j] * keep + drs * wrs[j] + dre * wre[j]) * (1 - pooled^2)
+// and the head weight gradients (B-way atomics on C*H + 2H addresses)
+__global__ void __launch_bounds__(256)
+pooled_bwd_kernel(const float* __restrict__ pooled, const float* __restrict__ reg_s,
+                  const float* __restrict__ reg_e, const float* __restrict__ d_cls, const float* __restrict__ d_rs,
+                  const float* __restrict__ d_re, HeadParams hp, HeadGrads hg, float* __restrict__ dpre, int H,
+                  int C, DropKey drop) {
+  const int b = blockIdx.x;
+  // through the sigmoid: d/dz = d/dsigma * sigma * (1 - sigma)
+  const float drs = d_rs[b] * reg_s[b] * (1.0f - reg_s[b]);
+  const float dre = d_re[b] * reg_e[b] * (1.0f - reg_e[b]);
+  for (int j = threadIdx.x; j < H; j += blockDim.x) {
+    const float pv = pooled[static_cast<size_t>(b) * H + j];
+    float keep = 1.0f;
+    if (drop.thresh != 0u) keep = drop_keep(drop, static_cast<uint32_t>(b) * H + j) ? drop.scale : 0.0f;
+    float dp = drs * hp.regs_w[j] + dre * hp.rege_w[j];
+    for (int c = 0; c < C; ++c) {
+      const float dc = d_cls[static_cast<size_t>(b) * C + c];
+      dp += dc * hp.cls_w[static_cast<size_t>(c) * H + j] * keep;
+      atomicAdd(hg.cls_w + static_cast<size_t>(c) * H + j, dc * pv * keep);
+    }
+    atomicAdd(hg.regs_w + j, drs * pv);
+    atomicAdd(hg.rege_w + j, dre * pv);
+    dpre[static_cast<size_t>(b) * H + j] = dp * (1.0f - pv * pv);
+  }
+  if (threadIdx.x < C) atomicAdd(hg.cls_b + threadIdx.x, d_cls[static_cast<size_t>(b) * C + threadIdx.x]);
+  if (threadIdx.x == 0) {
+    atomicAdd(hg.regs_b, drs);
+    atomicAdd(hg.rege_b, dre);
+  }
+}
+
+// dx0[b][i] = sum_j dpre[b][j] * Wp[j][i];  grid (ceil(H/256), B)
+__global__ void __launch_bounds__(256)
+pooler_dx_kernel(const float* __restrict__ dpre, const float* __restrict__ Wp, float* __restrict__ dx0, int H) {
+  __shared__ float s_d[1024];
+  const int b = blockIdx.y;
+  for (int j = threadIdx.x; j < H; j += blockDim.x) s_d[j] = dpre[static_cast<size_t>(b) * H + j];
+  __syncthreads();
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= H) return;
+  float acc = 0.0f;
+#pragma unroll 8
+  for (int j = 0; j < H; ++j) acc += s_d[j] * __ldg(Wp + static_cast<size_t>(j) * H + i);
+  dx0[static_cast<size_t>(b) * H + i] = acc;
+}
+
+// dWp[j][i] += sum_b dpre[b][j] * x0[b][i], dbp[j] += sum_b dpre[b][j];  grid H (one j per block)
+__global__ void __launch_bounds__(256)
+pooler_wgrad_kernel(const float* __restrict__ dpre, const bf16* __restrict__ y, float* __restrict__ dWp,
+                    float* __restrict__ dbp, int B, int S, int H) {
+  const int j = blockIdx.x;
+  for (int i = threadIdx.x; i < H; i += blockDim.x) {
+    float acc = 0.0f;
+    for (int b = 0; b < B; ++b)
+      acc += dpre[static_cast<size_t>(b) * H + j] * __bfloat162float(y[static_cast<size_t>(b) * S * H + i]);
+    dWp[static_cast<size_t>(j) * H + i] += acc;
+  }
+  if (threadIdx.x == 0) {
+    float acc = 0.0f;
+    for (int b = 0; b < B; ++b) acc += dpre[static_cast<size_t>(b) * H + j];
+    dbp[j] += acc;
+  }
+}
+
+// dy[t][:] = ds[t] * Ws[0][:] + de[t] * Ws[1][:] (+ dx0[b][:] on the [CLS] row)   -> bf16
+// dWs[k][:] += sum_t d_k[t] * y[t][:], dbs[k] += sum_t d_k[t]     (persistent grid, register partials)
+__global__ void __launch_bounds__(128)
+span_bwd_kernel(const bf16* __restrict__ y, const float* __restrict__ d_start, const float* __restrict__ d_end,
+                const float* __restrict__ Ws, const float* __restrict__ dx0, bf16* __restrict__ dy,
+                float* __restrict__ dWs, float* __restrict__ dbs, int T, int S, int H) {
+  __shared__ float red[4][2 * 1024 + 2];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int MV = 4;
+  float acc0[MV][8], acc1[MV][8];
+#pragma unroll
+  for (int j = 0; j < MV; ++j)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc0[j][i] = acc1[j][i] = 0.0f;
+  float sb0 = 0.0f, sb1 = 0.0f;
+  for (int t = blockIdx.x * 4 + warp; t < T; t += gridDim.x * 4) {
+    const float ds = d_start[t], de = d_end[t];
+    sb0 += ds;
+    sb1 += de;
+    const bool is_cls = (t % S) == 0;
+    const int b = t / S;
+#pragma unroll
+    for (int j = 0; j < MV; ++j) {
+      const int c = (j * 32 + lane) * 8;
+      if (c < H) {
+        const uint4 u = __ldg(reinterpret_cast<const uint4*>(y + static_cast<size_t>(t) * H + c));
+        float yv[8];
+        const float2 a = unpack_bf16x2(u.x), bb = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+        yv[0] = a.x; yv[1] = a.y; yv[2] = bb.x; yv[3] = bb.y; yv[4] = cc.x; yv[5] = cc.y; yv[6] = d.x; yv[7] = d.y;
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          acc0[j][i] += ds * yv[i];
+          acc1[j][i] += de * yv[i];
+          o[i] = ds * __ldg(Ws + c + i) + de * __ldg(Ws + H + c + i);
+          if (is_cls) o[i] += dx0[static_cast<size_t>(b) * H + c + i];
+        }
+        uint4 w;
+        w.x = pack_bf16x2(o[0], o[1]);
+        w.y = pack_bf16x2(o[2], o[3]);
+        w.z = pack_bf16x2(o[4], o[5]);
+        w.w = pack_bf16x2(o[6], o[7]);
+        *reinterpret_cast<uint4*>(dy + static_cast<size_t>(t) * H + c) = w;
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < MV; ++j)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      red[warp][(j * 32 + lane) * 8 + i] = acc0[j][i];
+      red[warp][1024 + (j * 32 + lane) * 8 + i] = acc1[j][i];
+    }
+  sb0 = warp_sum(sb0);
+  sb1 = warp_sum(sb1);
+  if (lane == 0) {
+    red[warp][2048] = sb0;
+    red[warp][2049] = sb1;
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < H; c += blockDim.x) {
+    atomicAdd(dWs + c, red[0][c] + red[1][c] + red[2][c] + red[3][c]);
+    atomicAdd(dWs + H + c, red[0][1024 + c] + red[1][1024 + c] + red[2][1024 + c] + red[3][1024 + c]);
+  }
+  if (threadIdx.x < 2)
+    atomicAdd(dbs + threadIdx.x, red[0][2048 + threadIdx.x] + red[1][2048 + threadIdx.x] +
+                                     red[2][2048 + threadIdx.x] + red[3][2048 + threadIdx.x]);
+}
+
+// ---------------------------------------------------------------------------------------
+// decode (predictor.py:114-120): torch.max(dim=-1) -> first maximal index on ties
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void argmax_combine(float& v, int& i, float ov, int oi) {
+  if (ov > v || (ov == v && oi < i)) {
+    v = ov;
+    i = oi;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+decode_kernel(const float* __restrict__ start, const float* __restrict__ end, const float* __restrict__ cls,
+              int64_t* __restrict__ start_idx, int64_t* __restrict__ end_idx, int64_t* __restrict__ cls_idx,
+              float* __restrict__ start_max, float* __restrict__ end_max, float* __restrict__ cls_prob,
+              float* __restrict__ score, int S, int C) {
+  __shared__ float s_v[8];
+  __shared__ int s_i[8];
+  __shared__ float s_best[2];
+  const int b = blockIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int which = 0; which < 2; ++which) {
+    const float* x = (which == 0 ? start : end) + static_cast<size_t>(b) * S;
+    float v = -INFINITY;
+    int idx = 0x7fffffff;
+    for (int s = threadIdx.x; s < S; s += blockDim.x) argmax_combine(v, idx, x[s], s);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, v, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+      argmax_combine(v, idx, ov, oi);
+    }
+    __syncthreads();
+    if (lane == 0) {
+      s_v[warp] = v;
+      s_i[warp] = idx;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      for (int w = 1; w < 8; ++w) argmax_combine(v, idx, s_v[w], s_i[w]);
+      if (idx == 0x7fffffff) idx = 0;
+      (which == 0 ? start_idx : end_idx)[b] = idx;
+      (which == 0 ? start_max : end_max)[b] = v;
+      s_best[which] = v;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    // same association as predictor.py:120: (max_s + max_e) - (s[0] + e[0])
+    score[b] = (s_best[0] + s_best[1]) - (start[static_cast<size_t>(b) * S] + end[static_cast<size_t>(b) * S]);
+    const float* z = cls + static_cast<size_t>(b) * C;
+    float mx = z[0];
+    int mi = 0;
+    for (int c = 1; c < C; ++c)
+      if (z[c] > mx) {
+        mx = z[c];
+        mi = c;
+      }
+    float se = 0.0f;
+    for (int c = 0; c < C; ++c) se += expf(z[c] - mx);
+    cls_idx[b] = mi;
+    cls_prob[b] = 1.0f / se;  // softmax value at the arg max
+  }
+}
+
+}  // namespace
+
+int launch_span_head_fwd(const bf16* y, const float* span_w, const float* span_b, float* start, float* end, int T,
+                         int H, cudaStream_t st) {
+  span_head_fwd_kernel<<<(T + 3) / 4, 128, 0, st>>>(y, span_w, span_b, start, end, T, H);
+  return check_launch("span_head_fwd");
+}
+
+int launch_pooler_heads_fwd(const bf16* y, const HeadParams& hp, float* pooled, float* cls, float* reg_s,
+                            float* reg_e, int B, int S, int H, int C, DropKey cls_drop, cudaStream_t st) {
+  dim3 grid((H + 31) / 32, B);
+  pooler_fwd_kernel<<<grid, 256, 0, st>>>(y, hp.pool_w, hp.pool_b, pooled, S, H);
+  if (check_launch("pooler_fwd")) return 1;
+  heads_fwd_kernel<<<B, 256, 0, st>>>(pooled, hp, cls, reg_s, reg_e, H, C, cls_drop);
+  return check_launch("heads_fwd");
+}
+
+int launch_loss_fwd_bwd(const float* start, const float* end, const float* cls, const float* reg_s,
+                        const float* reg_e, const int64_t* y_start, const int64_t* y_end, const int64_t* y_cls,
+                        const float* y_reg_s, const float* y_reg_e, float* d_start, float* d_end, float* d_cls,
+                        float* d_reg_s, float* d_reg_e, float* row_scratch, float* losses_out, int B, int S,
+                        int C, const LossConfig& lc, int with_grad, cudaStream_t st) {
+  loss_rows_kernel<<<B, 256, 0, st>>>(start, end, cls, reg_s, reg_e, y_start, y_end, y_cls, y_reg_s, y_reg_e,
+                                      d_start, d_end, d_cls, d_reg_s, d_reg_e, row_scratch, B, S, C, lc,
+                                      with_grad);
+  if (check_launch("loss_rows")) return 1;
+  loss_finalize_kernel<<<1, 32, 0, st>>>(row_scratch, losses_out, B, lc);
+  return check_launch("loss_finalize");
+}
+
+int launch_heads_bwd(const bf16* y, const float* pooled, const float* reg_s, const float* reg_e,
+                     const float* d_start, const float* d_end, const float* d_cls, const float* d_reg_s,
+                     const float* d_reg_e, const HeadParams& hp, const HeadGrads& hg, float* dpre_scratch,
+                     float* dx0_scratch, bf16* dy, int B, int S, int H, int C, DropKey cls_drop, int num_sms,
+                     cudaStream_t st) {
+  if (H > 1024 || H % 8 != 0) {
+    set_error("heads backward: H=%d must be a multiple of 8 and <= 1024", H);
+    return 1;
+  }
+  pooled_bwd_kernel<<<B, 256, 0, st>>>(pooled, reg_s, reg_e, d_cls, d_reg_s, d_reg_e, hp, hg, dpre_scratch, H, C,
+                                       cls_drop);
+  if (check_launch("pooled_bwd")) return 1;
+  dim3 g2((H + 255) / 256, B);
+  pooler_dx_kernel<<<g2, 256, 0, st>>>(dpre_scratch, hp.pool_w, dx0_scratch, H);
+  if (check_launch("pooler_dx")) return 1;
+  pooler_wgrad_kernel<<<H, 256, 0, st>>>(dpre_scratch, y, hg.pool_w, hg.pool_b, B, S, H);
+  if (check_launch("pooler_wgrad")) return 1;
+  const int T = B * S;
+  int grid = num_sms * 4;
+  if (grid > (T + 3) / 4) grid = (T + 3) / 4;
+  span_bwd_kernel<<<grid, 128, 0, st>>>(y, d_start, d_end, hp.span_w, dx0_scratch, dy, hg.span_w, hg.span_b, T, S,
+                                        H);
+  return check_launch("span_bwd");
+}
+
+int launch_decode(const float* start, const float* end, const float* cls, int64_t* start_idx, int64_t* end_idx,
+                  int64_t* cls_idx, float* start_max, float* end_max, float* cls_prob, float* score, int B, int S,
+                  int C, cudaStream_t st) {
+  decode_kernel<<<B, 256, 0, st>>>(start, end, cls, start_idx, end_idx, cls_idx, start_max, end_max, cls_prob,
+                                   score, S, C);
+  return check_launch("decode");
+}
+
+}  // namespace bqa
