@@ -197,6 +197,15 @@ BQA_API int bqa_loss(bqa_handle* h, const float* start, const float* end, const 
                      const float* reg_start, const float* reg_end, const int64_t* y_start, const int64_t* y_end,
                      const int64_t* y_cls, const float* y_reg_start, const float* y_reg_end,
                      const bqa_loss_config* lc, int32_t with_grad, float* losses, void* stream);
+/* Handle-free form of bqa_loss for callers that own every buffer (the autograd-facing
+ * WeightedLoss): d_* receive d(total * loss_scale)/d(output) when with_grad != 0 (d_reg_* are
+ * w.r.t. the sigmoid outputs); row_scratch: >= 5 * B floats. */
+BQA_API int bqa_qa_loss(const float* start, const float* end, const float* cls, const float* reg_start,
+                        const float* reg_end, const int64_t* y_start, const int64_t* y_end, const int64_t* y_cls,
+                        const float* y_reg_start, const float* y_reg_end, float* d_start, float* d_end,
+                        float* d_cls, float* d_reg_start, float* d_reg_end, float* row_scratch, float* losses,
+                        int32_t B, int32_t S, int32_t C, const bqa_loss_config* lc, int32_t with_grad,
+                        void* stream);
 /* Alternative to bqa_loss(with_grad): supply d(loss)/d(outputs) computed elsewhere (autograd). */
 BQA_API int bqa_set_output_grads(bqa_handle* h, const float* d_start, const float* d_end, const float* d_cls,
                                  const float* d_reg_start, const float* d_reg_end, void* stream);
@@ -206,6 +215,12 @@ BQA_API int bqa_set_output_grads(bqa_handle* h, const float* d_start, const floa
 BQA_API int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* stream);
 BQA_API int bqa_num_backward_phases(const bqa_handle* h);
 BQA_API int64_t bqa_phase_grad_begin(const bqa_handle* h, int32_t phase);
+/* Per-launch device timing of the tensor-core kernels (CUDA events on the launch stream around
+ * every GEMM / attention launch between begin and end).  end() synchronises and fills HOST
+ * arrays of 5 entries: 0 GEMM forward, 1 dgrad, 2 wgrad, 3 attention forward, 4 attention
+ * backward (milliseconds, algorithmic matmul FLOPs, launches).  Measurement aid for bench.py. */
+BQA_API int bqa_profile_begin(bqa_handle* h);
+BQA_API int bqa_profile_end(bqa_handle* h, double* host_ms, double* host_flops, int64_t* host_count);
 /* Number of kernels launched by this handle since creation (bench.py's gpu_launches). */
 BQA_API int64_t bqa_launch_count(const bqa_handle* h);
 

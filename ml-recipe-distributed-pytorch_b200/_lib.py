@@ -85,11 +85,15 @@ SIGNATURES = {
     "bqa_bind": (ctypes.c_int, [vp, vp, vp, vp, vp, c_u64]),
     "bqa_forward": (ctypes.c_int, [vp, vp, vp, vp, c_i32, c_i32, c_i32, c_u64, c_u64, vp, vp, vp, vp, vp, vp]),
     "bqa_loss": (ctypes.c_int, [vp] + [vp] * 10 + [ctypes.POINTER(LossConfig), c_i32, vp, vp]),
+    "bqa_qa_loss": (ctypes.c_int, [vp] * 17 + [c_i32, c_i32, c_i32, ctypes.POINTER(LossConfig), c_i32, vp]),
     "bqa_set_output_grads": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp]),
     "bqa_backward": (ctypes.c_int, [vp, c_i32, c_i32, vp]),
     "bqa_num_backward_phases": (ctypes.c_int, [vp]),
     "bqa_phase_grad_begin": (c_i64, [vp, c_i32]),
     "bqa_launch_count": (c_i64, [vp]),
+    "bqa_profile_begin": (ctypes.c_int, [vp]),
+    "bqa_profile_end": (ctypes.c_int, [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
+                                       ctypes.POINTER(c_i64)]),
 }
 
 

@@ -205,6 +205,35 @@ struct bqa_handle {
   bool last_training = false;
   bool has_mask = false;
   int64_t launches = 0;
+  // optional per-launch timing of the tensor-core kernels (bench.py's roofline leg)
+  struct Timed {
+    cudaEvent_t a, b;
+    double flops;
+    int kind;  // 0 = GEMM forward, 1 = dgrad, 2 = wgrad, 3 = attention forward, 4 = attention backward
+  };
+  bool profiling = false;
+  std::vector<Timed> timed;
+  std::vector<cudaEvent_t> event_pool;
+  cudaEvent_t get_event() {
+    if (!event_pool.empty()) {
+      cudaEvent_t e = event_pool.back();
+      event_pool.pop_back();
+      return e;
+    }
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    return e;
+  }
+  void time_begin(int kind, double flops, cudaStream_t st) {
+    if (!profiling) return;
+    Timed t{get_event(), get_event(), flops, kind};
+    cudaEventRecord(t.a, st);
+    timed.push_back(t);
+  }
+  void time_end(cudaStream_t st) {
+    if (!profiling) return;
+    cudaEventRecord(timed.back().b, st);
+  }
 
   const float* P(int64_t off) const { return params + off; }
   float* G(int64_t off) const { return grads + off; }
@@ -321,7 +350,17 @@ int build_plan(bqa_handle* h, int B, int S, bool training) {
 int launch_gemm(bqa_handle* h, GemmPlan& plan, DropKey drop, cudaStream_t st) {
   plan.args.drop = drop;
   h->launches += 1;
-  return gemm_launch(plan, st);
+  const int kind = (plan.variant >> 2) == EPI_F32_ADD ? 2 : ((plan.variant & 2) ? 1 : 0);
+  h->time_begin(kind, 2.0 * plan.args.M * plan.args.N * plan.args.K, st);
+  const int rc = gemm_launch(plan, st);
+  h->time_end(st);
+  return rc;
+}
+
+// matmul FLOPs of one attention call: QK^T and PV forward (4 S^2 d per head), 7 products backward
+double attn_flops(const bqa_handle* h, int B, int S, bool backward) {
+  const double per = 2.0 * B * h->cfg.heads * static_cast<double>(S) * S * 64.0;
+  return backward ? 7.0 * per : 2.0 * per;
 }
 
 HeadParams head_params(const bqa_handle* h) {
@@ -400,7 +439,50 @@ int bqa_create(const bqa_config* cfg, bqa_handle** out) {
 }
 
 int bqa_destroy(bqa_handle* h) {
+  if (h != nullptr) {
+    for (auto& t : h->timed) {
+      cudaEventDestroy(t.a);
+      cudaEventDestroy(t.b);
+    }
+    for (auto e : h->event_pool) cudaEventDestroy(e);
+  }
   delete h;
+  return 0;
+}
+
+int bqa_profile_begin(bqa_handle* h) {
+  if (h == nullptr) {
+    set_error("bqa_profile_begin: null handle");
+    return 1;
+  }
+  for (auto& t : h->timed) {
+    h->event_pool.push_back(t.a);
+    h->event_pool.push_back(t.b);
+  }
+  h->timed.clear();
+  h->profiling = true;
+  return 0;
+}
+
+int bqa_profile_end(bqa_handle* h, double* host_ms, double* host_flops, int64_t* host_count) {
+  if (h == nullptr || host_ms == nullptr || host_flops == nullptr || host_count == nullptr) {
+    set_error("bqa_profile_end: null argument");
+    return 1;
+  }
+  h->profiling = false;
+  for (int k = 0; k < 5; ++k) {
+    host_ms[k] = 0.0;
+    host_flops[k] = 0.0;
+    host_count[k] = 0;
+  }
+  for (auto& t : h->timed) {
+    BQA_CUDA_CHECK(cudaEventSynchronize(t.b));
+    float ms = 0.0f;
+    BQA_CUDA_CHECK(cudaEventElapsedTime(&ms, t.a, t.b));
+    host_ms[t.kind] += ms;
+    host_flops[t.kind] += t.flops;
+    host_count[t.kind] += 1;
+  }
   return 0;
 }
 
@@ -480,7 +562,9 @@ int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_ty
     const LayerActs& act = w.layer[l % slots];
     const int64_t lo = h->layer_off(l);
     if (launch_gemm(h, lp.qkv, nodrop, st)) return 1;
+    h->time_begin(3, attn_flops(h, B, S, false), st);
     if (attn_forward(lp.attn, mask, h->key(site_attn(l), c.attn_dropout), st)) return 1;
+    h->time_end(st);
     if (launch_gemm(h, lp.ao, h->key(site_ao(l), c.hidden_dropout), st)) return 1;
     if (launch_ln_fwd(act.z1, h->P(lo + Y.ln1_g), h->P(lo + Y.ln1_b), act.a, T, H, c.ln_eps, st)) return 1;
     if (launch_gemm(h, lp.ffn1, nodrop, st)) return 1;
@@ -506,6 +590,45 @@ int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_ty
   return 0;
 }
 
+static int to_loss_config(const bqa_loss_config* lc, LossConfig* k) {
+  if (lc == nullptr) {
+    set_error("loss: null configuration");
+    return 1;
+  }
+  if (lc->cls_loss != BQA_CLS_SMOOTH && lc->cls_loss != BQA_CLS_CE) {
+    set_error("loss: unsupported class loss %d (focal loss is not implemented)", lc->cls_loss);
+    return 1;
+  }
+  k->w_start = lc->w_start; k->w_end = lc->w_end;
+  k->w_start_reg = lc->w_start_reg; k->w_end_reg = lc->w_end_reg; k->w_cls = lc->w_cls;
+  k->cls_kind = lc->cls_loss == BQA_CLS_CE ? CLS_LOSS_CE : CLS_LOSS_SMOOTH;
+  k->smooth_alpha = lc->smooth_alpha;
+  k->cls_weight = lc->cls_weight;
+  k->grad_scale = lc->loss_scale;
+  return 0;
+}
+
+int bqa_qa_loss(const float* start, const float* end, const float* cls, const float* reg_start,
+                const float* reg_end, const int64_t* y_start, const int64_t* y_end, const int64_t* y_cls,
+                const float* y_reg_start, const float* y_reg_end, float* d_start, float* d_end, float* d_cls,
+                float* d_reg_start, float* d_reg_end, float* row_scratch, float* losses, int32_t B, int32_t S,
+                int32_t C, const bqa_loss_config* lc, int32_t with_grad, void* stream) {
+  LossConfig k;
+  if (to_loss_config(lc, &k)) return 1;
+  if (B < 1 || S < 1 || C < 1 || C > 32) {
+    set_error("bqa_qa_loss: bad shape B=%d S=%d C=%d", B, S, C);
+    return 1;
+  }
+  if (with_grad && (d_start == nullptr || d_end == nullptr || d_cls == nullptr || d_reg_start == nullptr ||
+                    d_reg_end == nullptr)) {
+    set_error("bqa_qa_loss: gradient buffers missing");
+    return 1;
+  }
+  return launch_loss_fwd_bwd(start, end, cls, reg_start, reg_end, y_start, y_end, y_cls, y_reg_start, y_reg_end,
+                             d_start, d_end, d_cls, d_reg_start, d_reg_end, row_scratch, losses, B, S, C, k,
+                             with_grad, reinterpret_cast<cudaStream_t>(stream));
+}
+
 int bqa_loss(bqa_handle* h, const float* start, const float* end, const float* cls, const float* reg_start,
              const float* reg_end, const int64_t* y_start, const int64_t* y_end, const int64_t* y_cls,
              const float* y_reg_start, const float* y_reg_end, const bqa_loss_config* lc, int32_t with_grad,
@@ -518,18 +641,9 @@ int bqa_loss(bqa_handle* h, const float* start, const float* end, const float* c
     set_error("bqa_loss: gradients requested but the last forward was not a training forward");
     return 1;
   }
-  if (lc->cls_loss != BQA_CLS_SMOOTH && lc->cls_loss != BQA_CLS_CE) {
-    set_error("bqa_loss: unsupported class loss %d (focal loss is not implemented)", lc->cls_loss);
-    return 1;
-  }
   Workspace& w = h->plan.ws;
   LossConfig k;
-  k.w_start = lc->w_start; k.w_end = lc->w_end;
-  k.w_start_reg = lc->w_start_reg; k.w_end_reg = lc->w_end_reg; k.w_cls = lc->w_cls;
-  k.cls_kind = lc->cls_loss == BQA_CLS_CE ? CLS_LOSS_CE : CLS_LOSS_SMOOTH;
-  k.smooth_alpha = lc->smooth_alpha;
-  k.cls_weight = lc->cls_weight;
-  k.grad_scale = lc->loss_scale;
+  if (to_loss_config(lc, &k)) return 1;
   h->launches += 2;
   return launch_loss_fwd_bwd(start, end, cls, reg_start, reg_end, y_start, y_end, y_cls, y_reg_start, y_reg_end,
                              w.d_start, w.d_end, w.d_cls, w.d_reg_s, w.d_reg_e, w.loss_rows, losses, h->plan.B,
@@ -622,7 +736,9 @@ int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* s
         return 1;
       if (launch_gemm(h, lp.w_ao, nodrop, st)) return 1;
       if (launch_gemm(h, lp.d_ao, nodrop, st)) return 1;  // dctx = dgm . Wo
+      h->time_begin(4, attn_flops(h, B, S, true), st);
       if (attn_backward(lp.attn, mask, h->key(site_attn(l), c.attn_dropout), st)) return 1;
+      h->time_end(st);
       if (launch_colsum(w.dqkv, 3 * H, h->G(lo + Y.qkv_b), T, 3 * H, h->num_sms, st)) return 1;
       if (launch_gemm(h, lp.w_qkv, nodrop, st)) return 1;
       if (launch_gemm(h, lp.d_qkv, nodrop, st)) return 1;  // dx = dqkv . Wqkv + dres
@@ -633,7 +749,8 @@ int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* s
       if (launch_ln_bwd(dy_in, w.z0, h->P(Y.emb_ln_g), w.dres, nullptr, h->G(Y.emb_ln_g), h->G(Y.emb_ln_b), nullptr,
                         T, H, c.ln_eps, h->key(site_embed(), c.hidden_dropout), nodrop, h->num_sms, st))
         return 1;
-      if (launch_embed_bwd(w.dres, w.ids, w.tt, h->G(Y.word_emb), h->G(Y.pos_emb), h->G(Y.type_emb), T, S, H, st))
+      if (launch_embed_bwd(w.dres, w.ids, w.tt, h->G(Y.word_emb), h->G(Y.pos_emb), h->G(Y.type_emb), T, S, H,
+                           /*pad_token_id (BertConfig default)=*/0, st))
         return 1;
       h->launches += 2;
     }

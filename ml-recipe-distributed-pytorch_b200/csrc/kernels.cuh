@@ -30,7 +30,7 @@ int launch_ln_bwd(const bf16* dy, const bf16* z, const float* gamma, bf16* dz, b
                   int num_sms, cudaStream_t st);
 int launch_colsum(const bf16* X, int ld, float* out, int T, int N, int num_sms, cudaStream_t st);
 int launch_embed_bwd(const bf16* dz0, const int64_t* ids, const int64_t* token_type, float* dword, float* dpos,
-                     float* dtype, int T, int S, int H, cudaStream_t st);
+                     float* dtype, int T, int S, int H, int pad_id, cudaStream_t st);
 
 // ---- heads_loss.cu ----------------------------------------------------------------------
 struct HeadParams {  // fp32 master weights of the pooler and the four heads (+ their gradients)

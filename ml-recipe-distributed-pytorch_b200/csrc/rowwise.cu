@@ -300,11 +300,13 @@ colsum_kernel(const bf16* __restrict__ X, int ld, float* __restrict__ out, int T
   if (gc < N) atomicAdd(out + gc, s);
 }
 
-// Embedding gradient: dword[ids[t]] += dz0[t], dpos[t % S] += dz0[t], dtype[tt[t]] += dz0[t]
+// Embedding gradient: dword[ids[t]] += dz0[t], dpos[t % S] += dz0[t], dtype[tt[t]] += dz0[t].
+// The word table is nn.Embedding(..., padding_idx=pad_token_id) in BertEmbeddings
+// (modeling_bert.py:59): the padding row receives no gradient.
 __global__ void __launch_bounds__(ROW_WARPS * 32)
 embed_bwd_kernel(const bf16* __restrict__ dz0, const int64_t* __restrict__ ids, const int64_t* __restrict__ token_type,
                  float* __restrict__ dword, float* __restrict__ dpos, float* __restrict__ dtype, int T, int S,
-                 int H) {
+                 int H, int pad_id) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * ROW_WARPS + (threadIdx.x >> 5);
   if (row >= T) return;
@@ -321,7 +323,7 @@ embed_bwd_kernel(const bf16* __restrict__ dz0, const int64_t* __restrict__ ids, 
     if (c < H) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        atomicAdd(w + c + i, d.v[j][i]);
+        if (id != pad_id) atomicAdd(w + c + i, d.v[j][i]);
         atomicAdd(p + c + i, d.v[j][i]);
         atomicAdd(t + c + i, d.v[j][i]);
       }
@@ -384,8 +386,9 @@ int launch_colsum(const bf16* X, int ld, float* out, int T, int N, int num_sms, 
 }
 
 int launch_embed_bwd(const bf16* dz0, const int64_t* ids, const int64_t* token_type, float* dword, float* dpos,
-                     float* dtype, int T, int S, int H, cudaStream_t st) {
-  embed_bwd_kernel<<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(dz0, ids, token_type, dword, dpos, dtype, T, S, H);
+                     float* dtype, int T, int S, int H, int pad_id, cudaStream_t st) {
+  embed_bwd_kernel<<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(dz0, ids, token_type, dword, dpos, dtype, T, S, H,
+                                                             pad_id);
   return check_launch("embed_bwd");
 }
 

@@ -191,6 +191,16 @@ class Engine:
     def phase_grad_begin(self, phase):
         return int(L.lib.bqa_phase_grad_begin(self.handle, phase))
 
+    def profile_begin(self):
+        L.check(L.lib.bqa_profile_begin(self.handle), "bqa_profile_begin")
+
+    def profile_end(self):
+        """-> {kind: (ms, flops, launches)} for the tensor-core kernels launched since profile_begin."""
+        ms, fl, n = (ctypes.c_double * 5)(), (ctypes.c_double * 5)(), (L.c_i64 * 5)()
+        L.check(L.lib.bqa_profile_end(self.handle, ms, fl, n), "bqa_profile_end")
+        names = ("gemm_fwd", "gemm_dgrad", "gemm_wgrad", "attn_fwd", "attn_bwd")
+        return {k: (ms[i], fl[i], int(n[i])) for i, k in enumerate(names)}
+
     def launch_count(self):
         return int(L.lib.bqa_launch_count(self.handle))
 

@@ -1,0 +1,137 @@
+"""Optimizer of the recipe: HF AdamW(correct_bias=False) as constructed by the reference in
+modules/init.py:125-138, fused with the global-norm clip of trainer.py:221-225 and
+`optimizer.zero_grad()` (trainer.py:287) into two kernel passes over the model's flat buffers
+(csrc/optimizer.cu).  The reference file of this name holds AdaMod (optim.py:42-100), which no
+BASELINE config uses and which has no kernel here.
+
+The object is a real `torch.optim.Optimizer`: `param_groups[i]['lr']` is what LambdaLR rewrites
+and what `Trainer._get_lr` reads (trainer.py:194-195), and `state_dict()` / `load_state_dict()`
+produce / accept the per-parameter `{step, exp_avg, exp_avg_sq}` layout of the reference's
+checkpoints (trainer.py:366,396); the moment tensors are views into two flat buffers.
+"""
+import ctypes
+
+import torch
+
+from .... import _lib as L
+
+CHUNK_ELEMS = 65536
+
+
+class AdaMod(torch.optim.Optimizer):
+    def __init__(self, *a, **k):
+        raise NotImplementedError("optimizer=adamod (reference optim.py:42-100) has no kernel; use optimizer=adam")
+
+
+class FusedAdamW(torch.optim.Optimizer):
+    def __init__(self, params, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.0, correct_bias=False):
+        if correct_bias:
+            raise NotImplementedError("the reference always passes correct_bias=False (init.py:137); "
+                                      "bias correction has no kernel")
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
+        if len(self.param_groups) > 8:
+            raise ValueError("at most 8 parameter groups")
+        self._model = model
+        self._max_grad_norm = 0.0
+        self._built_for = None
+        self._grads_clean = False
+
+    # ---- flat state ------------------------------------------------------------------------
+    def _build(self):
+        eng = self._model.engine
+        if self._built_for is eng:
+            return eng
+        dev = eng.device
+        old_m = getattr(self, "_m", None)
+        self._m = torch.zeros(eng.total, dtype=torch.float32, device=dev)
+        self._v = torch.zeros(eng.total, dtype=torch.float32, device=dev)
+        self._sumsq = torch.zeros(1, dtype=torch.float64, device=dev)
+        self._scratch = torch.empty(L.lib.bqa_sumsq_scratch_floats(), dtype=torch.float32, device=dev)
+        key_of = {id(p): k for k, p in self._model.named_parameters()}
+        chunks = []
+        self._keys = []
+        for gi, group in enumerate(self.param_groups):
+            for p in group['params']:
+                key = key_of.get(id(p))
+                if key is None:
+                    raise ValueError("FusedAdamW only optimises parameters of the bound BertForQuestionAnswering")
+                off, shape = eng.layout[key]
+                n = p.numel()
+                self._keys.append((p, key))
+                for b in range(0, n, CHUNK_ELEMS):
+                    e = min(b + CHUNK_ELEMS, n)
+                    e_pad = (e + 3) // 4 * 4  # tensors are 128-element aligned: padding belongs to nobody
+                    chunks.append((off + b, off + e_pad, float(group['weight_decay']), gi))
+        arr = (L.AdamWChunk * len(chunks))()
+        for i, (b, e, wd, gi) in enumerate(chunks):
+            arr[i].begin, arr[i].end, arr[i].weight_decay, arr[i].group = b, e, wd, gi
+        raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+        self._chunks = raw.to(dev)
+        self._n_chunks = len(chunks)
+        # expose the moments through the standard optimizer state (checkpoint compatibility)
+        for p, key in self._keys:
+            st = self.state[p]
+            prev_m, prev_v = st.get('exp_avg'), st.get('exp_avg_sq')
+            m_view, v_view = eng.view(self._m, key), eng.view(self._v, key)
+            if prev_m is not None and old_m is not None:
+                m_view.copy_(prev_m)
+                v_view.copy_(prev_v)
+            st.setdefault('step', 0)
+            st['exp_avg'], st['exp_avg_sq'] = m_view, v_view
+        self._built_for = eng
+        return eng
+
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        eng = self._build()
+        for p, key in self._keys:
+            st = self.state[p]
+            for name, flat in (('exp_avg', self._m), ('exp_avg_sq', self._v)):
+                view = eng.view(flat, key)
+                if name in st and st[name].data_ptr() != view.data_ptr():
+                    view.copy_(st[name])
+                st[name] = view
+            st.setdefault('step', 0)
+
+    # ---- step --------------------------------------------------------------------------------
+    def prepare_clip(self, max_grad_norm):
+        """Trainer._clip_grad_norm: launches the sum-of-squares pass; the coefficient is applied by
+        the following step() on the device (no host synchronisation)."""
+        eng = self._build()
+        self._max_grad_norm = float(max_grad_norm) if max_grad_norm else 0.0
+        if self._max_grad_norm > 0.0:
+            self._sumsq.zero_()
+            L.check(L.lib.bqa_grad_sumsq(eng.grads.data_ptr(), eng.total, self._sumsq.data_ptr(),
+                                         self._scratch.data_ptr(), L.current_stream_ptr()), "bqa_grad_sumsq")
+
+    def grad_norm(self):
+        """Total gradient norm seen by the last prepare_clip (synchronises)."""
+        return float(self._sumsq.sqrt().item())
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        if closure is not None:
+            raise NotImplementedError("closures are not supported")
+        eng = self._build()
+        g0 = self.param_groups[0]
+        lrs = (ctypes.c_float * len(self.param_groups))(*[float(g['lr']) for g in self.param_groups])
+        b1, b2 = g0['betas']
+        L.check(L.lib.bqa_clip_adamw(eng.params.data_ptr(), eng.grads.data_ptr(), self._m.data_ptr(),
+                                     self._v.data_ptr(), eng.shadow.data_ptr(), self._chunks.data_ptr(),
+                                     self._n_chunks, self._sumsq.data_ptr(), self._max_grad_norm, lrs,
+                                     len(self.param_groups), b1, b2, g0['eps'], 1, L.current_stream_ptr()),
+                "bqa_clip_adamw")
+        for p, _ in self._keys:
+            self.state[p]['step'] += 1
+        self._max_grad_norm = 0.0
+        self._grads_clean = True
+        self._model.mark_weights_synced()
+
+    def zero_grad(self, set_to_none=False):
+        """Gradients live in the engine's flat buffer; step() already cleared it."""
+        eng = self._build()
+        if not (self._grads_clean and not self._model.grads_dirty):
+            eng.grads.zero_()
+        self._grads_clean = True
+        self._model.grads_dirty = False
+        self._model.restore_grad_views()

@@ -1,0 +1,70 @@
+"""Data-parallel gradient exchange: bucketed all-reduce (mean) of the flat gradient buffer,
+issued bucket by bucket on a side stream while the backward of earlier layers is still running.
+
+Replaces torch.nn.parallel.DistributedDataParallel as wrapped by the reference
+(modules/model/trainer/trainer.py:136-142): same arithmetic (average of the ranks' gradients,
+once per optimizer step), without the autograd-hook reducer, the per-iteration unused-parameter
+graph walk (`find_unused_parameters=True`) or the parameter/buffer broadcasts.  Buckets are
+contiguous slices of the flat buffer in the order the backward finalises them
+(heads -> layer L-1 .. 0 -> embeddings, `bqa_phase_grad_begin`).  The collective itself is
+NCCL's all-reduce over NVLink/NVSwitch through torch.distributed; device-agnostic so that the
+bucket logic is testable with gloo on CPU tensors.
+"""
+import torch
+import torch.distributed as dist
+
+
+def bucket_plan(phase_begins, total, min_bucket_elems):
+    """phase_begins[k] = first flat element that is final after backward phase k (decreasing, last
+    one 0).  Returns [(last_phase, begin, end)] covering [0, total) from the top down, merging
+    consecutive phases until a bucket holds at least `min_bucket_elems` elements."""
+    plan, end = [], total
+    for k, begin in enumerate(phase_begins):
+        last = k == len(phase_begins) - 1
+        if end - begin >= min_bucket_elems or last:
+            if end > begin:
+                plan.append((k, begin, end))
+            end = begin
+    assert not plan or plan[-1][1] == 0, "phases must cover the buffer down to element 0"
+    return plan
+
+
+class GradReducer:
+    def __init__(self, flat_grads, phase_begins, *, group=None, min_bucket_mb=25.0):
+        self.flat = flat_grads
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.plan = bucket_plan(phase_begins, flat_grads.numel(), int(min_bucket_mb * (1 << 20) / 4))
+        self.cuda = flat_grads.is_cuda
+        self.stream = torch.cuda.Stream(device=flat_grads.device) if self.cuda else None
+        self._works = []
+
+    def phases(self):
+        """[(first_phase, last_phase, bucket_index)] to run the backward bucket by bucket."""
+        out, first = [], 0
+        for i, (last, _, _) in enumerate(self.plan):
+            out.append((first, last, i))
+            first = last + 1
+        return out
+
+    def reduce_bucket(self, i):
+        """All-reduce (mean) bucket i; on CUDA it is enqueued on the side stream behind everything
+        issued so far on the current stream."""
+        if self.world == 1:
+            return
+        _, b, e = self.plan[i]
+        t = self.flat[b:e]
+        if self.cuda:
+            ready = torch.cuda.Event()
+            ready.record(torch.cuda.current_stream(self.flat.device))
+            with torch.cuda.stream(self.stream):
+                self.stream.wait_event(ready)
+                dist.all_reduce(t, op=dist.ReduceOp.AVG, group=self.group)
+        else:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+            t.div_(self.world)
+
+    def wait(self):
+        """Make the current stream wait for every bucket enqueued so far."""
+        if self.cuda and self.world > 1:
+            torch.cuda.current_stream(self.flat.device).wait_stream(self.stream)

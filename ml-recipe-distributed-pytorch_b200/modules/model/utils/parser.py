@@ -10,7 +10,7 @@ from pathlib import Path
 try:
     import configargparse
 except ImportError:  # this image has no configargparse: use the in-tree stand-in
-    from ... import configargparse_shim as configargparse
+    from .... import configargparse_shim as configargparse
 
 logger = logging.getLogger(__name__)
 

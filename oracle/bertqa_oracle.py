@@ -136,10 +136,14 @@ def _q(x, bf16):
     return x.to(torch.bfloat16).to(torch.float32) if bf16 else x
 
 
-def _drop(x, p, spec: Optional[DropSpec], site, flat_index_shape=None):
-    """x * keep / (1 - p) with the library's decision rule; element index = C-order position."""
+def _drop(x, p, spec, site, flat_index_shape=None):
+    """x * keep / (1 - p) with the library's decision rule; element index = C-order position.
+    spec == "torch" uses torch's own dropout stream instead (what the reference does; used only
+    when the oracle is TIMED as the CPU baseline, never for parity)."""
     if spec is None or p <= 0:
         return x
+    if isinstance(spec, str):
+        return F.dropout(x, p, training=True)
     keep = keep_mask(spec.stream_seed(), site, p, x.numel(), device=x.device).view(x.shape)
     return torch.where(keep, x * (1.0 / (1.0 - p)), torch.zeros_like(x))
 
@@ -162,7 +166,9 @@ def forward(P: Dict[str, torch.Tensor], cfg: OracleConfig, input_ids, attention_
         token_type_ids = torch.zeros_like(input_ids)
     pos = torch.arange(S, device=input_ids.device)
     e = "transformer.embeddings."
-    z0 = (P[e + "word_embeddings.weight"][input_ids] + P[e + "token_type_embeddings.weight"][token_type_ids]) \
+    # nn.Embedding(vocab, H, padding_idx=pad_token_id=0) in BertEmbeddings: row 0 receives no gradient
+    z0 = (F.embedding(input_ids, P[e + "word_embeddings.weight"], padding_idx=0)
+          + P[e + "token_type_embeddings.weight"][token_type_ids]) \
         + P[e + "position_embeddings.weight"][pos][None]
     z0 = q(z0)
     x = _layer_norm(z0, P[e + "LayerNorm.weight"], P[e + "LayerNorm.bias"], cfg.ln_eps)

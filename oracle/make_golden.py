@@ -1,0 +1,169 @@
+"""Generates tests/golden/*.npz by running the REFERENCE's own classes (imported from
+/root/reference through oracle/reference_shims.py) on fixed seeds.  TEST INFRASTRUCTURE ONLY.
+
+Run here (the authoring container; /root/reference does not exist on the GPU box):
+    python -m oracle.make_golden
+The fixtures pin oracle/bertqa_oracle.py (tests/test_oracle_golden.py) and, through it, the
+CUDA path.  Shapes are small so that the files stay small, but legal for the kernels
+(hidden = 64 * heads).
+"""
+import os
+import sys
+import types
+from collections import defaultdict
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle.reference_shims import StubTokenizer, import_reference  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+SHAPE = dict(num_hidden_layers=2, hidden_size=64, num_attention_heads=1, intermediate_size=128, vocab_size=200,
+             max_position_embeddings=128, type_vocab_size=2)
+NAME = "bert-golden-tiny"
+
+
+def model_params(drop=0.0):
+    return types.SimpleNamespace(model=NAME, model_name="bert", hidden_dropout_prob=drop,
+                                 attention_probs_dropout_prob=drop, layer_norm_eps=1e-12)
+
+
+def trainer_params(**kw):
+    p = types.SimpleNamespace(loss="smooth", smooth_alpha=0.01, focal_alpha=1, focal_gamma=2, w_start=1, w_end=1,
+                              w_start_reg=1, w_end_reg=1, w_cls=1, lr=1e-3, weight_decay=1e-2, optimizer="adam",
+                              finetune=False, apex_level=None)
+    p.__dict__.update(kw)
+    return p
+
+
+def np_dict(d, prefix):
+    return {f"{prefix}/{k}": v.detach().cpu().numpy() for k, v in d.items()}
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    ref = import_reference(extra_shapes={NAME: SHAPE})
+    torch.manual_seed(1234)
+    np.random.seed(1234)
+
+    # ---- (1) forward / loss / gradients of the reference model on a padded batch ---------------
+    model = ref.model.BertForQuestionAnswering(model_params(0.0), num_labels=5)
+    # non-trivial LayerNorm / bias values so that every gradient path is exercised
+    g = torch.Generator().manual_seed(7)
+    with torch.no_grad():
+        for n, p in model.named_parameters():
+            if n.endswith("LayerNorm.weight"):
+                p.copy_(1.0 + 0.1 * torch.randn(p.shape, generator=g))
+            elif n.endswith(".bias") and n.startswith("transformer."):
+                p.copy_(0.05 * torch.randn(p.shape, generator=g))
+    model.train()  # dropout probabilities are 0: train == eval arithmetic
+    tok = StubTokenizer(SHAPE["vocab_size"])
+    tok.pad_token_id, tok.unk_token_id, tok.cls_token_id, tok.sep_token_id = 0, 1, 2, 3
+    rng = np.random.RandomState(5)
+    items = []
+    for i, n_doc in enumerate((70, 41, 55)):
+        q = rng.randint(4, 200, 12).tolist()
+        d = rng.randint(4, 200, n_doc).tolist()
+        ids = [tok.cls_token_id] + q + [tok.sep_token_id] + d + [tok.sep_token_id]
+        items.append(ref.dataset.DatasetItem(example_id=str(i), input_ids=ids, start_id=[20, -1, 30][i],
+                                             end_id=[25, -1, 33][i], label_id=[2, 4, 0][i],
+                                             start_position=[0.25, 0.0, 0.6][i], end_position=[0.3, 0.0, 0.7][i]))
+    inputs, labels = ref.dataset.collate_fun(items, tok)
+    loss = ref.init.init_loss(trainer_params(), defaultdict(lambda: None))
+    out = model(**inputs)
+    meters = {}
+    total = loss(out, labels, avg_meters=meters)
+    total.backward()
+    fx = {}
+    fx.update(np_dict(model.state_dict(), "param"))
+    fx.update(np_dict(inputs, "input"))
+    fx.update(np_dict(labels, "label"))
+    fx.update(np_dict(out, "out"))
+    fx.update({f"loss/{k}": np.float32(v) for k, v in meters.items()})
+    fx.update({f"grad/{n}": p.grad.detach().numpy() for n, p in model.named_parameters()})
+    # 'ce' class loss with label weights on the same logits
+    w = torch.tensor([0.1, 0.3, 0.2, 0.25, 0.15])
+    loss_ce = ref.init.init_loss(trainer_params(loss="ce"), {"label_weights": w})
+    meters_ce = {}
+    with torch.no_grad():
+        loss_ce({k: v.detach() for k, v in out.items()}, labels, avg_meters=meters_ce)
+    fx["ce/label_weights"] = w.numpy()
+    fx.update({f"ce/{k}": np.float32(v) for k, v in meters_ce.items()})
+    np.savez_compressed(os.path.join(OUT, "ref_forward_backward.npz"), **fx)
+
+    # ---- (2) reference Trainer: 3 optimizer steps on DummyDataset (clip + HF-AdamW shim + schedule)
+    torch.manual_seed(99)
+    np.random.seed(99)
+    model2 = ref.model.BertForQuestionAnswering(model_params(0.0), num_labels=5)
+    tp = trainer_params()
+    opt = ref.init.init_optimizer(tp, model2)
+    ds = ref.dataset.DummyDataset(tok, max_seq_len=48, max_question_len=8, dataset_len=8)
+    init_state = {k: v.detach().clone() for k, v in model2.state_dict().items()}
+    batches = []
+
+    def recording_collate(items_):
+        b = ref.dataset.collate_fun(items_, tok)
+        batches.append(b)
+        return b
+
+    tr = ref.trainer.Trainer(model=model2, loss=ref.init.init_loss(tp, defaultdict(lambda: None)),
+                             collate_fun=recording_collate, optimizer=opt, train_dataset=ds, test_dataset=None,
+                             device=torch.device("cpu"), n_epochs=2, train_batch_size=4, batch_split=2, n_jobs=0,
+                             warmup_coef=0.5, max_grad_norm=0.5)
+    lrs = []
+    orig_step = opt.step
+
+    def step_and_record(*a, **k):
+        lrs.append(opt.param_groups[0]["lr"])
+        return orig_step(*a, **k)
+
+    opt.step = step_and_record
+    tr.train()
+    fx2 = {}
+    fx2.update(np_dict(init_state, "init"))
+    fx2.update(np_dict(model2.state_dict(), "final"))
+    for i, (inp, lab) in enumerate(batches):
+        fx2.update(np_dict(inp, f"batch{i}/input"))
+        fx2.update(np_dict(lab, f"batch{i}/label"))
+    fx2["n_batches"] = np.int64(len(batches))
+    fx2["lrs"] = np.asarray(lrs, dtype=np.float64)
+    fx2["hparams"] = np.asarray([tp.lr, tp.weight_decay, 0.5, 2, 0.5], dtype=np.float64)  # lr, wd, clip, split, warmup
+    fx2["global_step"] = np.int64(tr.global_step)
+    np.savez_compressed(os.path.join(OUT, "ref_trainer_steps.npz"), **fx2)
+
+    # ---- (3) decode: the reference's predictor arithmetic (predictor.py:114-120) on crafted logits
+    torch.manual_seed(3)
+    B, S = 6, 37
+    start = torch.randn(B, S)
+    end = torch.randn(B, S)
+    start[1, 5] = start[1, 30] = start[1].max() + 1.0  # exact tie: first index must win
+    end[2, 0] = end[2].max() + 2.0
+    cls = torch.randn(B, 5)
+    s_logits, s_ids = torch.max(start, dim=-1)
+    e_logits, e_ids = torch.max(end, dim=-1)
+    c_prob, c_ids = torch.max(torch.softmax(cls, dim=-1), dim=-1)
+    scores = s_logits + e_logits - (start[:, 0] + end[:, 0])
+    np.savez_compressed(os.path.join(OUT, "ref_decode.npz"), start=start.numpy(), end=end.numpy(), cls=cls.numpy(),
+                        start_ids=s_ids.numpy(), end_ids=e_ids.numpy(), cls_ids=c_ids.numpy(), scores=scores.numpy(),
+                        cls_probas=c_prob.numpy())
+
+    # ---- (4) LR schedule of the installed transformers (trainer.py:116-126)
+    from transformers import get_linear_schedule_with_warmup
+    lin = torch.nn.Linear(1, 1)
+    o = torch.optim.SGD(lin.parameters(), lr=1.0)
+    sch = get_linear_schedule_with_warmup(o, num_warmup_steps=6, num_training_steps=20)
+    vals = []
+    for _ in range(24):
+        vals.append(o.param_groups[0]["lr"])
+        o.step()
+        sch.step()
+    np.savez_compressed(os.path.join(OUT, "ref_schedule.npz"), lr=np.asarray(vals), warmup=np.int64(6),
+                        total=np.int64(20))
+    for f in sorted(os.listdir(OUT)):
+        print(f, os.path.getsize(os.path.join(OUT, f)))
+
+
+if __name__ == "__main__":
+    main()

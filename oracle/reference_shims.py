@@ -71,8 +71,7 @@ class _OfflineBert:
     @classmethod
     def from_pretrained(cls, name, **kw):
         from transformers import BertConfig, BertModel
-        kw = dict(kw)
-        kw.pop("num_labels", None)
+        kw = dict(kw)  # num_labels stays: model.py:35 reads config.num_labels for the class head
         shape = dict(cls.shapes.get(name, {}))
         cfg = BertConfig(attn_implementation="eager", **shape, **kw)
         return BertModel(cfg)

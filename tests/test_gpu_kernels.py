@@ -1,0 +1,267 @@
+"""Parity of the individual sm_100a kernels (through the C ABI) against torch fp32 on the same
+bf16 inputs.  Tolerances: outputs are bf16 (relative rounding 2^-9 = 2e-3 per element), fp32
+accumulation; the bounds below are a few times the expected bf16 rounding error."""
+import ctypes
+
+import pytest
+import torch
+
+from oracle.dropout_hash import keep_mask
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def rel(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / (b.norm() + 1e-20)).item()
+
+
+def rnd(*s, scale=0.5):
+    return (torch.randn(*s, device=DEV) * scale).to(torch.bfloat16)
+
+
+GEMM_CASES = [
+    # M, N, K, mode, extras
+    (128, 256, 64, "tn", {}),
+    (1000, 768, 768, "tn", {"bias": True, "residual": True}),            # ragged M
+    (256, 320, 128, "tn", {"bias": True}),                                 # partial N tile
+    (1024, 768, 768, "tn", {"bias": True, "residual": True, "dropout": 0.1}),
+    (1024, 3072, 768, "tn_gelu", {"bias": True}),
+    (1024, 768, 3072, "nn", {"residual": True}),
+    (1024, 3072, 768, "nn_gelu_bwd", {}),
+    (768, 768, 1000, "nt", {"k_splits": 3}),                               # ragged K, split-K reduce-add
+    (3072, 768, 12288, "nt", {"k_splits": 8}),                             # wgrad at the BASELINE size
+    (12288, 2304, 768, "tn", {"bias": True}),                              # fused QKV at the BASELINE size
+]
+
+
+@pytest.mark.parametrize("M,N,K,mode,ex", GEMM_CASES)
+def test_gemm_variants(pkg, M, N, K, mode, ex):
+    L = pkg._lib
+    torch.manual_seed(0)
+    bias = torch.randn(N, device=DEV) * 0.5 if ex.get("bias") else None
+    residual = rnd(M, N) if ex.get("residual") else None
+    p = ex.get("dropout", 0.0)
+    kw, C2, aux = {}, None, None
+    if mode.startswith("tn"):
+        A, B = rnd(M, K), rnd(N, K)
+        ref = A.float() @ B.float().t()
+    elif mode.startswith("nn"):
+        A, B = rnd(M, K), rnd(K, N)
+        ref = A.float() @ B.float()
+        kw = {"b_mn_major": True}
+    else:
+        A, B = rnd(K, M), rnd(K, N)
+        ref = A.float().t() @ B.float()
+        kw = {"a_mn_major": True, "b_mn_major": True}
+    if bias is not None:
+        ref = ref + bias
+    if mode == "tn_gelu":
+        C, C2, epi = torch.empty(M, N, device=DEV, dtype=torch.bfloat16), torch.empty(M, N, device=DEV, dtype=torch.bfloat16), L.EPI_GELU_FWD
+    elif mode == "nn_gelu_bwd":
+        aux = rnd(M, N, scale=1.0)
+        u = aux.float().requires_grad_(True)
+        torch.nn.functional.gelu(u).sum().backward()
+        ref = ref * u.grad
+        C, epi = torch.empty(M, N, device=DEV, dtype=torch.bfloat16), L.EPI_GELU_BWD
+    elif mode == "nt":
+        C = torch.randn(M, N, device=DEV)
+        ref = ref + C
+        epi = L.EPI_F32_ADD
+    else:
+        C, epi = torch.empty(M, N, device=DEV, dtype=torch.bfloat16), L.EPI_LINEAR
+        if p > 0:
+            keep = keep_mask(1234, 7, p, M * N, device=DEV).view(M, N)
+            ref = torch.where(keep, ref / (1 - p), torch.zeros_like(ref))
+        if residual is not None:
+            ref = ref + residual.float()
+    L.gemm_bf16(A, B, C, epilogue=epi, C2=C2, bias=bias, residual=residual, aux=aux, k_splits=ex.get("k_splits", 1),
+                dropout_p=p, drop_seed=1234, drop_site=7, **kw)
+    torch.cuda.synchronize()
+    scale = ref.abs().max().item()
+    tol = 1e-5 * scale + 1e-3 if epi == L.EPI_F32_ADD else 8e-3 * scale  # bf16 output: 2^-8 of the largest value
+    assert (C.float() - ref).abs().max().item() <= tol
+    if C2 is not None:
+        assert (C2.float() - torch.nn.functional.gelu(ref)).abs().max().item() <= tol
+
+
+def test_gemm_linearity_at_full_size(pkg):
+    """Size-independent property at the BASELINE FFN shape: C(A1 + A2) == C(A1) + C(A2) up to rounding."""
+    L = pkg._lib
+    torch.manual_seed(1)
+    M, N, K = 12288, 3072, 768
+    A1, A2, B = rnd(M, K), rnd(M, K), rnd(N, K)
+    A12 = (A1.float() + A2.float()).to(torch.bfloat16)
+    outs = []
+    for A in (A1, A2, A12):
+        C = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+        L.gemm_bf16(A, B, C)
+        outs.append(C.float())
+    assert rel(outs[2], outs[0] + outs[1]) < 6e-3
+
+
+ATTN_CASES = [(2, 128, 2, 0.0, False), (2, 384, 12, 0.0, False), (2, 512, 2, 0.0, False), (3, 200, 2, 0.0, True),
+              (2, 384, 4, 0.1, False), (2, 50, 1, 0.0, True), (1, 1, 1, 0.0, False)]
+
+
+@pytest.mark.parametrize("B,S,A,p,use_mask", ATTN_CASES)
+def test_attention_forward_backward(pkg, B, S, A, p, use_mask):
+    L = pkg._lib
+    torch.manual_seed(1)
+    H = A * 64
+    qkv = torch.randn(B, S, 3 * H, device=DEV).to(torch.bfloat16)
+    mask = None
+    if use_mask:
+        lens = torch.randint(max(1, S // 2), S + 1, (B,), device=DEV)
+        mask = torch.arange(S, device=DEV)[None, :] < lens[:, None]
+    m8 = mask.to(torch.uint8).contiguous() if mask is not None else None
+    ctx = torch.zeros(B, S, H, device=DEV, dtype=torch.bfloat16)
+    lse2 = torch.zeros(B, A, S, device=DEV)
+    st = L.current_stream_ptr()
+    L.check(L.lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), L.ptr(m8), B, S, A, p, 77, 5,
+                                        st), "attention forward")
+    x = qkv.float().requires_grad_(True)
+    q, k, v = [t.view(B, S, A, 64).transpose(1, 2) for t in x.split(H, dim=-1)]
+    sc = (q @ k.transpose(-1, -2)) / 8.0
+    if mask is not None:
+        sc = sc.masked_fill(~mask[:, None, None, :], float("-inf"))
+    pr = torch.softmax(sc, -1)
+    if p > 0:
+        keep = keep_mask(77, 5, p, pr.numel(), device=DEV).view(pr.shape)
+        pr = torch.where(keep, pr / (1 - p), torch.zeros_like(pr))
+    o = (pr @ v).transpose(1, 2).reshape(B, S, H)
+    assert rel(ctx, o) < 8e-3
+    assert (lse2 - torch.logsumexp(sc, -1) * 1.4426950408889634).abs().max().item() < 1e-3
+    dctx = torch.randn(B, S, H, device=DEV).to(torch.bfloat16)
+    o.backward(dctx.float())
+    dqkv = torch.zeros(B, S, 3 * H, device=DEV, dtype=torch.bfloat16)
+    dsum = torch.zeros(B, A, S, device=DEV)
+    L.check(L.lib.bqa_attention_backward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), dctx.data_ptr(),
+                                         dqkv.data_ptr(), dsum.data_ptr(), L.ptr(m8), B, S, A, p, 77, 5, st),
+            "attention backward")
+    torch.cuda.synchronize()
+    gscale = x.grad.abs().max().item()
+    for i in range(3):
+        got, want = dqkv[..., i * H:(i + 1) * H].float(), x.grad[..., i * H:(i + 1) * H]
+        # norm-wise 1e-2, with a floor for blocks whose exact gradient is zero (e.g. dQ, dK when S == 1)
+        assert (got - want).norm().item() <= 1e-2 * want.norm().item() + 1e-5 * max(1.0, gscale) * want.numel() ** 0.5
+
+
+def test_attention_rows_sum_to_one_at_full_size(pkg):
+    """V = ones => every context row must be exactly the softmax mass (1.0), any B / S / mask."""
+    L = pkg._lib
+    B, S, A = 32, 384, 12
+    H = A * 64
+    torch.manual_seed(2)
+    qkv = torch.randn(B, S, 3 * H, device=DEV).to(torch.bfloat16)
+    qkv[..., 2 * H:] = 1.0
+    ctx = torch.zeros(B, S, H, device=DEV, dtype=torch.bfloat16)
+    lse2 = torch.zeros(B, A, S, device=DEV)
+    L.check(L.lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), None, B, S, A, 0.0, 0, 0,
+                                        L.current_stream_ptr()), "attention forward")
+    torch.cuda.synchronize()
+    assert (ctx.float() - 1.0).abs().max().item() < 1e-2
+
+
+@pytest.mark.parametrize("T,H", [(1000, 768), (515, 1024), (64, 128), (7, 64)])
+def test_layernorm_and_colsum(pkg, T, H):
+    L = pkg._lib
+    torch.manual_seed(2)
+    z, dy = torch.randn(T, H, device=DEV).to(torch.bfloat16), torch.randn(T, H, device=DEV).to(torch.bfloat16)
+    g, b = torch.randn(H, device=DEV), torch.randn(H, device=DEV)
+    y = torch.empty_like(z)
+    st = L.current_stream_ptr()
+    L.check(L.lib.bqa_layernorm_forward(z.data_ptr(), g.data_ptr(), b.data_ptr(), y.data_ptr(), T, H, 1e-12, st), "ln")
+    zf, gf, bf = z.float().requires_grad_(True), g.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    ref = torch.nn.functional.layer_norm(zf, (H,), gf, bf, 1e-12)
+    assert rel(y, ref) < 4e-3
+    ref.backward(dy.float())
+    dz, dzm = torch.empty_like(z), torch.empty_like(z)
+    dg, db, dbias = (torch.zeros(H, device=DEV) for _ in range(3))
+    L.check(L.lib.bqa_layernorm_backward(dy.data_ptr(), z.data_ptr(), g.data_ptr(), dz.data_ptr(), dzm.data_ptr(),
+                                         dg.data_ptr(), db.data_ptr(), dbias.data_ptr(), T, H, 1e-12, 0.0, 0, 0.1, 9,
+                                         4321, st), "ln bwd")
+    torch.cuda.synchronize()
+    assert rel(dz, zf.grad) < 4e-3 and rel(dg, gf.grad) < 1e-4 and rel(db, bf.grad) < 1e-4
+    keep = keep_mask(4321, 9, 0.1, T * H, device=DEV).view(T, H)
+    want = torch.where(keep, dz.float() / 0.9, torch.zeros_like(dz.float()))
+    assert rel(dzm, want) < 4e-3
+    assert rel(dbias, dzm.float().sum(0)) < 1e-4
+    X = torch.randn(T, 3 * H, device=DEV).to(torch.bfloat16)
+    cs = torch.zeros(3 * H, device=DEV)
+    L.check(L.lib.bqa_colsum_bf16(X.data_ptr(), 3 * H, cs.data_ptr(), T, 3 * H, st), "colsum")
+    torch.cuda.synchronize()
+    assert rel(cs, X.float().sum(0)) < 1e-5
+
+
+def test_decode_bit_exact_against_reference_golden(pkg):
+    from conftest import load_npz
+    fx = load_npz("ref_decode.npz")
+    L = pkg._lib
+    s, e, c = (torch.from_numpy(fx[k]).to(DEV).contiguous() for k in ("start", "end", "cls"))
+    B, S = s.shape
+    idx = torch.zeros(3, B, dtype=torch.int64, device=DEV)
+    val = torch.zeros(4, B, device=DEV)
+    L.check(L.lib.bqa_decode(s.data_ptr(), e.data_ptr(), c.data_ptr(), idx[0].data_ptr(), idx[1].data_ptr(),
+                             idx[2].data_ptr(), val[0].data_ptr(), val[1].data_ptr(), val[2].data_ptr(),
+                             val[3].data_ptr(), B, S, 5, L.current_stream_ptr()), "decode")
+    torch.cuda.synchronize()
+    assert (idx[0].cpu().numpy() == fx["start_ids"]).all()   # includes a planted exact tie: first index wins
+    assert (idx[1].cpu().numpy() == fx["end_ids"]).all()
+    assert (idx[2].cpu().numpy() == fx["cls_ids"]).all()
+    assert (val[3].cpu().numpy() == fx["scores"]).all()
+    assert abs(val[2].cpu().numpy() - fx["cls_probas"]).max() < 1e-6
+
+
+def test_decode_full_size_argmax_property(pkg):
+    """At the inference batch of BASELINE config 5: kernel arg max == torch.max on the same logits."""
+    L = pkg._lib
+    B, S = 256, 512
+    torch.manual_seed(3)
+    s, e, c = torch.randn(B, S, device=DEV), torch.randn(B, S, device=DEV), torch.randn(B, 5, device=DEV)
+    s[:, 100] = s[:, 400] = 50.0
+    idx = torch.zeros(3, B, dtype=torch.int64, device=DEV)
+    val = torch.zeros(4, B, device=DEV)
+    L.check(L.lib.bqa_decode(s.data_ptr(), e.data_ptr(), c.data_ptr(), idx[0].data_ptr(), idx[1].data_ptr(),
+                             idx[2].data_ptr(), val[0].data_ptr(), val[1].data_ptr(), val[2].data_ptr(),
+                             val[3].data_ptr(), B, S, 5, L.current_stream_ptr()), "decode")
+    torch.cuda.synchronize()
+    assert (idx[0] == 100).all() and torch.equal(idx[1], e.max(-1)[1]) and torch.equal(idx[2], c.max(-1)[1])
+    assert torch.equal(val[3], s.max(-1)[0] + e.max(-1)[0] - (s[:, 0] + e[:, 0]))
+
+
+def test_optimizer_kernels_match_oracle(pkg):
+    from oracle import bertqa_oracle as O
+    L = pkg._lib
+    torch.manual_seed(4)
+    n = 3 * 65536 + 1000
+    p, g = torch.randn(n, device=DEV), torch.randn(n, device=DEV) * 3
+    m, v = torch.randn(n, device=DEV) * 0.1, torch.rand(n, device=DEV) * 0.1
+    P = {"w.weight": p[:200000].clone(), "w.bias": p[200000:].clone()}
+    G = {"w.weight": g[:200000].clone(), "w.bias": g[200000:].clone()}
+    state = {"w.weight": {"step": 0, "exp_avg": m[:200000].clone(), "exp_avg_sq": v[:200000].clone()},
+             "w.bias": {"step": 0, "exp_avg": m[200000:].clone(), "exp_avg_sq": v[200000:].clone()}}
+    total = O.clip_grad_norm_(G, 1.0)
+    O.hf_adamw_step(P, G, state, lr=1e-2, weight_decay=0.1)
+    chunks = (L.AdamWChunk * 5)()
+    spans = [(0, 65536, 0.1, 0), (65536, 131072, 0.1, 0), (131072, 200000, 0.1, 0), (200000, 262144, 0.0, 1),
+             (262144, n, 0.0, 1)]
+    for i, (b, e, wd, gi) in enumerate(spans):
+        chunks[i].begin, chunks[i].end, chunks[i].weight_decay, chunks[i].group = b, e, wd, gi
+    cd = torch.frombuffer(bytearray(bytes(chunks)), dtype=torch.uint8).to(DEV)
+    sumsq = torch.zeros(1, dtype=torch.float64, device=DEV)
+    scratch = torch.empty(L.lib.bqa_sumsq_scratch_floats(), device=DEV)
+    shadow = torch.zeros(n, dtype=torch.bfloat16, device=DEV)
+    st = L.current_stream_ptr()
+    L.check(L.lib.bqa_grad_sumsq(g.data_ptr(), n, sumsq.data_ptr(), scratch.data_ptr(), st), "sumsq")
+    lrs = (ctypes.c_float * 2)(1e-2, 1e-2)
+    L.check(L.lib.bqa_clip_adamw(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), shadow.data_ptr(),
+                                 cd.data_ptr(), 5, sumsq.data_ptr(), 1.0, lrs, 2, 0.9, 0.999, 1e-6, 1, st), "adamw")
+    torch.cuda.synchronize()
+    assert abs(sumsq.sqrt().item() - total.item()) < 1e-3 * total.item()
+    want = torch.cat([P["w.weight"], P["w.bias"]])
+    torch.testing.assert_close(p, want, rtol=2e-5, atol=2e-6)
+    torch.testing.assert_close(m, torch.cat([state["w.weight"]["exp_avg"], state["w.bias"]["exp_avg"]]), rtol=1e-5, atol=1e-7)
+    torch.testing.assert_close(shadow.float(), want.to(torch.bfloat16).float(), rtol=0, atol=0)
+    assert (g == 0).all()

@@ -1,0 +1,307 @@
+"""Parity of the whole step on the GPU: engine forward / loss / backward vs the oracle (which is
+pinned to the reference by tests/test_oracle_golden.py), on the reference-generated golden batch,
+on DummyDataset batches at BERT-base size, through the drop-in model class, the Trainer and the
+Predictor.
+
+Tolerances.  The CUDA path computes in bf16 with fp32 accumulation; compared with the oracle in
+its bf16-faithful mode (same rounding points) the remaining differences are accumulation order
+and bf16 rounding of back-propagated activations: outputs within 1e-2 relative (norm-wise),
+losses within 3e-3, the concatenated gradient within 2e-2, each tensor within 5e-2 of its norm
+plus a floor of 1e-3 of the largest tensor-gradient norm (gradients that are exactly zero in
+exact arithmetic — span bias, key biases — are pure rounding noise in both implementations).
+Against the fp32 reference fixture the bounds are 3x looser.  Decoded indices are bit-exact."""
+import importlib
+import types
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_npz
+from oracle import bertqa_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+TINY = dict(num_layers=2, hidden=128, heads=2, intermediate=512, vocab=1000, max_pos=512, type_vocab=2)
+GOLD = dict(num_layers=2, hidden=64, heads=1, intermediate=128, vocab=200, max_pos=128, type_vocab=2)
+BASE = dict(num_layers=12, hidden=768, heads=12, intermediate=3072, vocab=30522, max_pos=512, type_vocab=2)
+OUT_KEYS = ("start_class", "end_class", "cls", "start_reg", "end_reg")
+
+
+def rel(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / (b.norm() + 1e-20)).item()
+
+
+def make_engine(pkg, shape, p_drop, P):
+    E = pkg.engine
+    eng = E.Engine(E.make_config(shape, hidden_dropout=p_drop, attn_dropout=p_drop), DEV)
+    for k, v in eng.param_views().items():
+        v.copy_(P[k])
+    eng.sync_weights()
+    return eng
+
+
+def perturbed_params(cfgo, seed=1234):
+    P = O.init_params(cfgo, seed, device=DEV)
+    g = torch.Generator().manual_seed(5)
+    for k in P:
+        if k.endswith("LayerNorm.weight"):
+            P[k] = (1.0 + 0.1 * torch.randn(P[k].shape, generator=g)).to(DEV)
+        elif k.endswith(".bias") and k.startswith("transformer."):
+            P[k] = (0.02 * torch.randn(P[k].shape, generator=g)).to(DEV)
+    return P
+
+
+def check_grads(eng, grads, glob_tol=2e-2, tensor_tol=5e-2):
+    gv = eng.grad_views()
+    ref_flat = torch.cat([grads[k].flatten() for k in grads])
+    got_flat = torch.cat([gv[k].flatten() for k in grads])
+    assert rel(got_flat, ref_flat) < glob_tol
+    floor = 1e-3 * max(g.norm().item() for g in grads.values())
+    for k, g in grads.items():
+        err = (gv[k].float() - g).norm().item()
+        assert err <= tensor_tol * g.norm().item() + floor, f"{k}: err {err:.3e} vs norm {g.norm().item():.3e}"
+
+
+@pytest.mark.parametrize("shape,B,S,p_drop,use_mask", [(TINY, 4, 128, 0.0, False), (TINY, 4, 128, 0.1, False),
+                                                       (TINY, 3, 200, 0.1, True), (BASE, 4, 384, 0.0, False)])
+def test_step_matches_oracle(pkg, shape, B, S, p_drop, use_mask):
+    E = pkg.engine
+    cfgo = O.OracleConfig(hidden_dropout=p_drop, attn_dropout=p_drop, **shape)
+    P = perturbed_params(cfgo)
+    eng = make_engine(pkg, shape, p_drop, P)
+    inputs, labels = O.dummy_batch(B, S, vocab=shape["vocab"], device=DEV)
+    if use_mask:
+        lens = torch.randint(S // 2, S + 1, (B,), device=DEV)
+        m = torch.arange(S, device=DEV)[None, :] < lens[:, None]
+        inputs["input_ids"] = inputs["input_ids"] * m
+        inputs["attention_mask"] = m
+        labels["start_class"][0] = -1
+    else:
+        inputs["attention_mask"] = None
+    seed, step = 4242, 3
+    outs = eng.forward(inputs["input_ids"], inputs["token_type_ids"], inputs["attention_mask"], training=True,
+                       seed=seed, step=step)
+    losses = eng.loss(outs, labels, E.make_loss_config(), with_grad=True).clone()
+    eng.backward()
+    torch.cuda.synchronize()
+    drop = O.DropSpec(seed, step) if p_drop > 0 else None
+    total, parts, grads, oout = O.loss_and_grads(P, cfgo, inputs, labels, O.LossConfig(), drop=drop, bf16=True)
+    for k, t in zip(OUT_KEYS, outs):
+        assert rel(t, oout[k]) < (2.5e-2 if shape is BASE else 1e-2), k
+    ref_l = [parts[k].item() for k in ("start_class", "end_class", "start_reg", "end_reg", "cls")] + [total.item()]
+    for a, b in zip(losses.tolist(), ref_l):
+        assert abs(a - b) <= 3e-3 * max(1.0, abs(b))
+    check_grads(eng, grads)
+    # exact-arithmetic zeros: softmax is invariant to a key bias, CE gradients sum to zero over positions
+    gv = eng.grad_views()
+    gmax = max(g.norm().item() for g in grads.values())
+    assert gv["position_outputs.bias"].abs().max().item() < 1e-4 * max(1.0, gmax)
+
+
+def test_step_matches_reference_golden(pkg):
+    """Inputs, weights, outputs, losses and gradients produced by the reference's own classes (fp32)."""
+    E = pkg.engine
+    fx = load_npz("ref_forward_backward.npz")
+    grp = lambda p: {k[len(p) + 1:]: torch.from_numpy(np.asarray(v)).to(DEV) for k, v in fx.items()  # noqa: E731
+                     if k.startswith(p + "/")}
+    P, inp, lab, out_ref, grad_ref = (grp(p) for p in ("param", "input", "label", "out", "grad"))
+    eng = make_engine(pkg, GOLD, 0.0, P)
+    outs = eng.forward(inp["input_ids"], inp["token_type_ids"], inp["attention_mask"], training=True, seed=1, step=1)
+    losses = eng.loss(outs, lab, E.make_loss_config(), with_grad=True).clone()
+    eng.backward()
+    torch.cuda.synchronize()
+    valid = inp["attention_mask"]
+    for k, t in zip(OUT_KEYS, outs):
+        a, b = (t[valid], out_ref[k][valid]) if t.dim() == 2 and t.shape == valid.shape else (t, out_ref[k])
+        assert rel(a, b) < 3e-2, k
+    ref_l = [float(fx[f"loss/{k}"]) for k in ("start_class", "end_class", "start_reg", "end_reg", "cls", "loss")]
+    for a, b in zip(losses.tolist(), ref_l):
+        assert abs(a - b) <= 1e-2 * max(1.0, abs(b))
+    check_grads(eng, grad_ref, glob_tol=6e-2, tensor_tol=0.15)
+    # padding row of the word table: nn.Embedding(padding_idx=0) -> exactly zero gradient
+    assert eng.grad_views()["transformer.embeddings.word_embeddings.weight"][0].abs().max().item() == 0.0
+
+
+def test_ce_loss_with_label_weights_matches_reference_golden(pkg):
+    E = pkg.engine
+    L = pkg._lib
+    fx = load_npz("ref_forward_backward.npz")
+    M = importlib.import_module("bqa_b200.modules.model.model.loss")
+    out = {k[4:]: torch.from_numpy(v).to(DEV) for k, v in fx.items() if k.startswith("out/")}
+    lab = {k[6:]: torch.from_numpy(v).to(DEV) for k, v in fx.items() if k.startswith("label/")}
+    w = torch.from_numpy(fx["ce/label_weights"]).to(DEV)
+    lc = E.make_loss_config(loss="ce", cls_weight=w)
+    losses, _ = M._run_loss_kernel([out[k] for k in ("start_class", "end_class", "start_reg", "end_reg", "cls")], lab, lc,
+                                   False)
+    got = losses.tolist()
+    for i, k in enumerate(("start_class", "end_class", "start_reg", "end_reg", "cls", "loss")):
+        assert abs(got[i] - float(fx[f"ce/{k}"])) < 2e-5 * max(1.0, abs(float(fx[f"ce/{k}"]))), k
+
+
+def _model(pkg, shape, p_drop=0.0, seed=11):
+    M = importlib.import_module("bqa_b200.modules.model.model")
+    mp = types.SimpleNamespace(model="bert-base-uncased", model_shape=shape, hidden_dropout_prob=p_drop,
+                               attention_probs_dropout_prob=p_drop, layer_norm_eps=1e-12)
+    torch.manual_seed(seed)
+    return M.BertForQuestionAnswering(mp, 5).to(DEV)
+
+
+def _loss_obj(**kw):
+    I = importlib.import_module("bqa_b200.modules.init")
+    p = types.SimpleNamespace(loss="smooth", smooth_alpha=0.01, focal_alpha=1, focal_gamma=2, w_start=1, w_end=1,
+                              w_start_reg=1, w_end_reg=1, w_cls=1)
+    p.__dict__.update(kw)
+    return I.init_loss(p, {"label_weights": None})
+
+
+def test_dropin_autograd_path_equals_fused_path(pkg):
+    """model(**inputs) -> WeightedLoss -> (loss / split).backward() gives the same gradients as the
+    fused forward_loss_backward, and they land in p.grad of the reference-named parameters."""
+    model = _model(pkg, TINY)
+    loss = _loss_obj()
+    inputs, labels = O.dummy_batch(4, 128, vocab=1000, device=DEV)
+    model.train()
+    meters = {}
+    out = model(**inputs)
+    assert set(out.keys()) == {"start_class", "end_class", "start_reg", "end_reg", "cls"}
+    full = loss(out, labels, avg_meters=meters)
+    (full / 2).backward()
+    torch.cuda.synchronize()
+    g_auto = {k: p.grad.clone() for k, p in model.named_parameters()}
+    assert set(meters) == {"start_class", "end_class", "start_reg", "end_reg", "cls", "loss"}
+    assert abs(meters["loss"] - full.item()) < 1e-6
+    for p in model.parameters():
+        p.grad.zero_()
+    lc = loss.loss_config(loss_scale=0.5, device=torch.device(DEV))
+    _, losses = model.forward_loss_backward(inputs, labels, lc)
+    torch.cuda.synchronize()
+    assert abs(losses[5].item() - full.item()) < 1e-6
+    for k, p in model.named_parameters():
+        torch.testing.assert_close(p.grad, g_auto[k], rtol=2e-3, atol=1e-6, msg=lambda m, k=k: f"{k}: {m}")
+    # eval path: no grad, no dropout, deterministic
+    model.eval()
+    with torch.no_grad():
+        a = model(**inputs)
+        b = model(**inputs)
+    assert all(torch.equal(a[k], b[k]) for k in a)
+
+
+def test_training_trajectory_matches_oracle(pkg):
+    """4 optimizer steps through the package's Trainer (grad accumulation over 2 micro-batches, clip,
+    fused AdamW with the two decay groups, warm-up schedule) vs the oracle loop on the same batches."""
+    I = importlib.import_module("bqa_b200.modules.init")
+    T = importlib.import_module("bqa_b200.modules.model.trainer.trainer")
+    shape = TINY
+    model = _model(pkg, shape)
+    P = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    hp = types.SimpleNamespace(lr=1e-3, weight_decay=1e-2, optimizer="adam", finetune=False, apex_level=None)
+    opt = I.init_optimizer(hp, model)
+    tr = T.Trainer(model=model, loss=_loss_obj(), collate_fun=None, optimizer=opt, device=torch.device(DEV), n_epochs=1,
+                   train_batch_size=4, batch_split=2, n_jobs=0, warmup_coef=0.0, max_grad_norm=0.5)
+    steps, warmup = 4, 2
+    tr.scheduler = torch.optim.lr_scheduler.LambdaLR(opt, T.linear_warmup_lambda(warmup, steps))
+    tr.set_train()
+    opt.zero_grad()
+    cfgo = O.OracleConfig(hidden_dropout=0.0, attn_dropout=0.0, **shape)
+    state, norms = {}, []
+    for s in range(steps):
+        acc = None
+        for mb in range(2):
+            inputs, labels = O.dummy_batch(2, 128, vocab=1000, seed=100 + 2 * s + mb, device=DEV)
+            losses = tr.train_micro_batch(inputs, labels, last_of_step=(mb == 1))
+            total, _, grads, _ = O.loss_and_grads(P, cfgo, inputs, labels, O.LossConfig(), bf16=True, loss_scale=0.5)
+            assert abs(losses[5].item() - total.item()) < 3e-3 * max(1.0, total.item())
+            acc = grads if acc is None else {k: acc[k] + grads[k] for k in acc}
+        lr = 1e-3 * O.linear_schedule_lambda(s, warmup, steps)
+        assert abs(opt.param_groups[0]["lr"] - lr) < 1e-12
+        norms.append(O.clip_grad_norm_(acc, 0.5).item())
+        O.hf_adamw_step(P, acc, state, lr, 1e-2)
+        tr.optimizer_step()
+        assert abs(opt.grad_norm() - norms[-1]) < 2e-2 * norms[-1]
+    torch.cuda.synchronize()
+    sd = model.state_dict()
+    upd_ref = torch.cat([(P[k] - v0).flatten() for k, v0 in ((k, _model(pkg, shape).state_dict()[k]) for k in P)])
+    upd_got = torch.cat([(sd[k] - _model(pkg, shape).state_dict()[k]).flatten() for k in P])
+    assert rel(upd_got, upd_ref) < 0.1          # the UPDATE (not the weights) within 10 %
+    for k in P:
+        assert (sd[k] - P[k]).abs().max().item() < 2e-3, k
+    assert (model.engine.grads == 0).all()      # optimizer.zero_grad() semantics
+    assert all(opt.state[p]["step"] == steps for p in model.parameters())
+
+
+def test_checkpoint_roundtrip_and_state_dict_layout(pkg, tmp_path):
+    I = importlib.import_module("bqa_b200.modules.init")
+    T = importlib.import_module("bqa_b200.modules.model.trainer.trainer")
+    hp = types.SimpleNamespace(lr=1e-3, weight_decay=1e-2, optimizer="adam", finetune=False, apex_level=None)
+
+    def make():
+        model = _model(pkg, TINY)
+        opt = I.init_optimizer(hp, model)
+        tr = T.Trainer(model=model, loss=_loss_obj(), collate_fun=None, optimizer=opt, device=torch.device(DEV),
+                       n_epochs=1, train_batch_size=2, batch_split=1, n_jobs=0, warmup_coef=0.0, max_grad_norm=1.0)
+        tr.set_train()
+        opt.zero_grad()
+        return model, opt, tr
+
+    model, opt, tr = make()
+    inputs, labels = O.dummy_batch(2, 128, vocab=1000, device=DEV)
+    for _ in range(2):
+        tr.train_micro_batch(inputs, labels, last_of_step=True)
+        tr.optimizer_step()
+        tr.global_step += 1
+    path = tmp_path / "last.ch"
+    tr.save_state_dict(path)
+    ck = torch.load(path, map_location="cpu")
+    assert set(ck) == {"model", "optimizer", "scheduler", "global_step"} and ck["global_step"] == 2
+    assert list(ck["model"].keys()) == O.param_names(O.OracleConfig(**TINY))
+    st0 = ck["optimizer"]["state"][0]
+    assert set(st0) == {"step", "exp_avg", "exp_avg_sq"} and len(ck["optimizer"]["param_groups"]) == 2
+    model2, opt2, tr2 = make()
+    tr2.load_state_dict(path)
+    for (k, a), (_, b) in zip(model.state_dict().items(), model2.state_dict().items()):
+        assert torch.equal(a, b), k
+    # same next step from the restored state (moments restored into the flat buffers)
+    for t in (tr, tr2):
+        t.train_micro_batch(inputs, labels, last_of_step=True)
+        t.optimizer_step()
+    torch.cuda.synchronize()
+    for (k, a), (_, b) in zip(model.state_dict().items(), model2.state_dict().items()):
+        torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-7, msg=lambda m, k=k: f"{k}: {m}")
+
+
+def test_predictor_decodes_like_reference_arithmetic(pkg):
+    """Predictor over synthetic padded chunks: device decode == predictor.py:114-120 on the same logits,
+    and the per-document candidate rule is applied."""
+    Pm = importlib.import_module("bqa_b200.modules.model.inference.predictor")
+    V = importlib.import_module("bqa_b200.modules.validate")
+    I = importlib.import_module("bqa_b200.modules.init")
+    model = _model(pkg, dict(TINY, vocab=30522))
+    tok = I.DummyTokenizer()
+    ds = V.SyntheticChunkDataset(5, max_seq_len=256, max_question_len=32, doc_stride=64, max_doc_len=600)
+    pred = Pm.Predictor(model, DEV, collate_fun=I.init_collate_fun(tok, return_items=True), batch_size=8, n_jobs=0)
+    pred(ds, save_dump=True)
+    assert pred.dump
+    model.eval()
+    for scores, s_ids, e_ids, c_ids, items in pred.dump:
+        inputs, _, _ = I.init_collate_fun(tok, return_items=True)(items)
+        with torch.no_grad():
+            out = model(**{k: v.to(DEV) for k, v in inputs.items()})
+        d = O.decode({k: v.cpu() for k, v in out.items()})
+        assert (d["start_ids"].numpy() == s_ids).all() and (d["end_ids"].numpy() == e_ids).all()
+        assert (d["cls_ids"].numpy() == c_ids).all() and (d["scores"].numpy() == scores).all()
+    for item_id, cand in pred.candidates.items():
+        item = pred.items[item_id]
+        assert cand.start_id <= cand.end_id and cand.start_id >= item.question_len + 2
+
+
+def test_bad_inputs_fail_loudly(pkg):
+    model = _model(pkg, TINY)
+    with pytest.raises(RuntimeError, match="out of range"):
+        model.eval()
+        with torch.no_grad():
+            model(torch.zeros(1, 600, dtype=torch.int64, device=DEV))
+    with pytest.raises(NotImplementedError):
+        model(torch.zeros(1, 8, dtype=torch.int64, device=DEV), head_mask=torch.ones(2))

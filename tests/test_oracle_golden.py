@@ -1,0 +1,101 @@
+"""Pins oracle/bertqa_oracle.py to fixtures produced by the reference's own classes
+(oracle/make_golden.py): model forward, all five losses, every gradient, a 4-step Trainer run
+(grad accumulation, clip, HF-AdamW shim, warm-up schedule), decode, LR schedule.  CPU only."""
+import numpy as np
+import torch
+
+from conftest import load_npz
+from oracle import bertqa_oracle as O
+
+TINY = O.OracleConfig(num_layers=2, hidden=64, heads=1, intermediate=128, vocab=200, max_pos=128, type_vocab=2,
+                      hidden_dropout=0.0, attn_dropout=0.0)
+
+
+def _group(fx, prefix):
+    return {k[len(prefix) + 1:]: torch.from_numpy(np.asarray(v)) for k, v in fx.items() if k.startswith(prefix + "/")}
+
+
+def test_forward_loss_backward_match_reference():
+    fx = load_npz("ref_forward_backward.npz")
+    P, inp, lab, out_ref, grad_ref = (_group(fx, p) for p in ("param", "input", "label", "out", "grad"))
+    assert list(P.keys()) == O.param_names(TINY)
+    total, parts, grads, out = O.loss_and_grads(P, TINY, inp, lab, O.LossConfig())
+    for k in out_ref:
+        torch.testing.assert_close(out[k], out_ref[k], rtol=2e-5, atol=2e-6)
+    for k in ("start_class", "end_class", "start_reg", "end_reg", "cls"):
+        assert abs(parts[k].item() - float(fx[f"loss/{k}"])) < 2e-6 * max(1.0, abs(float(fx[f"loss/{k}"])))
+    assert abs(total.item() - float(fx["loss/loss"])) < 1e-5
+    for k, g in grad_ref.items():
+        torch.testing.assert_close(grads[k], g, rtol=2e-4, atol=2e-7, msg=lambda m, k=k: f"{k}: {m}")
+
+
+def test_ce_class_loss_with_label_weights():
+    fx = load_npz("ref_forward_backward.npz")
+    out, lab = _group(fx, "out"), _group(fx, "label")
+    lc = O.LossConfig(loss="ce", label_weights=torch.from_numpy(fx["ce/label_weights"]))
+    total, parts = O.weighted_loss(out, lab, lc)
+    assert abs(parts["cls"].item() - float(fx["ce/cls"])) < 1e-6
+    assert abs(total.item() - float(fx["ce/loss"])) < 1e-5
+
+
+def test_trainer_trajectory_matches_reference():
+    """Reference Trainer.train(): 2 epochs x 4 micro-batches, batch_split 2 -> 4 optimizer steps."""
+    fx = load_npz("ref_trainer_steps.npz")
+    P = {k: v.clone() for k, v in _group(fx, "init").items()}
+    final = _group(fx, "final")
+    lr, wd, clip, split, warmup_coef = fx["hparams"].tolist()
+    split = int(split)
+    n = int(fx["n_batches"])
+    steps = n // split
+    warmup = int(steps * warmup_coef)
+    state, lrs = {}, []
+    acc = None
+    for i in range(n):
+        inp, lab = _group(fx, f"batch{i}/input"), _group(fx, f"batch{i}/label")
+        _, _, grads, _ = O.loss_and_grads(P, TINY, inp, lab, O.LossConfig(), loss_scale=1.0 / split)
+        acc = grads if acc is None else {k: acc[k] + grads[k] for k in acc}
+        if (i + 1) % split == 0:
+            step = (i + 1) // split - 1
+            cur = lr * O.linear_schedule_lambda(step, warmup, steps)
+            lrs.append(cur)
+            O.clip_grad_norm_(acc, clip)
+            O.hf_adamw_step(P, acc, state, cur, wd)
+            acc = None
+    np.testing.assert_allclose(lrs, fx["lrs"], rtol=1e-12)
+    assert int(fx["global_step"]) == steps
+    for k in final:
+        torch.testing.assert_close(P[k], final[k], rtol=1e-4, atol=2e-6, msg=lambda m, k=k: f"{k}: {m}")
+
+
+def test_decode_matches_reference():
+    fx = load_npz("ref_decode.npz")
+    d = O.decode({k: torch.from_numpy(fx[k]) for k in ("start", "end", "cls")} |
+                 {"start_class": torch.from_numpy(fx["start"]), "end_class": torch.from_numpy(fx["end"])})
+    assert (d["start_ids"].numpy() == fx["start_ids"]).all()
+    assert (d["end_ids"].numpy() == fx["end_ids"]).all()
+    assert (d["cls_ids"].numpy() == fx["cls_ids"]).all()
+    assert (d["scores"].numpy() == fx["scores"]).all()  # same float32 association order -> bit-exact
+
+
+def test_schedule_matches_transformers():
+    fx = load_npz("ref_schedule.npz")
+    got = [O.linear_schedule_lambda(t, int(fx["warmup"]), int(fx["total"])) for t in range(len(fx["lr"]))]
+    np.testing.assert_allclose(got, fx["lr"], rtol=1e-12, atol=0)
+
+
+def test_dummy_batch_shape_matches_dummy_dataset():
+    inputs, labels = O.dummy_batch(3, 96, vocab=500, max_question_len=16)
+    ids = inputs["input_ids"]
+    assert ids.shape == (3, 96) and (ids[:, 0] == 101).all() and (ids[:, 17] == 102).all() and (ids[:, -1] == 102).all()
+    assert inputs["attention_mask"].all()
+    assert (inputs["token_type_ids"][:, :18] == 0).all() and (inputs["token_type_ids"][:, 18:] == 1).all()
+    assert labels["end_class"].tolist() == [95] * 3 and labels["end_reg"].tolist() == [1.0] * 3
+
+
+def test_bf16_mode_stays_close_to_fp32():
+    fx = load_npz("ref_forward_backward.npz")
+    P, inp = _group(fx, "param"), _group(fx, "input")
+    a = O.forward(P, TINY, inp["input_ids"], inp["attention_mask"], inp["token_type_ids"])
+    b = O.forward(P, TINY, inp["input_ids"], inp["attention_mask"], inp["token_type_ids"], bf16=True)
+    for k in a:
+        assert (a[k] - b[k]).abs().max() < 0.05
