@@ -47,8 +47,8 @@ BQA_API int bqa_abi_version(void);
  * ------------------------------------------------------------------------------------ */
 enum bqa_epilogue {
   BQA_EPI_LINEAR = 0,   /* C = dropout(acc + bias) + residual (each optional), bf16 out      */
-  BQA_EPI_GELU_FWD = 1, /* C = acc + bias, C2 = gelu_erf(C), bf16 out                        */
-  BQA_EPI_GELU_BWD = 2, /* C = acc * gelu_erf'(aux), bf16 out                                */
+  BQA_EPI_GELU_FWD = 1, /* u = acc + bias: C = gelu_erf'(u), C2 = gelu_erf(u), bf16 out         */
+  BQA_EPI_GELU_BWD = 2, /* C = acc * aux with aux = C of BQA_EPI_GELU_FWD (gelu'), bf16 out      */
   BQA_EPI_F32_ADD = 3   /* C += acc, fp32 out, split-K allowed (weight gradients)            */
 };
 
@@ -67,7 +67,7 @@ typedef struct bqa_gemm_desc {
   const float* bias;    /* [N] fp32 or NULL                                                  */
   const void* residual; /* bf16 [M][ld_res] or NULL                                          */
   int32_t ld_res;
-  const void* aux; /* bf16 [M][ld_aux], pre-activation for BQA_EPI_GELU_BWD                   */
+  const void* aux; /* bf16 [M][ld_aux], gelu' values for BQA_EPI_GELU_BWD                     */
   int32_t ld_aux;
   int32_t k_splits;   /* >= 1                                                                */
   float dropout_p;    /* 0 disables; applied to (acc + bias) before the residual             */
@@ -82,14 +82,17 @@ BQA_API int bqa_gemm_bf16(const bqa_gemm_desc* desc, void* stream);
  * softmax(QK^T/8 + mask) -> dropout -> PV (modeling_bert.py:115-140,168-207) and its backward.
  *   qkv  [B*S][3H] bf16 (Q | K | V slabs), ctx [B*S][H] bf16, lse2 [B][A][S] fp32
  *   key_mask [B][S] uint8 (1 = attend) or NULL
+ *   keep_bits [B][A][S][bqa_attention_keep_words(S)] uint32: dropout decisions written by the
+ *   forward and read by the backward (bit k of word w = key 32 w + k); may be NULL when dropout_p == 0
  *   backward: dctx [B*S][H] bf16 in, dqkv [B*S][3H] bf16 out, dsum [B][A][S] fp32 scratch
  * ------------------------------------------------------------------------------------ */
-BQA_API int bqa_attention_forward(const void* qkv, void* ctx, float* lse2, const uint8_t* key_mask, int32_t B,
-                                  int32_t S, int32_t A, float dropout_p, uint64_t drop_seed, uint32_t drop_site,
-                                  void* stream);
-BQA_API int bqa_attention_backward(const void* qkv, const void* ctx, const float* lse2, const void* dctx,
-                                   void* dqkv, float* dsum, const uint8_t* key_mask, int32_t B, int32_t S,
-                                   int32_t A, float dropout_p, uint64_t drop_seed, uint32_t drop_site,
+BQA_API int bqa_attention_keep_words(int32_t S);
+BQA_API int bqa_attention_forward(const void* qkv, void* ctx, float* lse2, uint32_t* keep_bits,
+                                  const uint8_t* key_mask, int32_t B, int32_t S, int32_t A, float dropout_p,
+                                  uint64_t drop_seed, uint32_t drop_site, void* stream);
+BQA_API int bqa_attention_backward(const void* qkv, const void* ctx, const float* lse2, const uint32_t* keep_bits,
+                                   const void* dctx, void* dqkv, float* dsum, const uint8_t* key_mask, int32_t B,
+                                   int32_t S, int32_t A, float dropout_p, uint64_t drop_seed, uint32_t drop_site,
                                    void* stream);
 
 /* ------------------------------------------------------------------------------------

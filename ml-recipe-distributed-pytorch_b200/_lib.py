@@ -65,9 +65,10 @@ SIGNATURES = {
     "bqa_last_error": (ctypes.c_char_p, []),
     "bqa_abi_version": (ctypes.c_int, []),
     "bqa_gemm_bf16": (ctypes.c_int, [ctypes.POINTER(GemmDesc), vp]),
-    "bqa_attention_forward": (ctypes.c_int, [vp, vp, vp, vp, c_i32, c_i32, c_i32, c_f32, c_u64, c_u32, vp]),
-    "bqa_attention_backward": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, c_i32, c_i32, c_i32, c_f32, c_u64, c_u32,
-                                              vp]),
+    "bqa_attention_keep_words": (ctypes.c_int, [c_i32]),
+    "bqa_attention_forward": (ctypes.c_int, [vp, vp, vp, vp, vp, c_i32, c_i32, c_i32, c_f32, c_u64, c_u32, vp]),
+    "bqa_attention_backward": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, c_i32, c_i32, c_i32, c_f32, c_u64,
+                                              c_u32, vp]),
     "bqa_layernorm_forward": (ctypes.c_int, [vp, vp, vp, vp, c_i32, c_i32, c_f32, vp]),
     "bqa_layernorm_backward": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, c_i32, c_i32, c_f32, c_f32, c_u32,
                                               c_f32, c_u32, c_u64, vp]),

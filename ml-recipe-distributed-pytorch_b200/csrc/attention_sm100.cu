@@ -28,8 +28,9 @@ namespace bqa {
 namespace {
 
 constexpr int CH = 16384;  // bytes of one 128 x 64 bf16 tile
-constexpr int ATT_THREADS = 160;
-constexpr int ROW_THREADS = 128;
+constexpr int ROW_THREADS = 512;               // 16 warps: 4 threads per tile row (column quarters)
+constexpr int ATT_THREADS = ROW_THREADS + 32;  // + 1 control warp (TMA + MMA issue, TMEM alloc)
+constexpr int CTRL_WARP = ROW_THREADS / 32;
 
 struct AttnArgs {
   int B, S, A, H, nchunk, tmem_cols;
@@ -39,6 +40,7 @@ struct AttnArgs {
   float* lse2;
   float* dsum;
   bf16* dqkv;
+  uint32_t* keep;  // [B][A][S][4 * nchunk] dropout keep bits (bit k of word w = key 32 w + k), or null
   DropKey drop;
 };
 
@@ -74,9 +76,9 @@ __device__ __forceinline__ void st_tile16(uint8_t* tile, int r, int c16, const f
   *reinterpret_cast<uint4*>(tile + (c16 >> 3) * CH + r * 128 + (((c16 & 7) ^ (r & 7)) << 4)) = o;
 }
 
-__device__ __forceinline__ void st_row_bf16_32(bf16* dst, const float* f) {
+__device__ __forceinline__ void st_row_bf16_16(bf16* dst, const float* f) {
 #pragma unroll
-  for (int q = 0; q < 4; ++q) {
+  for (int q = 0; q < 2; ++q) {
     uint4 o;
     o.x = pack_bf16x2(f[8 * q], f[8 * q + 1]);
     o.y = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
@@ -88,9 +90,28 @@ __device__ __forceinline__ void st_row_bf16_32(bf16* dst, const float* f) {
 
 __device__ __forceinline__ uint8_t* align1024(uint8_t* p) { return p + ((1024u - (smem_u32(p) & 1023u)) & 1023u); }
 
+// keep decisions for the 32 consecutive elements starting at `idx`, one bit each
+__device__ __forceinline__ uint32_t keep_bits32(const DropKey& dk, uint32_t idx) {
+  uint32_t bits = 0;
+  if ((idx & 1u) == 0u) {
+#pragma unroll
+    for (int e = 0; e < 32; e += 2) {
+      const uint32_t h = drop_hash(dk, (idx + e) >> 1);
+      bits |= ((h & 0xffffu) >= dk.thresh ? 1u : 0u) << e;
+      bits |= ((h >> 16) >= dk.thresh ? 1u : 0u) << (e + 1);
+    }
+  } else {
+#pragma unroll
+    for (int e = 0; e < 32; ++e) bits |= (drop_keep(dk, idx + e) ? 1u : 0u) << e;
+  }
+  return bits;
+}
+
 // =========================================================================================
 // forward
 // =========================================================================================
+// KB: whether the additive key bias (padding mask / ragged last chunk) is needed
+template <bool KB>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -101,7 +122,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnArgs a) {
   uint8_t* sV = sK + N * CH;
   uint8_t* sP = sV + N * CH;  // 2 buffers x (2 * CH)
   float* kbias = reinterpret_cast<float*>(sP + 4 * CH);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(kbias + 512);
+  float* xmax = kbias + 512;  // [4][128] row statistics exchanged between the four column quarters
+  float* xsum = xmax + 512;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(xsum + 512);
   uint64_t* bar_qk = bars + 0;
   uint64_t* bar_v = bars + 1;
   uint64_t* bar_s = bars + 2;
@@ -126,11 +149,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnArgs a) {
     }
     fence_mbar_init();
   }
-  if (warp == 4) {
+  if (warp == CTRL_WARP) {
     tmem_alloc(tmem_slot, a.tmem_cols);
     tmem_relinquish();
   }
-  if (tid < ROW_THREADS) {
+  if (KB && tid < ROW_THREADS) {
     for (int k = tid; k < Sp; k += ROW_THREADS) {
       const bool ok = k < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + k] != 0);
       kbias[k] = ok ? 0.0f : -INFINITY;
@@ -164,72 +187,90 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnArgs a) {
     }
     umma_commit(bar_o);
   } else if (tid < ROW_THREADS) {
-    // ---------------- softmax threads: one query row each ----------------
-    const int r = tid;
+    // ---- softmax threads: thread (r, qd) owns columns [32 qd, 32 qd + 32) of every 128-key chunk of row r
+    const int r = tid & 127, qd = tid >> 7;
     const int q = qt * 128 + r;
-    const uint32_t lane_addr = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+    const uint32_t lane_base = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+    const uint32_t lane_addr = lane_base + qd * 32;
     const float sl2 = a.scale_log2;
     mbar_wait(bar_s, 0);
     tc_fence_after();
     float mx = -INFINITY;
-    for (int c = 0; c < Sp / 32; ++c) {
+    for (int j = 0; j < N; ++j) {
       uint32_t v[32];
-      tmem_ld_32x32(lane_addr + c * 32, v);
+      tmem_ld_32x32(lane_addr + j * 128, v);
       tmem_wait_ld();
+      if (KB) {
+        const float* kb = kbias + j * 128 + qd * 32;
 #pragma unroll
-      for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaf(__uint_as_float(v[i]), sl2, kbias[c * 32 + i]));
+        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaf(__uint_as_float(v[i]), sl2, kb[i]));
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+      }
     }
+    if (!KB) mx *= sl2;
+    xmax[qd * 128 + r] = mx;
+    named_bar_sync(1, ROW_THREADS);
+    mx = fmaxf(fmaxf(xmax[r], xmax[128 + r]), fmaxf(xmax[256 + r], xmax[384 + r]));
     if (mx == -INFINITY) mx = 0.0f;
     float l = 0.0f;
     const uint32_t drop_base = ((static_cast<uint32_t>(b) * a.A + h) * S + static_cast<uint32_t>(q)) * S;
+    uint32_t* keep_row = a.keep + ((static_cast<size_t>(b) * a.A + h) * S + (q < S ? q : 0)) * (4 * N) + qd;
     for (int j = 0; j < N; ++j) {
       uint8_t* tile = sP + (j & 1) * 2 * CH;
+      uint32_t v[32];
+      tmem_ld_32x32(lane_addr + j * 128, v);
+      tmem_wait_ld();
+      const int key0 = j * 128 + qd * 32;
+      uint32_t bits = 0xffffffffu;
+      if (a.drop.thresh != 0u) {
+        bits = keep_bits32(a.drop, drop_base + key0);
+        if (q < S) keep_row[j * 4] = bits;
+      }
       if (j >= 2) mbar_wait(&bar_pfree[j & 1], ((j >> 1) - 1) & 1);
-#pragma unroll 1
-      for (int c4 = 0; c4 < 4; ++c4) {
-        uint32_t v[32];
-        tmem_ld_32x32(lane_addr + j * 128 + c4 * 32, v);
-        tmem_wait_ld();
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          float p[8];
+      for (int g = 0; g < 4; ++g) {
+        float p[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int key = j * 128 + c4 * 32 + g * 8 + e;
-            float pv = fast_exp2(fmaf(__uint_as_float(v[g * 8 + e]), sl2, kbias[key]) - mx);
-            l += pv;
-            if (a.drop.thresh != 0u) pv = drop_keep(a.drop, drop_base + key) ? pv * a.drop.scale : 0.0f;
-            p[e] = pv;
-          }
-          st_tile16(tile, r, c4 * 4 + g, p);
+        for (int e = 0; e < 8; ++e) {
+          const float x = KB ? fmaf(__uint_as_float(v[g * 8 + e]), sl2, kbias[key0 + g * 8 + e])
+                             : __uint_as_float(v[g * 8 + e]) * sl2;
+          const float pv = fast_exp2(x - mx);
+          l += pv;
+          p[e] = ((bits >> (g * 8 + e)) & 1u) ? pv * a.drop.scale : 0.0f;
         }
+        st_tile16(tile, r, qd * 4 + g, p);
       }
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(&bar_p[j & 1]);
     }
+    xsum[qd * 128 + r] = l;
+    named_bar_sync(1, ROW_THREADS);
+    l = (xsum[r] + xsum[128 + r]) + (xsum[256 + r] + xsum[384 + r]);
     mbar_wait(bar_o, 0);
     tc_fence_after();
     const float inv = l > 0.0f ? 1.0f / l : 0.0f;
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      uint32_t v[32];
-      tmem_ld_32x32(lane_addr + c * 32, v);
+    {
+      uint32_t v[16];
+      tmem_ld_32x16(lane_base + qd * 16, v);
       tmem_wait_ld();
       if (q < S) {
-        float f[32];
+        float f[16];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * inv;
-        st_row_bf16_32(a.ctx + (static_cast<size_t>(b) * S + q) * a.H + h * 64 + c * 32, f);
+        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]) * inv;
+        st_row_bf16_16(a.ctx + (static_cast<size_t>(b) * S + q) * a.H + h * 64 + qd * 16, f);
       }
     }
     // a row whose keys are all masked has l == 0: store +inf so that the backward recomputes P = 0
-    if (q < S) a.lse2[(static_cast<size_t>(b) * a.A + h) * S + q] = l > 0.0f ? mx + log2f(l) : INFINITY;
+    if (q < S && qd == 0)
+      a.lse2[(static_cast<size_t>(b) * a.A + h) * S + q] = l > 0.0f ? mx + log2f(l) : INFINITY;
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == CTRL_WARP) {
     tc_fence_after();
     tmem_dealloc(tmem, a.tmem_cols);
   }
@@ -266,6 +307,7 @@ attn_dsum_kernel(const bf16* __restrict__ ctx, const bf16* __restrict__ dctx, fl
 // =========================================================================================
 // backward, dQ
 // =========================================================================================
+template <bool KB>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
 attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_dctx,
                    const AttnArgs a) {
@@ -302,11 +344,11 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
     mbar_init(bar_dq, 1);
     fence_mbar_init();
   }
-  if (warp == 4) {
+  if (warp == CTRL_WARP) {
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
   }
-  if (tid < ROW_THREADS) {
+  if (KB && tid < ROW_THREADS) {
     for (int k = tid; k < Sp; k += ROW_THREADS) {
       const bool ok = k < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + k] != 0);
       kbias[k] = ok ? 0.0f : -INFINITY;
@@ -348,42 +390,47 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
     }
     umma_commit(bar_dq);
   } else if (tid < ROW_THREADS) {
-    const int r = tid;
+    const int r = tid & 127, qd = tid >> 7;
     const int q = qt * 128 + r;
-    const uint32_t lane_addr = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+    const uint32_t lane_base = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     const float sl2 = a.scale_log2;
     const bool q_ok = q < S;
     const size_t stat = (static_cast<size_t>(b) * a.A + h) * S + (q_ok ? q : 0);
     const float lse = q_ok ? a.lse2[stat] : INFINITY;
     const float dsum = q_ok ? a.dsum[stat] : 0.0f;
-    const uint32_t drop_base = ((static_cast<uint32_t>(b) * a.A + h) * S + static_cast<uint32_t>(q)) * S;
+    const bool dropping = a.drop.thresh != 0u;
+    uint32_t kw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+    if (dropping) {
+      const uint32_t* keep_row = a.keep + stat * (4 * N) + qd;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (j < N) kw[j] = __ldg(keep_row + j * 4);
+    }
     for (int j = 0; j < N; ++j) {
       mbar_wait(bar_s, j & 1);
       tc_fence_after();
+      uint32_t vs[32], vd[32];
+      tmem_ld_32x32(lane_base + COL_S + qd * 32, vs);
+      tmem_ld_32x32(lane_base + COL_DP + qd * 32, vd);
+      tmem_wait_ld();
+      tc_fence_before();
+      mbar_arrive(bar_sfree);
       if (j >= 1) mbar_wait(bar_dsfree, (j - 1) & 1);
-#pragma unroll 1
-      for (int c4 = 0; c4 < 4; ++c4) {
-        uint32_t vs[32], vd[32];
-        tmem_ld_32x32(lane_addr + COL_S + c4 * 32, vs);
-        tmem_ld_32x32(lane_addr + COL_DP + c4 * 32, vd);
-        tmem_wait_ld();
-        if (c4 == 3) {
-          tc_fence_before();
-          mbar_arrive(bar_sfree);
-        }
+      const int key0 = j * 128 + qd * 32;
+      const uint32_t bits = kw[j & 3];
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          float ds[8];
+      for (int g = 0; g < 4; ++g) {
+        float ds[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int key = j * 128 + c4 * 32 + g * 8 + e;
-            const float p = fast_exp2(fmaf(__uint_as_float(vs[g * 8 + e]), sl2, kbias[key]) - lse);
-            float dp = __uint_as_float(vd[g * 8 + e]);
-            if (a.drop.thresh != 0u) dp = drop_keep(a.drop, drop_base + key) ? dp * a.drop.scale : 0.0f;
-            ds[e] = p * (dp - dsum) * a.scale;
-          }
-          st_tile16(sdS, r, c4 * 4 + g, ds);
+        for (int e = 0; e < 8; ++e) {
+          const float x = KB ? fmaf(__uint_as_float(vs[g * 8 + e]), sl2, kbias[key0 + g * 8 + e])
+                             : __uint_as_float(vs[g * 8 + e]) * sl2;
+          const float p = fast_exp2(x - lse);
+          float dp = __uint_as_float(vd[g * 8 + e]);
+          if (dropping) dp = ((bits >> (g * 8 + e)) & 1u) ? dp * a.drop.scale : 0.0f;
+          ds[e] = p * (dp - dsum) * a.scale;
         }
+        st_tile16(sdS, r, qd * 4 + g, ds);
       }
       fence_proxy_async_smem();
       tc_fence_before();
@@ -391,23 +438,22 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
     }
     mbar_wait(bar_dq, 0);
     tc_fence_after();
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      uint32_t v[32];
-      tmem_ld_32x32(lane_addr + COL_DQ + c * 32, v);
+    {
+      uint32_t v[16];
+      tmem_ld_32x16(lane_base + COL_DQ + qd * 16, v);
       tmem_wait_ld();
       if (q_ok) {
-        float f[32];
+        float f[16];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
-        st_row_bf16_32(a.dqkv + (static_cast<size_t>(b) * S + q) * 3 * a.H + h * 64 + c * 32, f);
+        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+        st_row_bf16_16(a.dqkv + (static_cast<size_t>(b) * S + q) * 3 * a.H + h * 64 + qd * 16, f);
       }
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == CTRL_WARP) {
     tc_fence_after();
     tmem_dealloc(tmem, 512);
   }
@@ -430,7 +476,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
   uint8_t* sdSt = sPt + 2 * CH;  // 2 * CH
   float* s_lse = reinterpret_cast<float*>(sdSt + 2 * CH);
   float* s_dsum = s_lse + 512;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_dsum + 512);
+  uint32_t* s_keep = reinterpret_cast<uint32_t*>(s_dsum + 512);  // [2][128 queries][4 words]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_keep + 1024);
   uint64_t* bar_kv = bars + 0;
   uint64_t* bar_ld = bars + 1;  // [2]
   uint64_t* bar_s = bars + 3;
@@ -457,7 +504,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
     mbar_init(bar_out, 1);
     fence_mbar_init();
   }
-  if (warp == 4) {
+  if (warp == CTRL_WARP) {
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
   }
@@ -509,47 +556,60 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
     }
     umma_commit(bar_out);
   } else if (tid < ROW_THREADS) {
-    const int r = tid;
+    const int r = tid & 127, qd = tid >> 7;
     const int key = kt * 128 + r;
-    const uint32_t lane_addr = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+    const uint32_t lane_base = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     const float sl2 = a.scale_log2;
     const bool key_ok = key < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + key] != 0);
     const float kb = key_ok ? 0.0f : -INFINITY;
-    const uint32_t drop_base = (static_cast<uint32_t>(b) * a.A + h) * S;
+    const bool dropping = a.drop.thresh != 0u;
+    const uint32_t kbit = static_cast<uint32_t>(r & 31);
+    const int kword = r >> 5;
+    const size_t keep_base = (static_cast<size_t>(b) * a.A + h) * S;
     for (int i = 0; i < N; ++i) {
+      if (dropping) {
+        // stage this query chunk's keep words for the 128 keys of the tile: [query][4 words]
+        const int ql = tid >> 2, w = tid & 3;
+        const int qq = i * 128 + ql;
+        s_keep[(i & 1) * 512 + ql * 4 + w] =
+            qq < S ? __ldg(a.keep + (keep_base + qq) * (4 * N) + kt * 4 + w) : 0u;
+        named_bar_sync(1, ROW_THREADS);
+      }
       mbar_wait(bar_s, i & 1);
       tc_fence_after();
+      uint32_t vs[32], vd[32];
+      tmem_ld_32x32(lane_base + COL_S + qd * 32, vs);
+      tmem_ld_32x32(lane_base + COL_DP + qd * 32, vd);
+      tmem_wait_ld();
+      tc_fence_before();
+      mbar_arrive(bar_sfree);
       if (i >= 1) mbar_wait(bar_ptfree, (i - 1) & 1);
-#pragma unroll 1
-      for (int c4 = 0; c4 < 4; ++c4) {
-        uint32_t vs[32], vd[32];
-        tmem_ld_32x32(lane_addr + COL_S + c4 * 32, vs);
-        tmem_ld_32x32(lane_addr + COL_DP + c4 * 32, vd);
-        tmem_wait_ld();
-        if (c4 == 3) {
-          tc_fence_before();
-          mbar_arrive(bar_sfree);
-        }
+      const int q0 = i * 128 + qd * 32;
+      const uint32_t* keep_q = s_keep + (i & 1) * 512 + (qd * 32) * 4 + kword;
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          float pt[8], ds[8];
+      for (int g = 0; g < 4; ++g) {
+        float pt[8], ds[8];
+        const float4 l0 = *reinterpret_cast<const float4*>(s_lse + q0 + g * 8);
+        const float4 l1 = *reinterpret_cast<const float4*>(s_lse + q0 + g * 8 + 4);
+        const float4 d0 = *reinterpret_cast<const float4*>(s_dsum + q0 + g * 8);
+        const float4 d1 = *reinterpret_cast<const float4*>(s_dsum + q0 + g * 8 + 4);
+        const float lsev[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w};
+        const float dsv[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int q = i * 128 + c4 * 32 + g * 8 + e;
-            const float p = fast_exp2(fmaf(__uint_as_float(vs[g * 8 + e]), sl2, kb) - s_lse[q]);
-            float dp = __uint_as_float(vd[g * 8 + e]);
-            float pd = p;
-            if (a.drop.thresh != 0u) {
-              const bool keep = drop_keep(a.drop, (drop_base + static_cast<uint32_t>(q)) * S + key);
-              pd = keep ? p * a.drop.scale : 0.0f;
-              dp = keep ? dp * a.drop.scale : 0.0f;
-            }
-            pt[e] = pd;
-            ds[e] = p * (dp - s_dsum[q]) * a.scale;
+        for (int e = 0; e < 8; ++e) {
+          const float p = fast_exp2(fmaf(__uint_as_float(vs[g * 8 + e]), sl2, kb) - lsev[e]);
+          float dp = __uint_as_float(vd[g * 8 + e]);
+          float pd = p;
+          if (dropping) {
+            const bool keep = (keep_q[(g * 8 + e) * 4] >> kbit) & 1u;
+            pd = keep ? p * a.drop.scale : 0.0f;
+            dp = keep ? dp * a.drop.scale : 0.0f;
           }
-          st_tile16(sPt, r, c4 * 4 + g, pt);
-          st_tile16(sdSt, r, c4 * 4 + g, ds);
+          pt[e] = pd;
+          ds[e] = p * (dp - dsv[e]) * a.scale;
         }
+        st_tile16(sPt, r, qd * 4 + g, pt);
+        st_tile16(sdSt, r, qd * 4 + g, ds);
       }
       fence_proxy_async_smem();
       tc_fence_before();
@@ -558,31 +618,31 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
     mbar_wait(bar_out, 0);
     tc_fence_after();
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      uint32_t v[32];
-      tmem_ld_32x32(lane_addr + COL_DV + c * 32, v);  // c = 0,1: dV ; c = 2,3: dK (COL_DK = COL_DV + 64)
+    for (int c = 0; c < 2; ++c) {  // c = 0: dV, c = 1: dK (COL_DK = COL_DV + 64); 16 columns per thread
+      uint32_t v[16];
+      tmem_ld_32x16(lane_base + COL_DV + c * 64 + qd * 16, v);
       tmem_wait_ld();
       if (key < S) {
-        float f[32];
+        float f[16];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
-        const int which = c < 2 ? 2 : 1;  // V block is the third H-wide slab of dqkv, K the second
-        st_row_bf16_32(a.dqkv + (static_cast<size_t>(b) * S + key) * 3 * a.H + which * a.H + h * 64 + (c & 1) * 32, f);
+        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+        const int which = c == 0 ? 2 : 1;  // V block is the third H-wide slab of dqkv, K the second
+        st_row_bf16_16(a.dqkv + (static_cast<size_t>(b) * S + key) * 3 * a.H + which * a.H + h * 64 + qd * 16, f);
       }
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == CTRL_WARP) {
     tc_fence_after();
     tmem_dealloc(tmem, 512);
   }
 }
 
-int fwd_smem_bytes(int n) { return CH * (5 + 2 * n) + 2048 + 256 + 1024; }
+int fwd_smem_bytes(int n) { return CH * (5 + 2 * n) + 2048 + 4096 + 256 + 1024; }
 int dq_smem_bytes(int n) { return CH * (4 + 2 * n) + 2048 + 256 + 1024; }
-int dkv_smem_bytes() { return CH * 10 + 4096 + 256 + 1024; }
+int dkv_smem_bytes() { return CH * 10 + 4096 + 4096 + 256 + 1024; }
 
 AttnArgs make_args(const AttnPlan& p, const uint8_t* key_mask, DropKey drop) {
   AttnArgs a;
@@ -599,6 +659,7 @@ AttnArgs make_args(const AttnPlan& p, const uint8_t* key_mask, DropKey drop) {
   a.lse2 = p.lse2;
   a.dsum = p.dsum;
   a.dqkv = p.dqkv;
+  a.keep = p.keep;
   a.drop = drop;
   return a;
 }
@@ -606,7 +667,7 @@ AttnArgs make_args(const AttnPlan& p, const uint8_t* key_mask, DropKey drop) {
 }  // namespace
 
 int attn_plan(AttnPlan* plan, const AttnShape& s, const void* qkv, void* ctx, float* lse2, const void* dctx,
-              float* dsum, void* dqkv) {
+              float* dsum, void* dqkv, uint32_t* keep) {
   if (s.H != s.A * 64) {
     set_error("attention: head dim must be 64 (H=%d, A=%d)", s.H, s.A);
     return 1;
@@ -625,6 +686,7 @@ int attn_plan(AttnPlan* plan, const AttnShape& s, const void* qkv, void* ctx, fl
   plan->dctx = reinterpret_cast<const bf16*>(dctx);
   plan->dsum = dsum;
   plan->dqkv = reinterpret_cast<bf16*>(dqkv);
+  plan->keep = keep;
   const uint64_t H = s.H;
   if (qkv != nullptr &&
       encode_tmap_3d(&plan->tm_qkv, qkv, 2, 3 * H, s.S, s.B, 3 * H, static_cast<uint64_t>(s.S) * 3 * H, 64, 128, 1))
@@ -638,32 +700,52 @@ int attn_plan(AttnPlan* plan, const AttnShape& s, const void* qkv, void* ctx, fl
 int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st) {
   static bool configured = false;
   if (!configured) {
-    BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        fwd_smem_bytes(4)));
+    BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         fwd_smem_bytes(4)));
     configured = true;
   }
   const AttnArgs a = make_args(plan, key_mask, drop);
+  if (drop.thresh != 0u && plan.keep == nullptr) {
+    set_error("attention: dropout needs the keep-bit buffer");
+    return 1;
+  }
   dim3 grid(plan.nchunk, plan.shape.A, plan.shape.B);
-  attn_fwd_kernel<<<grid, ATT_THREADS, fwd_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, a);
+  const bool kb = key_mask != nullptr || (plan.shape.S % 128) != 0;
+  if (kb)
+    attn_fwd_kernel<true><<<grid, ATT_THREADS, fwd_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, a);
+  else
+    attn_fwd_kernel<false><<<grid, ATT_THREADS, fwd_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, a);
   return check_launch("attn_fwd");
 }
 
 int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st) {
   static bool configured = false;
   if (!configured) {
-    BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        dq_smem_bytes(4)));
+    BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         dq_smem_bytes(4)));
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dkv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         dkv_smem_bytes()));
     configured = true;
   }
   const AttnArgs a = make_args(plan, key_mask, drop);
+  if (drop.thresh != 0u && plan.keep == nullptr) {
+    set_error("attention: dropout needs the keep-bit buffer written by the forward");
+    return 1;
+  }
   const int T = plan.shape.B * plan.shape.S;
   attn_dsum_kernel<<<(T + 3) / 4, 128, 0, st>>>(plan.ctx, plan.dctx, plan.dsum, plan.shape.B, plan.shape.S,
                                                plan.shape.A, plan.shape.H);
   if (check_launch("attn_dsum")) return 1;
   dim3 grid(plan.nchunk, plan.shape.A, plan.shape.B);
-  attn_bwd_dq_kernel<<<grid, ATT_THREADS, dq_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_dctx, a);
+  const bool kb = key_mask != nullptr || (plan.shape.S % 128) != 0;
+  if (kb)
+    attn_bwd_dq_kernel<true><<<grid, ATT_THREADS, dq_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_dctx, a);
+  else
+    attn_bwd_dq_kernel<false><<<grid, ATT_THREADS, dq_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_dctx, a);
   if (check_launch("attn_bwd_dq")) return 1;
   attn_bwd_dkv_kernel<<<grid, ATT_THREADS, dkv_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_dctx, a);
   return check_launch("attn_bwd_dkv");

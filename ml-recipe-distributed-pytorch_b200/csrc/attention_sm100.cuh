@@ -25,11 +25,14 @@ struct AttnPlan {
   const bf16* dctx;
   float* dsum;   // [B][A][S] rowsum(dO * O)
   bf16* dqkv;    // [B*S][3H]
+  uint32_t* keep;  // [B][A][S][4 * nchunk] dropout keep bits (forward writes, backward reads) or null
 };
 
 // qkv/ctx/dctx/dqkv may be null when only the forward (or only a plan for it) is needed.
 int attn_plan(AttnPlan* plan, const AttnShape& s, const void* qkv, void* ctx, float* lse2, const void* dctx,
-              float* dsum, void* dqkv);
+              float* dsum, void* dqkv, uint32_t* keep);
+// 32-bit words of keep bits per (batch, head, query) row for sequence length S
+inline int attn_keep_words(int S) { return 4 * ((S + 127) / 128); }
 // key_mask: [B][S] uint8 (1 = attend) or null.  drop.thresh == 0 disables dropout.
 int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st);
 int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st);

@@ -55,21 +55,26 @@ int bqa_gemm_bf16(const bqa_gemm_desc* d, void* stream) {
 
 extern "C" {
 
-int bqa_attention_forward(const void* qkv, void* ctx, float* lse2, const uint8_t* key_mask, int32_t B, int32_t S,
-                          int32_t A, float dropout_p, uint64_t drop_seed, uint32_t drop_site, void* stream) {
+int bqa_attention_keep_words(int32_t S) { return attn_keep_words(S); }
+
+int bqa_attention_forward(const void* qkv, void* ctx, float* lse2, uint32_t* keep_bits, const uint8_t* key_mask,
+                          int32_t B, int32_t S, int32_t A, float dropout_p, uint64_t drop_seed, uint32_t drop_site,
+                          void* stream) {
   AttnPlan plan;
   AttnShape s{B, S, A, A * 64};
-  if (attn_plan(&plan, s, qkv, ctx, lse2, nullptr, nullptr, nullptr)) return 1;
+  if (attn_plan(&plan, s, qkv, ctx, lse2, nullptr, nullptr, nullptr, keep_bits)) return 1;
   return attn_forward(plan, key_mask, make_drop_key(drop_seed, drop_site, dropout_p),
                       reinterpret_cast<cudaStream_t>(stream));
 }
 
-int bqa_attention_backward(const void* qkv, const void* ctx, const float* lse2, const void* dctx, void* dqkv,
-                           float* dsum, const uint8_t* key_mask, int32_t B, int32_t S, int32_t A, float dropout_p,
-                           uint64_t drop_seed, uint32_t drop_site, void* stream) {
+int bqa_attention_backward(const void* qkv, const void* ctx, const float* lse2, const uint32_t* keep_bits,
+                           const void* dctx, void* dqkv, float* dsum, const uint8_t* key_mask, int32_t B, int32_t S,
+                           int32_t A, float dropout_p, uint64_t drop_seed, uint32_t drop_site, void* stream) {
   AttnPlan plan;
   AttnShape s{B, S, A, A * 64};
-  if (attn_plan(&plan, s, qkv, const_cast<void*>(ctx), const_cast<float*>(lse2), dctx, dsum, dqkv)) return 1;
+  if (attn_plan(&plan, s, qkv, const_cast<void*>(ctx), const_cast<float*>(lse2), dctx, dsum, dqkv,
+                const_cast<uint32_t*>(keep_bits)))
+    return 1;
   return attn_backward(plan, key_mask, make_drop_key(drop_seed, drop_site, dropout_p),
                        reinterpret_cast<cudaStream_t>(stream));
 }

@@ -194,6 +194,16 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&v)[32])
       : "memory");
 }
 
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+
 // ----------------------------------------------------------------------------------------
 // UMMA descriptors (bf16, 128-byte swizzle, BLOCK_K = 64 elements)
 // ----------------------------------------------------------------------------------------
@@ -240,17 +250,44 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t v) {
   return __bfloat1622float2(t);
 }
 
-__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
-
-__device__ __forceinline__ float gelu_erf_grad(float x) {
-  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
-  const float pdf = 0.39894228040143268f * __expf(-0.5f * x * x);
-  return cdf + x * pdf;
+// GELU (erf form: transformers activations.py -> F.gelu) and its derivative from ONE shared core.
+//   Phi(x) = 0.5 (1 + erf(x / sqrt 2)),  gelu(x) = x Phi(x),  gelu'(x) = Phi(x) + x phi(x)
+// erf(z), z >= 0, by Abramowitz-Stegun 7.1.25: 1 - (a1 t + a2 t^2 + a3 t^3) exp(-z^2),
+// t = 1 / (1 + p z), |error| <= 2.5e-5 — two orders below the bf16 resolution of the stored
+// results — using one MUFU.RCP, one MUFU.EX2 and no branches, so that the GEMM epilogue that
+// applies it keeps pace with the tensor cores.  exp(-z^2) = exp(-x^2 / 2) is also the Gaussian
+// the derivative needs.
+__device__ __forceinline__ void gelu_and_grad(float x, float& g, float& dg) {
+  // w = |x| * sqrt(log2(e) / 2): exp(-x^2/2) = 2^(-w^2);  p z = (p / sqrt(log2 e)) w
+  const float w = fabsf(x) * 0.84932180028801904f;
+  float e, t;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-w * w));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.39169197f, w, 1.0f)));
+  // h = 0.5 * (1 - erf(z)) = 0.5 t (a1 + a2 t + a3 t^2) e
+  float poly = fmaf(t, 0.3739278f, -0.0479399f);
+  poly = fmaf(t, poly, 0.1740121f);
+  const float h = poly * t * e;
+  const float phi_cdf = 0.5f + copysignf(0.5f - h, x);
+  g = x * phi_cdf;
+  dg = fmaf(x * 0.39894228040143268f, e, phi_cdf);
 }
 
-// Stateless per-element dropout: two rounds of a 32-bit avalanche mixer keyed by (k0, k1),
-// which the host derives from (seed, step, site).  The same (key, element index) gives the
-// same decision in the forward kernel and in every backward kernel that needs the mask.
+__device__ __forceinline__ float gelu_erf(float x) {
+  float g, dg;
+  gelu_and_grad(x, g, dg);
+  return g;
+}
+
+__device__ __forceinline__ float gelu_erf_grad(float x) {
+  float g, dg;
+  gelu_and_grad(x, g, dg);
+  return dg;
+}
+
+// Stateless dropout: a Weyl step plus one round of a 32-bit avalanche mixer keyed by (k0, k1),
+// which the host derives from (seed, step, site).  One hash serves TWO consecutive elements (its low and high
+// 16 bits), decision = (16-bit value >= thresh).  The same (key, element index) gives the same
+// decision in the forward kernel and in every backward kernel that needs the mask.
 __device__ __forceinline__ uint32_t mix32(uint32_t x) {
   x ^= x >> 16;
   x *= 0x7feb352dU;
@@ -262,13 +299,24 @@ __device__ __forceinline__ uint32_t mix32(uint32_t x) {
 
 struct DropKey {
   uint32_t k0, k1;
-  uint32_t thresh;  // drop iff (hash >> 8) < thresh ; thresh = round(p * 2^24); 0 disables
+  uint32_t thresh;  // drop iff 16-bit value < thresh ; thresh = round(p * 65536); 0 disables
   float scale;      // 1 / (1 - p)
 };
 
+__device__ __forceinline__ uint32_t drop_hash(const DropKey& dk, uint32_t pair_idx) {
+  return mix32(pair_idx * 0x9E3779B1u + dk.k0) ^ dk.k1;
+}
+
 __device__ __forceinline__ bool drop_keep(const DropKey& dk, uint32_t idx) {
-  const uint32_t h = mix32(mix32(idx + dk.k0) ^ dk.k1);
-  return (h >> 8) >= dk.thresh;
+  const uint32_t h = drop_hash(dk, idx >> 1);
+  return ((idx & 1u) ? (h >> 16) : (h & 0xffffu)) >= dk.thresh;
+}
+
+// decisions for elements idx_even and idx_even + 1 (idx_even must be even)
+__device__ __forceinline__ void drop_keep2(const DropKey& dk, uint32_t idx_even, bool& keep0, bool& keep1) {
+  const uint32_t h = drop_hash(dk, idx_even >> 1);
+  keep0 = (h & 0xffffu) >= dk.thresh;
+  keep1 = (h >> 16) >= dk.thresh;
 }
 
 __device__ __forceinline__ float warp_sum(float v) {

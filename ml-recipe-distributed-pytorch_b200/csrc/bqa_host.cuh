@@ -49,7 +49,8 @@ inline DropKey make_drop_key(uint64_t seed, uint32_t site, float p) {
   k.k0 = static_cast<uint32_t>(h);
   k.k1 = static_cast<uint32_t>(h >> 32);
   if (p > 0.0f) {
-    k.thresh = static_cast<uint32_t>(lrintf(p * 16777216.0f));
+    k.thresh = static_cast<uint32_t>(lrintf(p * 65536.0f));
+    if (k.thresh > 65535u) k.thresh = 65535u;
     k.scale = 1.0f / (1.0f - p);
   } else {
     k.thresh = 0u;

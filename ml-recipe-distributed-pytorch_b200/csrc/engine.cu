@@ -34,9 +34,9 @@ inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 int compute_layout(const bqa_config& c, bqa_layout* L) {
   if (c.num_layers < 1 || c.hidden < 64 || c.hidden % 64 != 0 || c.heads * 64 != c.hidden || c.hidden > 1024 ||
       c.intermediate % 64 != 0 || c.intermediate < 64 || c.vocab < 1 || c.max_pos < 1 || c.type_vocab < 1 ||
-      c.num_labels < 1 || c.num_labels > 32) {
+      c.type_vocab > 2 || c.num_labels < 1 || c.num_labels > 32) {
     set_error("config: unsupported shape (L=%d H=%d A=%d I=%d V=%d P=%d TV=%d C=%d): need H = 64*A <= 1024, "
-              "H and I multiples of 64",
+              "H and I multiples of 64, type_vocab <= 2",
               c.num_layers, c.hidden, c.heads, c.intermediate, c.vocab, c.max_pos, c.type_vocab, c.num_labels);
     return 1;
   }
@@ -101,8 +101,9 @@ struct Bump {
 };
 
 struct LayerActs {
-  bf16 *qkv, *ctx, *z1, *a, *u, *g, *z2, *x_out;
+  bf16 *qkv, *ctx, *z1, *a, *u, *g, *z2, *x_out;  // u holds gelu'(pre-activation), g the activation
   float* lse2;
+  uint32_t* keep;  // attention-dropout keep bits
 };
 
 struct Workspace {
@@ -138,6 +139,9 @@ void carve(Workspace* w, uint8_t* base, const bqa_config& c, int B, int S, bool 
     a.z2 = b.take<bf16>(T * H);
     a.x_out = b.take<bf16>(T * H);
     a.lse2 = b.take<float>(static_cast<uint64_t>(B) * c.heads * S);
+    a.keep = (training && c.attn_dropout > 0.0f)
+                 ? b.take<uint32_t>(static_cast<uint64_t>(B) * c.heads * S * attn_keep_words(S))
+                 : nullptr;
   }
   w->pooled = b.take<float>(static_cast<uint64_t>(B) * H);
   w->start = b.take<float>(T);
@@ -298,7 +302,7 @@ int build_plan(bqa_handle* h, int B, int S, bool training) {
     if (fwd(&lp.ffn2, act.g, I, h->W(lo + Y.o_w), H, act.z2, nullptr, EPI_LINEAR, h->P(lo + Y.o_b), act.a)) return 1;
     AttnShape as{B, S, c.heads, H};
     if (attn_plan(&lp.attn, as, act.qkv, act.ctx, act.lse2, training ? p.ws.dctx : nullptr, p.ws.dsum,
-                  p.ws.dqkv))
+                  p.ws.dqkv, act.keep))
       return 1;
     if (!training) continue;
     // dgrad: dX[T,Kin] = dY[T,Nout] . W[Nout,Kin]   (A K-major, W is the MN-major operand)

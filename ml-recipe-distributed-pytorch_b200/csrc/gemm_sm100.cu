@@ -5,11 +5,12 @@
 // (site-packages/transformers/models/bert/modeling_bert.py:179-181,294-298,339-342,352-356)
 // and their autograd backward (reference trainer.py:197-204).
 //
-// CTA = 256 threads, one CTA per SM, static round-robin tile schedule:
+// CTA = 384 threads, one CTA per SM, static round-robin tile schedule:
 //   warp 0 (1 thread)  TMA producer: 4-stage ring of {A 128x64, B 256x64} bf16 tiles, 128B swizzle
 //   warp 1 (1 thread)  MMA issuer  : tcgen05.mma cta_group::1 kind::f16, M=128 N=256 K=16, fp32 in TMEM
 //   warp 2             TMEM allocator (512 columns = two 128x256 fp32 accumulators, double-buffered)
-//   warps 4-7          epilogue    : tcgen05.ld -> registers -> fused op -> swizzled smem -> TMA store
+//   warps 4-11         epilogue    : tcgen05.ld -> registers -> fused op -> swizzled smem -> TMA store
+//                      (two warps per TMEM lane quarter, each draining half of every column chunk)
 // Operands may be K-major or MN-major (instruction-descriptor major bits + smem descriptor
 // strides), so forward, dgrad and wgrad all read the tensors in the layout PyTorch gives them.
 #include "gemm_sm100.cuh"
@@ -33,8 +34,8 @@ constexpr int SMEM_BARRIER_BYTES = 256;
 constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + 2 * C_STAGE_BYTES + SMEM_BARRIER_BYTES;
 constexpr int SMEM_ALLOC = SMEM_BYTES + 1024;  // slack for manual 1024-byte alignment
 constexpr int TMEM_COLS = 512;
-constexpr int NUM_THREADS = 256;
-constexpr int EPI_THREADS = 128;
+constexpr int NUM_THREADS = 384;
+constexpr int EPI_THREADS = 256;
 
 static_assert(SMEM_ALLOC <= 232448, "exceeds the 227 KiB per-CTA shared memory limit");
 
@@ -159,11 +160,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else if (warp >= 4) {
     // ------------------------------ epilogue ------------------------------
-    const int ew = warp - 4;          // == warp % 4: the TMEM lane quarter this warp may read
-    const int row = ew * 32 + lane;   // accumulator row owned by this thread
+    // 8 warps: warp w may read TMEM lanes 32*(w%4)..+31; the two warps sharing a lane quarter split
+    // every column chunk in halves, so each accumulator row is drained by two threads.
+    const int ew = warp & 3;                  // TMEM lane quarter
+    const int cg = (warp - 4) >> 2;           // column half handled by this warp (0 / 1)
+    const int row = ew * 32 + lane;           // accumulator row owned by this thread
     const bool leader = (threadIdx.x == NUM_THREADS - EPI_THREADS);
     const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(ew * 32) << 16);
-    constexpr int CHUNK_COLS = (EPI == EPI_F32_ADD) ? 32 : 64;
+    constexpr int CHUNK_COLS = (EPI == EPI_F32_ADD) ? 32 : 64;  // 128 bytes of output per row
+    constexpr int TCOLS = CHUNK_COLS / 2;                       // columns per thread per chunk
     constexpr int NCHUNK = BLOCK_N / CHUNK_COLS;
     uint32_t it = 0;
     uint32_t nstore = 0;  // staging-buffer ring position (EPI with a single output)
@@ -192,111 +197,129 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           ++nstore;
         }
         named_bar_sync(1, EPI_THREADS);
-#pragma unroll
-        for (int half = 0; half < CHUNK_COLS / 32; ++half) {
-          uint32_t v[32];
-          tmem_ld_32x32(lane_base + as * BLOCK_N + c * CHUNK_COLS + half * 32, v);
-          tmem_wait_ld();
-          if (c == NCHUNK - 1 && half == CHUNK_COLS / 32 - 1) {
-            // accumulator fully drained into registers: hand the TMEM stage back to the MMA warp
-            tc_fence_before();
-            mbar_arrive(&bar_tempty[as]);
-          }
-          const int n = n0 + c * CHUNK_COLS + half * 32;
-          float f[32];
-#pragma unroll
-          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
-
-          if (EPI == EPI_F32_ADD) {
-#pragma unroll
-            for (int q = 0; q < 8; ++q) {
-              float4 o = make_float4(f[4 * q], f[4 * q + 1], f[4 * q + 2], f[4 * q + 3]);
-              *reinterpret_cast<float4*>(stage0 + row * 128 + ((q ^ (row & 7)) << 4)) = o;
-            }
+        float f[TCOLS];
+        {
+          uint32_t v[TCOLS];
+          const uint32_t taddr = lane_base + as * BLOCK_N + c * CHUNK_COLS + cg * TCOLS;
+          if (TCOLS == 32) {
+            tmem_ld_32x32(taddr, reinterpret_cast<uint32_t(&)[32]>(v));
           } else {
-            if (EPI != EPI_GELU_BWD && args.bias != nullptr && n < args.N) {
-              const float4* bp = reinterpret_cast<const float4*>(args.bias + n);
+            tmem_ld_32x16(taddr, reinterpret_cast<uint32_t(&)[16]>(v));
+          }
+          tmem_wait_ld();
 #pragma unroll
-              for (int q = 0; q < 8; ++q) {
-                const float4 b = __ldg(bp + q);
-                f[4 * q] += b.x;
-                f[4 * q + 1] += b.y;
-                f[4 * q + 2] += b.z;
-                f[4 * q + 3] += b.w;
+          for (int i = 0; i < TCOLS; ++i) f[i] = __uint_as_float(v[i]);
+        }
+        if (c == NCHUNK - 1) {
+          // accumulator fully drained into registers: hand the TMEM stage back to the MMA warp
+          tc_fence_before();
+          mbar_arrive(&bar_tempty[as]);
+        }
+        const int n = n0 + c * CHUNK_COLS + cg * TCOLS;
+
+        if (EPI == EPI_F32_ADD) {
+#pragma unroll
+          for (int q = 0; q < TCOLS / 4; ++q) {
+            float4 o = make_float4(f[4 * q], f[4 * q + 1], f[4 * q + 2], f[4 * q + 3]);
+            const int j = cg * (TCOLS / 4) + q;
+            *reinterpret_cast<float4*>(stage0 + row * 128 + ((j ^ (row & 7)) << 4)) = o;
+          }
+        } else {
+          if (EPI != EPI_GELU_BWD && args.bias != nullptr && n < args.N) {
+            const float4* bp = reinterpret_cast<const float4*>(args.bias + n);
+#pragma unroll
+            for (int q = 0; q < TCOLS / 4; ++q) {
+              const float4 b = __ldg(bp + q);
+              f[4 * q] += b.x;
+              f[4 * q + 1] += b.y;
+              f[4 * q + 2] += b.z;
+              f[4 * q + 3] += b.w;
+            }
+          }
+          if (EPI == EPI_LINEAR) {
+            if (args.drop.thresh != 0u) {
+              const uint32_t base_idx = static_cast<uint32_t>(m) * static_cast<uint32_t>(args.N) +
+                                        static_cast<uint32_t>(n);  // even: N and n are even
+#pragma unroll
+              for (int i = 0; i < TCOLS; i += 2) {
+                bool k0, k1;
+                drop_keep2(args.drop, base_idx + i, k0, k1);
+                f[i] = k0 ? f[i] * args.drop.scale : 0.0f;
+                f[i + 1] = k1 ? f[i + 1] * args.drop.scale : 0.0f;
               }
             }
-            if (EPI == EPI_LINEAR) {
-              if (args.drop.thresh != 0u) {
-                const uint32_t base_idx = static_cast<uint32_t>(m) * static_cast<uint32_t>(args.N) +
-                                          static_cast<uint32_t>(n);
+            if (args.residual != nullptr && row_ok && n < args.N) {
+              const uint4* rp =
+                  reinterpret_cast<const uint4*>(args.residual + static_cast<size_t>(m) * args.ld_res + n);
 #pragma unroll
-                for (int i = 0; i < 32; ++i)
-                  f[i] = drop_keep(args.drop, base_idx + i) ? f[i] * args.drop.scale : 0.0f;
-              }
-              if (args.residual != nullptr && row_ok && n < args.N) {
-                const uint4* rp =
-                    reinterpret_cast<const uint4*>(args.residual + static_cast<size_t>(m) * args.ld_res + n);
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  const uint4 r = __ldg(rp + q);
-                  const float2 r0 = unpack_bf16x2(r.x), r1 = unpack_bf16x2(r.y);
-                  const float2 r2 = unpack_bf16x2(r.z), r3 = unpack_bf16x2(r.w);
-                  f[8 * q] += r0.x;
-                  f[8 * q + 1] += r0.y;
-                  f[8 * q + 2] += r1.x;
-                  f[8 * q + 3] += r1.y;
-                  f[8 * q + 4] += r2.x;
-                  f[8 * q + 5] += r2.y;
-                  f[8 * q + 6] += r3.x;
-                  f[8 * q + 7] += r3.y;
-                }
+              for (int q = 0; q < TCOLS / 8; ++q) {
+                const uint4 r = __ldg(rp + q);
+                const float2 r0 = unpack_bf16x2(r.x), r1 = unpack_bf16x2(r.y);
+                const float2 r2 = unpack_bf16x2(r.z), r3 = unpack_bf16x2(r.w);
+                f[8 * q] += r0.x;
+                f[8 * q + 1] += r0.y;
+                f[8 * q + 2] += r1.x;
+                f[8 * q + 3] += r1.y;
+                f[8 * q + 4] += r2.x;
+                f[8 * q + 5] += r2.y;
+                f[8 * q + 6] += r3.x;
+                f[8 * q + 7] += r3.y;
               }
             }
-            if (EPI == EPI_GELU_BWD) {
-              if (row_ok && n < args.N) {
-                const uint4* up =
-                    reinterpret_cast<const uint4*>(args.aux + static_cast<size_t>(m) * args.ld_aux + n);
+          }
+          if (EPI == EPI_GELU_BWD) {
+            // aux holds gelu'(pre-activation), written by the forward GEMM's epilogue
+            if (row_ok && n < args.N) {
+              const uint4* up =
+                  reinterpret_cast<const uint4*>(args.aux + static_cast<size_t>(m) * args.ld_aux + n);
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  const uint4 r = __ldg(up + q);
-                  const float2 u0 = unpack_bf16x2(r.x), u1 = unpack_bf16x2(r.y);
-                  const float2 u2 = unpack_bf16x2(r.z), u3 = unpack_bf16x2(r.w);
-                  f[8 * q] *= gelu_erf_grad(u0.x);
-                  f[8 * q + 1] *= gelu_erf_grad(u0.y);
-                  f[8 * q + 2] *= gelu_erf_grad(u1.x);
-                  f[8 * q + 3] *= gelu_erf_grad(u1.y);
-                  f[8 * q + 4] *= gelu_erf_grad(u2.x);
-                  f[8 * q + 5] *= gelu_erf_grad(u2.y);
-                  f[8 * q + 6] *= gelu_erf_grad(u3.x);
-                  f[8 * q + 7] *= gelu_erf_grad(u3.y);
-                }
+              for (int q = 0; q < TCOLS / 8; ++q) {
+                const uint4 r = __ldg(up + q);
+                const float2 u0 = unpack_bf16x2(r.x), u1 = unpack_bf16x2(r.y);
+                const float2 u2 = unpack_bf16x2(r.z), u3 = unpack_bf16x2(r.w);
+                f[8 * q] *= u0.x;
+                f[8 * q + 1] *= u0.y;
+                f[8 * q + 2] *= u1.x;
+                f[8 * q + 3] *= u1.y;
+                f[8 * q + 4] *= u2.x;
+                f[8 * q + 5] *= u2.y;
+                f[8 * q + 6] *= u3.x;
+                f[8 * q + 7] *= u3.y;
               }
             }
-            // bf16 pack: 32 values = 4 x 16 B, swizzled like the TMA store expects (SWIZZLE_128B)
+          }
+          if (EPI == EPI_GELU_FWD) {
+            // one evaluation of the shared core gives the activation (second output) and its
+            // derivative (first output, consumed by the dgrad epilogue instead of recomputing it)
+            float gv[TCOLS];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
+            for (int i = 0; i < TCOLS; ++i) {
+              float g, dg;
+              gelu_and_grad(f[i], g, dg);
+              gv[i] = g;
+              f[i] = dg;
+            }
+#pragma unroll
+            for (int q = 0; q < TCOLS / 8; ++q) {
               uint4 o;
-              o.x = pack_bf16x2(f[8 * q], f[8 * q + 1]);
-              o.y = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
-              o.z = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]);
-              o.w = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
-              const int j = half * 4 + q;
-              *reinterpret_cast<uint4*>(stage0 + row * 128 + ((j ^ (row & 7)) << 4)) = o;
+              o.x = pack_bf16x2(gv[8 * q], gv[8 * q + 1]);
+              o.y = pack_bf16x2(gv[8 * q + 2], gv[8 * q + 3]);
+              o.z = pack_bf16x2(gv[8 * q + 4], gv[8 * q + 5]);
+              o.w = pack_bf16x2(gv[8 * q + 6], gv[8 * q + 7]);
+              const int j = cg * (TCOLS / 8) + q;
+              *reinterpret_cast<uint4*>(stage1 + row * 128 + ((j ^ (row & 7)) << 4)) = o;
             }
-            if (EPI == EPI_GELU_FWD) {
-              // the reference applies GELU to the bf16-rounded pre-activation under autocast;
-              // here it is applied to the fp32 value, which is the more accurate of the two.
+          }
+          // bf16 pack, swizzled like the TMA store expects (SWIZZLE_128B)
 #pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                uint4 o;
-                o.x = pack_bf16x2(gelu_erf(f[8 * q]), gelu_erf(f[8 * q + 1]));
-                o.y = pack_bf16x2(gelu_erf(f[8 * q + 2]), gelu_erf(f[8 * q + 3]));
-                o.z = pack_bf16x2(gelu_erf(f[8 * q + 4]), gelu_erf(f[8 * q + 5]));
-                o.w = pack_bf16x2(gelu_erf(f[8 * q + 6]), gelu_erf(f[8 * q + 7]));
-                const int j = half * 4 + q;
-                *reinterpret_cast<uint4*>(stage1 + row * 128 + ((j ^ (row & 7)) << 4)) = o;
-              }
-            }
+          for (int q = 0; q < TCOLS / 8; ++q) {
+            uint4 o;
+            o.x = pack_bf16x2(f[8 * q], f[8 * q + 1]);
+            o.y = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
+            o.z = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]);
+            o.w = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
+            const int j = cg * (TCOLS / 8) + q;
+            *reinterpret_cast<uint4*>(stage0 + row * 128 + ((j ^ (row & 7)) << 4)) = o;
           }
         }
         fence_proxy_async_smem();

@@ -18,8 +18,8 @@ namespace bqa {
 
 enum GemmEpilogue : int {
   EPI_LINEAR = 0,    // C = dropout(acc + bias) + residual   (each part optional)   -> bf16
-  EPI_GELU_FWD = 1,  // C = acc + bias (pre-activation), C2 = gelu_erf(C)           -> bf16 x2
-  EPI_GELU_BWD = 2,  // C = acc * gelu_erf'(aux)                                     -> bf16
+  EPI_GELU_FWD = 1,  // u = acc + bias: C = gelu_erf'(u), C2 = gelu_erf(u)             -> bf16 x2
+  EPI_GELU_BWD = 2,  // C = acc * aux, aux = the C of EPI_GELU_FWD (gelu')            -> bf16
   EPI_F32_ADD = 3,   // C += acc  (TMA reduce-add, supports split-K)                 -> fp32
 };
 
@@ -38,7 +38,7 @@ struct GemmProblem {
   const float* bias;     // [N] fp32 or null
   const void* residual;  // bf16 [M][ld_res] or null   (EPI_LINEAR)
   int ld_res;
-  const void* aux;  // bf16 [M][ld_aux]                 (EPI_GELU_BWD)
+  const void* aux;  // bf16 [M][ld_aux], gelu'(u)       (EPI_GELU_BWD)
   int ld_aux;
   int k_splits;  // >= 1; > 1 only with EPI_F32_ADD
   DropKey drop;  // thresh == 0 -> no dropout           (EPI_LINEAR)

@@ -69,6 +69,28 @@ __device__ __forceinline__ void load_vec_f32(const float* __restrict__ p, int H,
   }
 }
 
+struct RawRow {
+  uint4 u[MAXV];
+};
+
+__device__ __forceinline__ void load_raw(const bf16* __restrict__ row, int H, int lane, RawRow& r) {
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    const int c = (j * 32 + lane) * 8;
+    r.u[j] = c < H ? __ldg(reinterpret_cast<const uint4*>(row + c)) : make_uint4(0u, 0u, 0u, 0u);
+  }
+}
+
+__device__ __forceinline__ void unpack_raw(const RawRow& raw, RowVec& r) {
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    const float2 a = unpack_bf16x2(raw.u[j].x), b = unpack_bf16x2(raw.u[j].y);
+    const float2 c = unpack_bf16x2(raw.u[j].z), d = unpack_bf16x2(raw.u[j].w);
+    r.v[j][0] = a.x; r.v[j][1] = a.y; r.v[j][2] = b.x; r.v[j][3] = b.y;
+    r.v[j][4] = c.x; r.v[j][5] = c.y; r.v[j][6] = d.x; r.v[j][7] = d.y;
+  }
+}
+
 // round a register row to bf16 precision in place (what a later kernel will read back)
 __device__ __forceinline__ void round_row_bf16(RowVec& r) {
 #pragma unroll
@@ -175,102 +197,180 @@ embed_ln_fwd_kernel(const int64_t* __restrict__ ids, const int64_t* __restrict__
 //   drop_in : dy is first multiplied by the keep mask of a dropout applied AFTER this LN (embeddings)
 //   drop_out: additionally emits dz * keep-mask (gradient of the GEMM output that was dropped
 //             BEFORE the residual add) and accumulates its column sums into dbias
-// Rows are distributed round-robin over a persistent grid; per-warp column partials live in
-// registers and are reduced once per block (smem) then once per grid (atomicAdd).
+// Rows are distributed round-robin over a persistent grid.  NV = 16-byte vectors per lane
+// (H <= 256 NV).  To keep the register count low enough for ~20 resident warps per SM the
+// per-warp column partials and gamma live in shared memory; the loads of the next row are issued
+// before the current row is reduced (software pipeline), partials are reduced once per block and
+// once per grid (atomicAdd).
+template <int NV>
 __global__ void __launch_bounds__(ROW_WARPS * 32)
 ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const float* __restrict__ gamma,
               bf16* __restrict__ dz, bf16* __restrict__ dz_masked, float* __restrict__ dgamma,
               float* __restrict__ dbeta, float* __restrict__ dbias, int T, int H, float eps, DropKey drop_in,
               DropKey drop_out) {
-  __shared__ float red[ROW_WARPS][MAXV * 32 * 8 + 8];
+  extern __shared__ float ln_smem[];
+  constexpr int W = NV * 256;           // padded row width
+  float* s_gamma = ln_smem;             // [W]
+  float* s_acc = ln_smem + W;           // [ROW_WARPS][3][W]
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
-  RowVec g;
-  load_vec_f32(gamma, H, lane, g);
-  RowVec acc_g, acc_b, acc_bias;
-#pragma unroll
-  for (int j = 0; j < MAXV; ++j)
-#pragma unroll
-    for (int i = 0; i < 8; ++i) acc_g.v[j][i] = acc_b.v[j][i] = acc_bias.v[j][i] = 0.0f;
+  for (int c = threadIdx.x; c < W; c += blockDim.x) s_gamma[c] = c < H ? gamma[c] : 0.0f;
+  for (int c = threadIdx.x; c < ROW_WARPS * 3 * W; c += blockDim.x) s_acc[c] = 0.0f;
+  __syncthreads();
+  float* acc_g = s_acc + (warp * 3 + 0) * W;
+  float* acc_b = s_acc + (warp * 3 + 1) * W;
+  float* acc_m = s_acc + (warp * 3 + 2) * W;
+  const float invH = 1.0f / static_cast<float>(H);
 
-  for (int row = blockIdx.x * ROW_WARPS + warp; row < T; row += gridDim.x * ROW_WARPS) {
-    RowVec x, d;
-    load_row_bf16(z + static_cast<size_t>(row) * H, H, lane, x);
-    load_row_bf16(dy + static_cast<size_t>(row) * H, H, lane, d);
-    float mean, rstd;
-    row_stats(x, H, lane, eps, mean, rstd);
-    float s1 = 0.0f, s2 = 0.0f;
+  const int row_stride = gridDim.x * ROW_WARPS;
+  int row = blockIdx.x * ROW_WARPS + warp;
+  uint4 nz[NV], nd[NV];
 #pragma unroll
-    for (int j = 0; j < MAXV; ++j) {
-      const int c = (j * 32 + lane) * 8;
-      if (c < H) {
+  for (int j = 0; j < NV; ++j) {
+    const int c = (j * 32 + lane) * 8;
+    const bool ok = row < T && c < H;
+    nz[j] = ok ? __ldg(reinterpret_cast<const uint4*>(z + static_cast<size_t>(row) * H + c)) : make_uint4(0, 0, 0, 0);
+    nd[j] = ok ? __ldg(reinterpret_cast<const uint4*>(dy + static_cast<size_t>(row) * H + c)) : make_uint4(0, 0, 0, 0);
+  }
+  for (; row < T; row += row_stride) {
+    float x[NV][8], d[NV][8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          float dyv = d.v[j][i];
-          if (drop_in.thresh != 0u)
-            dyv = drop_keep(drop_in, static_cast<uint32_t>(row) * H + c + i) ? dyv * drop_in.scale : 0.0f;
-          const float xhat = (x.v[j][i] - mean) * rstd;
-          const float dxhat = dyv * g.v[j][i];
-          acc_g.v[j][i] += dyv * xhat;
-          acc_b.v[j][i] += dyv;
-          s1 += dxhat;
-          s2 += dxhat * xhat;
-          x.v[j][i] = xhat;
-          d.v[j][i] = dxhat;
-        }
-      }
+    for (int j = 0; j < NV; ++j) {
+      const float2 a0 = unpack_bf16x2(nz[j].x), a1 = unpack_bf16x2(nz[j].y), a2 = unpack_bf16x2(nz[j].z),
+                   a3 = unpack_bf16x2(nz[j].w);
+      x[j][0] = a0.x; x[j][1] = a0.y; x[j][2] = a1.x; x[j][3] = a1.y;
+      x[j][4] = a2.x; x[j][5] = a2.y; x[j][6] = a3.x; x[j][7] = a3.y;
+      const float2 b0 = unpack_bf16x2(nd[j].x), b1 = unpack_bf16x2(nd[j].y), b2 = unpack_bf16x2(nd[j].z),
+                   b3 = unpack_bf16x2(nd[j].w);
+      d[j][0] = b0.x; d[j][1] = b0.y; d[j][2] = b1.x; d[j][3] = b1.y;
+      d[j][4] = b2.x; d[j][5] = b2.y; d[j][6] = b3.x; d[j][7] = b3.y;
     }
-    s1 = warp_sum(s1) / static_cast<float>(H);
-    s2 = warp_sum(s2) / static_cast<float>(H);
+    const int nrow = row + row_stride;
+    if (nrow < T) {
 #pragma unroll
-    for (int j = 0; j < MAXV; ++j)
-#pragma unroll
-      for (int i = 0; i < 8; ++i) d.v[j][i] = rstd * (d.v[j][i] - s1 - x.v[j][i] * s2);
-    store_row_bf16(dz + static_cast<size_t>(row) * H, H, lane, d);
-    if (dz_masked != nullptr) {
-      // what the GEMM-side consumers (dgrad, wgrad, bias grad) read is the bf16-rounded value
-      round_row_bf16(d);
-#pragma unroll
-      for (int j = 0; j < MAXV; ++j) {
+      for (int j = 0; j < NV; ++j) {
         const int c = (j * 32 + lane) * 8;
         if (c < H) {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            float m = d.v[j][i];
-            if (drop_out.thresh != 0u)
-              m = drop_keep(drop_out, static_cast<uint32_t>(row) * H + c + i) ? m * drop_out.scale : 0.0f;
-            d.v[j][i] = m;
-          }
+          nz[j] = __ldg(reinterpret_cast<const uint4*>(z + static_cast<size_t>(nrow) * H + c));
+          nd[j] = __ldg(reinterpret_cast<const uint4*>(dy + static_cast<size_t>(nrow) * H + c));
         }
       }
-      if (dz_masked != dz) store_row_bf16(dz_masked + static_cast<size_t>(row) * H, H, lane, d);
     }
-    if (dbias != nullptr) {
-      round_row_bf16(d);
+    // row statistics (biased two-pass variance, as torch)
+    float s = 0.0f;
 #pragma unroll
-      for (int j = 0; j < MAXV; ++j)
+    for (int j = 0; j < NV; ++j)
 #pragma unroll
-        for (int i = 0; i < 8; ++i) acc_bias.v[j][i] += d.v[j][i];
+      for (int i = 0; i < 8; ++i) s += x[j][i];
+    const float mean = warp_sum(s) * invH;
+    float qv = 0.0f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      if ((j * 32 + lane) * 8 < H) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float t = x[j][i] - mean;
+          qv += t * t;
+        }
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(qv) * invH + eps);
+    float s1 = 0.0f, s2 = 0.0f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int c = (j * 32 + lane) * 8;
+      if (c < H) {
+        float4 g0 = *reinterpret_cast<const float4*>(s_gamma + c), g1 = *reinterpret_cast<const float4*>(s_gamma + c + 4);
+        const float gv[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+        float4 ag0 = *reinterpret_cast<float4*>(acc_g + c), ag1 = *reinterpret_cast<float4*>(acc_g + c + 4);
+        float4 ab0 = *reinterpret_cast<float4*>(acc_b + c), ab1 = *reinterpret_cast<float4*>(acc_b + c + 4);
+        float* ag = reinterpret_cast<float*>(&ag0);
+        float* ab = reinterpret_cast<float*>(&ab0);
+        float agv[8] = {ag0.x, ag0.y, ag0.z, ag0.w, ag1.x, ag1.y, ag1.z, ag1.w};
+        float abv[8] = {ab0.x, ab0.y, ab0.z, ab0.w, ab1.x, ab1.y, ab1.z, ab1.w};
+        (void)ag; (void)ab;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float dyv = d[j][i];
+          if (drop_in.thresh != 0u)
+            dyv = drop_keep(drop_in, static_cast<uint32_t>(row) * H + c + i) ? dyv * drop_in.scale : 0.0f;
+          const float xhat = (x[j][i] - mean) * rstd;
+          const float dxhat = dyv * gv[i];
+          agv[i] += dyv * xhat;
+          abv[i] += dyv;
+          s1 += dxhat;
+          s2 += dxhat * xhat;
+          x[j][i] = xhat;
+          d[j][i] = dxhat;
+        }
+        *reinterpret_cast<float4*>(acc_g + c) = make_float4(agv[0], agv[1], agv[2], agv[3]);
+        *reinterpret_cast<float4*>(acc_g + c + 4) = make_float4(agv[4], agv[5], agv[6], agv[7]);
+        *reinterpret_cast<float4*>(acc_b + c) = make_float4(abv[0], abv[1], abv[2], abv[3]);
+        *reinterpret_cast<float4*>(acc_b + c + 4) = make_float4(abv[4], abv[5], abv[6], abv[7]);
+      }
+    }
+    s1 = warp_sum(s1) * invH;
+    s2 = warp_sum(s2) * invH;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int c = (j * 32 + lane) * 8;
+      if (c < H) {
+        uint32_t pk[4];
+#pragma unroll
+        for (int i = 0; i < 8; i += 2) {
+          const float v0 = rstd * (d[j][i] - s1 - x[j][i] * s2);
+          const float v1 = rstd * (d[j][i + 1] - s1 - x[j][i + 1] * s2);
+          pk[i >> 1] = pack_bf16x2(v0, v1);
+          // consumers on the GEMM side read the bf16-rounded value
+          const float2 rr = unpack_bf16x2(pk[i >> 1]);
+          d[j][i] = rr.x;
+          d[j][i + 1] = rr.y;
+        }
+        *reinterpret_cast<uint4*>(dz + static_cast<size_t>(row) * H + c) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        if (dz_masked != nullptr) {
+          if (drop_out.thresh != 0u) {
+            const uint32_t base = static_cast<uint32_t>(row) * H + c;  // even: H and c are multiples of 8
+#pragma unroll
+            for (int i = 0; i < 8; i += 2) {
+              bool k0, k1;
+              drop_keep2(drop_out, base + i, k0, k1);
+              d[j][i] = k0 ? d[j][i] * drop_out.scale : 0.0f;
+              d[j][i + 1] = k1 ? d[j][i + 1] * drop_out.scale : 0.0f;
+            }
+          }
+          uint32_t pm[4];
+#pragma unroll
+          for (int i = 0; i < 8; i += 2) {
+            pm[i >> 1] = pack_bf16x2(d[j][i], d[j][i + 1]);
+            const float2 rr = unpack_bf16x2(pm[i >> 1]);
+            d[j][i] = rr.x;
+            d[j][i + 1] = rr.y;
+          }
+          if (dz_masked != dz)
+            *reinterpret_cast<uint4*>(dz_masked + static_cast<size_t>(row) * H + c) = make_uint4(pm[0], pm[1], pm[2], pm[3]);
+        }
+        if (dbias != nullptr) {
+          float4 am0 = *reinterpret_cast<float4*>(acc_m + c), am1 = *reinterpret_cast<float4*>(acc_m + c + 4);
+          am0.x += d[j][0]; am0.y += d[j][1]; am0.z += d[j][2]; am0.w += d[j][3];
+          am1.x += d[j][4]; am1.y += d[j][5]; am1.z += d[j][6]; am1.w += d[j][7];
+          *reinterpret_cast<float4*>(acc_m + c) = am0;
+          *reinterpret_cast<float4*>(acc_m + c + 4) = am1;
+        }
+      }
     }
   }
-
-  // block reduction of the three column partials, one at a time through the same buffer
-  for (int which = 0; which < 3; ++which) {
-    float* out = which == 0 ? dgamma : (which == 1 ? dbeta : dbias);
-    if (out == nullptr) continue;  // uniform across the block
-    const RowVec& a = which == 0 ? acc_g : (which == 1 ? acc_b : acc_bias);
-    __syncthreads();
+  __syncthreads();
+  for (int c = threadIdx.x; c < H; c += blockDim.x) {
+    float sg = 0.0f, sb = 0.0f, sm = 0.0f;
 #pragma unroll
-    for (int j = 0; j < MAXV; ++j)
-#pragma unroll
-      for (int i = 0; i < 8; ++i) red[warp][(j * 32 + lane) * 8 + i] = a.v[j][i];
-    __syncthreads();
-    for (int c = threadIdx.x; c < H; c += blockDim.x) {
-      float s = 0.0f;
-#pragma unroll
-      for (int w = 0; w < ROW_WARPS; ++w) s += red[w][c];
-      atomicAdd(out + c, s);
+    for (int w = 0; w < ROW_WARPS; ++w) {
+      sg += s_acc[(w * 3 + 0) * W + c];
+      sb += s_acc[(w * 3 + 1) * W + c];
+      sm += s_acc[(w * 3 + 2) * W + c];
     }
+    if (dgamma != nullptr) atomicAdd(dgamma + c, sg);
+    if (dbeta != nullptr) atomicAdd(dbeta + c, sb);
+    if (dbias != nullptr) atomicAdd(dbias + c, sm);
   }
 }
 
@@ -303,32 +403,61 @@ colsum_kernel(const bf16* __restrict__ X, int ld, float* __restrict__ out, int T
 // Embedding gradient: dword[ids[t]] += dz0[t], dpos[t % S] += dz0[t], dtype[tt[t]] += dz0[t].
 // The word table is nn.Embedding(..., padding_idx=pad_token_id) in BertEmbeddings
 // (modeling_bert.py:59): the padding row receives no gradient.
+//   word rows : one warp per token, fp32 atomics (rows are mostly distinct; [CLS]/[SEP] collide B-fold)
+//   pos/type  : one block per position s sums its B rows in registers: dpos[s] has a single writer
+//               (no atomics), the two type rows get one atomic per block and column instead of one
+//               per token and column (T-way contention on two rows was 1.1 ms per step).
 __global__ void __launch_bounds__(ROW_WARPS * 32)
-embed_bwd_kernel(const bf16* __restrict__ dz0, const int64_t* __restrict__ ids, const int64_t* __restrict__ token_type,
-                 float* __restrict__ dword, float* __restrict__ dpos, float* __restrict__ dtype, int T, int S,
-                 int H, int pad_id) {
+embed_word_bwd_kernel(const bf16* __restrict__ dz0, const int64_t* __restrict__ ids, float* __restrict__ dword,
+                      int T, int H, int pad_id) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * ROW_WARPS + (threadIdx.x >> 5);
   if (row >= T) return;
+  const long long id = ids[row];
+  if (id == pad_id) return;
   RowVec d;
   load_row_bf16(dz0 + static_cast<size_t>(row) * H, H, lane, d);
-  const long long id = ids[row];
-  const long long tt = token_type != nullptr ? token_type[row] : 0;
   float* w = dword + static_cast<size_t>(id) * H;
-  float* p = dpos + static_cast<size_t>(row % S) * H;
-  float* t = dtype + static_cast<size_t>(tt) * H;
 #pragma unroll
   for (int j = 0; j < MAXV; ++j) {
     const int c = (j * 32 + lane) * 8;
     if (c < H) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        if (id != pad_id) atomicAdd(w + c + i, d.v[j][i]);
-        atomicAdd(p + c + i, d.v[j][i]);
-        atomicAdd(t + c + i, d.v[j][i]);
-      }
+      for (int i = 0; i < 8; ++i) atomicAdd(w + c + i, d.v[j][i]);
     }
   }
+}
+
+__global__ void __launch_bounds__(128)
+embed_pos_type_bwd_kernel(const bf16* __restrict__ dz0, const int64_t* __restrict__ token_type,
+                          float* __restrict__ dpos, float* __restrict__ dtype, int B, int S, int H) {
+  const int s = blockIdx.x;
+  const int c = threadIdx.x * 8;  // H <= 1024 -> one 16-byte vector per thread
+  if (c >= H) return;
+  float acc[2][8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[0][i] = acc[1][i] = 0.0f;
+  bool any[2] = {false, false};
+  for (int b = 0; b < B; ++b) {
+    const size_t row = static_cast<size_t>(b) * S + s;
+    const int tt = token_type != nullptr ? static_cast<int>(token_type[row]) & 1 : 0;
+    const uint4 u = __ldg(reinterpret_cast<const uint4*>(dz0 + row * H + c));
+    const float2 a = unpack_bf16x2(u.x), bb = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+    const float v[8] = {a.x, a.y, bb.x, bb.y, cc.x, cc.y, d.x, d.y};
+    any[tt] = true;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (tt) acc[1][i] += v[i]; else acc[0][i] += v[i];
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) dpos[static_cast<size_t>(s) * H + c + i] += acc[0][i] + acc[1][i];
+#pragma unroll
+  for (int t = 0; t < 2; ++t)
+    if (any[t]) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) atomicAdd(dtype + static_cast<size_t>(t) * H + c + i, acc[t][i]);
+    }
 }
 
 }  // namespace
@@ -364,10 +493,28 @@ int launch_ln_bwd(const bf16* dy, const bf16* z, const float* gamma, bf16* dz, b
     set_error("layernorm backward: H=%d must be a multiple of 8 and <= %d", H, MAXV * 256);
     return 1;
   }
+  const int nv = (H + 255) / 256;
+  const size_t smem = static_cast<size_t>(nv) * 256 * (1 + 3 * ROW_WARPS) * sizeof(float);
   int grid = num_sms * 4;
   if (grid > row_blocks(T)) grid = row_blocks(T);
-  ln_bwd_kernel<<<grid, ROW_WARPS * 32, 0, st>>>(dy, z, gamma, dz, dz_masked, dgamma, dbeta, dbias, T, H, eps,
-                                                 drop_in, drop_out);
+#define BQA_LN_BWD(NV)                                                                                         \
+  {                                                                                                            \
+    static bool configured = false;                                                                            \
+    if (!configured) {                                                                                         \
+      BQA_CUDA_CHECK(cudaFuncSetAttribute(ln_bwd_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
+                                          static_cast<int>(smem)));                                            \
+      configured = true;                                                                                       \
+    }                                                                                                          \
+    ln_bwd_kernel<NV><<<grid, ROW_WARPS * 32, smem, st>>>(dy, z, gamma, dz, dz_masked, dgamma, dbeta, dbias, T, H, \
+                                                          eps, drop_in, drop_out);                             \
+  }
+  switch (nv) {
+    case 1: BQA_LN_BWD(1) break;
+    case 2: BQA_LN_BWD(2) break;
+    case 3: BQA_LN_BWD(3) break;
+    default: BQA_LN_BWD(4) break;
+  }
+#undef BQA_LN_BWD
   return check_launch("ln_bwd");
 }
 
@@ -387,9 +534,14 @@ int launch_colsum(const bf16* X, int ld, float* out, int T, int N, int num_sms, 
 
 int launch_embed_bwd(const bf16* dz0, const int64_t* ids, const int64_t* token_type, float* dword, float* dpos,
                      float* dtype, int T, int S, int H, int pad_id, cudaStream_t st) {
-  embed_bwd_kernel<<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(dz0, ids, token_type, dword, dpos, dtype, T, S, H,
-                                                             pad_id);
-  return check_launch("embed_bwd");
+  if (H % 8 != 0 || H > 1024) {
+    set_error("embedding backward: H=%d must be a multiple of 8 and <= 1024", H);
+    return 1;
+  }
+  embed_word_bwd_kernel<<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(dz0, ids, dword, T, H, pad_id);
+  if (check_launch("embed_word_bwd")) return 1;
+  embed_pos_type_bwd_kernel<<<S, 128, 0, st>>>(dz0, token_type, dpos, dtype, T / S, S, H);
+  return check_launch("embed_pos_type_bwd");
 }
 
 }  // namespace bqa

@@ -125,6 +125,7 @@ class FusedAdamW(torch.optim.Optimizer):
             self.state[p]['step'] += 1
         self._max_grad_norm = 0.0
         self._grads_clean = True
+        self._model.grads_dirty = False  # the kernel zeroed the flat gradient buffer
         self._model.mark_weights_synced()
 
     def zero_grad(self, set_to_none=False):

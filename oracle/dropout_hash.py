@@ -36,11 +36,13 @@ def _mix32(x):
 
 
 def keep_mask(seed, site, p, numel, device="cpu", start=0):
-    """Boolean keep decisions for element indices [start, start+numel)."""
+    """Boolean keep decisions for element indices [start, start+numel): one 32-bit hash per PAIR
+    of consecutive indices, low 16 bits for the even element, high 16 bits for the odd one."""
     if p <= 0:
         return torch.ones(numel, dtype=torch.bool, device=device)
     k0, k1 = drop_key(seed, site)
-    thresh = int(round(p * 16777216.0))
+    thresh = min(int(round(p * 65536.0)), 65535)
     idx = torch.arange(start, start + numel, dtype=torch.int64, device=device) & _M32
-    h = _mix32(_mix32((idx + k0) & _M32) ^ k1)
-    return (h >> 8) >= thresh
+    h = _mix32(((idx >> 1) * 0x9E3779B1 + k0) & _M32) ^ k1
+    r = torch.where((idx & 1) == 1, h >> 16, h & 0xFFFF)
+    return r >= thresh

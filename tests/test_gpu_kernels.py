@@ -61,9 +61,7 @@ def test_gemm_variants(pkg, M, N, K, mode, ex):
         C, C2, epi = torch.empty(M, N, device=DEV, dtype=torch.bfloat16), torch.empty(M, N, device=DEV, dtype=torch.bfloat16), L.EPI_GELU_FWD
     elif mode == "nn_gelu_bwd":
         aux = rnd(M, N, scale=1.0)
-        u = aux.float().requires_grad_(True)
-        torch.nn.functional.gelu(u).sum().backward()
-        ref = ref * u.grad
+        ref = ref * aux.float()
         C, epi = torch.empty(M, N, device=DEV, dtype=torch.bfloat16), L.EPI_GELU_BWD
     elif mode == "nt":
         C = torch.randn(M, N, device=DEV)
@@ -81,9 +79,14 @@ def test_gemm_variants(pkg, M, N, K, mode, ex):
     torch.cuda.synchronize()
     scale = ref.abs().max().item()
     tol = 1e-5 * scale + 1e-3 if epi == L.EPI_F32_ADD else 8e-3 * scale  # bf16 output: 2^-8 of the largest value
-    assert (C.float() - ref).abs().max().item() <= tol
-    if C2 is not None:
-        assert (C2.float() - torch.nn.functional.gelu(ref)).abs().max().item() <= tol
+    if C2 is None:
+        assert (C.float() - ref).abs().max().item() <= tol
+    if C2 is not None:  # C holds gelu'(u), C2 gelu(u) for u = ref
+        u = ref.clone().requires_grad_(True)
+        g = torch.nn.functional.gelu(u)
+        g.sum().backward()
+        assert (C2.float() - g.detach()).abs().max().item() <= tol
+        assert (C.float() - u.grad).abs().max().item() <= 8e-3
 
 
 def test_gemm_linearity_at_full_size(pkg):
@@ -118,8 +121,9 @@ def test_attention_forward_backward(pkg, B, S, A, p, use_mask):
     m8 = mask.to(torch.uint8).contiguous() if mask is not None else None
     ctx = torch.zeros(B, S, H, device=DEV, dtype=torch.bfloat16)
     lse2 = torch.zeros(B, A, S, device=DEV)
+    keep_bits = torch.zeros(B, A, S, L.lib.bqa_attention_keep_words(S), dtype=torch.int32, device=DEV)
     st = L.current_stream_ptr()
-    L.check(L.lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), L.ptr(m8), B, S, A, p, 77, 5,
+    L.check(L.lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep_bits.data_ptr(), L.ptr(m8), B, S, A, p, 77, 5,
                                         st), "attention forward")
     x = qkv.float().requires_grad_(True)
     q, k, v = [t.view(B, S, A, 64).transpose(1, 2) for t in x.split(H, dim=-1)]
@@ -137,7 +141,7 @@ def test_attention_forward_backward(pkg, B, S, A, p, use_mask):
     o.backward(dctx.float())
     dqkv = torch.zeros(B, S, 3 * H, device=DEV, dtype=torch.bfloat16)
     dsum = torch.zeros(B, A, S, device=DEV)
-    L.check(L.lib.bqa_attention_backward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), dctx.data_ptr(),
+    L.check(L.lib.bqa_attention_backward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep_bits.data_ptr(), dctx.data_ptr(),
                                          dqkv.data_ptr(), dsum.data_ptr(), L.ptr(m8), B, S, A, p, 77, 5, st),
             "attention backward")
     torch.cuda.synchronize()
@@ -158,7 +162,8 @@ def test_attention_rows_sum_to_one_at_full_size(pkg):
     qkv[..., 2 * H:] = 1.0
     ctx = torch.zeros(B, S, H, device=DEV, dtype=torch.bfloat16)
     lse2 = torch.zeros(B, A, S, device=DEV)
-    L.check(L.lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), None, B, S, A, 0.0, 0, 0,
+    keep_bits = torch.zeros(B, A, S, L.lib.bqa_attention_keep_words(S), dtype=torch.int32, device=DEV)
+    L.check(L.lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep_bits.data_ptr(), None, B, S, A, 0.0, 0, 0,
                                         L.current_stream_ptr()), "attention forward")
     torch.cuda.synchronize()
     assert (ctx.float() - 1.0).abs().max().item() < 1e-2
@@ -235,7 +240,7 @@ def test_optimizer_kernels_match_oracle(pkg):
     from oracle import bertqa_oracle as O
     L = pkg._lib
     torch.manual_seed(4)
-    n = 3 * 65536 + 1000
+    n = 4 * 65536 + 1000
     p, g = torch.randn(n, device=DEV), torch.randn(n, device=DEV) * 3
     m, v = torch.randn(n, device=DEV) * 0.1, torch.rand(n, device=DEV) * 0.1
     P = {"w.weight": p[:200000].clone(), "w.bias": p[200000:].clone()}

@@ -37,9 +37,10 @@ def attn_case(B, S, A, p, use_mask, bwd=True):
         mask = (torch.arange(S, device=dev)[None, :] < lens[:, None])
     ctx = torch.zeros(B, S, H, device=dev, dtype=torch.bfloat16)
     lse2 = torch.zeros(B, A, S, device=dev)
+    keep_bits = torch.zeros(B, A, S, L.lib.bqa_attention_keep_words(S), dtype=torch.int32, device=dev)
     st = L.current_stream_ptr()
     m8 = mask.to(torch.uint8).contiguous() if mask is not None else None
-    L.check(L.lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), L.ptr(m8), B, S, A, p, 77, 5,
+    L.check(L.lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep_bits.data_ptr(), L.ptr(m8), B, S, A, p, 77, 5,
                                         st), "attn fwd")
     torch.cuda.synchronize()
     # reference
@@ -61,7 +62,7 @@ def attn_case(B, S, A, p, use_mask, bwd=True):
         o.backward(dctx.float())
         dqkv = torch.zeros(B, S, 3 * H, device=dev, dtype=torch.bfloat16)
         dsum = torch.zeros(B, A, S, device=dev)
-        L.check(L.lib.bqa_attention_backward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), dctx.data_ptr(),
+        L.check(L.lib.bqa_attention_backward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep_bits.data_ptr(), dctx.data_ptr(),
                                              dqkv.data_ptr(), dsum.data_ptr(), L.ptr(m8), B, S, A, p, 77, 5, st),
                 "attn bwd")
         torch.cuda.synchronize()
