@@ -6,7 +6,7 @@
 // and their autograd backward (reference trainer.py:197-204).
 //
 // CTA = 384 threads, one CTA per SM, static round-robin tile schedule:
-//   warp 0 (1 thread)  TMA producer: 4-stage ring of {A 128x64, B 256x64} bf16 tiles, 128B swizzle
+//   warp 0 (1 thread)  TMA producer: 3-stage ring of {A 128x64, B 256x64} bf16 tiles, 128B swizzle
 //   warp 1 (1 thread)  MMA issuer  : tcgen05.mma cta_group::1 kind::f16, M=128 N=256 K=16, fp32 in TMEM
 //   warp 2             TMEM allocator (512 columns = two 128x256 fp32 accumulators, double-buffered)
 //   warps 4-11         epilogue    : tcgen05.ld -> registers -> fused op -> swizzled smem -> TMA store
@@ -26,12 +26,16 @@ namespace {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_N = 256;
 constexpr int BLOCK_K = 64;
-constexpr int STAGES = 4;
+#ifndef BQA_GEMM_STAGES
+#define BQA_GEMM_STAGES 3
+#endif
+constexpr int STAGES = BQA_GEMM_STAGES;                // TMA -> MMA ring depth
+constexpr int CSTAGES = STAGES == 3 ? 4 : 2;          // epilogue staging buffers (TMA store ring)
 constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KiB
 constexpr int B_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;  // 32 KiB
 constexpr int C_STAGE_BYTES = BLOCK_M * 128;          // 128 rows x 128 B (64 bf16 or 32 fp32)
 constexpr int SMEM_BARRIER_BYTES = 256;
-constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + 2 * C_STAGE_BYTES + SMEM_BARRIER_BYTES;
+constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + CSTAGES * C_STAGE_BYTES + SMEM_BARRIER_BYTES;
 constexpr int SMEM_ALLOC = SMEM_BYTES + 1024;  // slack for manual 1024-byte alignment
 constexpr int TMEM_COLS = 512;
 constexpr int NUM_THREADS = 384;
@@ -49,7 +53,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint8_t* sA = smem;
   uint8_t* sB = sA + STAGES * A_STAGE_BYTES;
   uint8_t* sC = sB + STAGES * B_STAGE_BYTES;
-  uint64_t* bar_full = reinterpret_cast<uint64_t*>(sC + 2 * C_STAGE_BYTES);
+  uint64_t* bar_full = reinterpret_cast<uint64_t*>(sC + CSTAGES * C_STAGE_BYTES);
   uint64_t* bar_empty = bar_full + STAGES;
   uint64_t* bar_tfull = bar_empty + STAGES;
   uint64_t* bar_tempty = bar_tfull + 2;
@@ -185,16 +189,35 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const bool row_ok = m < args.M;
 #pragma unroll 1
       for (int c = 0; c < NCHUNK; ++c) {
+        // staging ring: a buffer (pair of buffers for the two-output epilogue) is reused only after the
+        // TMA store that read it has drained
         uint8_t* stage0;
         uint8_t* stage1 = nullptr;
         if (EPI == EPI_GELU_FWD) {
-          if (leader) tma_wait_group_read<0>();
-          stage0 = sC;
-          stage1 = sC + C_STAGE_BYTES;
-        } else {
-          if (leader) tma_wait_group_read<1>();
-          stage0 = sC + (nstore & 1u) * C_STAGE_BYTES;
+          constexpr int PAIRS = CSTAGES / 2;
+          if (leader) tma_wait_group_read<PAIRS - 1>();
+          stage0 = sC + (nstore % PAIRS) * 2 * C_STAGE_BYTES;
+          stage1 = stage0 + C_STAGE_BYTES;
           ++nstore;
+        } else {
+          if (leader) tma_wait_group_read<CSTAGES - 1>();
+          stage0 = sC + (nstore % CSTAGES) * C_STAGE_BYTES;
+          ++nstore;
+        }
+        // operand of the fused elementwise op: issue its loads now, they land while the staging barrier
+        // and the TMEM load are waited on
+        uint4 side[TCOLS / 8];
+        bool side_ok = false;
+        {
+          const int nn = n0 + c * CHUNK_COLS + cg * TCOLS;
+          const bf16* sp = nullptr;
+          if (EPI == EPI_LINEAR && args.residual != nullptr) sp = args.residual + static_cast<size_t>(m) * args.ld_res + nn;
+          if (EPI == EPI_GELU_BWD) sp = args.aux + static_cast<size_t>(m) * args.ld_aux + nn;
+          side_ok = sp != nullptr && row_ok && nn < args.N;
+          if (side_ok) {
+#pragma unroll
+            for (int q = 0; q < TCOLS / 8; ++q) side[q] = __ldg(reinterpret_cast<const uint4*>(sp) + q);
+          }
         }
         named_bar_sync(1, EPI_THREADS);
         float f[TCOLS];
@@ -248,12 +271,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 f[i + 1] = k1 ? f[i + 1] * args.drop.scale : 0.0f;
               }
             }
-            if (args.residual != nullptr && row_ok && n < args.N) {
-              const uint4* rp =
-                  reinterpret_cast<const uint4*>(args.residual + static_cast<size_t>(m) * args.ld_res + n);
+            if (side_ok) {
 #pragma unroll
               for (int q = 0; q < TCOLS / 8; ++q) {
-                const uint4 r = __ldg(rp + q);
+                const uint4 r = side[q];
                 const float2 r0 = unpack_bf16x2(r.x), r1 = unpack_bf16x2(r.y);
                 const float2 r2 = unpack_bf16x2(r.z), r3 = unpack_bf16x2(r.w);
                 f[8 * q] += r0.x;
@@ -269,12 +290,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
           if (EPI == EPI_GELU_BWD) {
             // aux holds gelu'(pre-activation), written by the forward GEMM's epilogue
-            if (row_ok && n < args.N) {
-              const uint4* up =
-                  reinterpret_cast<const uint4*>(args.aux + static_cast<size_t>(m) * args.ld_aux + n);
+            if (side_ok) {
 #pragma unroll
               for (int q = 0; q < TCOLS / 8; ++q) {
-                const uint4 r = __ldg(up + q);
+                const uint4 r = side[q];
                 const float2 u0 = unpack_bf16x2(r.x), u1 = unpack_bf16x2(r.y);
                 const float2 u2 = unpack_bf16x2(r.z), u3 = unpack_bf16x2(r.w);
                 f[8 * q] *= u0.x;

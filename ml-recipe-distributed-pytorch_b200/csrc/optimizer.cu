@@ -41,12 +41,19 @@ sumsq_partial_kernel(const float* __restrict__ g, size_t n, float* __restrict__ 
   }
 }
 
-__global__ void sumsq_final_kernel(const float* __restrict__ partial, int n, double* __restrict__ accum) {
-  if (threadIdx.x == 0 && blockIdx.x == 0) {
-    double s = 0.0;
-    for (int i = 0; i < n; ++i) s += static_cast<double>(partial[i]);
-    *accum += s;
+__global__ void __launch_bounds__(256)
+sumsq_final_kernel(const float* __restrict__ partial, int n, double* __restrict__ accum) {
+  // fixed-shape tree: the result does not depend on scheduling (deterministic given the partials)
+  __shared__ double red[256];
+  double s = 0.0;
+  for (int i = threadIdx.x; i < n; i += 256) s += static_cast<double>(partial[i]);
+  red[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+    __syncthreads();
   }
+  if (threadIdx.x == 0) *accum += red[0];
 }
 
 __global__ void __launch_bounds__(256)
@@ -122,7 +129,7 @@ int launch_grad_sumsq(const float* g, size_t n, double* sumsq_accum, float* part
   if (static_cast<size_t>(grid) > need) grid = static_cast<int>(need ? need : 1);
   sumsq_partial_kernel<<<grid, 256, 0, st>>>(g, n, partial_scratch);
   if (check_launch("sumsq_partial")) return 1;
-  sumsq_final_kernel<<<1, 32, 0, st>>>(partial_scratch, grid, sumsq_accum);
+  sumsq_final_kernel<<<1, 256, 0, st>>>(partial_scratch, grid, sumsq_accum);
   return check_launch("sumsq_final");
 }
 

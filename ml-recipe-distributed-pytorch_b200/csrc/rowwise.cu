@@ -138,21 +138,59 @@ __device__ __forceinline__ void ln_apply(RowVec& r, const RowVec& g, const RowVe
   }
 }
 
+// NV = 16-byte vectors per lane (H <= 256 NV); gamma/beta are read at use (L1-resident) so that only the
+// row itself lives in registers and many rows are in flight per SM.
+template <int NV>
 __global__ void __launch_bounds__(ROW_WARPS * 32)
 ln_fwd_kernel(const bf16* __restrict__ z, const float* __restrict__ gamma, const float* __restrict__ beta,
               bf16* __restrict__ y, int T, int H, float eps) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * ROW_WARPS + (threadIdx.x >> 5);
   if (row >= T) return;
-  RowVec r, g, b;
-  load_row_bf16(z + static_cast<size_t>(row) * H, H, lane, r);
-  load_vec_f32(gamma, H, lane, g);
-  load_vec_f32(beta, H, lane, b);
-  float mean, rstd;
-  row_stats(r, H, lane, eps, mean, rstd);
-  DropKey none{0, 0, 0, 1.0f};
-  ln_apply(r, g, b, H, lane, mean, rstd, none, row);
-  store_row_bf16(y + static_cast<size_t>(row) * H, H, lane, r);
+  float x[NV][8];
+  const bf16* zr = z + static_cast<size_t>(row) * H;
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int c = (j * 32 + lane) * 8;
+    const uint4 u = c < H ? __ldg(reinterpret_cast<const uint4*>(zr + c)) : make_uint4(0, 0, 0, 0);
+    const float2 a0 = unpack_bf16x2(u.x), a1 = unpack_bf16x2(u.y), a2 = unpack_bf16x2(u.z), a3 = unpack_bf16x2(u.w);
+    x[j][0] = a0.x; x[j][1] = a0.y; x[j][2] = a1.x; x[j][3] = a1.y;
+    x[j][4] = a2.x; x[j][5] = a2.y; x[j][6] = a3.x; x[j][7] = a3.y;
+  }
+  const float invH = 1.0f / static_cast<float>(H);
+  float s = 0.0f;
+#pragma unroll
+  for (int j = 0; j < NV; ++j)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += x[j][i];
+  const float mean = warp_sum(s) * invH;
+  float qv = 0.0f;
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    if ((j * 32 + lane) * 8 < H) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float t = x[j][i] - mean;
+        qv += t * t;
+      }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(qv) * invH + eps);
+  bf16* yr = y + static_cast<size_t>(row) * H;
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int c = (j * 32 + lane) * 8;
+    if (c < H) {
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c + 4));
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + c)), b1 = __ldg(reinterpret_cast<const float4*>(beta + c + 4));
+      uint4 o;
+      o.x = pack_bf16x2((x[j][0] - mean) * rstd * g0.x + b0.x, (x[j][1] - mean) * rstd * g0.y + b0.y);
+      o.y = pack_bf16x2((x[j][2] - mean) * rstd * g0.z + b0.z, (x[j][3] - mean) * rstd * g0.w + b0.w);
+      o.z = pack_bf16x2((x[j][4] - mean) * rstd * g1.x + b1.x, (x[j][5] - mean) * rstd * g1.y + b1.y);
+      o.w = pack_bf16x2((x[j][6] - mean) * rstd * g1.z + b1.z, (x[j][7] - mean) * rstd * g1.w + b1.w);
+      *reinterpret_cast<uint4*>(yr + c) = o;
+    }
+  }
 }
 
 // z0 = word[ids] + pos[s] + type[tt]  (fp32 tables, fp32 sum, stored as bf16)
@@ -382,7 +420,20 @@ colsum_kernel(const bf16* __restrict__ X, int ld, float* __restrict__ out, int T
   const int c = (blockIdx.x * 32 + tx) * 8;
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (c < N) {
-    for (int r = blockIdx.y * 8 + ty; r < T; r += gridDim.y * 8) {
+    const int step = gridDim.y * 8;
+    int r = blockIdx.y * 8 + ty;
+    for (; r + 3 * step < T; r += 4 * step) {  // four independent 16-byte loads in flight per thread
+      uint4 u[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) u[k] = __ldg(reinterpret_cast<const uint4*>(X + static_cast<size_t>(r + k * step) * ld + c));
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 a = unpack_bf16x2(u[k].x), b = unpack_bf16x2(u[k].y), cc = unpack_bf16x2(u[k].z), d = unpack_bf16x2(u[k].w);
+        acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y;
+        acc[4] += cc.x; acc[5] += cc.y; acc[6] += d.x; acc[7] += d.y;
+      }
+    }
+    for (; r < T; r += step) {
       const uint4 u = __ldg(reinterpret_cast<const uint4*>(X + static_cast<size_t>(r) * ld + c));
       const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
       acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y;
@@ -470,7 +521,12 @@ int launch_ln_fwd(const bf16* z, const float* gamma, const float* beta, bf16* y,
     set_error("layernorm: H=%d must be a multiple of 8 and <= %d", H, MAXV * 256);
     return 1;
   }
-  ln_fwd_kernel<<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps);
+  switch ((H + 255) / 256) {
+    case 1: ln_fwd_kernel<1><<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
+    case 2: ln_fwd_kernel<2><<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
+    case 3: ln_fwd_kernel<3><<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
+    default: ln_fwd_kernel<4><<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
+  }
   return check_launch("ln_fwd");
 }
 
