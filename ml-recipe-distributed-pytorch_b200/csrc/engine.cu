@@ -251,15 +251,6 @@ struct bqa_handle {
 
 namespace {
 
-int wgrad_splits(int M, int N, int K, int num_sms) {
-  const int tiles = ((M + 127) / 128) * ((N + 255) / 256);
-  const int kb = (K + 63) / 64;
-  int s = (2 * num_sms + tiles - 1) / tiles;
-  const int max_s = kb / 4 > 0 ? kb / 4 : 1;
-  if (s > max_s) s = max_s;
-  return s < 1 ? 1 : s;
-}
-
 int build_plan(bqa_handle* h, int B, int S, bool training) {
   const bqa_config& c = h->cfg;
   Plan& p = h->plan;
@@ -328,7 +319,7 @@ int build_plan(bqa_handle* h, int B, int S, bool training) {
       g.B = X; g.ldb = Kin; g.b_mn_major = 1;
       g.C = dW; g.ldc = Kin;
       g.epilogue = EPI_F32_ADD;
-      g.k_splits = wgrad_splits(Nout, Kin, T, h->num_sms);
+      g.k_splits = 0;  // automatic: whole waves of tiles, see gemm_plan
       g.drop = make_drop_key(0, 0, 0.0f);
       return gemm_plan(out, g, h->num_sms);
     };

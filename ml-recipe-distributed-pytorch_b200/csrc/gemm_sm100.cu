@@ -5,7 +5,9 @@
 // (site-packages/transformers/models/bert/modeling_bert.py:179-181,294-298,339-342,352-356)
 // and their autograd backward (reference trainer.py:197-204).
 //
-// CTA = 384 threads, one CTA per SM, static round-robin tile schedule:
+// CTA = 384 threads, one CTA per SM, static round-robin tile schedule; large problems run as CTA pairs
+// (cluster of 2, tcgen05 cta_group::2, 256 x 256 tiles, 6-stage ring), small ones as single CTAs
+// (128 x 256 tiles, 4-stage ring):
 //   warp 0 (1 thread)  TMA producer: 3-stage ring of {A 128x64, B 256x64} bf16 tiles, 128B swizzle
 //   warp 1 (1 thread)  MMA issuer  : tcgen05.mma cta_group::1 kind::f16, M=128 N=256 K=16, fp32 in TMEM
 //   warp 2             TMEM allocator (512 columns = two 128x256 fp32 accumulators, double-buffered)
@@ -23,31 +25,37 @@ namespace bqa {
 
 namespace {
 
-constexpr int BLOCK_M = 128;
 constexpr int BLOCK_N = 256;
 constexpr int BLOCK_K = 64;
-#ifndef BQA_GEMM_STAGES
-#define BQA_GEMM_STAGES 3
-#endif
-constexpr int STAGES = BQA_GEMM_STAGES;                // TMA -> MMA ring depth
-constexpr int CSTAGES = STAGES == 3 ? 4 : 2;          // epilogue staging buffers (TMA store ring)
-constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KiB
-constexpr int B_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;  // 32 KiB
-constexpr int C_STAGE_BYTES = BLOCK_M * 128;          // 128 rows x 128 B (64 bf16 or 32 fp32)
-constexpr int SMEM_BARRIER_BYTES = 256;
-constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + CSTAGES * C_STAGE_BYTES + SMEM_BARRIER_BYTES;
-constexpr int SMEM_ALLOC = SMEM_BYTES + 1024;  // slack for manual 1024-byte alignment
 constexpr int TMEM_COLS = 512;
 constexpr int NUM_THREADS = 384;
 constexpr int EPI_THREADS = 256;
+constexpr int C_STAGE_BYTES = 128 * 128;  // 128 rows x 128 B (64 bf16 or 32 fp32)
+constexpr int SMEM_BARRIER_BYTES = 256;
 
-static_assert(SMEM_ALLOC <= 232448, "exceeds the 227 KiB per-CTA shared memory limit");
+// NCTA = 1: one CTA computes a 128 x 256 tile.  NCTA = 2: a CTA pair (cluster of 2, cta_group::2)
+// computes a 256 x 256 tile; each CTA stages its own 128 rows of A and 128 of the 256 rows of B,
+// so operand traffic per SM drops by a third and the ring can be deeper.
+template <int NCTA>
+struct Cfg {
+  static constexpr int BLOCK_M = 128 * NCTA;             // rows of the (pair) tile
+  static constexpr int B_ROWS = BLOCK_N / NCTA;          // B rows staged by one CTA
+  static constexpr int A_STAGE_BYTES = 128 * BLOCK_K * 2;
+  static constexpr int B_STAGE_BYTES = B_ROWS * BLOCK_K * 2;
+  static constexpr int STAGES = NCTA == 2 ? 6 : 4;       // TMA -> MMA ring depth
+  static constexpr int CSTAGES = 2;                      // epilogue staging buffers (TMA store ring)
+  static constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + CSTAGES * C_STAGE_BYTES +
+                                    SMEM_BARRIER_BYTES;
+  static constexpr int SMEM_ALLOC = SMEM_BYTES + 1024;   // slack for manual 1024-byte alignment
+  static_assert(SMEM_ALLOC <= 232448, "exceeds the 227 KiB per-CTA shared memory limit");
+};
 
-template <int A_MN, int B_MN, int EPI>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
-gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-            const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
-            const GemmArgs args) {
+template <int A_MN, int B_MN, int EPI, int NCTA>
+__device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                                          const CUtensorMap& tmC2, const GemmArgs& args) {
+  using C = Cfg<NCTA>;
+  constexpr int STAGES = C::STAGES, CSTAGES = C::CSTAGES;
+  constexpr int A_STAGE_BYTES = C::A_STAGE_BYTES, B_STAGE_BYTES = C::B_STAGE_BYTES, BLOCK_M = C::BLOCK_M;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sA = smem;
@@ -61,6 +69,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const uint32_t rank = NCTA == 2 ? cluster_ctarank() : 0u;  // 0 = the CTA that issues the MMAs
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA);
@@ -68,57 +77,70 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     tma_prefetch_desc(&tmC);
     if (EPI == EPI_GELU_FWD) tma_prefetch_desc(&tmC2);
     for (int i = 0; i < STAGES; ++i) {
-      mbar_init(&bar_full[i], 1);
+      mbar_init(&bar_full[i], NCTA);   // pair: one arrival per CTA's producer, on the even CTA's barrier
       mbar_init(&bar_empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bar_tfull[i], 1);
-      mbar_init(&bar_tempty[i], EPI_THREADS);
+      mbar_init(&bar_tempty[i], NCTA * EPI_THREADS);  // pair: both CTAs' epilogues arrive on the even CTA
     }
     fence_mbar_init();
   }
   if (warp == 2) {
-    tmem_alloc(tmem_slot, TMEM_COLS);
-    tmem_relinquish();
+    if (NCTA == 2) {
+      tmem_alloc_pair(tmem_slot, TMEM_COLS);
+      tmem_relinquish_pair();
+    } else {
+      tmem_alloc(tmem_slot, TMEM_COLS);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if (NCTA == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   const int tiles_mn = args.m_tiles * args.n_tiles;
   const int num_tiles = tiles_mn * args.k_splits;
+  const int tile0 = blockIdx.x / NCTA, tile_step = gridDim.x / NCTA;
 
   if (warp == 0 && lane == 0) {
-    // ------------------------------ TMA producer ------------------------------
+    // ------------------------------ TMA producer (every CTA) ------------------------------
     int stage = 0;
     uint32_t phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
       const int split = tile / tiles_mn;
       const int mn = tile - split * tiles_mn;
-      const int m0 = (mn / args.n_tiles) * BLOCK_M;
-      const int n0 = (mn % args.n_tiles) * BLOCK_N;
+      const int m0 = (mn / args.n_tiles) * BLOCK_M + static_cast<int>(rank) * 128;      // own A rows
+      const int n0 = (mn % args.n_tiles) * BLOCK_N + static_cast<int>(rank) * C::B_ROWS;  // own B rows
       const int kb0 = split * args.kb_per_split;
       const int kb1 = min(kb0 + args.kb_per_split, args.kb_total);
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(&bar_empty[stage], phase ^ 1u);
-        mbar_arrive_expect_tx(&bar_full[stage], A_STAGE_BYTES + B_STAGE_BYTES);
         const int k0 = kb * BLOCK_K;
         uint8_t* a_dst = sA + stage * A_STAGE_BYTES;
         uint8_t* b_dst = sB + stage * B_STAGE_BYTES;
+        uint64_t* fb = &bar_full[stage];
+        if (NCTA == 1) mbar_arrive_expect_tx(fb, A_STAGE_BYTES + B_STAGE_BYTES);
+        auto load = [&](void* dst, const CUtensorMap* tm, int c0, int c1) {
+          if (NCTA == 2) tma_load_2d_pair(dst, tm, c0, c1, fb); else tma_load_2d(dst, tm, c0, c1, fb);
+        };
         if (A_MN) {
 #pragma unroll
-          for (int i = 0; i < BLOCK_M / 64; ++i)
-            tma_load_2d(a_dst + i * (BLOCK_K * 128), &tmA, m0 + i * 64, k0, &bar_full[stage]);
+          for (int i = 0; i < 2; ++i) load(a_dst + i * (BLOCK_K * 128), &tmA, m0 + i * 64, k0);
         } else {
-          tma_load_2d(a_dst, &tmA, k0, m0, &bar_full[stage]);
+          load(a_dst, &tmA, k0, m0);
         }
         if (B_MN) {
 #pragma unroll
-          for (int i = 0; i < BLOCK_N / 64; ++i)
-            tma_load_2d(b_dst + i * (BLOCK_K * 128), &tmB, n0 + i * 64, k0, &bar_full[stage]);
+          for (int i = 0; i < C::B_ROWS / 64; ++i) load(b_dst + i * (BLOCK_K * 128), &tmB, n0 + i * 64, k0);
         } else {
-          tma_load_2d(b_dst, &tmB, k0, n0, &bar_full[stage]);
+          load(b_dst, &tmB, k0, n0);
+        }
+        if (NCTA == 2) {
+          // both CTAs' bytes are credited to the even CTA's barrier, which expects them all
+          if (rank == 0) mbar_arrive_expect_tx(fb, 2 * (A_STAGE_BYTES + B_STAGE_BYTES));
+          else mbar_arrive_cluster(fb, 0);
         }
         if (++stage == STAGES) {
           stage = 0;
@@ -126,13 +148,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
       }
     }
-  } else if (warp == 1 && lane == 0) {
-    // ------------------------------ MMA issuer ------------------------------
+  } else if (warp == 1 && lane == 0 && rank == 0) {
+    // ------------------------------ MMA issuer (even CTA only) ------------------------------
     constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BLOCK_N, A_MN, B_MN);
     int stage = 0;
     uint32_t phase = 0;
     uint32_t it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = tile0; tile < num_tiles; tile += tile_step, ++it) {
       const int split = tile / tiles_mn;
       const int kb0 = split * args.kb_per_split;
       const int kb1 = min(kb0 + args.kb_per_split, args.kb_total);
@@ -152,10 +174,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                                       : umma_desc_kmajor(a_addr + k * 32);
           const uint64_t bdesc = B_MN ? umma_desc_mnmajor(b_addr + k * 2048, BLOCK_K * 128)
                                       : umma_desc_kmajor(b_addr + k * 32);
-          umma_bf16(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          if (NCTA == 2) umma_bf16_pair(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          else umma_bf16(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
         }
-        umma_commit(&bar_empty[stage]);
-        if (kb == kb1 - 1) umma_commit(&bar_tfull[as]);
+        if (NCTA == 2) {
+          umma_commit_pair(&bar_empty[stage]);  // frees the stage in both CTAs
+          if (kb == kb1 - 1) umma_commit_pair(&bar_tfull[as]);
+        } else {
+          umma_commit(&bar_empty[stage]);
+          if (kb == kb1 - 1) umma_commit(&bar_tfull[as]);
+        }
         if (++stage == STAGES) {
           stage = 0;
           phase ^= 1u;
@@ -176,10 +204,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     constexpr int NCHUNK = BLOCK_N / CHUNK_COLS;
     uint32_t it = 0;
     uint32_t nstore = 0;  // staging-buffer ring position (EPI with a single output)
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = tile0; tile < num_tiles; tile += tile_step, ++it) {
       const int split = tile / tiles_mn;
       const int mn = tile - split * tiles_mn;
-      const int m0 = (mn / args.n_tiles) * BLOCK_M;
+      const int m0 = (mn / args.n_tiles) * BLOCK_M + static_cast<int>(rank) * 128;  // rows held in this CTA's TMEM
       const int n0 = (mn % args.n_tiles) * BLOCK_N;
       const uint32_t as = it & 1u;
       const uint32_t aphase = (it >> 1) & 1u;
@@ -236,7 +264,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         if (c == NCHUNK - 1) {
           // accumulator fully drained into registers: hand the TMEM stage back to the MMA warp
           tc_fence_before();
-          mbar_arrive(&bar_tempty[as]);
+          if (NCTA == 2 && rank != 0) mbar_arrive_cluster(&bar_tempty[as], 0);
+          else mbar_arrive(&bar_tempty[as]);
         }
         const int n = n0 + c * CHUNK_COLS + cg * TCOLS;
 
@@ -361,11 +390,27 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (NCTA == 2) cluster_sync_all(); else __syncthreads();  // pair: the peer may still be reading barriers / TMEM
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    if (NCTA == 2) tmem_dealloc_pair(tmem_base, TMEM_COLS); else tmem_dealloc(tmem_base, TMEM_COLS);
   }
+}
+
+template <int A_MN, int B_MN, int EPI>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
+            const GemmArgs args) {
+  gemm_body<A_MN, B_MN, EPI, 1>(tmA, tmB, tmC, tmC2, args);
+}
+
+template <int A_MN, int B_MN, int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
+                 const GemmArgs args) {
+  gemm_body<A_MN, B_MN, EPI, 2>(tmA, tmB, tmC, tmC2, args);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -388,16 +433,21 @@ EncodeTiledFn get_encode_fn() {
 template <int A_MN, int B_MN, int EPI>
 int launch_variant(const GemmPlan& plan, cudaStream_t stream) {
   static bool configured = false;  // per-process; the attribute is per-device but all devices share the value
-  auto kfn = gemm_kernel<A_MN, B_MN, EPI>;
+  auto k1 = gemm_kernel<A_MN, B_MN, EPI>;
+  auto k2 = gemm_pair_kernel<A_MN, B_MN, EPI>;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_ALLOC);
+    cudaError_t e = cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<1>::SMEM_ALLOC);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<2>::SMEM_ALLOC);
     if (e != cudaSuccess) {
       set_error("gemm: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
       return 1;
     }
     configured = true;
   }
-  kfn<<<plan.grid, NUM_THREADS, SMEM_ALLOC, stream>>>(plan.tmA, plan.tmB, plan.tmC, plan.tmC2, plan.args);
+  if (plan.pair)
+    k2<<<plan.grid, NUM_THREADS, Cfg<2>::SMEM_ALLOC, stream>>>(plan.tmA, plan.tmB, plan.tmC, plan.tmC2, plan.args);
+  else
+    k1<<<plan.grid, NUM_THREADS, Cfg<1>::SMEM_ALLOC, stream>>>(plan.tmA, plan.tmB, plan.tmC, plan.tmC2, plan.args);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("gemm: launch failed: %s", cudaGetErrorString(e));
@@ -485,25 +535,29 @@ int gemm_plan(GemmPlan* plan, const GemmProblem& p, int num_sms) {
     return 1;
   }
   const int a_mn = p.a_mn_major ? 1 : 0, b_mn = p.b_mn_major ? 1 : 0;
+  // CTA pairs (256-row tiles) whenever there are at least two 128-row tiles of M
+  const bool pair = p.M > 128 && !p.force_single;
+  plan->pair = pair ? 1 : 0;
+  const int b_rows = pair ? BLOCK_N / 2 : BLOCK_N;
   int rc = 0;
   if (a_mn)
     rc |= encode_tmap_2d(&plan->tmA, p.A, 2, p.M, p.K, p.lda, 64, BLOCK_K);
   else
-    rc |= encode_tmap_2d(&plan->tmA, p.A, 2, p.K, p.M, p.lda, BLOCK_K, BLOCK_M);
+    rc |= encode_tmap_2d(&plan->tmA, p.A, 2, p.K, p.M, p.lda, BLOCK_K, 128);
   if (b_mn)
     rc |= encode_tmap_2d(&plan->tmB, p.B, 2, p.N, p.K, p.ldb, 64, BLOCK_K);
   else
-    rc |= encode_tmap_2d(&plan->tmB, p.B, 2, p.K, p.N, p.ldb, BLOCK_K, BLOCK_N);
+    rc |= encode_tmap_2d(&plan->tmB, p.B, 2, p.K, p.N, p.ldb, BLOCK_K, b_rows);
   if (p.epilogue == EPI_F32_ADD)
-    rc |= encode_tmap_2d(&plan->tmC, p.C, 4, p.N, p.M, p.ldc, 32, BLOCK_M);
+    rc |= encode_tmap_2d(&plan->tmC, p.C, 4, p.N, p.M, p.ldc, 32, 128);
   else
-    rc |= encode_tmap_2d(&plan->tmC, p.C, 2, p.N, p.M, p.ldc, 64, BLOCK_M);
+    rc |= encode_tmap_2d(&plan->tmC, p.C, 2, p.N, p.M, p.ldc, 64, 128);
   if (p.epilogue == EPI_GELU_FWD) {
     if (p.C2 == nullptr) {
       set_error("gemm: EPI_GELU_FWD needs a second output");
       return 1;
     }
-    rc |= encode_tmap_2d(&plan->tmC2, p.C2, 2, p.N, p.M, p.ldc, 64, BLOCK_M);
+    rc |= encode_tmap_2d(&plan->tmC2, p.C2, 2, p.N, p.M, p.ldc, 64, 128);
   } else {
     plan->tmC2 = plan->tmC;
   }
@@ -513,10 +567,26 @@ int gemm_plan(GemmPlan* plan, const GemmProblem& p, int num_sms) {
   a.M = p.M;
   a.N = p.N;
   a.K = p.K;
-  a.m_tiles = (p.M + BLOCK_M - 1) / BLOCK_M;
+  const int block_m = pair ? 256 : 128;
+  const int units = pair ? num_sms / 2 : num_sms;  // concurrently running tiles
+  a.m_tiles = (p.M + block_m - 1) / block_m;
   a.n_tiles = (p.N + BLOCK_N - 1) / BLOCK_N;
   a.kb_total = (p.K + BLOCK_K - 1) / BLOCK_K;
   int splits = p.k_splits < 1 ? 1 : p.k_splits;
+  if (p.k_splits == 0 && p.epilogue == EPI_F32_ADD) {
+    // automatic split-K: fill whole waves of `units` tiles, keep >= 8 k-blocks per split
+    const int tiles = a.m_tiles * a.n_tiles;
+    double best = -1.0;
+    for (int sp = 1; sp <= 32 && a.kb_total / sp >= 8; ++sp) {
+      const int total = tiles * sp;
+      const int waves = (total + units - 1) / units;
+      const double eff = static_cast<double>(total) / (static_cast<double>(waves) * units);
+      if (eff > best + 0.02) {
+        best = eff;
+        splits = sp;
+      }
+    }
+  }
   if (splits > a.kb_total) splits = a.kb_total;
   a.kb_per_split = (a.kb_total + splits - 1) / splits;
   a.k_splits = (a.kb_total + a.kb_per_split - 1) / a.kb_per_split;
@@ -532,7 +602,7 @@ int gemm_plan(GemmPlan* plan, const GemmProblem& p, int num_sms) {
   }
   plan->variant = a_mn | (b_mn << 1) | (p.epilogue << 2);
   const long tiles = static_cast<long>(a.m_tiles) * a.n_tiles * a.k_splits;
-  plan->grid = static_cast<int>(tiles < num_sms ? tiles : num_sms);
+  plan->grid = static_cast<int>(tiles < units ? tiles : units) * (pair ? 2 : 1);
   return 0;
 }
 

@@ -40,7 +40,8 @@ struct GemmProblem {
   int ld_res;
   const void* aux;  // bf16 [M][ld_aux], gelu'(u)       (EPI_GELU_BWD)
   int ld_aux;
-  int k_splits;  // >= 1; > 1 only with EPI_F32_ADD
+  int k_splits;  // >= 1; > 1 only with EPI_F32_ADD; 0 = choose automatically (EPI_F32_ADD)
+  int force_single;  // 1 = never use CTA pairs (tests)
   DropKey drop;  // thresh == 0 -> no dropout           (EPI_LINEAR)
 };
 
@@ -60,6 +61,7 @@ struct GemmPlan {
   GemmArgs args;
   int variant;  // a_mn_major | b_mn_major << 1 | epilogue << 2
   int grid;
+  int pair;  // 1 = CTA-pair kernel (cluster of 2)
 };
 
 // Returns 0 on success; on failure writes a message retrievable with bqa_last_error().
