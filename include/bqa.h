@@ -123,6 +123,19 @@ typedef struct bqa_adamw_chunk { /* one run of elements of one parameter tensor 
 /* *sumsq (device double) += sum(g[0..n)^2).  scratch: >= bqa_sumsq_scratch_floats() floats. */
 BQA_API int bqa_sumsq_scratch_floats(void);
 BQA_API int bqa_grad_sumsq(const float* g, uint64_t n, double* sumsq, float* scratch, void* stream);
+/* No counterpart in the reference.  Same result as bqa_grad_sumsq (*sumsq += sum(g[0..n)^2)) for
+ * callers that have no scratch buffer to give and may not create one: processes that pre-reserve all
+ * device memory in their own pool and forbid cudaMalloc afterwards, plugins without access to the
+ * host application's allocator, latency-critical paths that cannot take cudaMalloc's device-wide
+ * synchronisation.  The per-block partial sums live in a fixed 8 KiB array inside the library
+ * (resident on every GPU that loads it until the process exits); the call allocates nothing.
+ *   - n <= 2^31 elements, otherwise the call fails with a message (use bqa_grad_sumsq instead).
+ *   - The first call on each device looks up the array's device address; make that first call before
+ *     starting any stream capture on that device.
+ *   - All calls on a device share the array and it keeps whatever the last call wrote; each call
+ *     overwrites every entry it later reads, so no clearing is needed, but two calls that can run
+ *     concurrently on the GPU (different streams) race on it — serialise them. */
+BQA_API int bqa_grad_sumsq_noalloc(const float* g, uint64_t n, double* sumsq, void* stream);
 /* chunks: DEVICE array.  host_lr: HOST array of n_groups (<= 8) learning rates.
  * max_grad_norm <= 0 disables clipping.  p_bf16 may be NULL.  zero_grad != 0 clears g. */
 BQA_API int bqa_clip_adamw(float* p, float* g, float* m, float* v, void* p_bf16, const bqa_adamw_chunk* chunks,

@@ -75,6 +75,7 @@ SIGNATURES = {
     "bqa_colsum_bf16": (ctypes.c_int, [vp, c_i32, vp, c_i32, c_i32, vp]),
     "bqa_sumsq_scratch_floats": (ctypes.c_int, []),
     "bqa_grad_sumsq": (ctypes.c_int, [vp, c_u64, vp, vp, vp]),
+    "bqa_grad_sumsq_noalloc": (ctypes.c_int, [vp, c_u64, vp, vp]),
     "bqa_clip_adamw": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, c_i32, vp, c_f32, ctypes.POINTER(c_f32), c_i32,
                                       c_f32, c_f32, c_f32, c_i32, vp]),
     "bqa_f32_to_bf16": (ctypes.c_int, [vp, vp, c_u64, vp]),

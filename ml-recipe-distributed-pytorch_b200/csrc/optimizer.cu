@@ -151,3 +151,81 @@ int launch_f32_to_bf16(const float* src, bf16* dst, size_t n, int num_sms, cudaS
 }
 
 }  // namespace bqa
+
+// ---------------------------------------------------------------------------------------
+// Sum of squares without any allocation (extern "C", declared in include/bqa.h).
+//
+// bqa_grad_sumsq needs a small scratch buffer for its per-block partial sums and leaves it to the
+// caller to provide one.  Some callers cannot: a serving process that hands all device memory to
+// its own pool at start-up and forbids cudaMalloc afterwards, a plugin running inside a host
+// application whose allocator it has no access to, or code on a latency-critical path where
+// cudaMalloc's implicit device-wide synchronisation is not acceptable.  For them the same two
+// kernels run with the partial sums in the fixed array below, which is part of the library image:
+// every GPU that loads libbqa keeps these 8 KiB until the process exits.
+// ---------------------------------------------------------------------------------------
+#include <mutex>
+
+#include "../../include/bqa.h"
+
+namespace {
+
+constexpr int kNoAllocPartials = 2048;                 // one float per thread block of the first pass
+constexpr uint64_t kNoAllocMaxElems = 1ull << 31;      // at most 2^20 elements behind each fp32 partial
+constexpr int kNoAllocMaxDevices = 64;
+
+static __device__ __align__(256) float g_noalloc_partials[kNoAllocPartials];
+
+// In host code `g_noalloc_partials` is only a handle for the runtime, not an address a kernel could
+// use; the device address is asked for once per device, with that device current.
+int noalloc_scratch_address(float** out) {
+  static std::mutex mu;
+  static float* addr[kNoAllocMaxDevices] = {};
+  int dev = 0;
+  BQA_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) {
+    bqa::set_error("bqa_grad_sumsq_noalloc: device ordinal %d outside [0, %d)", dev, kNoAllocMaxDevices);
+    return 1;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (addr[dev] == nullptr) {
+    void* p = nullptr;
+    BQA_CUDA_CHECK(cudaGetSymbolAddress(&p, g_noalloc_partials));
+    addr[dev] = static_cast<float*>(p);
+  }
+  *out = addr[dev];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int bqa_grad_sumsq_noalloc(const float* g, uint64_t n, double* sumsq, void* stream) {
+  if (g == nullptr || sumsq == nullptr) {
+    bqa::set_error("bqa_grad_sumsq_noalloc: null argument");
+    return 1;
+  }
+  if (n > kNoAllocMaxElems) {
+    bqa::set_error("bqa_grad_sumsq_noalloc: %llu elements exceed the built-in scratch's limit of %llu; "
+                   "use bqa_grad_sumsq with a caller-provided scratch buffer",
+                   (unsigned long long)n, (unsigned long long)kNoAllocMaxElems);
+    return 1;
+  }
+  if ((reinterpret_cast<uintptr_t>(g) & 15u) != 0) {
+    bqa::set_error("bqa_grad_sumsq_noalloc: gradient buffer must be 16-byte aligned");
+    return 1;
+  }
+  float* partials = nullptr;
+  if (noalloc_scratch_address(&partials)) return 1;
+  int sms = 0;
+  if (bqa::device_sm_count(&sms)) return 1;
+  int grid = sms * 8;
+  if (grid > kNoAllocPartials) grid = kNoAllocPartials;
+  const uint64_t need = (n / 4 + 255) / 256;
+  if (static_cast<uint64_t>(grid) > need) grid = static_cast<int>(need ? need : 1);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  // Every launched block overwrites its own partial and the second pass reads exactly `grid` of them,
+  // so what an earlier call left in the array is never read and nothing has to be cleared first.
+  bqa::sumsq_partial_kernel<<<grid, 256, 0, st>>>(g, n, partials);
+  if (bqa::check_launch("sumsq_partial (no-alloc)")) return 1;
+  bqa::sumsq_final_kernel<<<1, 256, 0, st>>>(partials, grid, sumsq);
+  return bqa::check_launch("sumsq_final (no-alloc)");
+}
