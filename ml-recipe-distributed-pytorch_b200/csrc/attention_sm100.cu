@@ -44,6 +44,17 @@ struct AttnArgs {
   DropKey drop;
 };
 
+#ifdef BQA_ATTN_TRACE
+__device__ unsigned long long g_attn_trace[4096 * 16];
+#define ATRACE(slot)                                                                                        \
+  do {                                                                                                      \
+    const unsigned bl = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);                     \
+    if (bl < 4096) g_attn_trace[bl * 16 + (slot)] = clock64();                                              \
+  } while (0)
+#else
+#define ATRACE(slot) do {} while (0)
+#endif
+
 __device__ __forceinline__ float fast_exp2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -88,6 +99,20 @@ __device__ __forceinline__ void st_row_bf16_16(bf16* dst, const float* f) {
   }
 }
 
+// 16 consecutive bf16 (columns 16 qd .. 16 qd + 15) of row r of a [128 x 64] output tile laid out for a
+// SWIZZLE_128B TMA store
+__device__ __forceinline__ void st_out16(uint8_t* tile, int r, int qd, const float* f) {
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    uint4 o;
+    o.x = pack_bf16x2(f[8 * q], f[8 * q + 1]);
+    o.y = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
+    o.z = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]);
+    o.w = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
+    *reinterpret_cast<uint4*>(tile + r * 128 + ((((qd * 2 + q)) ^ (r & 7)) << 4)) = o;
+  }
+}
+
 __device__ __forceinline__ uint8_t* align1024(uint8_t* p) { return p + ((1024u - (smem_u32(p) & 1023u)) & 1023u); }
 
 // keep decisions for the 32 consecutive elements starting at `idx`, one bit each
@@ -108,12 +133,32 @@ __device__ __forceinline__ uint32_t keep_bits32(const DropKey& dk, uint32_t idx)
 }
 
 // =========================================================================================
+// dropout keep bits of one attention call: word w of row (b, h, q) covers keys 32 w .. 32 w + 31
+// =========================================================================================
+__global__ void __launch_bounds__(256)
+attn_keep_bits_kernel(uint32_t* __restrict__ keep, int rows, int S, int words_per_row, DropKey dk) {
+  const size_t total = static_cast<size_t>(rows) * words_per_row;
+  for (size_t w = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; w < total;
+       w += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const uint32_t row = static_cast<uint32_t>(w / words_per_row);
+    const int key0 = static_cast<int>(w - static_cast<size_t>(row) * words_per_row) * 32;
+    uint32_t bits = 0u;
+    if (key0 < S) {
+      bits = keep_bits32(dk, row * static_cast<uint32_t>(S) + key0);
+      if (key0 + 32 > S) bits &= (1u << (S - key0)) - 1u;  // keys beyond S belong to the next row's indices
+    }
+    keep[w] = bits;
+  }
+}
+
+// =========================================================================================
 // forward
 // =========================================================================================
 // KB: whether the additive key bias (padding mask / ragged last chunk) is needed
 template <bool KB>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
-attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnArgs a) {
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_ctx,
+                const AttnArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
   const int N = a.nchunk;
@@ -136,6 +181,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnArgs a) {
   const int tid = threadIdx.x, warp = tid >> 5;
   const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int S = a.S, Sp = N * 128;
+  if (tid == 0) ATRACE(0);
 
   if (tid == ROW_THREADS) {
     tma_prefetch_desc(&tm_qkv);
@@ -148,6 +194,13 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnArgs a) {
       mbar_init(&bar_pfree[i], 1);
     }
     fence_mbar_init();
+    // operand loads need nothing but the barriers: start them before the rest of the prologue
+    tma_prefetch_desc(&tm_ctx);
+    mbar_arrive_expect_tx(bar_qk, (1 + N) * CH);
+    tma_load_3d(sQ, &tm_qkv, h * 64, qt * 128, b, bar_qk);
+    for (int c = 0; c < N; ++c) tma_load_3d(sK + c * CH, &tm_qkv, a.H + h * 64, c * 128, b, bar_qk);
+    mbar_arrive_expect_tx(bar_v, N * CH);
+    for (int c = 0; c < N; ++c) tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + h * 64, c * 128, b, bar_v);
   }
   if (warp == CTRL_WARP) {
     tmem_alloc(tmem_slot, a.tmem_cols);
@@ -165,20 +218,17 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnArgs a) {
   const uint32_t tmem = *tmem_slot;
 
   if (tid == ROW_THREADS) {
-    // ---------------- control thread: TMA loads + MMA issue ----------------
-    mbar_arrive_expect_tx(bar_qk, (1 + N) * CH);
-    tma_load_3d(sQ, &tm_qkv, h * 64, qt * 128, b, bar_qk);
-    for (int c = 0; c < N; ++c) tma_load_3d(sK + c * CH, &tm_qkv, a.H + h * 64, c * 128, b, bar_qk);
-    mbar_arrive_expect_tx(bar_v, N * CH);
-    for (int c = 0; c < N; ++c) tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + h * 64, c * 128, b, bar_v);
-
+    // ---------------- control thread: MMA issue ----------------
     constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
     constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+    ATRACE(1);
     mbar_wait(bar_qk, 0);
+    ATRACE(2);
     tc_fence_after();
     for (int c = 0; c < N; ++c) mma_k64(tmem + c * 128, smem_u32(sQ), smem_u32(sK + c * CH), idesc_s);
     umma_commit(bar_s);
     mbar_wait(bar_v, 0);
+    ATRACE(3);
     for (int j = 0; j < N; ++j) {
       mbar_wait(&bar_p[j & 1], (j >> 1) & 1);
       tc_fence_after();
@@ -194,6 +244,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnArgs a) {
     const uint32_t lane_addr = lane_base + qd * 32;
     const float sl2 = a.scale_log2;
     mbar_wait(bar_s, 0);
+    if (tid == 0) ATRACE(4);
     tc_fence_after();
     float mx = -INFINITY;
     for (int j = 0; j < N; ++j) {
@@ -214,20 +265,22 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnArgs a) {
     named_bar_sync(1, ROW_THREADS);
     mx = fmaxf(fmaxf(xmax[r], xmax[128 + r]), fmaxf(xmax[256 + r], xmax[384 + r]));
     if (mx == -INFINITY) mx = 0.0f;
+    if (tid == 0) ATRACE(5);
     float l = 0.0f;
-    const uint32_t drop_base = ((static_cast<uint32_t>(b) * a.A + h) * S + static_cast<uint32_t>(q)) * S;
-    uint32_t* keep_row = a.keep + ((static_cast<size_t>(b) * a.A + h) * S + (q < S ? q : 0)) * (4 * N) + qd;
+    const uint32_t* keep_row = a.keep + ((static_cast<size_t>(b) * a.A + h) * S + (q < S ? q : 0)) * (4 * N) + qd;
+    uint32_t kw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+    if (a.drop.thresh != 0u) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (j < N) kw[j] = __ldg(keep_row + j * 4);  // written by attn_keep_bits_kernel
+    }
     for (int j = 0; j < N; ++j) {
       uint8_t* tile = sP + (j & 1) * 2 * CH;
       uint32_t v[32];
       tmem_ld_32x32(lane_addr + j * 128, v);
       tmem_wait_ld();
       const int key0 = j * 128 + qd * 32;
-      uint32_t bits = 0xffffffffu;
-      if (a.drop.thresh != 0u) {
-        bits = keep_bits32(a.drop, drop_base + key0);
-        if (q < S) keep_row[j * 4] = bits;
-      }
+      const uint32_t bits = kw[j & 3];
       if (j >= 2) mbar_wait(&bar_pfree[j & 1], ((j >> 1) - 1) & 1);
 #pragma unroll
       for (int g = 0; g < 4; ++g) {
@@ -246,26 +299,36 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnArgs a) {
       tc_fence_before();
       mbar_arrive(&bar_p[j & 1]);
     }
+    if (tid == 0) ATRACE(6);
     xsum[qd * 128 + r] = l;
     named_bar_sync(1, ROW_THREADS);
     l = (xsum[r] + xsum[128 + r]) + (xsum[256 + r] + xsum[384 + r]);
     mbar_wait(bar_o, 0);
+    if (tid == 0) ATRACE(7);
     tc_fence_after();
     const float inv = l > 0.0f ? 1.0f / l : 0.0f;
     {
+      // O tile -> swizzled smem (the P buffers are free: every MMA has completed) -> one TMA store,
+      // which also clips the rows beyond S
       uint32_t v[16];
       tmem_ld_32x16(lane_base + qd * 16, v);
       tmem_wait_ld();
-      if (q < S) {
-        float f[16];
+      float f[16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]) * inv;
-        st_row_bf16_16(a.ctx + (static_cast<size_t>(b) * S + q) * a.H + h * 64 + qd * 16, f);
+      for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]) * inv;
+      st_out16(sP, r, qd, f);
+      fence_proxy_async_smem();
+      named_bar_sync(1, ROW_THREADS);
+      if (tid == 0) {
+        tma_store_3d(&tm_ctx, sP, h * 64, qt * 128, b);
+        tma_commit_group();
+        tma_wait_group_read<0>();
       }
     }
     // a row whose keys are all masked has l == 0: store +inf so that the backward recomputes P = 0
     if (q < S && qd == 0)
       a.lse2[(static_cast<size_t>(b) * a.A + h) * S + q] = l > 0.0f ? mx + log2f(l) : INFINITY;
+    if (tid == 0) ATRACE(8);
   }
 
   tc_fence_before();
@@ -273,6 +336,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnArgs a) {
   if (warp == CTRL_WARP) {
     tc_fence_after();
     tmem_dealloc(tmem, a.tmem_cols);
+  }
+  if (tid == 0) {
+    ATRACE(9);
+#ifdef BQA_ATTN_TRACE
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    const unsigned bl = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+    if (bl < 4096) g_attn_trace[bl * 16 + 15] = smid;
+#endif
   }
 }
 
@@ -310,7 +382,7 @@ attn_dsum_kernel(const bf16* __restrict__ ctx, const bf16* __restrict__ dctx, fl
 template <bool KB>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
 attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_dctx,
-                   const AttnArgs a) {
+                   const __grid_constant__ CUtensorMap tm_dqkv, const AttnArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
   const int N = a.nchunk;
@@ -332,6 +404,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
   const int tid = threadIdx.x, warp = tid >> 5;
   const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int S = a.S, Sp = N * 128;
+  if (tid == 0) ATRACE(0);
 
   if (tid == ROW_THREADS) {
     tma_prefetch_desc(&tm_qkv);
@@ -343,6 +416,14 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
     mbar_init(bar_dsfree, 1);
     mbar_init(bar_dq, 1);
     fence_mbar_init();
+    tma_prefetch_desc(&tm_dqkv);
+    mbar_arrive_expect_tx(bar_ld, (2 + 2 * N) * CH);
+    tma_load_3d(sQ, &tm_qkv, h * 64, qt * 128, b, bar_ld);
+    tma_load_3d(sdO, &tm_dctx, h * 64, qt * 128, b, bar_ld);
+    for (int c = 0; c < N; ++c) {
+      tma_load_3d(sK + c * CH, &tm_qkv, a.H + h * 64, c * 128, b, bar_ld);
+      tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + h * 64, c * 128, b, bar_ld);
+    }
   }
   if (warp == CTRL_WARP) {
     tmem_alloc(tmem_slot, 512);
@@ -361,16 +442,11 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
   constexpr uint32_t COL_S = 0, COL_DP = 128, COL_DQ = 256;
 
   if (tid == ROW_THREADS) {
-    mbar_arrive_expect_tx(bar_ld, (2 + 2 * N) * CH);
-    tma_load_3d(sQ, &tm_qkv, h * 64, qt * 128, b, bar_ld);
-    tma_load_3d(sdO, &tm_dctx, h * 64, qt * 128, b, bar_ld);
-    for (int c = 0; c < N; ++c) {
-      tma_load_3d(sK + c * CH, &tm_qkv, a.H + h * 64, c * 128, b, bar_ld);
-      tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + h * 64, c * 128, b, bar_ld);
-    }
     constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
     constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+    ATRACE(1);
     mbar_wait(bar_ld, 0);
+    ATRACE(2);
     tc_fence_after();
     mma_k64(tmem + COL_S, smem_u32(sQ), smem_u32(sK), idesc_s);
     mma_k64(tmem + COL_DP, smem_u32(sdO), smem_u32(sV), idesc_s);
@@ -408,6 +484,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
     }
     for (int j = 0; j < N; ++j) {
       mbar_wait(bar_s, j & 1);
+      if (tid == 0 && j == 0) ATRACE(4);
       tc_fence_after();
       uint32_t vs[32], vd[32];
       tmem_ld_32x32(lane_base + COL_S + qd * 32, vs);
@@ -416,6 +493,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
       tc_fence_before();
       mbar_arrive(bar_sfree);
       if (j >= 1) mbar_wait(bar_dsfree, (j - 1) & 1);
+      if (tid == 0 && j == 1) ATRACE(5);
       const int key0 = j * 128 + qd * 32;
       const uint32_t bits = kw[j & 3];
 #pragma unroll
@@ -436,19 +514,27 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
       tc_fence_before();
       mbar_arrive(bar_ds);
     }
+    if (tid == 0) ATRACE(6);
     mbar_wait(bar_dq, 0);
+    if (tid == 0) ATRACE(7);
     tc_fence_after();
     {
       uint32_t v[16];
       tmem_ld_32x16(lane_base + COL_DQ + qd * 16, v);
       tmem_wait_ld();
-      if (q_ok) {
-        float f[16];
+      float f[16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-        st_row_bf16_16(a.dqkv + (static_cast<size_t>(b) * S + q) * 3 * a.H + h * 64 + qd * 16, f);
+      for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+      st_out16(sdS, r, qd, f);  // sdS is free: every MMA has completed
+      fence_proxy_async_smem();
+      named_bar_sync(1, ROW_THREADS);
+      if (tid == 0) {
+        tma_store_3d(&tm_dqkv, sdS, h * 64, qt * 128, b);  // Q slab of dqkv; rows beyond S are clipped
+        tma_commit_group();
+        tma_wait_group_read<0>();
       }
     }
+    if (tid == 0) ATRACE(8);
   }
 
   tc_fence_before();
@@ -457,6 +543,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
     tc_fence_after();
     tmem_dealloc(tmem, 512);
   }
+  if (tid == 0) ATRACE(9);
 }
 
 // =========================================================================================
@@ -464,7 +551,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
 // =========================================================================================
 __global__ void __launch_bounds__(ATT_THREADS, 1)
 attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_dctx,
-                    const AttnArgs a) {
+                    const __grid_constant__ CUtensorMap tm_dqkv, const AttnArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
   const int N = a.nchunk;
@@ -490,6 +577,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
   const int tid = threadIdx.x, warp = tid >> 5;
   const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int S = a.S, Sp = N * 128;
+  if (tid == 0) ATRACE(0);
 
   if (tid == ROW_THREADS) {
     tma_prefetch_desc(&tm_qkv);
@@ -503,6 +591,15 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
     mbar_init(bar_ptfree, 1);
     mbar_init(bar_out, 1);
     fence_mbar_init();
+    tma_prefetch_desc(&tm_dqkv);
+    mbar_arrive_expect_tx(bar_kv, 2 * CH);
+    tma_load_3d(sK, &tm_qkv, a.H + h * 64, kt * 128, b, bar_kv);
+    tma_load_3d(sV, &tm_qkv, 2 * a.H + h * 64, kt * 128, b, bar_kv);
+    for (int i = 0; i < 2 && i < N; ++i) {
+      mbar_arrive_expect_tx(&bar_ld[i], 2 * CH);
+      tma_load_3d(sQ + i * CH, &tm_qkv, h * 64, i * 128, b, &bar_ld[i]);
+      tma_load_3d(sdO + i * CH, &tm_dctx, h * 64, i * 128, b, &bar_ld[i]);
+    }
   }
   if (warp == CTRL_WARP) {
     tmem_alloc(tmem_slot, 512);
@@ -522,17 +619,11 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
   constexpr uint32_t COL_S = 0, COL_DP = 128, COL_DV = 256, COL_DK = 320;
 
   if (tid == ROW_THREADS) {
-    mbar_arrive_expect_tx(bar_kv, 2 * CH);
-    tma_load_3d(sK, &tm_qkv, a.H + h * 64, kt * 128, b, bar_kv);
-    tma_load_3d(sV, &tm_qkv, 2 * a.H + h * 64, kt * 128, b, bar_kv);
-    for (int i = 0; i < 2 && i < N; ++i) {
-      mbar_arrive_expect_tx(&bar_ld[i], 2 * CH);
-      tma_load_3d(sQ + i * CH, &tm_qkv, h * 64, i * 128, b, &bar_ld[i]);
-      tma_load_3d(sdO + i * CH, &tm_dctx, h * 64, i * 128, b, &bar_ld[i]);
-    }
     constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
     constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+    ATRACE(1);
     mbar_wait(bar_kv, 0);
+    ATRACE(2);
     for (int i = 0; i < N; ++i) {
       const int st = i & 1;
       mbar_wait(&bar_ld[st], (i >> 1) & 1);
@@ -576,6 +667,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
         named_bar_sync(1, ROW_THREADS);
       }
       mbar_wait(bar_s, i & 1);
+      if (tid == 0 && i == 0) ATRACE(4);
       tc_fence_after();
       uint32_t vs[32], vd[32];
       tmem_ld_32x32(lane_base + COL_S + qd * 32, vs);
@@ -584,6 +676,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
       tc_fence_before();
       mbar_arrive(bar_sfree);
       if (i >= 1) mbar_wait(bar_ptfree, (i - 1) & 1);
+      if (tid == 0 && i == 1) ATRACE(5);
       const int q0 = i * 128 + qd * 32;
       const uint32_t* keep_q = s_keep + (i & 1) * 512 + (qd * 32) * 4 + kword;
 #pragma unroll
@@ -615,21 +708,30 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
       tc_fence_before();
       mbar_arrive(bar_pt);
     }
+    if (tid == 0) ATRACE(6);
     mbar_wait(bar_out, 0);
+    if (tid == 0) ATRACE(7);
     tc_fence_after();
 #pragma unroll
     for (int c = 0; c < 2; ++c) {  // c = 0: dV, c = 1: dK (COL_DK = COL_DV + 64); 16 columns per thread
       uint32_t v[16];
       tmem_ld_32x16(lane_base + COL_DV + c * 64 + qd * 16, v);
       tmem_wait_ld();
-      if (key < S) {
-        float f[16];
+      float f[16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-        const int which = c == 0 ? 2 : 1;  // V block is the third H-wide slab of dqkv, K the second
-        st_row_bf16_16(a.dqkv + (static_cast<size_t>(b) * S + key) * 3 * a.H + which * a.H + h * 64 + qd * 16, f);
-      }
+      for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+      st_out16(c == 0 ? sPt : sdSt, r, qd, f);  // both operand buffers are free: every MMA has completed
     }
+    fence_proxy_async_smem();
+    named_bar_sync(1, ROW_THREADS);
+    if (tid == 0) {
+      // V block is the third H-wide slab of dqkv, K the second; rows beyond S are clipped by the map
+      tma_store_3d(&tm_dqkv, sPt, 2 * a.H + h * 64, kt * 128, b);
+      tma_store_3d(&tm_dqkv, sdSt, a.H + h * 64, kt * 128, b);
+      tma_commit_group();
+      tma_wait_group_read<0>();
+    }
+    if (tid == 0) ATRACE(8);
   }
 
   tc_fence_before();
@@ -638,6 +740,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
     tc_fence_after();
     tmem_dealloc(tmem, 512);
   }
+  if (tid == 0) ATRACE(9);
 }
 
 int fwd_smem_bytes(int n) { return CH * (5 + 2 * n) + 2048 + 4096 + 256 + 1024; }
@@ -694,10 +797,31 @@ int attn_plan(AttnPlan* plan, const AttnShape& s, const void* qkv, void* ctx, fl
   if (dctx != nullptr &&
       encode_tmap_3d(&plan->tm_dctx, dctx, 2, H, s.S, s.B, H, static_cast<uint64_t>(s.S) * H, 64, 128, 1))
     return 1;
+  if (ctx != nullptr &&
+      encode_tmap_3d(&plan->tm_ctx, ctx, 2, H, s.S, s.B, H, static_cast<uint64_t>(s.S) * H, 64, 128, 1))
+    return 1;
+  if (dqkv != nullptr &&
+      encode_tmap_3d(&plan->tm_dqkv, dqkv, 2, 3 * H, s.S, s.B, 3 * H, static_cast<uint64_t>(s.S) * 3 * H, 64, 128, 1))
+    return 1;
   return 0;
 }
 
-int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st) {
+int attn_make_keep_bits(const AttnPlan& plan, DropKey drop, cudaStream_t st) {
+  if (drop.thresh == 0u) return 0;
+  if (plan.keep == nullptr) {
+    set_error("attention: dropout needs the keep-bit buffer");
+    return 1;
+  }
+  const int rows = plan.shape.B * plan.shape.A * plan.shape.S;
+  const int wpr = attn_keep_words(plan.shape.S);
+  const size_t total = static_cast<size_t>(rows) * wpr;
+  int grid = static_cast<int>((total + 255) / 256);
+  if (grid > 148 * 16) grid = 148 * 16;
+  attn_keep_bits_kernel<<<grid, 256, 0, st>>>(plan.keep, rows, plan.shape.S, wpr, drop);
+  return check_launch("attn_keep_bits");
+}
+
+int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st, bool bits_ready) {
   static bool configured = false;
   if (!configured) {
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -707,16 +831,13 @@ int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cu
     configured = true;
   }
   const AttnArgs a = make_args(plan, key_mask, drop);
-  if (drop.thresh != 0u && plan.keep == nullptr) {
-    set_error("attention: dropout needs the keep-bit buffer");
-    return 1;
-  }
+  if (drop.thresh != 0u && !bits_ready && attn_make_keep_bits(plan, drop, st)) return 1;
   dim3 grid(plan.nchunk, plan.shape.A, plan.shape.B);
   const bool kb = key_mask != nullptr || (plan.shape.S % 128) != 0;
   if (kb)
-    attn_fwd_kernel<true><<<grid, ATT_THREADS, fwd_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, a);
+    attn_fwd_kernel<true><<<grid, ATT_THREADS, fwd_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_ctx, a);
   else
-    attn_fwd_kernel<false><<<grid, ATT_THREADS, fwd_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, a);
+    attn_fwd_kernel<false><<<grid, ATT_THREADS, fwd_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_ctx, a);
   return check_launch("attn_fwd");
 }
 
@@ -743,12 +864,20 @@ int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, c
   dim3 grid(plan.nchunk, plan.shape.A, plan.shape.B);
   const bool kb = key_mask != nullptr || (plan.shape.S % 128) != 0;
   if (kb)
-    attn_bwd_dq_kernel<true><<<grid, ATT_THREADS, dq_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_dctx, a);
+    attn_bwd_dq_kernel<true><<<grid, ATT_THREADS, dq_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_dctx,
+                                                                                     plan.tm_dqkv, a);
   else
-    attn_bwd_dq_kernel<false><<<grid, ATT_THREADS, dq_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_dctx, a);
+    attn_bwd_dq_kernel<false><<<grid, ATT_THREADS, dq_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_dctx,
+                                                                                      plan.tm_dqkv, a);
   if (check_launch("attn_bwd_dq")) return 1;
-  attn_bwd_dkv_kernel<<<grid, ATT_THREADS, dkv_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_dctx, a);
+  attn_bwd_dkv_kernel<<<grid, ATT_THREADS, dkv_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_dctx, plan.tm_dqkv, a);
   return check_launch("attn_bwd_dkv");
 }
 
 }  // namespace bqa
+
+#ifdef BQA_ATTN_TRACE
+extern "C" __attribute__((visibility("default"))) int bqa_trace_read(unsigned long long* host_out) {
+  return cudaMemcpyFromSymbol(host_out, bqa::g_attn_trace, sizeof(unsigned long long) * 4096 * 16) != cudaSuccess;
+}
+#endif

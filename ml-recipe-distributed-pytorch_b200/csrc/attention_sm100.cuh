@@ -16,6 +16,8 @@ struct AttnShape {
 struct AttnPlan {
   CUtensorMap tm_qkv;   // [B][S][3H] bf16, box {64,128,1}
   CUtensorMap tm_dctx;  // [B][S][H]  bf16, box {64,128,1}
+  CUtensorMap tm_ctx;   // [B][S][H]  bf16 (forward output, TMA store)
+  CUtensorMap tm_dqkv;  // [B][S][3H] bf16 (backward output, TMA store)
   AttnShape shape;
   int nchunk;     // ceil(S / 128)
   int tmem_cols;  // forward allocation (power of two >= 128 * nchunk)
@@ -33,8 +35,13 @@ int attn_plan(AttnPlan* plan, const AttnShape& s, const void* qkv, void* ctx, fl
               float* dsum, void* dqkv, uint32_t* keep);
 // 32-bit words of keep bits per (batch, head, query) row for sequence length S
 inline int attn_keep_words(int S) { return 4 * ((S + 127) / 128); }
-// key_mask: [B][S] uint8 (1 = attend) or null.  drop.thresh == 0 disables dropout.
-int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st);
+// Writes the dropout keep bits of one attention call (plan.keep).  The decisions depend only on the
+// key, so this can run ahead of / concurrently with whatever produces qkv.
+int attn_make_keep_bits(const AttnPlan& plan, DropKey drop, cudaStream_t st);
+// key_mask: [B][S] uint8 (1 = attend) or null.  drop.thresh == 0 disables dropout; otherwise plan.keep
+// must already hold this call's keep bits (bits_ready) or they are generated first on `st`.
+int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st,
+                 bool bits_ready = false);
 int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st);
 
 }  // namespace bqa

@@ -215,6 +215,11 @@ struct bqa_handle {
     double flops;
     int kind;  // 0 = GEMM forward, 1 = dgrad, 2 = wgrad, 3 = attention forward, 4 = attention backward
   };
+  // side stream on which the attention-dropout keep bits of all layers are generated while the main
+  // stream runs the embeddings and the first GEMMs (the decisions depend only on the step's keys)
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr;
+  std::vector<cudaEvent_t> ev_bits;
   bool profiling = false;
   std::vector<Timed> timed;
   std::vector<cudaEvent_t> event_pool;
@@ -440,6 +445,9 @@ int bqa_destroy(bqa_handle* h) {
       cudaEventDestroy(t.b);
     }
     for (auto e : h->event_pool) cudaEventDestroy(e);
+    for (auto e : h->ev_bits) cudaEventDestroy(e);
+    if (h->ev_fork != nullptr) cudaEventDestroy(h->ev_fork);
+    if (h->side != nullptr) cudaStreamDestroy(h->side);
   }
   delete h;
   return 0;
@@ -545,6 +553,22 @@ int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_ty
   h->has_mask = mask != nullptr;
   BQA_CUDA_CHECK(cudaMemsetAsync(w.err_flag, 0, sizeof(int), st));
 
+  const bool attn_drop = tr && c.attn_dropout > 0.0f;
+  if (attn_drop) {
+    if (h->side == nullptr) {
+      BQA_CUDA_CHECK(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
+      BQA_CUDA_CHECK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+      h->ev_bits.resize(c.num_layers);
+      for (auto& e : h->ev_bits) BQA_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    BQA_CUDA_CHECK(cudaEventRecord(h->ev_fork, st));  // everything that read last step's bits is behind us
+    BQA_CUDA_CHECK(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+    for (int l = 0; l < c.num_layers; ++l) {
+      if (attn_make_keep_bits(h->plan.layer[l].attn, h->key(site_attn(l), c.attn_dropout), h->side)) return 1;
+      BQA_CUDA_CHECK(cudaEventRecord(h->ev_bits[l], h->side));
+    }
+    h->launches += c.num_layers;
+  }
   if (launch_embed_ln_fwd(w.ids, w.tt, h->P(Y.word_emb), h->P(Y.pos_emb), h->P(Y.type_emb), h->P(Y.emb_ln_g),
                           h->P(Y.emb_ln_b), w.z0, w.x0, T, S, H, c.vocab, c.type_vocab, c.ln_eps,
                           h->key(site_embed(), c.hidden_dropout), w.err_flag, st))
@@ -557,8 +581,9 @@ int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_ty
     const LayerActs& act = w.layer[l % slots];
     const int64_t lo = h->layer_off(l);
     if (launch_gemm(h, lp.qkv, nodrop, st)) return 1;
+    if (attn_drop) BQA_CUDA_CHECK(cudaStreamWaitEvent(st, h->ev_bits[l], 0));
     h->time_begin(3, attn_flops(h, B, S, false), st);
-    if (attn_forward(lp.attn, mask, h->key(site_attn(l), c.attn_dropout), st)) return 1;
+    if (attn_forward(lp.attn, mask, h->key(site_attn(l), c.attn_dropout), st, /*bits_ready=*/true)) return 1;
     h->time_end(st);
     if (launch_gemm(h, lp.ao, h->key(site_ao(l), c.hidden_dropout), st)) return 1;
     if (launch_ln_fwd(act.z1, h->P(lo + Y.ln1_g), h->P(lo + Y.ln1_b), act.a, T, H, c.ln_eps, st)) return 1;
