@@ -154,6 +154,10 @@ attn_keep_bits_kernel(uint32_t* __restrict__ keep, int rows, int S, int words_pe
 // =========================================================================================
 // forward
 // =========================================================================================
+// Persistent: each CTA walks a contiguous range of (batch, head, query-tile) tiles, so that K and V
+// stay in shared memory across the query tiles of one (batch, head), the next tile's Q (and K) load
+// and its S = Q K^T overlap the current tile's epilogue, and TMEM / barriers are set up once.
+// Barrier phases are derived from the per-CTA tile counter `it`, never from local toggles.
 // KB: whether the additive key bias (padding mask / ragged last chunk) is needed
 template <bool KB>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
@@ -170,25 +174,35 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   float* xmax = kbias + 512;  // [4][128] row statistics exchanged between the four column quarters
   float* xsum = xmax + 512;
   uint64_t* bars = reinterpret_cast<uint64_t*>(xsum + 512);
-  uint64_t* bar_qk = bars + 0;
-  uint64_t* bar_v = bars + 1;
-  uint64_t* bar_s = bars + 2;
-  uint64_t* bar_o = bars + 3;
-  uint64_t* bar_p = bars + 4;      // [2]
-  uint64_t* bar_pfree = bars + 6;  // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* bar_q = bars + 0;
+  uint64_t* bar_k = bars + 1;
+  uint64_t* bar_v = bars + 2;
+  uint64_t* bar_s = bars + 3;
+  uint64_t* bar_o = bars + 4;
+  uint64_t* bar_ofree = bars + 5;
+  uint64_t* bar_p = bars + 6;      // [2]
+  uint64_t* bar_pfree = bars + 8;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
 
   const int tid = threadIdx.x, warp = tid >> 5;
-  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int S = a.S, Sp = N * 128;
+  const int tiles = a.B * a.A * N;
+  const int t0 = static_cast<int>(static_cast<long long>(blockIdx.x) * tiles / gridDim.x);
+  const int t1 = static_cast<int>(static_cast<long long>(blockIdx.x + 1) * tiles / gridDim.x);
+  // O accumulator: beside the scores when they leave 64 columns free, else aliased onto columns [0, 64)
+  const bool alias = Sp > 448;
+  const uint32_t o_col = alias ? 0u : static_cast<uint32_t>(Sp);
+  const int cnt0 = (N + 1) >> 1, cnt1 = N >> 1;  // uses of P buffer 0 / 1 per tile
   if (tid == 0) ATRACE(0);
 
   if (tid == ROW_THREADS) {
     tma_prefetch_desc(&tm_qkv);
-    mbar_init(bar_qk, 1);
+    mbar_init(bar_q, 1);
+    mbar_init(bar_k, 1);
     mbar_init(bar_v, 1);
     mbar_init(bar_s, 1);
     mbar_init(bar_o, 1);
+    mbar_init(bar_ofree, ROW_THREADS);
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bar_p[i], ROW_THREADS);
       mbar_init(&bar_pfree[i], 1);
@@ -196,21 +210,19 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     fence_mbar_init();
     // operand loads need nothing but the barriers: start them before the rest of the prologue
     tma_prefetch_desc(&tm_ctx);
-    mbar_arrive_expect_tx(bar_qk, (1 + N) * CH);
-    tma_load_3d(sQ, &tm_qkv, h * 64, qt * 128, b, bar_qk);
-    for (int c = 0; c < N; ++c) tma_load_3d(sK + c * CH, &tm_qkv, a.H + h * 64, c * 128, b, bar_qk);
-    mbar_arrive_expect_tx(bar_v, N * CH);
-    for (int c = 0; c < N; ++c) tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + h * 64, c * 128, b, bar_v);
+    if (t0 < t1) {
+      const int bh = t0 / N, qt = t0 - bh * N, b = bh / a.A, h = bh - b * a.A;
+      mbar_arrive_expect_tx(bar_q, CH);
+      tma_load_3d(sQ, &tm_qkv, h * 64, qt * 128, b, bar_q);
+      mbar_arrive_expect_tx(bar_k, N * CH);
+      for (int c = 0; c < N; ++c) tma_load_3d(sK + c * CH, &tm_qkv, a.H + h * 64, c * 128, b, bar_k);
+      mbar_arrive_expect_tx(bar_v, N * CH);
+      for (int c = 0; c < N; ++c) tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + h * 64, c * 128, b, bar_v);
+    }
   }
   if (warp == CTRL_WARP) {
     tmem_alloc(tmem_slot, a.tmem_cols);
     tmem_relinquish();
-  }
-  if (KB && tid < ROW_THREADS) {
-    for (int k = tid; k < Sp; k += ROW_THREADS) {
-      const bool ok = k < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + k] != 0);
-      kbias[k] = ok ? 0.0f : -INFINITY;
-    }
   }
   tc_fence_before();
   __syncthreads();
@@ -218,117 +230,164 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   const uint32_t tmem = *tmem_slot;
 
   if (tid == ROW_THREADS) {
-    // ---------------- control thread: MMA issue ----------------
+    // ---------------- control thread: TMA + MMA issue ----------------
     constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
     constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
-    ATRACE(1);
-    mbar_wait(bar_qk, 0);
-    ATRACE(2);
-    tc_fence_after();
-    for (int c = 0; c < N; ++c) mma_k64(tmem + c * 128, smem_u32(sQ), smem_u32(sK + c * CH), idesc_s);
-    umma_commit(bar_s);
-    mbar_wait(bar_v, 0);
-    ATRACE(3);
-    for (int j = 0; j < N; ++j) {
-      mbar_wait(&bar_p[j & 1], (j >> 1) & 1);
+    uint32_t kv_loads = 0;  // K/V loads waited so far
+    int prev_bh = -1;
+    for (int t = t0, it = 0; t < t1; ++t, ++it) {
+      const int bh = t / N;
+      const bool fresh = bh != prev_bh;
+      prev_bh = bh;
+      const bool has_next = t + 1 < t1;
+      const int nbh = (t + 1) / N, nqt = (t + 1) - nbh * N, nb = nbh / a.A, nh = nbh - nb * a.A;
+      const bool next_fresh = has_next && nbh != bh;
+      mbar_wait(bar_q, it & 1);
+      if (fresh) mbar_wait(bar_k, kv_loads & 1);
+      if (alias && it > 0) mbar_wait(bar_ofree, (it - 1) & 1);
       tc_fence_after();
-      mma_k128_mn(tmem, smem_u32(sP + (j & 1) * 2 * CH), smem_u32(sV + j * CH), idesc_o, j > 0);
-      umma_commit(&bar_pfree[j & 1]);
+      for (int c = 0; c < N; ++c) mma_k64(tmem + c * 128, smem_u32(sQ), smem_u32(sK + c * CH), idesc_s);
+      umma_commit(bar_s);
+      // Q (and K when the head changes) are free once the score MMAs have completed
+      mbar_wait(bar_s, it & 1);
+      if (has_next) {
+        mbar_arrive_expect_tx(bar_q, CH);
+        tma_load_3d(sQ, &tm_qkv, nh * 64, nqt * 128, nb, bar_q);
+        if (next_fresh) {
+          mbar_arrive_expect_tx(bar_k, N * CH);
+          for (int c = 0; c < N; ++c) tma_load_3d(sK + c * CH, &tm_qkv, a.H + nh * 64, c * 128, nb, bar_k);
+        }
+      }
+      if (fresh) {
+        mbar_wait(bar_v, kv_loads & 1);
+        ++kv_loads;
+      }
+      for (int j = 0; j < N; ++j) {
+        const uint32_t idx = static_cast<uint32_t>(it) * ((j & 1) ? cnt1 : cnt0) + (j >> 1);
+        mbar_wait(&bar_p[j & 1], idx & 1);
+        tc_fence_after();
+        mma_k128_mn(tmem + o_col, smem_u32(sP + (j & 1) * 2 * CH), smem_u32(sV + j * CH), idesc_o, j > 0);
+        umma_commit(&bar_pfree[j & 1]);
+      }
+      umma_commit(bar_o);
+      if (next_fresh) {
+        mbar_wait(bar_o, it & 1);  // V is still being read by the P V MMAs until then
+        mbar_arrive_expect_tx(bar_v, N * CH);
+        for (int c = 0; c < N; ++c) tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + nh * 64, c * 128, nb, bar_v);
+      }
     }
-    umma_commit(bar_o);
   } else if (tid < ROW_THREADS) {
     // ---- softmax threads: thread (r, qd) owns columns [32 qd, 32 qd + 32) of every 128-key chunk of row r
     const int r = tid & 127, qd = tid >> 7;
-    const int q = qt * 128 + r;
     const uint32_t lane_base = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     const uint32_t lane_addr = lane_base + qd * 32;
     const float sl2 = a.scale_log2;
-    mbar_wait(bar_s, 0);
-    if (tid == 0) ATRACE(4);
-    tc_fence_after();
-    float mx = -INFINITY;
-    for (int j = 0; j < N; ++j) {
-      uint32_t v[32];
-      tmem_ld_32x32(lane_addr + j * 128, v);
-      tmem_wait_ld();
-      if (KB) {
-        const float* kb = kbias + j * 128 + qd * 32;
-#pragma unroll
-        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaf(__uint_as_float(v[i]), sl2, kb[i]));
-      } else {
-#pragma unroll
-        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
-      }
-    }
-    if (!KB) mx *= sl2;
-    xmax[qd * 128 + r] = mx;
-    named_bar_sync(1, ROW_THREADS);
-    mx = fmaxf(fmaxf(xmax[r], xmax[128 + r]), fmaxf(xmax[256 + r], xmax[384 + r]));
-    if (mx == -INFINITY) mx = 0.0f;
-    if (tid == 0) ATRACE(5);
-    float l = 0.0f;
-    const uint32_t* keep_row = a.keep + ((static_cast<size_t>(b) * a.A + h) * S + (q < S ? q : 0)) * (4 * N) + qd;
-    uint32_t kw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-    if (a.drop.thresh != 0u) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if (j < N) kw[j] = __ldg(keep_row + j * 4);  // written by attn_keep_bits_kernel
-    }
-    for (int j = 0; j < N; ++j) {
-      uint8_t* tile = sP + (j & 1) * 2 * CH;
-      uint32_t v[32];
-      tmem_ld_32x32(lane_addr + j * 128, v);
-      tmem_wait_ld();
-      const int key0 = j * 128 + qd * 32;
-      const uint32_t bits = kw[j & 3];
-      if (j >= 2) mbar_wait(&bar_pfree[j & 1], ((j >> 1) - 1) & 1);
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        float p[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float x = KB ? fmaf(__uint_as_float(v[g * 8 + e]), sl2, kbias[key0 + g * 8 + e])
-                             : __uint_as_float(v[g * 8 + e]) * sl2;
-          const float pv = fast_exp2(x - mx);
-          l += pv;
-          p[e] = ((bits >> (g * 8 + e)) & 1u) ? pv * a.drop.scale : 0.0f;
+    int prev_b = -1;
+    for (int t = t0, it = 0; t < t1; ++t, ++it) {
+      const int bh = t / N, qt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
+      const int q = qt * 128 + r;
+      if (KB && b != prev_b) {
+        // every thread is past the previous tile's second pass (it has been through the xsum barrier)
+        for (int k = tid; k < Sp; k += ROW_THREADS) {
+          const bool ok = k < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + k] != 0);
+          kbias[k] = ok ? 0.0f : -INFINITY;
         }
-        st_tile16(tile, r, qd * 4 + g, p);
+        named_bar_sync(1, ROW_THREADS);
+        prev_b = b;
       }
-      fence_proxy_async_smem();
-      tc_fence_before();
-      mbar_arrive(&bar_p[j & 1]);
-    }
-    if (tid == 0) ATRACE(6);
-    xsum[qd * 128 + r] = l;
-    named_bar_sync(1, ROW_THREADS);
-    l = (xsum[r] + xsum[128 + r]) + (xsum[256 + r] + xsum[384 + r]);
-    mbar_wait(bar_o, 0);
-    if (tid == 0) ATRACE(7);
-    tc_fence_after();
-    const float inv = l > 0.0f ? 1.0f / l : 0.0f;
-    {
-      // O tile -> swizzled smem (the P buffers are free: every MMA has completed) -> one TMA store,
-      // which also clips the rows beyond S
-      uint32_t v[16];
-      tmem_ld_32x16(lane_base + qd * 16, v);
-      tmem_wait_ld();
-      float f[16];
+      const uint32_t* keep_row =
+          a.keep + ((static_cast<size_t>(b) * a.A + h) * S + (q < S ? q : 0)) * (4 * N) + qd;
+      uint32_t kw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+      if (a.drop.thresh != 0u) {
 #pragma unroll
-      for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]) * inv;
-      st_out16(sP, r, qd, f);
-      fence_proxy_async_smem();
-      named_bar_sync(1, ROW_THREADS);
-      if (tid == 0) {
-        tma_store_3d(&tm_ctx, sP, h * 64, qt * 128, b);
-        tma_commit_group();
-        tma_wait_group_read<0>();
+        for (int j = 0; j < 4; ++j)
+          if (j < N) kw[j] = __ldg(keep_row + j * 4);  // written by attn_keep_bits_kernel
       }
+      mbar_wait(bar_s, it & 1);
+      if (tid == 0) ATRACE(4);
+      tc_fence_after();
+      float mx = -INFINITY;
+      for (int j = 0; j < N; ++j) {
+        uint32_t v[32];
+        tmem_ld_32x32(lane_addr + j * 128, v);
+        tmem_wait_ld();
+        if (KB) {
+          const float* kb = kbias + j * 128 + qd * 32;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaf(__uint_as_float(v[i]), sl2, kb[i]));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+        }
+      }
+      if (!KB) mx *= sl2;
+      xmax[qd * 128 + r] = mx;
+      named_bar_sync(1, ROW_THREADS);
+      mx = fmaxf(fmaxf(xmax[r], xmax[128 + r]), fmaxf(xmax[256 + r], xmax[384 + r]));
+      if (mx == -INFINITY) mx = 0.0f;
+      if (tid == 0) ATRACE(5);
+      float l = 0.0f;
+      for (int j = 0; j < N; ++j) {
+        uint8_t* tile = sP + (j & 1) * 2 * CH;
+        uint32_t v[32];
+        tmem_ld_32x32(lane_addr + j * 128, v);
+        tmem_wait_ld();
+        const int key0 = j * 128 + qd * 32;
+        const uint32_t bits = kw[j & 3];
+        const uint32_t idx = static_cast<uint32_t>(it) * ((j & 1) ? cnt1 : cnt0) + (j >> 1);
+        if (idx > 0) mbar_wait(&bar_pfree[j & 1], (idx - 1) & 1);
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          float p[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float x = KB ? fmaf(__uint_as_float(v[g * 8 + e]), sl2, kbias[key0 + g * 8 + e])
+                               : __uint_as_float(v[g * 8 + e]) * sl2;
+            const float pv = fast_exp2(x - mx);
+            l += pv;
+            p[e] = ((bits >> (g * 8 + e)) & 1u) ? pv * a.drop.scale : 0.0f;
+          }
+          st_tile16(tile, r, qd * 4 + g, p);
+        }
+        fence_proxy_async_smem();
+        tc_fence_before();
+        mbar_arrive(&bar_p[j & 1]);
+      }
+      if (tid == 0) ATRACE(6);
+      xsum[qd * 128 + r] = l;
+      named_bar_sync(1, ROW_THREADS);
+      l = (xsum[r] + xsum[128 + r]) + (xsum[256 + r] + xsum[384 + r]);
+      mbar_wait(bar_o, it & 1);
+      if (tid == 0) ATRACE(7);
+      tc_fence_after();
+      const float inv = l > 0.0f ? 1.0f / l : 0.0f;
+      {
+        // O tile -> swizzled smem (P buffer 0 is free: every MMA of this tile has completed) -> one TMA
+        // store, which also clips the rows beyond S.  The next tile writes P only after its row-max
+        // barrier, which thread 0 joins after the store has finished reading.
+        uint32_t v[16];
+        tmem_ld_32x16(lane_base + o_col + qd * 16, v);
+        tmem_wait_ld();
+        tc_fence_before();
+        mbar_arrive(bar_ofree);
+        float f[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]) * inv;
+        st_out16(sP, r, qd, f);
+        fence_proxy_async_smem();
+        named_bar_sync(1, ROW_THREADS);
+        if (tid == 0) {
+          tma_store_3d(&tm_ctx, sP, h * 64, qt * 128, b);
+          tma_commit_group();
+          tma_wait_group_read<0>();
+        }
+      }
+      // a row whose keys are all masked has l == 0: store +inf so that the backward recomputes P = 0
+      if (q < S && qd == 0)
+        a.lse2[(static_cast<size_t>(b) * a.A + h) * S + q] = l > 0.0f ? mx + log2f(l) : INFINITY;
+      if (tid == 0) ATRACE(8);
     }
-    // a row whose keys are all masked has l == 0: store +inf so that the backward recomputes P = 0
-    if (q < S && qd == 0)
-      a.lse2[(static_cast<size_t>(b) * a.A + h) * S + q] = l > 0.0f ? mx + log2f(l) : INFINITY;
-    if (tid == 0) ATRACE(8);
+    if (tid == 0) tma_wait_group<0>();
   }
 
   tc_fence_before();
@@ -337,15 +396,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     tc_fence_after();
     tmem_dealloc(tmem, a.tmem_cols);
   }
-  if (tid == 0) {
-    ATRACE(9);
-#ifdef BQA_ATTN_TRACE
-    unsigned smid;
-    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-    const unsigned bl = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
-    if (bl < 4096) g_attn_trace[bl * 16 + 15] = smid;
-#endif
-  }
+  if (tid == 0) ATRACE(9);
 }
 
 // =========================================================================================
@@ -781,7 +832,8 @@ int attn_plan(AttnPlan* plan, const AttnShape& s, const void* qkv, void* ctx, fl
   }
   plan->shape = s;
   plan->nchunk = (s.S + 127) / 128;
-  const int cols = plan->nchunk * 128;
+  // forward: the scores plus, when they leave room, 64 columns for the output accumulator
+  const int cols = plan->nchunk * 128 > 448 ? 512 : plan->nchunk * 128 + 64;
   plan->tmem_cols = cols <= 128 ? 128 : (cols <= 256 ? 256 : 512);
   plan->qkv = reinterpret_cast<const bf16*>(qkv);
   plan->ctx = reinterpret_cast<bf16*>(ctx);
@@ -832,7 +884,10 @@ int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cu
   }
   const AttnArgs a = make_args(plan, key_mask, drop);
   if (drop.thresh != 0u && !bits_ready && attn_make_keep_bits(plan, drop, st)) return 1;
-  dim3 grid(plan.nchunk, plan.shape.A, plan.shape.B);
+  int sms = 0;
+  if (device_sm_count(&sms)) return 1;
+  const int tiles = plan.nchunk * plan.shape.A * plan.shape.B;
+  const int grid = tiles < sms ? tiles : sms;  // persistent: contiguous tile ranges per CTA
   const bool kb = key_mask != nullptr || (plan.shape.S % 128) != 0;
   if (kb)
     attn_fwd_kernel<true><<<grid, ATT_THREADS, fwd_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_ctx, a);

@@ -20,7 +20,7 @@ struct AttnPlan {
   CUtensorMap tm_dqkv;  // [B][S][3H] bf16 (backward output, TMA store)
   AttnShape shape;
   int nchunk;     // ceil(S / 128)
-  int tmem_cols;  // forward allocation (power of two >= 128 * nchunk)
+  int tmem_cols;  // forward allocation (power of two holding the scores and, if it fits, the output)
   const bf16* qkv;
   bf16* ctx;
   float* lse2;   // [B][A][S] log2-domain log-sum-exp of the scaled, masked scores

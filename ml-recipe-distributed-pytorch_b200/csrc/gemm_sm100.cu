@@ -30,22 +30,24 @@ constexpr int BLOCK_K = 64;
 constexpr int TMEM_COLS = 512;
 constexpr int NUM_THREADS = 384;
 constexpr int EPI_THREADS = 256;
-constexpr int C_STAGE_BYTES = 128 * 128;  // 128 rows x 128 B (64 bf16 or 32 fp32)
+constexpr int W_STAGE_BYTES = 32 * 128;  // one epilogue warp's staging buffer: 32 rows x 128 B (64 bf16 or 32 fp32)
 constexpr int SMEM_BARRIER_BYTES = 256;
 
 // NCTA = 1: one CTA computes a 128 x 256 tile.  NCTA = 2: a CTA pair (cluster of 2, cta_group::2)
 // computes a 256 x 256 tile; each CTA stages its own 128 rows of A and 128 of the 256 rows of B,
 // so operand traffic per SM drops by a third and the ring can be deeper.
-template <int NCTA>
+template <int NCTA, int EPI>
 struct Cfg {
   static constexpr int BLOCK_M = 128 * NCTA;             // rows of the (pair) tile
   static constexpr int B_ROWS = BLOCK_N / NCTA;          // B rows staged by one CTA
   static constexpr int A_STAGE_BYTES = 128 * BLOCK_K * 2;
   static constexpr int B_STAGE_BYTES = B_ROWS * BLOCK_K * 2;
-  static constexpr int STAGES = NCTA == 2 ? 6 : 4;       // TMA -> MMA ring depth
-  static constexpr int CSTAGES = 2;                      // epilogue staging buffers (TMA store ring)
-  static constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + CSTAGES * C_STAGE_BYTES +
-                                    SMEM_BARRIER_BYTES;
+  // per-warp epilogue staging: one 32 x 128 B buffer per output
+  static constexpr int WARP_STAGE_BYTES = W_STAGE_BYTES * (EPI == EPI_GELU_FWD ? 2 : 1);
+  static constexpr int C_BYTES = 8 * WARP_STAGE_BYTES;
+  // TMA -> MMA ring depth: whatever the staging buffers leave of the 227 KiB
+  static constexpr int STAGES = (NCTA == 2 ? 6 : 4) - (EPI == EPI_GELU_FWD ? 1 : 0);
+  static constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + C_BYTES + SMEM_BARRIER_BYTES;
   static constexpr int SMEM_ALLOC = SMEM_BYTES + 1024;   // slack for manual 1024-byte alignment
   static_assert(SMEM_ALLOC <= 232448, "exceeds the 227 KiB per-CTA shared memory limit");
 };
@@ -53,15 +55,15 @@ struct Cfg {
 template <int A_MN, int B_MN, int EPI, int NCTA>
 __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
                                           const CUtensorMap& tmC2, const GemmArgs& args) {
-  using C = Cfg<NCTA>;
-  constexpr int STAGES = C::STAGES, CSTAGES = C::CSTAGES;
+  using C = Cfg<NCTA, EPI>;
+  constexpr int STAGES = C::STAGES;
   constexpr int A_STAGE_BYTES = C::A_STAGE_BYTES, B_STAGE_BYTES = C::B_STAGE_BYTES, BLOCK_M = C::BLOCK_M;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sA = smem;
   uint8_t* sB = sA + STAGES * A_STAGE_BYTES;
   uint8_t* sC = sB + STAGES * B_STAGE_BYTES;
-  uint64_t* bar_full = reinterpret_cast<uint64_t*>(sC + CSTAGES * C_STAGE_BYTES);
+  uint64_t* bar_full = reinterpret_cast<uint64_t*>(sC + C::C_BYTES);
   uint64_t* bar_empty = bar_full + STAGES;
   uint64_t* bar_tfull = bar_empty + STAGES;
   uint64_t* bar_tempty = bar_tfull + 2;
@@ -192,95 +194,83 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     }
   } else if (warp >= 4) {
     // ------------------------------ epilogue ------------------------------
-    // 8 warps: warp w may read TMEM lanes 32*(w%4)..+31; the two warps sharing a lane quarter split
-    // every column chunk in halves, so each accumulator row is drained by two threads.
+    // 8 independent warps.  Warp w may read TMEM lanes 32*(w%4)..+31; the two warps of a lane quarter
+    // take one 128-column half of the tile each.  A warp drains its 32 x 128 block in 32-column pieces
+    // through its own staging buffer (32 rows x 128 B) and issues its own TMA stores, so there is no
+    // CTA-wide barrier in the loop and the warps hide each other's TMEM / global / store latencies.
     const int ew = warp & 3;                  // TMEM lane quarter
     const int cg = (warp - 4) >> 2;           // column half handled by this warp (0 / 1)
     const int row = ew * 32 + lane;           // accumulator row owned by this thread
-    const bool leader = (threadIdx.x == NUM_THREADS - EPI_THREADS);
     const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(ew * 32) << 16);
-    constexpr int CHUNK_COLS = (EPI == EPI_F32_ADD) ? 32 : 64;  // 128 bytes of output per row
-    constexpr int TCOLS = CHUNK_COLS / 2;                       // columns per thread per chunk
-    constexpr int NCHUNK = BLOCK_N / CHUNK_COLS;
+    uint8_t* stage0 = sC + (warp - 4) * C::WARP_STAGE_BYTES;
+    uint8_t* stage1 = stage0 + W_STAGE_BYTES;  // second output of the GELU epilogue
+    uint8_t* srow = stage0 + lane * 128;
+    const int sw = lane & 7;                  // SWIZZLE_128B: 16-byte unit j of row r lives at unit j ^ (r & 7)
     uint32_t it = 0;
-    uint32_t nstore = 0;  // staging-buffer ring position (EPI with a single output)
     for (int tile = tile0; tile < num_tiles; tile += tile_step, ++it) {
       const int split = tile / tiles_mn;
       const int mn = tile - split * tiles_mn;
       const int m0 = (mn / args.n_tiles) * BLOCK_M + static_cast<int>(rank) * 128;  // rows held in this CTA's TMEM
-      const int n0 = (mn % args.n_tiles) * BLOCK_N;
+      const int n0 = (mn % args.n_tiles) * BLOCK_N + cg * 128;                       // this warp's first column
       const uint32_t as = it & 1u;
       const uint32_t aphase = (it >> 1) & 1u;
-      mbar_wait(&bar_tfull[as], aphase);
-      tc_fence_after();
       const int m = m0 + row;
       const bool row_ok = m < args.M;
-#pragma unroll 1
-      for (int c = 0; c < NCHUNK; ++c) {
-        // staging ring: a buffer (pair of buffers for the two-output epilogue) is reused only after the
-        // TMA store that read it has drained
-        uint8_t* stage0;
-        uint8_t* stage1 = nullptr;
-        if (EPI == EPI_GELU_FWD) {
-          constexpr int PAIRS = CSTAGES / 2;
-          if (leader) tma_wait_group_read<PAIRS - 1>();
-          stage0 = sC + (nstore % PAIRS) * 2 * C_STAGE_BYTES;
-          stage1 = stage0 + C_STAGE_BYTES;
-          ++nstore;
-        } else {
-          if (leader) tma_wait_group_read<CSTAGES - 1>();
-          stage0 = sC + (nstore % CSTAGES) * C_STAGE_BYTES;
-          ++nstore;
-        }
-        // operand of the fused elementwise op: issue its loads now, they land while the staging barrier
-        // and the TMEM load are waited on
-        uint4 side[TCOLS / 8];
-        bool side_ok = false;
-        {
-          const int nn = n0 + c * CHUNK_COLS + cg * TCOLS;
-          const bf16* sp = nullptr;
-          if (EPI == EPI_LINEAR && args.residual != nullptr) sp = args.residual + static_cast<size_t>(m) * args.ld_res + nn;
-          if (EPI == EPI_GELU_BWD) sp = args.aux + static_cast<size_t>(m) * args.ld_aux + nn;
-          side_ok = sp != nullptr && row_ok && nn < args.N;
-          if (side_ok) {
+      // operand of the fused elementwise op (residual / gelu'): one piece ahead of its use, the first
+      // piece before the accumulator is waited for
+      const bf16* side_row = nullptr;
+      if (EPI == EPI_LINEAR && args.residual != nullptr && row_ok) side_row = args.residual + static_cast<size_t>(m) * args.ld_res;
+      if (EPI == EPI_GELU_BWD && row_ok) side_row = args.aux + static_cast<size_t>(m) * args.ld_aux;
+      uint4 side[4];
+      bool side_ok = side_row != nullptr && n0 < args.N;
+      if (side_ok) {
 #pragma unroll
-            for (int q = 0; q < TCOLS / 8; ++q) side[q] = __ldg(reinterpret_cast<const uint4*>(sp) + q);
+        for (int q = 0; q < 4; ++q) side[q] = __ldg(reinterpret_cast<const uint4*>(side_row + n0) + q);
+      }
+      mbar_wait(&bar_tfull[as], aphase);
+      tc_fence_after();
+#pragma unroll
+      for (int piece = 0; piece < 4; ++piece) {
+        const int n = n0 + piece * 32;
+        uint32_t v[32];
+        tmem_ld_32x32(lane_base + as * BLOCK_N + cg * 128 + piece * 32, v);
+        uint4 nside[4];
+        bool nside_ok = false;
+        if (piece < 3) {
+          nside_ok = side_row != nullptr && n + 32 < args.N;
+          if (nside_ok) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) nside[q] = __ldg(reinterpret_cast<const uint4*>(side_row + n + 32) + q);
           }
         }
-        named_bar_sync(1, EPI_THREADS);
-        float f[TCOLS];
-        {
-          uint32_t v[TCOLS];
-          const uint32_t taddr = lane_base + as * BLOCK_N + c * CHUNK_COLS + cg * TCOLS;
-          if (TCOLS == 32) {
-            tmem_ld_32x32(taddr, reinterpret_cast<uint32_t(&)[32]>(v));
-          } else {
-            tmem_ld_32x16(taddr, reinterpret_cast<uint32_t(&)[16]>(v));
-          }
-          tmem_wait_ld();
-#pragma unroll
-          for (int i = 0; i < TCOLS; ++i) f[i] = __uint_as_float(v[i]);
-        }
-        if (c == NCHUNK - 1) {
+        tmem_wait_ld();
+        if (piece == 3) {
           // accumulator fully drained into registers: hand the TMEM stage back to the MMA warp
           tc_fence_before();
           if (NCTA == 2 && rank != 0) mbar_arrive_cluster(&bar_tempty[as], 0);
           else mbar_arrive(&bar_tempty[as]);
         }
-        const int n = n0 + c * CHUNK_COLS + cg * TCOLS;
+        float f[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
 
         if (EPI == EPI_F32_ADD) {
+          if (lane == 0) tma_wait_group_read<0>();
+          __syncwarp();
 #pragma unroll
-          for (int q = 0; q < TCOLS / 4; ++q) {
-            float4 o = make_float4(f[4 * q], f[4 * q + 1], f[4 * q + 2], f[4 * q + 3]);
-            const int j = cg * (TCOLS / 4) + q;
-            *reinterpret_cast<float4*>(stage0 + row * 128 + ((j ^ (row & 7)) << 4)) = o;
+          for (int q = 0; q < 8; ++q)
+            *reinterpret_cast<float4*>(srow + ((q ^ sw) << 4)) = make_float4(f[4 * q], f[4 * q + 1], f[4 * q + 2], f[4 * q + 3]);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (n < args.N) tma_reduce_add_2d(&tmC, stage0, n, m0 + ew * 32);
+            tma_commit_group();
           }
         } else {
           if (EPI != EPI_GELU_BWD && args.bias != nullptr && n < args.N) {
             const float4* bp = reinterpret_cast<const float4*>(args.bias + n);
 #pragma unroll
-            for (int q = 0; q < TCOLS / 4; ++q) {
+            for (int q = 0; q < 8; ++q) {
               const float4 b = __ldg(bp + q);
               f[4 * q] += b.x;
               f[4 * q + 1] += b.y;
@@ -293,7 +283,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
               const uint32_t base_idx = static_cast<uint32_t>(m) * static_cast<uint32_t>(args.N) +
                                         static_cast<uint32_t>(n);  // even: N and n are even
 #pragma unroll
-              for (int i = 0; i < TCOLS; i += 2) {
+              for (int i = 0; i < 32; i += 2) {
                 bool k0, k1;
                 drop_keep2(args.drop, base_idx + i, k0, k1);
                 f[i] = k0 ? f[i] * args.drop.scale : 0.0f;
@@ -302,7 +292,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
             }
             if (side_ok) {
 #pragma unroll
-              for (int q = 0; q < TCOLS / 8; ++q) {
+              for (int q = 0; q < 4; ++q) {
                 const uint4 r = side[q];
                 const float2 r0 = unpack_bf16x2(r.x), r1 = unpack_bf16x2(r.y);
                 const float2 r2 = unpack_bf16x2(r.z), r3 = unpack_bf16x2(r.w);
@@ -321,7 +311,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
             // aux holds gelu'(pre-activation), written by the forward GEMM's epilogue
             if (side_ok) {
 #pragma unroll
-              for (int q = 0; q < TCOLS / 8; ++q) {
+              for (int q = 0; q < 4; ++q) {
                 const uint4 r = side[q];
                 const float2 u0 = unpack_bf16x2(r.x), u1 = unpack_bf16x2(r.y);
                 const float2 u2 = unpack_bf16x2(r.z), u3 = unpack_bf16x2(r.w);
@@ -336,57 +326,63 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
               }
             }
           }
+          // two pieces fill one 128-byte staging row; the buffer is reused once the previous store has
+          // finished reading it
+          if ((piece & 1) == 0) {
+            if (lane == 0) tma_wait_group_read<0>();
+            __syncwarp();
+          }
           if (EPI == EPI_GELU_FWD) {
             // one evaluation of the shared core gives the activation (second output) and its
             // derivative (first output, consumed by the dgrad epilogue instead of recomputing it)
-            float gv[TCOLS];
 #pragma unroll
-            for (int i = 0; i < TCOLS; ++i) {
-              float g, dg;
-              gelu_and_grad(f[i], g, dg);
-              gv[i] = g;
-              f[i] = dg;
-            }
+            for (int q = 0; q < 4; ++q) {
+              float gv[8];
 #pragma unroll
-            for (int q = 0; q < TCOLS / 8; ++q) {
+              for (int e = 0; e < 8; ++e) {
+                float dg;
+                gelu_and_grad(f[8 * q + e], gv[e], dg);
+                f[8 * q + e] = dg;
+              }
               uint4 o;
-              o.x = pack_bf16x2(gv[8 * q], gv[8 * q + 1]);
-              o.y = pack_bf16x2(gv[8 * q + 2], gv[8 * q + 3]);
-              o.z = pack_bf16x2(gv[8 * q + 4], gv[8 * q + 5]);
-              o.w = pack_bf16x2(gv[8 * q + 6], gv[8 * q + 7]);
-              const int j = cg * (TCOLS / 8) + q;
-              *reinterpret_cast<uint4*>(stage1 + row * 128 + ((j ^ (row & 7)) << 4)) = o;
+              o.x = pack_bf16x2(gv[0], gv[1]);
+              o.y = pack_bf16x2(gv[2], gv[3]);
+              o.z = pack_bf16x2(gv[4], gv[5]);
+              o.w = pack_bf16x2(gv[6], gv[7]);
+              *reinterpret_cast<uint4*>(srow + W_STAGE_BYTES + ((((piece & 1) * 4 + q) ^ sw) << 4)) = o;
             }
           }
           // bf16 pack, swizzled like the TMA store expects (SWIZZLE_128B)
 #pragma unroll
-          for (int q = 0; q < TCOLS / 8; ++q) {
+          for (int q = 0; q < 4; ++q) {
             uint4 o;
             o.x = pack_bf16x2(f[8 * q], f[8 * q + 1]);
             o.y = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
             o.z = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]);
             o.w = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
-            const int j = cg * (TCOLS / 8) + q;
-            *reinterpret_cast<uint4*>(stage0 + row * 128 + ((j ^ (row & 7)) << 4)) = o;
+            *reinterpret_cast<uint4*>(srow + ((((piece & 1) * 4 + q) ^ sw) << 4)) = o;
           }
-        }
-        fence_proxy_async_smem();
-        named_bar_sync(1, EPI_THREADS);
-        if (leader) {
-          const int nc = n0 + c * CHUNK_COLS;
-          if (nc < args.N) {
-            if (EPI == EPI_F32_ADD) {
-              tma_reduce_add_2d(&tmC, stage0, nc, m0);
-            } else {
-              tma_store_2d(&tmC, stage0, nc, m0);
-              if (EPI == EPI_GELU_FWD) tma_store_2d(&tmC2, stage1, nc, m0);
+          if (piece & 1) {
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              const int nc = n - 32;
+              if (nc < args.N) {
+                tma_store_2d(&tmC, stage0, nc, m0 + ew * 32);
+                if (EPI == EPI_GELU_FWD) tma_store_2d(&tmC2, stage1, nc, m0 + ew * 32);
+              }
+              tma_commit_group();
             }
           }
-          tma_commit_group();
+        }
+        if (piece < 3) {
+          side_ok = nside_ok;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) side[q] = nside[q];
         }
       }
     }
-    if (leader) tma_wait_group<0>();
+    if (lane == 0) tma_wait_group<0>();
   }
 
   tc_fence_before();
@@ -436,8 +432,8 @@ int launch_variant(const GemmPlan& plan, cudaStream_t stream) {
   auto k1 = gemm_kernel<A_MN, B_MN, EPI>;
   auto k2 = gemm_pair_kernel<A_MN, B_MN, EPI>;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<1>::SMEM_ALLOC);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<2>::SMEM_ALLOC);
+    cudaError_t e = cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<1, EPI>::SMEM_ALLOC);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<2, EPI>::SMEM_ALLOC);
     if (e != cudaSuccess) {
       set_error("gemm: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
       return 1;
@@ -445,9 +441,9 @@ int launch_variant(const GemmPlan& plan, cudaStream_t stream) {
     configured = true;
   }
   if (plan.pair)
-    k2<<<plan.grid, NUM_THREADS, Cfg<2>::SMEM_ALLOC, stream>>>(plan.tmA, plan.tmB, plan.tmC, plan.tmC2, plan.args);
+    k2<<<plan.grid, NUM_THREADS, Cfg<2, EPI>::SMEM_ALLOC, stream>>>(plan.tmA, plan.tmB, plan.tmC, plan.tmC2, plan.args);
   else
-    k1<<<plan.grid, NUM_THREADS, Cfg<1>::SMEM_ALLOC, stream>>>(plan.tmA, plan.tmB, plan.tmC, plan.tmC2, plan.args);
+    k1<<<plan.grid, NUM_THREADS, Cfg<1, EPI>::SMEM_ALLOC, stream>>>(plan.tmA, plan.tmB, plan.tmC, plan.tmC2, plan.args);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("gemm: launch failed: %s", cudaGetErrorString(e));
@@ -549,15 +545,15 @@ int gemm_plan(GemmPlan* plan, const GemmProblem& p, int num_sms) {
   else
     rc |= encode_tmap_2d(&plan->tmB, p.B, 2, p.K, p.N, p.ldb, BLOCK_K, b_rows);
   if (p.epilogue == EPI_F32_ADD)
-    rc |= encode_tmap_2d(&plan->tmC, p.C, 4, p.N, p.M, p.ldc, 32, 128);
+    rc |= encode_tmap_2d(&plan->tmC, p.C, 4, p.N, p.M, p.ldc, 32, 32);
   else
-    rc |= encode_tmap_2d(&plan->tmC, p.C, 2, p.N, p.M, p.ldc, 64, 128);
+    rc |= encode_tmap_2d(&plan->tmC, p.C, 2, p.N, p.M, p.ldc, 64, 32);
   if (p.epilogue == EPI_GELU_FWD) {
     if (p.C2 == nullptr) {
       set_error("gemm: EPI_GELU_FWD needs a second output");
       return 1;
     }
-    rc |= encode_tmap_2d(&plan->tmC2, p.C2, 2, p.N, p.M, p.ldc, 64, 128);
+    rc |= encode_tmap_2d(&plan->tmC2, p.C2, 2, p.N, p.M, p.ldc, 64, 32);
   } else {
     plan->tmC2 = plan->tmC;
   }
