@@ -430,6 +430,10 @@ attn_dsum_kernel(const bf16* __restrict__ ctx, const bf16* __restrict__ dctx, fl
 // =========================================================================================
 // backward, dQ
 // =========================================================================================
+// Persistent like the forward: contiguous (batch, head, query-tile) ranges per CTA, K and V kept in
+// shared memory across the query tiles of a (batch, head), the next tile's Q / dO loaded as soon as the
+// last score MMAs of the current tile have completed.  Chunk-level barriers are indexed by the running
+// chunk counter g = it * N + j.
 template <bool KB>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
 attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_dctx,
@@ -439,28 +443,33 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
   const int N = a.nchunk;
   uint8_t* sQ = smem;
   uint8_t* sdO = sQ + CH;
-  uint8_t* sK = sdO + CH;
+  uint8_t* sOut = sdO + CH;  // dQ tile staged for the TMA store
+  uint8_t* sK = sOut + CH;
   uint8_t* sV = sK + N * CH;
   uint8_t* sdS = sV + N * CH;  // 2 * CH
   float* kbias = reinterpret_cast<float*>(sdS + 2 * CH);
   uint64_t* bars = reinterpret_cast<uint64_t*>(kbias + 512);
-  uint64_t* bar_ld = bars + 0;
-  uint64_t* bar_s = bars + 1;
-  uint64_t* bar_sfree = bars + 2;
-  uint64_t* bar_ds = bars + 3;
-  uint64_t* bar_dsfree = bars + 4;
-  uint64_t* bar_dq = bars + 5;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 6);
+  uint64_t* bar_qo = bars + 0;
+  uint64_t* bar_kv = bars + 1;
+  uint64_t* bar_s = bars + 2;
+  uint64_t* bar_sfree = bars + 3;
+  uint64_t* bar_ds = bars + 4;
+  uint64_t* bar_dsfree = bars + 5;
+  uint64_t* bar_dq = bars + 6;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 7);
 
   const int tid = threadIdx.x, warp = tid >> 5;
-  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int S = a.S, Sp = N * 128;
+  const int tiles = a.B * a.A * N;
+  const int t0 = static_cast<int>(static_cast<long long>(blockIdx.x) * tiles / gridDim.x);
+  const int t1 = static_cast<int>(static_cast<long long>(blockIdx.x + 1) * tiles / gridDim.x);
   if (tid == 0) ATRACE(0);
 
   if (tid == ROW_THREADS) {
     tma_prefetch_desc(&tm_qkv);
     tma_prefetch_desc(&tm_dctx);
-    mbar_init(bar_ld, 1);
+    mbar_init(bar_qo, 1);
+    mbar_init(bar_kv, 1);
     mbar_init(bar_s, 1);
     mbar_init(bar_sfree, ROW_THREADS);
     mbar_init(bar_ds, ROW_THREADS);
@@ -468,23 +477,21 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
     mbar_init(bar_dq, 1);
     fence_mbar_init();
     tma_prefetch_desc(&tm_dqkv);
-    mbar_arrive_expect_tx(bar_ld, (2 + 2 * N) * CH);
-    tma_load_3d(sQ, &tm_qkv, h * 64, qt * 128, b, bar_ld);
-    tma_load_3d(sdO, &tm_dctx, h * 64, qt * 128, b, bar_ld);
-    for (int c = 0; c < N; ++c) {
-      tma_load_3d(sK + c * CH, &tm_qkv, a.H + h * 64, c * 128, b, bar_ld);
-      tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + h * 64, c * 128, b, bar_ld);
+    if (t0 < t1) {
+      const int bh = t0 / N, qt = t0 - bh * N, b = bh / a.A, h = bh - b * a.A;
+      mbar_arrive_expect_tx(bar_qo, 2 * CH);
+      tma_load_3d(sQ, &tm_qkv, h * 64, qt * 128, b, bar_qo);
+      tma_load_3d(sdO, &tm_dctx, h * 64, qt * 128, b, bar_qo);
+      mbar_arrive_expect_tx(bar_kv, 2 * N * CH);
+      for (int c = 0; c < N; ++c) {
+        tma_load_3d(sK + c * CH, &tm_qkv, a.H + h * 64, c * 128, b, bar_kv);
+        tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + h * 64, c * 128, b, bar_kv);
+      }
     }
   }
   if (warp == CTRL_WARP) {
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
-  }
-  if (KB && tid < ROW_THREADS) {
-    for (int k = tid; k < Sp; k += ROW_THREADS) {
-      const bool ok = k < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + k] != 0);
-      kbias[k] = ok ? 0.0f : -INFINITY;
-    }
   }
   tc_fence_before();
   __syncthreads();
@@ -495,97 +502,144 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
   if (tid == ROW_THREADS) {
     constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
     constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
-    ATRACE(1);
-    mbar_wait(bar_ld, 0);
-    ATRACE(2);
-    tc_fence_after();
-    mma_k64(tmem + COL_S, smem_u32(sQ), smem_u32(sK), idesc_s);
-    mma_k64(tmem + COL_DP, smem_u32(sdO), smem_u32(sV), idesc_s);
-    umma_commit(bar_s);
-    for (int j = 0; j < N; ++j) {
-      if (j + 1 < N) {
-        mbar_wait(bar_sfree, j & 1);
-        tc_fence_after();
-        mma_k64(tmem + COL_S, smem_u32(sQ), smem_u32(sK + (j + 1) * CH), idesc_s);
-        mma_k64(tmem + COL_DP, smem_u32(sdO), smem_u32(sV + (j + 1) * CH), idesc_s);
-        umma_commit(bar_s);
+    uint32_t kv_loads = 0;
+    int prev_bh = -1;
+    for (int t = t0, it = 0; t < t1; ++t, ++it) {
+      const int bh = t / N;
+      const bool fresh = bh != prev_bh;
+      prev_bh = bh;
+      const bool has_next = t + 1 < t1;
+      const int nbh = (t + 1) / N, nqt = (t + 1) - nbh * N, nb = nbh / a.A, nh = nbh - nb * a.A;
+      const bool next_fresh = has_next && nbh != bh;
+      const uint32_t g0 = static_cast<uint32_t>(it) * N;
+      mbar_wait(bar_qo, it & 1);
+      if (fresh) {
+        mbar_wait(bar_kv, kv_loads & 1);
+        ++kv_loads;
       }
-      mbar_wait(bar_ds, j & 1);
+      if (it > 0) mbar_wait(bar_sfree, (g0 - 1) & 1);  // previous tile's last scores are in registers
       tc_fence_after();
-      mma_k128_mn(tmem + COL_DQ, smem_u32(sdS), smem_u32(sK + j * CH), idesc_o, j > 0);
-      umma_commit(bar_dsfree);
+      mma_k64(tmem + COL_S, smem_u32(sQ), smem_u32(sK), idesc_s);
+      mma_k64(tmem + COL_DP, smem_u32(sdO), smem_u32(sV), idesc_s);
+      umma_commit(bar_s);
+      for (int j = 0; j < N; ++j) {
+        const uint32_t g = g0 + j;
+        if (j + 1 < N) {
+          mbar_wait(bar_sfree, g & 1);
+          tc_fence_after();
+          mma_k64(tmem + COL_S, smem_u32(sQ), smem_u32(sK + (j + 1) * CH), idesc_s);
+          mma_k64(tmem + COL_DP, smem_u32(sdO), smem_u32(sV + (j + 1) * CH), idesc_s);
+          umma_commit(bar_s);
+        } else if (has_next) {
+          // the tile's last score MMAs have completed: Q and dO can be replaced
+          mbar_wait(bar_s, g & 1);
+          mbar_arrive_expect_tx(bar_qo, 2 * CH);
+          tma_load_3d(sQ, &tm_qkv, nh * 64, nqt * 128, nb, bar_qo);
+          tma_load_3d(sdO, &tm_dctx, nh * 64, nqt * 128, nb, bar_qo);
+        }
+        mbar_wait(bar_ds, g & 1);
+        tc_fence_after();
+        mma_k128_mn(tmem + COL_DQ, smem_u32(sdS), smem_u32(sK + j * CH), idesc_o, j > 0);
+        umma_commit(bar_dsfree);
+      }
+      umma_commit(bar_dq);
+      if (next_fresh) {
+        mbar_wait(bar_dq, it & 1);  // K is read by the dQ MMAs until then
+        mbar_arrive_expect_tx(bar_kv, 2 * N * CH);
+        for (int c = 0; c < N; ++c) {
+          tma_load_3d(sK + c * CH, &tm_qkv, a.H + nh * 64, c * 128, nb, bar_kv);
+          tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + nh * 64, c * 128, nb, bar_kv);
+        }
+      }
     }
-    umma_commit(bar_dq);
   } else if (tid < ROW_THREADS) {
     const int r = tid & 127, qd = tid >> 7;
-    const int q = qt * 128 + r;
     const uint32_t lane_base = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     const float sl2 = a.scale_log2;
-    const bool q_ok = q < S;
-    const size_t stat = (static_cast<size_t>(b) * a.A + h) * S + (q_ok ? q : 0);
-    const float lse = q_ok ? a.lse2[stat] : INFINITY;
-    const float dsum = q_ok ? a.dsum[stat] : 0.0f;
     const bool dropping = a.drop.thresh != 0u;
-    uint32_t kw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-    if (dropping) {
-      const uint32_t* keep_row = a.keep + stat * (4 * N) + qd;
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if (j < N) kw[j] = __ldg(keep_row + j * 4);
-    }
-    for (int j = 0; j < N; ++j) {
-      mbar_wait(bar_s, j & 1);
-      if (tid == 0 && j == 0) ATRACE(4);
-      tc_fence_after();
-      uint32_t vs[32], vd[32];
-      tmem_ld_32x32(lane_base + COL_S + qd * 32, vs);
-      tmem_ld_32x32(lane_base + COL_DP + qd * 32, vd);
-      tmem_wait_ld();
-      tc_fence_before();
-      mbar_arrive(bar_sfree);
-      if (j >= 1) mbar_wait(bar_dsfree, (j - 1) & 1);
-      if (tid == 0 && j == 1) ATRACE(5);
-      const int key0 = j * 128 + qd * 32;
-      const uint32_t bits = kw[j & 3];
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        float ds[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float x = KB ? fmaf(__uint_as_float(vs[g * 8 + e]), sl2, kbias[key0 + g * 8 + e])
-                             : __uint_as_float(vs[g * 8 + e]) * sl2;
-          const float p = fast_exp2(x - lse);
-          float dp = __uint_as_float(vd[g * 8 + e]);
-          if (dropping) dp = ((bits >> (g * 8 + e)) & 1u) ? dp * a.drop.scale : 0.0f;
-          ds[e] = p * (dp - dsum) * a.scale;
+    int prev_b = -1;
+    for (int t = t0, it = 0; t < t1; ++t, ++it) {
+      const int bh = t / N, qt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
+      const int q = qt * 128 + r;
+      const uint32_t g0 = static_cast<uint32_t>(it) * N;
+      if (KB && b != prev_b) {
+        named_bar_sync(1, ROW_THREADS);  // nobody still reads the previous batch row's bias
+        for (int k = tid; k < Sp; k += ROW_THREADS) {
+          const bool ok = k < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + k] != 0);
+          kbias[k] = ok ? 0.0f : -INFINITY;
         }
-        st_tile16(sdS, r, qd * 4 + g, ds);
+        named_bar_sync(1, ROW_THREADS);
+        prev_b = b;
       }
-      fence_proxy_async_smem();
-      tc_fence_before();
-      mbar_arrive(bar_ds);
-    }
-    if (tid == 0) ATRACE(6);
-    mbar_wait(bar_dq, 0);
-    if (tid == 0) ATRACE(7);
-    tc_fence_after();
-    {
-      uint32_t v[16];
-      tmem_ld_32x16(lane_base + COL_DQ + qd * 16, v);
-      tmem_wait_ld();
-      float f[16];
+      const bool q_ok = q < S;
+      const size_t stat = (static_cast<size_t>(b) * a.A + h) * S + (q_ok ? q : 0);
+      const float lse = q_ok ? a.lse2[stat] : INFINITY;
+      const float dsum = q_ok ? a.dsum[stat] : 0.0f;
+      uint32_t kw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+      if (dropping) {
+        const uint32_t* keep_row = a.keep + stat * (4 * N) + qd;
 #pragma unroll
-      for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-      st_out16(sdS, r, qd, f);  // sdS is free: every MMA has completed
-      fence_proxy_async_smem();
-      named_bar_sync(1, ROW_THREADS);
-      if (tid == 0) {
-        tma_store_3d(&tm_dqkv, sdS, h * 64, qt * 128, b);  // Q slab of dqkv; rows beyond S are clipped
-        tma_commit_group();
-        tma_wait_group_read<0>();
+        for (int j = 0; j < 4; ++j)
+          if (j < N) kw[j] = __ldg(keep_row + j * 4);
       }
+      for (int j = 0; j < N; ++j) {
+        const uint32_t g = g0 + j;
+        mbar_wait(bar_s, g & 1);
+        if (tid == 0 && j == 0) ATRACE(4);
+        tc_fence_after();
+        uint32_t vs[32], vd[32];
+        tmem_ld_32x32(lane_base + COL_S + qd * 32, vs);
+        tmem_ld_32x32(lane_base + COL_DP + qd * 32, vd);
+        tmem_wait_ld();
+        tc_fence_before();
+        mbar_arrive(bar_sfree);
+        if (g >= 1) mbar_wait(bar_dsfree, (g - 1) & 1);
+        if (tid == 0 && j == 1) ATRACE(5);
+        const int key0 = j * 128 + qd * 32;
+        const uint32_t bits = kw[j & 3];
+#pragma unroll
+        for (int gq = 0; gq < 4; ++gq) {
+          float ds[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float x = KB ? fmaf(__uint_as_float(vs[gq * 8 + e]), sl2, kbias[key0 + gq * 8 + e])
+                               : __uint_as_float(vs[gq * 8 + e]) * sl2;
+            const float p = fast_exp2(x - lse);
+            float dp = __uint_as_float(vd[gq * 8 + e]);
+            if (dropping) dp = ((bits >> (gq * 8 + e)) & 1u) ? dp * a.drop.scale : 0.0f;
+            ds[e] = p * (dp - dsum) * a.scale;
+          }
+          st_tile16(sdS, r, qd * 4 + gq, ds);
+        }
+        fence_proxy_async_smem();
+        tc_fence_before();
+        mbar_arrive(bar_ds);
+      }
+      if (tid == 0) ATRACE(6);
+      mbar_wait(bar_dq, it & 1);
+      if (tid == 0) ATRACE(7);
+      tc_fence_after();
+      {
+        uint32_t v[16];
+        tmem_ld_32x16(lane_base + COL_DQ + qd * 16, v);
+        tmem_wait_ld();
+        float f[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+        // the previous tile's store must have finished reading the staging buffer
+        if (tid == 0) tma_wait_group_read<0>();
+        named_bar_sync(1, ROW_THREADS);
+        st_out16(sOut, r, qd, f);
+        fence_proxy_async_smem();
+        named_bar_sync(1, ROW_THREADS);
+        if (tid == 0) {
+          tma_store_3d(&tm_dqkv, sOut, h * 64, qt * 128, b);  // Q slab of dqkv; rows beyond S are clipped
+          tma_commit_group();
+        }
+      }
+      if (tid == 0) ATRACE(8);
     }
-    if (tid == 0) ATRACE(8);
+    if (tid == 0) tma_wait_group_read<0>();
   }
 
   tc_fence_before();
@@ -600,6 +654,9 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
 // =========================================================================================
 // backward, dK and dV (rows = keys)
 // =========================================================================================
+// Persistent: contiguous (batch, head, key-tile) ranges per CTA.  The Q / dO chunks stream through a
+// 2-stage ring that keeps running across tile boundaries (chunk counter g = it * N + i), the next
+// tile's K / V are fetched once the current tile's last score MMAs have completed.
 __global__ void __launch_bounds__(ATT_THREADS, 1)
 attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_dctx,
                     const __grid_constant__ CUtensorMap tm_dqkv, const AttnArgs a) {
@@ -612,7 +669,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
   uint8_t* sdO = sQ + 2 * CH;  // 2 stages
   uint8_t* sPt = sdO + 2 * CH;   // 2 * CH
   uint8_t* sdSt = sPt + 2 * CH;  // 2 * CH
-  float* s_lse = reinterpret_cast<float*>(sdSt + 2 * CH);
+  uint8_t* sOut = sdSt + 2 * CH;  // 2 * CH: dV and dK tiles staged for the TMA stores
+  float* s_lse = reinterpret_cast<float*>(sOut + 2 * CH);
   float* s_dsum = s_lse + 512;
   uint32_t* s_keep = reinterpret_cast<uint32_t*>(s_dsum + 512);  // [2][128 queries][4 words]
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_keep + 1024);
@@ -626,9 +684,28 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
 
   const int tid = threadIdx.x, warp = tid >> 5;
-  const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int S = a.S, Sp = N * 128;
+  const int tiles = a.B * a.A * N;
+  const int t0 = static_cast<int>(static_cast<long long>(blockIdx.x) * tiles / gridDim.x);
+  const int t1 = static_cast<int>(static_cast<long long>(blockIdx.x + 1) * tiles / gridDim.x);
+  const uint32_t chunks = static_cast<uint32_t>(t1 - t0) * N;  // Q / dO chunks this CTA streams
   if (tid == 0) ATRACE(0);
+
+  // chunk g of this CTA's stream -> TMA coordinates of its Q / dO rows
+  auto load_chunk = [&](uint32_t g) {
+    const int t = t0 + static_cast<int>(g) / N, i = static_cast<int>(g) % N;
+    const int bh = t / N, b = bh / a.A, h = bh - b * a.A;
+    const int st = g & 1;
+    mbar_arrive_expect_tx(&bar_ld[st], 2 * CH);
+    tma_load_3d(sQ + st * CH, &tm_qkv, h * 64, i * 128, b, &bar_ld[st]);
+    tma_load_3d(sdO + st * CH, &tm_dctx, h * 64, i * 128, b, &bar_ld[st]);
+  };
+  auto load_kv = [&](int t) {
+    const int bh = t / N, kt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
+    mbar_arrive_expect_tx(bar_kv, 2 * CH);
+    tma_load_3d(sK, &tm_qkv, a.H + h * 64, kt * 128, b, bar_kv);
+    tma_load_3d(sV, &tm_qkv, 2 * a.H + h * 64, kt * 128, b, bar_kv);
+  };
 
   if (tid == ROW_THREADS) {
     tma_prefetch_desc(&tm_qkv);
@@ -643,25 +720,14 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
     mbar_init(bar_out, 1);
     fence_mbar_init();
     tma_prefetch_desc(&tm_dqkv);
-    mbar_arrive_expect_tx(bar_kv, 2 * CH);
-    tma_load_3d(sK, &tm_qkv, a.H + h * 64, kt * 128, b, bar_kv);
-    tma_load_3d(sV, &tm_qkv, 2 * a.H + h * 64, kt * 128, b, bar_kv);
-    for (int i = 0; i < 2 && i < N; ++i) {
-      mbar_arrive_expect_tx(&bar_ld[i], 2 * CH);
-      tma_load_3d(sQ + i * CH, &tm_qkv, h * 64, i * 128, b, &bar_ld[i]);
-      tma_load_3d(sdO + i * CH, &tm_dctx, h * 64, i * 128, b, &bar_ld[i]);
+    if (t0 < t1) {
+      load_kv(t0);
+      for (uint32_t g = 0; g < 2 && g < chunks; ++g) load_chunk(g);
     }
   }
   if (warp == CTRL_WARP) {
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
-  }
-  if (tid < ROW_THREADS) {
-    const size_t stat = (static_cast<size_t>(b) * a.A + h) * S;
-    for (int k = tid; k < Sp; k += ROW_THREADS) {
-      s_lse[k] = k < S ? a.lse2[stat + k] : INFINITY;
-      s_dsum[k] = k < S ? a.dsum[stat + k] : 0.0f;
-    }
   }
   tc_fence_before();
   __syncthreads();
@@ -672,117 +738,142 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
   if (tid == ROW_THREADS) {
     constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
     constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
-    ATRACE(1);
-    mbar_wait(bar_kv, 0);
-    ATRACE(2);
-    for (int i = 0; i < N; ++i) {
-      const int st = i & 1;
-      mbar_wait(&bar_ld[st], (i >> 1) & 1);
-      if (i > 0) mbar_wait(bar_sfree, (i - 1) & 1);
-      tc_fence_after();
-      mma_k64(tmem + COL_S, smem_u32(sK), smem_u32(sQ + st * CH), idesc_s);
-      mma_k64(tmem + COL_DP, smem_u32(sV), smem_u32(sdO + st * CH), idesc_s);
-      umma_commit(bar_s);
-      mbar_wait(bar_pt, i & 1);
-      tc_fence_after();
-      mma_k128_mn(tmem + COL_DV, smem_u32(sPt), smem_u32(sdO + st * CH), idesc_o, i > 0);
-      mma_k128_mn(tmem + COL_DK, smem_u32(sdSt), smem_u32(sQ + st * CH), idesc_o, i > 0);
-      umma_commit(bar_ptfree);
-      if (i + 2 < N) {
-        // stage `st` is re-filled only after every MMA that reads it has completed
-        mbar_wait(bar_ptfree, i & 1);
-        mbar_arrive_expect_tx(&bar_ld[st], 2 * CH);
-        tma_load_3d(sQ + st * CH, &tm_qkv, h * 64, (i + 2) * 128, b, &bar_ld[st]);
-        tma_load_3d(sdO + st * CH, &tm_dctx, h * 64, (i + 2) * 128, b, &bar_ld[st]);
+    for (int t = t0, it = 0; t < t1; ++t, ++it) {
+      const uint32_t g0 = static_cast<uint32_t>(it) * N;
+      mbar_wait(bar_kv, it & 1);
+      for (int i = 0; i < N; ++i) {
+        const uint32_t g = g0 + i;
+        const int st = g & 1;
+        mbar_wait(&bar_ld[st], (g >> 1) & 1);
+        if (g > 0) mbar_wait(bar_sfree, (g - 1) & 1);
+        tc_fence_after();
+        mma_k64(tmem + COL_S, smem_u32(sK), smem_u32(sQ + st * CH), idesc_s);
+        mma_k64(tmem + COL_DP, smem_u32(sV), smem_u32(sdO + st * CH), idesc_s);
+        umma_commit(bar_s);
+        if (i == N - 1 && t + 1 < t1) {
+          // the tile's last score MMAs have completed: K and V can be replaced
+          mbar_wait(bar_s, g & 1);
+          load_kv(t + 1);
+        }
+        mbar_wait(bar_pt, g & 1);
+        tc_fence_after();
+        mma_k128_mn(tmem + COL_DV, smem_u32(sPt), smem_u32(sdO + st * CH), idesc_o, i > 0);
+        mma_k128_mn(tmem + COL_DK, smem_u32(sdSt), smem_u32(sQ + st * CH), idesc_o, i > 0);
+        umma_commit(bar_ptfree);
+        if (i == N - 1) umma_commit(bar_out);
+        if (g + 2 < chunks) {
+          // stage `st` is re-filled only after every MMA that reads it has completed
+          mbar_wait(bar_ptfree, g & 1);
+          load_chunk(g + 2);
+        }
       }
     }
-    umma_commit(bar_out);
   } else if (tid < ROW_THREADS) {
     const int r = tid & 127, qd = tid >> 7;
-    const int key = kt * 128 + r;
     const uint32_t lane_base = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     const float sl2 = a.scale_log2;
-    const bool key_ok = key < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + key] != 0);
-    const float kb = key_ok ? 0.0f : -INFINITY;
     const bool dropping = a.drop.thresh != 0u;
     const uint32_t kbit = static_cast<uint32_t>(r & 31);
     const int kword = r >> 5;
-    const size_t keep_base = (static_cast<size_t>(b) * a.A + h) * S;
-    for (int i = 0; i < N; ++i) {
-      if (dropping) {
-        // stage this query chunk's keep words for the 128 keys of the tile: [query][4 words]
-        const int ql = tid >> 2, w = tid & 3;
-        const int qq = i * 128 + ql;
-        s_keep[(i & 1) * 512 + ql * 4 + w] =
-            qq < S ? __ldg(a.keep + (keep_base + qq) * (4 * N) + kt * 4 + w) : 0u;
-        named_bar_sync(1, ROW_THREADS);
-      }
-      mbar_wait(bar_s, i & 1);
-      if (tid == 0 && i == 0) ATRACE(4);
-      tc_fence_after();
-      uint32_t vs[32], vd[32];
-      tmem_ld_32x32(lane_base + COL_S + qd * 32, vs);
-      tmem_ld_32x32(lane_base + COL_DP + qd * 32, vd);
-      tmem_wait_ld();
-      tc_fence_before();
-      mbar_arrive(bar_sfree);
-      if (i >= 1) mbar_wait(bar_ptfree, (i - 1) & 1);
-      if (tid == 0 && i == 1) ATRACE(5);
-      const int q0 = i * 128 + qd * 32;
-      const uint32_t* keep_q = s_keep + (i & 1) * 512 + (qd * 32) * 4 + kword;
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        float pt[8], ds[8];
-        const float4 l0 = *reinterpret_cast<const float4*>(s_lse + q0 + g * 8);
-        const float4 l1 = *reinterpret_cast<const float4*>(s_lse + q0 + g * 8 + 4);
-        const float4 d0 = *reinterpret_cast<const float4*>(s_dsum + q0 + g * 8);
-        const float4 d1 = *reinterpret_cast<const float4*>(s_dsum + q0 + g * 8 + 4);
-        const float lsev[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w};
-        const float dsv[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float p = fast_exp2(fmaf(__uint_as_float(vs[g * 8 + e]), sl2, kb) - lsev[e]);
-          float dp = __uint_as_float(vd[g * 8 + e]);
-          float pd = p;
-          if (dropping) {
-            const bool keep = (keep_q[(g * 8 + e) * 4] >> kbit) & 1u;
-            pd = keep ? p * a.drop.scale : 0.0f;
-            dp = keep ? dp * a.drop.scale : 0.0f;
-          }
-          pt[e] = pd;
-          ds[e] = p * (dp - dsv[e]) * a.scale;
+    int prev_bh = -1;
+    for (int t = t0, it = 0; t < t1; ++t, ++it) {
+      const int bh = t / N, kt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
+      const uint32_t g0 = static_cast<uint32_t>(it) * N;
+      const int key = kt * 128 + r;
+      const bool key_ok = key < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + key] != 0);
+      const float kb = key_ok ? 0.0f : -INFINITY;
+      const size_t keep_base = static_cast<size_t>(bh) * S;
+      if (bh != prev_bh) {
+        // row statistics of every query of this (batch, head); the previous tile's epilogue barriers
+        // guarantee that nobody still reads the old ones
+        const size_t stat = static_cast<size_t>(bh) * S;
+        for (int k = tid; k < Sp; k += ROW_THREADS) {
+          s_lse[k] = k < S ? a.lse2[stat + k] : INFINITY;
+          s_dsum[k] = k < S ? a.dsum[stat + k] : 0.0f;
         }
-        st_tile16(sPt, r, qd * 4 + g, pt);
-        st_tile16(sdSt, r, qd * 4 + g, ds);
+        named_bar_sync(1, ROW_THREADS);
+        prev_bh = bh;
+      }
+      for (int i = 0; i < N; ++i) {
+        const uint32_t g = g0 + i;
+        if (dropping) {
+          // stage this query chunk's keep words for the 128 keys of the tile: [query][4 words]
+          const int ql = tid >> 2, w = tid & 3;
+          const int qq = i * 128 + ql;
+          s_keep[(g & 1) * 512 + ql * 4 + w] =
+              qq < S ? __ldg(a.keep + (keep_base + qq) * (4 * N) + kt * 4 + w) : 0u;
+          named_bar_sync(1, ROW_THREADS);
+        }
+        mbar_wait(bar_s, g & 1);
+        if (tid == 0 && i == 0) ATRACE(4);
+        tc_fence_after();
+        uint32_t vs[32], vd[32];
+        tmem_ld_32x32(lane_base + COL_S + qd * 32, vs);
+        tmem_ld_32x32(lane_base + COL_DP + qd * 32, vd);
+        tmem_wait_ld();
+        tc_fence_before();
+        mbar_arrive(bar_sfree);
+        if (g >= 1) mbar_wait(bar_ptfree, (g - 1) & 1);
+        if (tid == 0 && i == 1) ATRACE(5);
+        const int q0 = i * 128 + qd * 32;
+        const uint32_t* keep_q = s_keep + (g & 1) * 512 + (qd * 32) * 4 + kword;
+#pragma unroll
+        for (int gq = 0; gq < 4; ++gq) {
+          float pt[8], ds[8];
+          const float4 l0 = *reinterpret_cast<const float4*>(s_lse + q0 + gq * 8);
+          const float4 l1 = *reinterpret_cast<const float4*>(s_lse + q0 + gq * 8 + 4);
+          const float4 d0 = *reinterpret_cast<const float4*>(s_dsum + q0 + gq * 8);
+          const float4 d1 = *reinterpret_cast<const float4*>(s_dsum + q0 + gq * 8 + 4);
+          const float lsev[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w};
+          const float dsv[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float p = fast_exp2(fmaf(__uint_as_float(vs[gq * 8 + e]), sl2, kb) - lsev[e]);
+            float dp = __uint_as_float(vd[gq * 8 + e]);
+            float pd = p;
+            if (dropping) {
+              const bool keep = (keep_q[(gq * 8 + e) * 4] >> kbit) & 1u;
+              pd = keep ? p * a.drop.scale : 0.0f;
+              dp = keep ? dp * a.drop.scale : 0.0f;
+            }
+            pt[e] = pd;
+            ds[e] = p * (dp - dsv[e]) * a.scale;
+          }
+          st_tile16(sPt, r, qd * 4 + gq, pt);
+          st_tile16(sdSt, r, qd * 4 + gq, ds);
+        }
+        fence_proxy_async_smem();
+        tc_fence_before();
+        mbar_arrive(bar_pt);
+      }
+      if (tid == 0) ATRACE(6);
+      mbar_wait(bar_out, it & 1);
+      if (tid == 0) ATRACE(7);
+      tc_fence_after();
+      // the previous tile's stores must have finished reading the staging buffers
+      if (tid == 0) tma_wait_group_read<0>();
+      named_bar_sync(1, ROW_THREADS);
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {  // c = 0: dV, c = 1: dK (COL_DK = COL_DV + 64); 16 columns per thread
+        uint32_t v[16];
+        tmem_ld_32x16(lane_base + COL_DV + c * 64 + qd * 16, v);
+        tmem_wait_ld();
+        float f[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+        st_out16(sOut + c * CH, r, qd, f);
       }
       fence_proxy_async_smem();
-      tc_fence_before();
-      mbar_arrive(bar_pt);
+      named_bar_sync(1, ROW_THREADS);
+      if (tid == 0) {
+        // V block is the third H-wide slab of dqkv, K the second; rows beyond S are clipped by the map
+        tma_store_3d(&tm_dqkv, sOut, 2 * a.H + h * 64, kt * 128, b);
+        tma_store_3d(&tm_dqkv, sOut + CH, a.H + h * 64, kt * 128, b);
+        tma_commit_group();
+      }
+      if (tid == 0) ATRACE(8);
     }
-    if (tid == 0) ATRACE(6);
-    mbar_wait(bar_out, 0);
-    if (tid == 0) ATRACE(7);
-    tc_fence_after();
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {  // c = 0: dV, c = 1: dK (COL_DK = COL_DV + 64); 16 columns per thread
-      uint32_t v[16];
-      tmem_ld_32x16(lane_base + COL_DV + c * 64 + qd * 16, v);
-      tmem_wait_ld();
-      float f[16];
-#pragma unroll
-      for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-      st_out16(c == 0 ? sPt : sdSt, r, qd, f);  // both operand buffers are free: every MMA has completed
-    }
-    fence_proxy_async_smem();
-    named_bar_sync(1, ROW_THREADS);
-    if (tid == 0) {
-      // V block is the third H-wide slab of dqkv, K the second; rows beyond S are clipped by the map
-      tma_store_3d(&tm_dqkv, sPt, 2 * a.H + h * 64, kt * 128, b);
-      tma_store_3d(&tm_dqkv, sdSt, a.H + h * 64, kt * 128, b);
-      tma_commit_group();
-      tma_wait_group_read<0>();
-    }
-    if (tid == 0) ATRACE(8);
+    if (tid == 0) tma_wait_group_read<0>();
   }
 
   tc_fence_before();
@@ -795,8 +886,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
 }
 
 int fwd_smem_bytes(int n) { return CH * (5 + 2 * n) + 2048 + 4096 + 256 + 1024; }
-int dq_smem_bytes(int n) { return CH * (4 + 2 * n) + 2048 + 256 + 1024; }
-int dkv_smem_bytes() { return CH * 10 + 4096 + 4096 + 256 + 1024; }
+int dq_smem_bytes(int n) { return CH * (5 + 2 * n) + 2048 + 256 + 1024; }
+int dkv_smem_bytes() { return CH * 12 + 4096 + 4096 + 256 + 1024; }
 
 AttnArgs make_args(const AttnPlan& p, const uint8_t* key_mask, DropKey drop) {
   AttnArgs a;
@@ -916,7 +1007,10 @@ int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, c
   attn_dsum_kernel<<<(T + 3) / 4, 128, 0, st>>>(plan.ctx, plan.dctx, plan.dsum, plan.shape.B, plan.shape.S,
                                                plan.shape.A, plan.shape.H);
   if (check_launch("attn_dsum")) return 1;
-  dim3 grid(plan.nchunk, plan.shape.A, plan.shape.B);
+  int sms = 0;
+  if (device_sm_count(&sms)) return 1;
+  const int tiles = plan.nchunk * plan.shape.A * plan.shape.B;
+  const int grid = tiles < sms ? tiles : sms;  // persistent: contiguous tile ranges per CTA
   const bool kb = key_mask != nullptr || (plan.shape.S % 128) != 0;
   if (kb)
     attn_bwd_dq_kernel<true><<<grid, ATT_THREADS, dq_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_dctx,
