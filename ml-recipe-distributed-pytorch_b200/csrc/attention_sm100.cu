@@ -19,6 +19,8 @@
 // Dropout decisions are the stateless hash of (batch, head, query, key), identical in all kernels.
 #include "attention_sm100.cuh"
 
+#include <type_traits>
+
 #include "bqa_host.cuh"
 #include "gemm_sm100.cuh"
 #include "kernels.cuh"
@@ -87,6 +89,11 @@ __device__ __forceinline__ void st_tile16(uint8_t* tile, int r, int c16, const f
   *reinterpret_cast<uint4*>(tile + (c16 >> 3) * CH + r * 128 + (((c16 & 7) ^ (r & 7)) << 4)) = o;
 }
 
+// same, from already packed bf16 pairs
+__device__ __forceinline__ void st_tile16p(uint8_t* tile, int r, int c16, uint4 o) {
+  *reinterpret_cast<uint4*>(tile + (c16 >> 3) * CH + r * 128 + (((c16 & 7) ^ (r & 7)) << 4)) = o;
+}
+
 __device__ __forceinline__ void st_row_bf16_16(bf16* dst, const float* f) {
 #pragma unroll
   for (int q = 0; q < 2; ++q) {
@@ -114,6 +121,16 @@ __device__ __forceinline__ void st_out16(uint8_t* tile, int r, int qd, const flo
 }
 
 __device__ __forceinline__ uint8_t* align1024(uint8_t* p) { return p + ((1024u - (smem_u32(p) & 1023u)) & 1023u); }
+
+// additive key bias (0 / -inf) of batch row b and, per 32 keys, the bit mask of attended keys.
+// Called by the ROW_THREADS (= 512 >= Sp) softmax threads, whole warps.
+__device__ __forceinline__ void fill_key_bias(float* kbias, uint32_t* kvalid, const uint8_t* key_mask, int b, int S,
+                                              int Sp, int tid) {
+  const bool ok = tid < S && (key_mask == nullptr || key_mask[static_cast<size_t>(b) * S + tid] != 0);
+  if (tid < Sp) kbias[tid] = ok ? 0.0f : -INFINITY;
+  const uint32_t w = __ballot_sync(0xffffffffu, ok);
+  if ((tid & 31) == 0) kvalid[tid >> 5] = w;
+}
 
 // keep decisions for the 32 consecutive elements starting at `idx`, one bit each
 __device__ __forceinline__ uint32_t keep_bits32(const DropKey& dk, uint32_t idx) {
@@ -183,6 +200,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   uint64_t* bar_p = bars + 6;      // [2]
   uint64_t* bar_pfree = bars + 8;  // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+  uint32_t* kvalid = reinterpret_cast<uint32_t*>(bars + 16);  // [16] bit k of word w: key 32 w + k is attended
 
   const int tid = threadIdx.x, warp = tid >> 5;
   const int S = a.S, Sp = N * 128;
@@ -288,10 +306,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       const int q = qt * 128 + r;
       if (KB && b != prev_b) {
         // every thread is past the previous tile's second pass (it has been through the xsum barrier)
-        for (int k = tid; k < Sp; k += ROW_THREADS) {
-          const bool ok = k < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + k] != 0);
-          kbias[k] = ok ? 0.0f : -INFINITY;
-        }
+        fill_key_bias(kbias, kvalid, a.key_mask, b, S, Sp, tid);
         named_bar_sync(1, ROW_THREADS);
         prev_b = b;
       }
@@ -306,21 +321,22 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       mbar_wait(bar_s, it & 1);
       if (tid == 0) ATRACE(4);
       tc_fence_after();
-      float mx = -INFINITY;
+      // 32-key groups without a masked key (all of them unless KB) take the path without the bias
+      float mx = -INFINITY, mraw = -INFINITY;
       for (int j = 0; j < N; ++j) {
         uint32_t v[32];
         tmem_ld_32x32(lane_addr + j * 128, v);
         tmem_wait_ld();
-        if (KB) {
+        if (KB && kvalid[j * 4 + qd] != 0xffffffffu) {
           const float* kb = kbias + j * 128 + qd * 32;
 #pragma unroll
           for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaf(__uint_as_float(v[i]), sl2, kb[i]));
         } else {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+          for (int i = 0; i < 32; ++i) mraw = fmaxf(mraw, __uint_as_float(v[i]));
         }
       }
-      if (!KB) mx *= sl2;
+      mx = fmaxf(mx, mraw * sl2);
       xmax[qd * 128 + r] = mx;
       named_bar_sync(1, ROW_THREADS);
       mx = fmaxf(fmaxf(xmax[r], xmax[128 + r]), fmaxf(xmax[256 + r], xmax[384 + r]));
@@ -336,19 +352,23 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         const uint32_t bits = kw[j & 3];
         const uint32_t idx = static_cast<uint32_t>(it) * ((j & 1) ? cnt1 : cnt0) + (j >> 1);
         if (idx > 0) mbar_wait(&bar_pfree[j & 1], (idx - 1) & 1);
+        auto chunk = [&](auto biased) {
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          float p[8];
+          for (int g = 0; g < 4; ++g) {
+            float p[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const float x = KB ? fmaf(__uint_as_float(v[g * 8 + e]), sl2, kbias[key0 + g * 8 + e])
-                               : __uint_as_float(v[g * 8 + e]) * sl2;
-            const float pv = fast_exp2(x - mx);
-            l += pv;
-            p[e] = ((bits >> (g * 8 + e)) & 1u) ? pv * a.drop.scale : 0.0f;
+            for (int e = 0; e < 8; ++e) {
+              const float x = decltype(biased)::value
+                                  ? fmaf(__uint_as_float(v[g * 8 + e]), sl2, kbias[key0 + g * 8 + e])
+                                  : __uint_as_float(v[g * 8 + e]) * sl2;
+              const float pv = fast_exp2(x - mx);
+              l += pv;
+              p[e] = ((bits >> (g * 8 + e)) & 1u) ? pv * a.drop.scale : 0.0f;
+            }
+            st_tile16(tile, r, qd * 4 + g, p);
           }
-          st_tile16(tile, r, qd * 4 + g, p);
-        }
+        };
+        if (KB && kvalid[j * 4 + qd] != 0xffffffffu) chunk(std::true_type{}); else chunk(std::false_type{});
         fence_proxy_async_smem();
         tc_fence_before();
         mbar_arrive(&bar_p[j & 1]);
@@ -457,6 +477,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
   uint64_t* bar_dsfree = bars + 5;
   uint64_t* bar_dq = bars + 6;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 7);
+  uint32_t* kvalid = reinterpret_cast<uint32_t*>(bars + 16);  // [16] bit k of word w: key 32 w + k is attended
 
   const int tid = threadIdx.x, warp = tid >> 5;
   const int S = a.S, Sp = N * 128;
@@ -539,7 +560,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
         }
         mbar_wait(bar_ds, g & 1);
         tc_fence_after();
-        mma_k128_mn(tmem + COL_DQ, smem_u32(sdS), smem_u32(sK + j * CH), idesc_o, j > 0);
+        mma_k128_mn(tmem + COL_DQ + (it & 1) * 64, smem_u32(sdS), smem_u32(sK + j * CH), idesc_o, j > 0);
         umma_commit(bar_dsfree);
       }
       umma_commit(bar_dq);
@@ -557,6 +578,30 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
     const uint32_t lane_base = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     const float sl2 = a.scale_log2;
     const bool dropping = a.drop.thresh != 0u;
+    // dQ of this CTA's tile `it` (accumulator buffer it & 1) -> bf16 -> swizzled smem -> TMA store
+    auto drain = [&](int it) {
+      const int t = t0 + it;
+      const int bh = t / N, qt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
+      mbar_wait(bar_dq, it & 1);
+      tc_fence_after();
+      uint32_t v[16];
+      tmem_ld_32x16(lane_base + COL_DQ + (it & 1) * 64 + qd * 16, v);
+      tmem_wait_ld();
+      tc_fence_before();
+      float f[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+      // the previous store must have finished reading the staging buffer
+      if (tid == 0) tma_wait_group_read<0>();
+      named_bar_sync(1, ROW_THREADS);
+      st_out16(sOut, r, qd, f);
+      fence_proxy_async_smem();
+      named_bar_sync(1, ROW_THREADS);
+      if (tid == 0) {
+        tma_store_3d(&tm_dqkv, sOut, h * 64, qt * 128, b);  // Q slab of dqkv; rows beyond S are clipped
+        tma_commit_group();
+      }
+    };
     int prev_b = -1;
     for (int t = t0, it = 0; t < t1; ++t, ++it) {
       const int bh = t / N, qt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
@@ -564,10 +609,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
       const uint32_t g0 = static_cast<uint32_t>(it) * N;
       if (KB && b != prev_b) {
         named_bar_sync(1, ROW_THREADS);  // nobody still reads the previous batch row's bias
-        for (int k = tid; k < Sp; k += ROW_THREADS) {
-          const bool ok = k < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + k] != 0);
-          kbias[k] = ok ? 0.0f : -INFINITY;
-        }
+        fill_key_bias(kbias, kvalid, a.key_mask, b, S, Sp, tid);
         named_bar_sync(1, ROW_THREADS);
         prev_b = b;
       }
@@ -593,52 +635,43 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
         tmem_wait_ld();
         tc_fence_before();
         mbar_arrive(bar_sfree);
-        if (g >= 1) mbar_wait(bar_dsfree, (g - 1) & 1);
-        if (tid == 0 && j == 1) ATRACE(5);
         const int key0 = j * 128 + qd * 32;
         const uint32_t bits = kw[j & 3];
+        uint4 pk[4];
+        auto chunk = [&](auto biased) {
 #pragma unroll
-        for (int gq = 0; gq < 4; ++gq) {
-          float ds[8];
+          for (int gq = 0; gq < 4; ++gq) {
+            float ds[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const float x = KB ? fmaf(__uint_as_float(vs[gq * 8 + e]), sl2, kbias[key0 + gq * 8 + e])
-                               : __uint_as_float(vs[gq * 8 + e]) * sl2;
-            const float p = fast_exp2(x - lse);
-            float dp = __uint_as_float(vd[gq * 8 + e]);
-            if (dropping) dp = ((bits >> (gq * 8 + e)) & 1u) ? dp * a.drop.scale : 0.0f;
-            ds[e] = p * (dp - dsum) * a.scale;
+            for (int e = 0; e < 8; ++e) {
+              const float x = decltype(biased)::value
+                                  ? fmaf(__uint_as_float(vs[gq * 8 + e]), sl2, kbias[key0 + gq * 8 + e])
+                                  : __uint_as_float(vs[gq * 8 + e]) * sl2;
+              const float p = fast_exp2(x - lse);
+              float dp = __uint_as_float(vd[gq * 8 + e]);
+              if (dropping) dp = ((bits >> (gq * 8 + e)) & 1u) ? dp * a.drop.scale : 0.0f;
+              ds[e] = p * (dp - dsum) * a.scale;
+            }
+            pk[gq] = make_uint4(pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]), pack_bf16x2(ds[4], ds[5]),
+                                pack_bf16x2(ds[6], ds[7]));
           }
-          st_tile16(sdS, r, qd * 4 + gq, ds);
-        }
+        };
+        // 32-key groups without a masked key (all of them unless KB) take the path without the bias
+        if (KB && kvalid[j * 4 + qd] != 0xffffffffu) chunk(std::true_type{}); else chunk(std::false_type{});
+        // the dS buffer is needed only now: the previous chunk's dQ MMA has had the whole computation to finish
+        if (g >= 1) mbar_wait(bar_dsfree, (g - 1) & 1);
+        if (tid == 0 && j == 1) ATRACE(5);
+#pragma unroll
+        for (int gq = 0; gq < 4; ++gq) st_tile16p(sdS, r, qd * 4 + gq, pk[gq]);
         fence_proxy_async_smem();
         tc_fence_before();
         mbar_arrive(bar_ds);
+        // the previous tile's accumulator (the other TMEM buffer) is drained here, after this tile's first
+        // chunk, so that nobody idles while that tile's last MMA completes
+        if (j == 0 && it > 0) drain(it - 1);
       }
-      if (tid == 0) ATRACE(6);
-      mbar_wait(bar_dq, it & 1);
-      if (tid == 0) ATRACE(7);
-      tc_fence_after();
-      {
-        uint32_t v[16];
-        tmem_ld_32x16(lane_base + COL_DQ + qd * 16, v);
-        tmem_wait_ld();
-        float f[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-        // the previous tile's store must have finished reading the staging buffer
-        if (tid == 0) tma_wait_group_read<0>();
-        named_bar_sync(1, ROW_THREADS);
-        st_out16(sOut, r, qd, f);
-        fence_proxy_async_smem();
-        named_bar_sync(1, ROW_THREADS);
-        if (tid == 0) {
-          tma_store_3d(&tm_dqkv, sOut, h * 64, qt * 128, b);  // Q slab of dqkv; rows beyond S are clipped
-          tma_commit_group();
-        }
-      }
-      if (tid == 0) ATRACE(8);
     }
+    if (t1 > t0) drain(t1 - t0 - 1);
     if (tid == 0) tma_wait_group_read<0>();
   }
 
@@ -738,34 +771,40 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
   if (tid == ROW_THREADS) {
     constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
     constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
-    for (int t = t0, it = 0; t < t1; ++t, ++it) {
-      const uint32_t g0 = static_cast<uint32_t>(it) * N;
-      mbar_wait(bar_kv, it & 1);
-      for (int i = 0; i < N; ++i) {
-        const uint32_t g = g0 + i;
-        const int st = g & 1;
-        mbar_wait(&bar_ld[st], (g >> 1) & 1);
-        if (g > 0) mbar_wait(bar_sfree, (g - 1) & 1);
-        tc_fence_after();
-        mma_k64(tmem + COL_S, smem_u32(sK), smem_u32(sQ + st * CH), idesc_s);
-        mma_k64(tmem + COL_DP, smem_u32(sV), smem_u32(sdO + st * CH), idesc_s);
-        umma_commit(bar_s);
-        if (i == N - 1 && t + 1 < t1) {
-          // the tile's last score MMAs have completed: K and V can be replaced
-          mbar_wait(bar_s, g & 1);
-          load_kv(t + 1);
-        }
-        mbar_wait(bar_pt, g & 1);
-        tc_fence_after();
-        mma_k128_mn(tmem + COL_DV, smem_u32(sPt), smem_u32(sdO + st * CH), idesc_o, i > 0);
-        mma_k128_mn(tmem + COL_DK, smem_u32(sdSt), smem_u32(sQ + st * CH), idesc_o, i > 0);
-        umma_commit(bar_ptfree);
-        if (i == N - 1) umma_commit(bar_out);
-        if (g + 2 < chunks) {
-          // stage `st` is re-filled only after every MMA that reads it has completed
-          mbar_wait(bar_ptfree, g & 1);
-          load_chunk(g + 2);
-        }
+    // score MMAs of chunk g: S^T = K Q^T and dP^T = V dO^T into the single-buffered TMEM columns
+    auto issue_scores = [&](uint32_t g) {
+      const int st = g & 1;
+      if (g % N == 0) mbar_wait(bar_kv, (g / N) & 1);
+      mbar_wait(&bar_ld[st], (g >> 1) & 1);
+      if (g > 0) mbar_wait(bar_sfree, (g - 1) & 1);
+      tc_fence_after();
+      mma_k64(tmem + COL_S, smem_u32(sK), smem_u32(sQ + st * CH), idesc_s);
+      mma_k64(tmem + COL_DP, smem_u32(sV), smem_u32(sdO + st * CH), idesc_s);
+      umma_commit(bar_s);
+    };
+    if (chunks > 0) issue_scores(0);
+    for (uint32_t g = 0; g < chunks; ++g) {
+      const int i = static_cast<int>(g % N), st = g & 1;
+      const int t = t0 + static_cast<int>(g / N);
+      if (i == N - 1 && t + 1 < t1) {
+        // the tile's last score MMAs have completed: K and V can be replaced
+        mbar_wait(bar_s, g & 1);
+        load_kv(t + 1);
+      }
+      // the next chunk's scores are issued before this chunk's P^T / dS^T are waited for, so that they
+      // run while the row threads are still busy with this chunk
+      if (g + 1 < chunks) issue_scores(g + 1);
+      mbar_wait(bar_pt, g & 1);
+      tc_fence_after();
+      const uint32_t acc = tmem + ((g / N) & 1u) * 128;  // the tile's accumulator buffer
+      mma_k128_mn(acc + COL_DV, smem_u32(sPt), smem_u32(sdO + st * CH), idesc_o, i > 0);
+      mma_k128_mn(acc + COL_DK, smem_u32(sdSt), smem_u32(sQ + st * CH), idesc_o, i > 0);
+      umma_commit(bar_ptfree);
+      if (i == N - 1) umma_commit(bar_out);
+      if (g + 2 < chunks) {
+        // stage `st` is re-filled only after every MMA that reads it has completed
+        mbar_wait(bar_ptfree, g & 1);
+        load_chunk(g + 2);
       }
     }
   } else if (tid < ROW_THREADS) {
@@ -775,17 +814,54 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
     const bool dropping = a.drop.thresh != 0u;
     const uint32_t kbit = static_cast<uint32_t>(r & 31);
     const int kword = r >> 5;
+    // keep words of chunk g of this CTA's stream for thread (query tid / 4, word tid % 4)
+    auto fetch_keep = [&](uint32_t g) -> uint32_t {
+      if (g >= chunks) return 0u;
+      const int t = t0 + static_cast<int>(g / N), i = static_cast<int>(g % N);
+      const int bh = t / N, kt = t - bh * N;
+      const int qq = i * 128 + (tid >> 2);
+      return qq < S ? __ldg(a.keep + (static_cast<size_t>(bh) * S + qq) * (4 * N) + kt * 4 + (tid & 3)) : 0u;
+    };
+    uint32_t keep_next = dropping ? fetch_keep(0) : 0u;
+    // dV and dK of this CTA's tile `it` (accumulator buffer it & 1) -> bf16 -> swizzled smem -> TMA stores
+    auto drain = [&](int it) {
+      const int t = t0 + it;
+      const int bh = t / N, kt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
+      mbar_wait(bar_out, it & 1);
+      tc_fence_after();
+      // the previous stores must have finished reading the staging buffers
+      if (tid == 0) tma_wait_group_read<0>();
+      named_bar_sync(1, ROW_THREADS);
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {  // c = 0: dV, c = 1: dK (COL_DK = COL_DV + 64); 16 columns per thread
+        uint32_t v[16];
+        tmem_ld_32x16(lane_base + (it & 1) * 128 + COL_DV + c * 64 + qd * 16, v);
+        tmem_wait_ld();
+        float f[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+        st_out16(sOut + c * CH, r, qd, f);
+      }
+      tc_fence_before();
+      fence_proxy_async_smem();
+      named_bar_sync(1, ROW_THREADS);
+      if (tid == 0) {
+        // V block is the third H-wide slab of dqkv, K the second; rows beyond S are clipped by the map
+        tma_store_3d(&tm_dqkv, sOut, 2 * a.H + h * 64, kt * 128, b);
+        tma_store_3d(&tm_dqkv, sOut + CH, a.H + h * 64, kt * 128, b);
+        tma_commit_group();
+      }
+    };
     int prev_bh = -1;
     for (int t = t0, it = 0; t < t1; ++t, ++it) {
-      const int bh = t / N, kt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
+      const int bh = t / N, kt = t - bh * N, b = bh / a.A;
       const uint32_t g0 = static_cast<uint32_t>(it) * N;
       const int key = kt * 128 + r;
       const bool key_ok = key < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + key] != 0);
       const float kb = key_ok ? 0.0f : -INFINITY;
-      const size_t keep_base = static_cast<size_t>(bh) * S;
       if (bh != prev_bh) {
-        // row statistics of every query of this (batch, head); the previous tile's epilogue barriers
-        // guarantee that nobody still reads the old ones
+        // row statistics of every query of this (batch, head), once nobody still reads the old ones
+        if (it > 0) named_bar_sync(1, ROW_THREADS);
         const size_t stat = static_cast<size_t>(bh) * S;
         for (int k = tid; k < Sp; k += ROW_THREADS) {
           s_lse[k] = k < S ? a.lse2[stat + k] : INFINITY;
@@ -797,12 +873,11 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
       for (int i = 0; i < N; ++i) {
         const uint32_t g = g0 + i;
         if (dropping) {
-          // stage this query chunk's keep words for the 128 keys of the tile: [query][4 words]
-          const int ql = tid >> 2, w = tid & 3;
-          const int qq = i * 128 + ql;
-          s_keep[(g & 1) * 512 + ql * 4 + w] =
-              qq < S ? __ldg(a.keep + (keep_base + qq) * (4 * N) + kt * 4 + w) : 0u;
+          // stage this query chunk's keep words for the 128 keys of the tile: [query][4 words]; the
+          // words were fetched one chunk ahead
+          s_keep[(g & 1) * 512 + tid] = keep_next;
           named_bar_sync(1, ROW_THREADS);
+          keep_next = fetch_keep(g + 1);
         }
         mbar_wait(bar_s, g & 1);
         if (tid == 0 && i == 0) ATRACE(4);
@@ -813,10 +888,9 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
         tmem_wait_ld();
         tc_fence_before();
         mbar_arrive(bar_sfree);
-        if (g >= 1) mbar_wait(bar_ptfree, (g - 1) & 1);
-        if (tid == 0 && i == 1) ATRACE(5);
         const int q0 = i * 128 + qd * 32;
         const uint32_t* keep_q = s_keep + (g & 1) * 512 + (qd * 32) * 4 + kword;
+        uint4 ppk[4], dpk[4];
 #pragma unroll
         for (int gq = 0; gq < 4; ++gq) {
           float pt[8], ds[8];
@@ -839,40 +913,29 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
             pt[e] = pd;
             ds[e] = p * (dp - dsv[e]) * a.scale;
           }
-          st_tile16(sPt, r, qd * 4 + gq, pt);
-          st_tile16(sdSt, r, qd * 4 + gq, ds);
+          ppk[gq] = make_uint4(pack_bf16x2(pt[0], pt[1]), pack_bf16x2(pt[2], pt[3]), pack_bf16x2(pt[4], pt[5]),
+                               pack_bf16x2(pt[6], pt[7]));
+          dpk[gq] = make_uint4(pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]), pack_bf16x2(ds[4], ds[5]),
+                               pack_bf16x2(ds[6], ds[7]));
+        }
+        // the operand buffers are needed only now: the previous chunk's dV / dK MMAs have had the whole
+        // computation to finish
+        if (g >= 1) mbar_wait(bar_ptfree, (g - 1) & 1);
+        if (tid == 0 && i == 1) ATRACE(5);
+#pragma unroll
+        for (int gq = 0; gq < 4; ++gq) {
+          st_tile16p(sPt, r, qd * 4 + gq, ppk[gq]);
+          st_tile16p(sdSt, r, qd * 4 + gq, dpk[gq]);
         }
         fence_proxy_async_smem();
         tc_fence_before();
         mbar_arrive(bar_pt);
+        // the previous tile's accumulators (the other TMEM buffer) are drained here, after this tile's
+        // first chunk, so that nobody idles while that tile's last MMAs complete
+        if (i == 0 && it > 0) drain(it - 1);
       }
-      if (tid == 0) ATRACE(6);
-      mbar_wait(bar_out, it & 1);
-      if (tid == 0) ATRACE(7);
-      tc_fence_after();
-      // the previous tile's stores must have finished reading the staging buffers
-      if (tid == 0) tma_wait_group_read<0>();
-      named_bar_sync(1, ROW_THREADS);
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {  // c = 0: dV, c = 1: dK (COL_DK = COL_DV + 64); 16 columns per thread
-        uint32_t v[16];
-        tmem_ld_32x16(lane_base + COL_DV + c * 64 + qd * 16, v);
-        tmem_wait_ld();
-        float f[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-        st_out16(sOut + c * CH, r, qd, f);
-      }
-      fence_proxy_async_smem();
-      named_bar_sync(1, ROW_THREADS);
-      if (tid == 0) {
-        // V block is the third H-wide slab of dqkv, K the second; rows beyond S are clipped by the map
-        tma_store_3d(&tm_dqkv, sOut, 2 * a.H + h * 64, kt * 128, b);
-        tma_store_3d(&tm_dqkv, sOut + CH, a.H + h * 64, kt * 128, b);
-        tma_commit_group();
-      }
-      if (tid == 0) ATRACE(8);
     }
+    if (t1 > t0) drain(t1 - t0 - 1);
     if (tid == 0) tma_wait_group_read<0>();
   }
 
