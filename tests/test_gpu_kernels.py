@@ -105,7 +105,10 @@ def test_gemm_linearity_at_full_size(pkg):
 
 
 ATTN_CASES = [(2, 128, 2, 0.0, False), (2, 384, 12, 0.0, False), (2, 512, 2, 0.0, False), (3, 200, 2, 0.0, True),
-              (2, 384, 4, 0.1, False), (2, 50, 1, 0.0, True), (1, 1, 1, 0.0, False)]
+              (2, 384, 4, 0.1, False), (2, 50, 1, 0.0, True), (1, 1, 1, 0.0, False),
+              # more tiles than SMs: every CTA of the persistent kernels walks several tiles, crosses
+              # (batch, head) boundaries (K/V reload, key-bias refill) and reuses its barriers / TMEM buffers
+              (16, 384, 12, 0.1, True), (8, 512, 12, 0.1, False), (40, 200, 2, 0.0, True), (150, 100, 2, 0.1, True)]
 
 
 @pytest.mark.parametrize("B,S,A,p,use_mask", ATTN_CASES)
