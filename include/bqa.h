@@ -83,7 +83,8 @@ BQA_API int bqa_gemm_bf16(const bqa_gemm_desc* desc, void* stream);
  *   qkv  [B*S][3H] bf16 (Q | K | V slabs), ctx [B*S][H] bf16, lse2 [B][A][S] fp32
  *   key_mask [B][S] uint8 (1 = attend) or NULL
  *   keep_bits [B][A][S][bqa_attention_keep_words(S)] uint32: dropout decisions written by the
- *   forward and read by the backward (bit k of word w = key 32 w + k); may be NULL when dropout_p == 0
+ *   forward and read by the backward; opaque to the caller (per position r: the decisions of
+ *   query r over the keys, then those of key r over the queries); may be NULL when dropout_p == 0
  *   backward: dctx [B*S][H] bf16 in, dqkv [B*S][3H] bf16 out, dsum [B][A][S] fp32 scratch
  * ------------------------------------------------------------------------------------ */
 BQA_API int bqa_attention_keep_words(int32_t S);

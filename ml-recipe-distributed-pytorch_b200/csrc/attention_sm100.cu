@@ -150,21 +150,41 @@ __device__ __forceinline__ uint32_t keep_bits32(const DropKey& dk, uint32_t idx)
 }
 
 // =========================================================================================
-// dropout keep bits of one attention call: word w of row (b, h, q) covers keys 32 w .. 32 w + 31
+// dropout keep bits of one attention call, in two layouts per (batch, head) row r (W = 4 * nchunk words):
+//   keep[(bh * S + r) * 2 W + w]      bit k : (query r, key 32 w + k)      forward, dQ kernel
+//   keep[(bh * S + r) * 2 W + W + w]  bit q : (query 32 w + q, key r)      dK/dV kernel (rows are keys)
+// One warp per 32 queries x 32 keys block: lane = query; the key-major words are the 32 x 32 bit
+// transpose of the query-major ones (5 shuffle steps).
 // =========================================================================================
 __global__ void __launch_bounds__(256)
-attn_keep_bits_kernel(uint32_t* __restrict__ keep, int rows, int S, int words_per_row, DropKey dk) {
-  const size_t total = static_cast<size_t>(rows) * words_per_row;
-  for (size_t w = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; w < total;
-       w += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const uint32_t row = static_cast<uint32_t>(w / words_per_row);
-    const int key0 = static_cast<int>(w - static_cast<size_t>(row) * words_per_row) * 32;
+attn_keep_bits_kernel(uint32_t* __restrict__ keep, int BH, int S, int W, DropKey dk) {
+  const int lane = threadIdx.x & 31;
+  const int qblocks = (S + 31) >> 5;
+  const long long items = static_cast<long long>(BH) * qblocks * W;
+  const long long stride = static_cast<long long>(gridDim.x) * (blockDim.x >> 5);
+  for (long long it = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5); it < items;
+       it += stride) {
+    const int w = static_cast<int>(it % W);
+    const int qb = static_cast<int>((it / W) % qblocks);
+    const int bh = static_cast<int>(it / (static_cast<long long>(W) * qblocks));
+    const int q = qb * 32 + lane, key0 = w * 32;
     uint32_t bits = 0u;
-    if (key0 < S) {
-      bits = keep_bits32(dk, row * static_cast<uint32_t>(S) + key0);
+    if (q < S && key0 < S) {
+      bits = keep_bits32(dk, (static_cast<uint32_t>(bh) * S + q) * static_cast<uint32_t>(S) + key0);
       if (key0 + 32 > S) bits &= (1u << (S - key0)) - 1u;  // keys beyond S belong to the next row's indices
     }
-    keep[w] = bits;
+    if (q < S) keep[(static_cast<size_t>(bh) * S + q) * (2 * W) + w] = bits;
+    // 32 x 32 bit transpose across the warp: afterwards bit i of lane k = bit k of lane i
+    uint32_t x = bits;
+#pragma unroll
+    for (int j = 16; j >= 1; j >>= 1) {
+      const uint32_t m = j == 16 ? 0x0000ffffu : j == 8 ? 0x00ff00ffu : j == 4 ? 0x0f0f0f0fu : j == 2 ? 0x33333333u
+                                                                                                   : 0x55555555u;
+      const uint32_t o = __shfl_xor_sync(0xffffffffu, x, j);
+      x = (lane & j) ? (((o >> j) & m) | (x & ~m)) : ((x & m) | ((o & m) << j));
+    }
+    const int key = key0 + lane;
+    if (key < S) keep[(static_cast<size_t>(bh) * S + key) * (2 * W) + W + qb] = x;
   }
 }
 
@@ -311,7 +331,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         prev_b = b;
       }
       const uint32_t* keep_row =
-          a.keep + ((static_cast<size_t>(b) * a.A + h) * S + (q < S ? q : 0)) * (4 * N) + qd;
+          a.keep + ((static_cast<size_t>(b) * a.A + h) * S + (q < S ? q : 0)) * (8 * N) + qd;
       uint32_t kw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
       if (a.drop.thresh != 0u) {
 #pragma unroll
@@ -352,18 +372,17 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         const uint32_t bits = kw[j & 3];
         const uint32_t idx = static_cast<uint32_t>(it) * ((j & 1) ? cnt1 : cnt0) + (j >> 1);
         if (idx > 0) mbar_wait(&bar_pfree[j & 1], (idx - 1) & 1);
+        // P is stored unscaled; the dropout scale 1 / (1 - p) is applied with the final 1 / rowsum
         auto chunk = [&](auto biased) {
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             float p[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
-              const float x = decltype(biased)::value
-                                  ? fmaf(__uint_as_float(v[g * 8 + e]), sl2, kbias[key0 + g * 8 + e])
-                                  : __uint_as_float(v[g * 8 + e]) * sl2;
-              const float pv = fast_exp2(x - mx);
+              const float off = decltype(biased)::value ? kbias[key0 + g * 8 + e] - mx : -mx;
+              const float pv = fast_exp2(fmaf(__uint_as_float(v[g * 8 + e]), sl2, off));
               l += pv;
-              p[e] = ((bits >> (g * 8 + e)) & 1u) ? pv * a.drop.scale : 0.0f;
+              p[e] = ((bits >> (g * 8 + e)) & 1u) ? pv : 0.0f;
             }
             st_tile16(tile, r, qd * 4 + g, p);
           }
@@ -380,7 +399,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       mbar_wait(bar_o, it & 1);
       if (tid == 0) ATRACE(7);
       tc_fence_after();
-      const float inv = l > 0.0f ? 1.0f / l : 0.0f;
+      const float inv = l > 0.0f ? a.drop.scale / l : 0.0f;
       {
         // O tile -> swizzled smem (P buffer 0 is free: every MMA of this tile has completed) -> one TMA
         // store, which also clips the rows beyond S.  The next tile writes P only after its row-max
@@ -615,11 +634,13 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
       }
       const bool q_ok = q < S;
       const size_t stat = (static_cast<size_t>(b) * a.A + h) * S + (q_ok ? q : 0);
-      const float lse = q_ok ? a.lse2[stat] : INFINITY;
-      const float dsum = q_ok ? a.dsum[stat] : 0.0f;
+      // ds = p * (keep ? dp : 0) * c1 - p * D * scale with p = exp2(s * sl2 - lse)
+      const float nlse = q_ok ? -a.lse2[stat] : -INFINITY;
+      const float nds = q_ok ? -a.dsum[stat] * a.scale : 0.0f;
+      const float c1 = a.drop.scale * a.scale;
       uint32_t kw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
       if (dropping) {
-        const uint32_t* keep_row = a.keep + stat * (4 * N) + qd;
+        const uint32_t* keep_row = a.keep + stat * (8 * N) + qd;
 #pragma unroll
         for (int j = 0; j < 4; ++j)
           if (j < N) kw[j] = __ldg(keep_row + j * 4);
@@ -644,13 +665,10 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
             float ds[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
-              const float x = decltype(biased)::value
-                                  ? fmaf(__uint_as_float(vs[gq * 8 + e]), sl2, kbias[key0 + gq * 8 + e])
-                                  : __uint_as_float(vs[gq * 8 + e]) * sl2;
-              const float p = fast_exp2(x - lse);
-              float dp = __uint_as_float(vd[gq * 8 + e]);
-              if (dropping) dp = ((bits >> (gq * 8 + e)) & 1u) ? dp * a.drop.scale : 0.0f;
-              ds[e] = p * (dp - dsum) * a.scale;
+              const float off = decltype(biased)::value ? kbias[key0 + gq * 8 + e] + nlse : nlse;
+              const float p = fast_exp2(fmaf(__uint_as_float(vs[gq * 8 + e]), sl2, off));
+              const float dp = ((bits >> (gq * 8 + e)) & 1u) ? __uint_as_float(vd[gq * 8 + e]) : 0.0f;
+              ds[e] = p * fmaf(dp, c1, nds);
             }
             pk[gq] = make_uint4(pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]), pack_bf16x2(ds[4], ds[5]),
                                 pack_bf16x2(ds[6], ds[7]));
@@ -705,8 +723,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
   uint8_t* sOut = sdSt + 2 * CH;  // 2 * CH: dV and dK tiles staged for the TMA stores
   float* s_lse = reinterpret_cast<float*>(sOut + 2 * CH);
   float* s_dsum = s_lse + 512;
-  uint32_t* s_keep = reinterpret_cast<uint32_t*>(s_dsum + 512);  // [2][128 queries][4 words]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_keep + 1024);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_dsum + 512);
   uint64_t* bar_kv = bars + 0;
   uint64_t* bar_ld = bars + 1;  // [2]
   uint64_t* bar_s = bars + 3;
@@ -812,21 +829,14 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
     const uint32_t lane_base = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     const float sl2 = a.scale_log2;
     const bool dropping = a.drop.thresh != 0u;
-    const uint32_t kbit = static_cast<uint32_t>(r & 31);
-    const int kword = r >> 5;
-    // keep words of chunk g of this CTA's stream for thread (query tid / 4, word tid % 4)
-    auto fetch_keep = [&](uint32_t g) -> uint32_t {
-      if (g >= chunks) return 0u;
-      const int t = t0 + static_cast<int>(g / N), i = static_cast<int>(g % N);
-      const int bh = t / N, kt = t - bh * N;
-      const int qq = i * 128 + (tid >> 2);
-      return qq < S ? __ldg(a.keep + (static_cast<size_t>(bh) * S + qq) * (4 * N) + kt * 4 + (tid & 3)) : 0u;
-    };
-    uint32_t keep_next = dropping ? fetch_keep(0) : 0u;
     // dV and dK of this CTA's tile `it` (accumulator buffer it & 1) -> bf16 -> swizzled smem -> TMA stores
     auto drain = [&](int it) {
       const int t = t0 + it;
       const int bh = t / N, kt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
+      // rows of masked keys hold garbage (their probabilities are not forced to zero in the loop): they
+      // get exact zeros here.  P^T was accumulated without the dropout scale: dV takes it here.
+      const int key = kt * 128 + r;
+      const bool key_ok = key < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + key] != 0);
       mbar_wait(bar_out, it & 1);
       tc_fence_after();
       // the previous stores must have finished reading the staging buffers
@@ -837,9 +847,10 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
         uint32_t v[16];
         tmem_ld_32x16(lane_base + (it & 1) * 128 + COL_DV + c * 64 + qd * 16, v);
         tmem_wait_ld();
+        const float mul = c == 0 ? a.drop.scale : 1.0f;
         float f[16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+        for (int i = 0; i < 16; ++i) f[i] = key_ok ? __uint_as_float(v[i]) * mul : 0.0f;
         st_out16(sOut + c * CH, r, qd, f);
       }
       tc_fence_before();
@@ -852,33 +863,35 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
         tma_commit_group();
       }
     };
+    const float c1 = a.drop.scale * a.scale;
     int prev_bh = -1;
     for (int t = t0, it = 0; t < t1; ++t, ++it) {
-      const int bh = t / N, kt = t - bh * N, b = bh / a.A;
+      const int bh = t / N, kt = t - bh * N;
       const uint32_t g0 = static_cast<uint32_t>(it) * N;
       const int key = kt * 128 + r;
-      const bool key_ok = key < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + key] != 0);
-      const float kb = key_ok ? 0.0f : -INFINITY;
+      // this key's keep decisions over the queries (key-major layout): word i * 4 + qd covers the 32
+      // queries this thread handles in chunk i
+      uint32_t kw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+      if (dropping && key < S) {
+        const uint32_t* keep_row = a.keep + (static_cast<size_t>(bh) * S + key) * (8 * N) + 4 * N + qd;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (j < N) kw[j] = __ldg(keep_row + j * 4);
+      }
       if (bh != prev_bh) {
-        // row statistics of every query of this (batch, head), once nobody still reads the old ones
+        // row statistics of every query of this (batch, head), once nobody still reads the old ones:
+        // -lse2 and -D * scale, so that p = exp2(s * sl2 + nlse) and ds = p * (dp * c1 + nds)
         if (it > 0) named_bar_sync(1, ROW_THREADS);
         const size_t stat = static_cast<size_t>(bh) * S;
-        for (int k = tid; k < Sp; k += ROW_THREADS) {
-          s_lse[k] = k < S ? a.lse2[stat + k] : INFINITY;
-          s_dsum[k] = k < S ? a.dsum[stat + k] : 0.0f;
+        for (int kq = tid; kq < Sp; kq += ROW_THREADS) {
+          s_lse[kq] = kq < S ? -a.lse2[stat + kq] : -INFINITY;
+          s_dsum[kq] = kq < S ? -a.dsum[stat + kq] * a.scale : 0.0f;
         }
         named_bar_sync(1, ROW_THREADS);
         prev_bh = bh;
       }
       for (int i = 0; i < N; ++i) {
         const uint32_t g = g0 + i;
-        if (dropping) {
-          // stage this query chunk's keep words for the 128 keys of the tile: [query][4 words]; the
-          // words were fetched one chunk ahead
-          s_keep[(g & 1) * 512 + tid] = keep_next;
-          named_bar_sync(1, ROW_THREADS);
-          keep_next = fetch_keep(g + 1);
-        }
         mbar_wait(bar_s, g & 1);
         if (tid == 0 && i == 0) ATRACE(4);
         tc_fence_after();
@@ -889,7 +902,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
         tc_fence_before();
         mbar_arrive(bar_sfree);
         const int q0 = i * 128 + qd * 32;
-        const uint32_t* keep_q = s_keep + (g & 1) * 512 + (qd * 32) * 4 + kword;
+        const uint32_t bits = kw[i & 3];
         uint4 ppk[4], dpk[4];
 #pragma unroll
         for (int gq = 0; gq < 4; ++gq) {
@@ -898,20 +911,15 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
           const float4 l1 = *reinterpret_cast<const float4*>(s_lse + q0 + gq * 8 + 4);
           const float4 d0 = *reinterpret_cast<const float4*>(s_dsum + q0 + gq * 8);
           const float4 d1 = *reinterpret_cast<const float4*>(s_dsum + q0 + gq * 8 + 4);
-          const float lsev[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w};
-          const float dsv[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+          const float nlse[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w};
+          const float nds[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
-            const float p = fast_exp2(fmaf(__uint_as_float(vs[gq * 8 + e]), sl2, kb) - lsev[e]);
-            float dp = __uint_as_float(vd[gq * 8 + e]);
-            float pd = p;
-            if (dropping) {
-              const bool keep = (keep_q[(gq * 8 + e) * 4] >> kbit) & 1u;
-              pd = keep ? p * a.drop.scale : 0.0f;
-              dp = keep ? dp * a.drop.scale : 0.0f;
-            }
-            pt[e] = pd;
-            ds[e] = p * (dp - dsv[e]) * a.scale;
+            const bool keep = (bits >> (gq * 8 + e)) & 1u;
+            const float p = fast_exp2(fmaf(__uint_as_float(vs[gq * 8 + e]), sl2, nlse[e]));
+            const float dp = keep ? __uint_as_float(vd[gq * 8 + e]) : 0.0f;
+            pt[e] = keep ? p : 0.0f;
+            ds[e] = p * fmaf(dp, c1, nds[e]);
           }
           ppk[gq] = make_uint4(pack_bf16x2(pt[0], pt[1]), pack_bf16x2(pt[2], pt[3]), pack_bf16x2(pt[4], pt[5]),
                                pack_bf16x2(pt[6], pt[7]));
@@ -950,7 +958,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
 
 int fwd_smem_bytes(int n) { return CH * (5 + 2 * n) + 2048 + 4096 + 256 + 1024; }
 int dq_smem_bytes(int n) { return CH * (5 + 2 * n) + 2048 + 256 + 1024; }
-int dkv_smem_bytes() { return CH * 12 + 4096 + 4096 + 256 + 1024; }
+int dkv_smem_bytes() { return CH * 12 + 4096 + 256 + 1024; }
 
 AttnArgs make_args(const AttnPlan& p, const uint8_t* key_mask, DropKey drop) {
   AttnArgs a;
@@ -1018,12 +1026,12 @@ int attn_make_keep_bits(const AttnPlan& plan, DropKey drop, cudaStream_t st) {
     set_error("attention: dropout needs the keep-bit buffer");
     return 1;
   }
-  const int rows = plan.shape.B * plan.shape.A * plan.shape.S;
-  const int wpr = attn_keep_words(plan.shape.S);
-  const size_t total = static_cast<size_t>(rows) * wpr;
-  int grid = static_cast<int>((total + 255) / 256);
+  const int BH = plan.shape.B * plan.shape.A;
+  const int W = 4 * plan.nchunk;
+  const long long items = static_cast<long long>(BH) * ((plan.shape.S + 31) / 32) * W;  // one warp each
+  long long grid = (items + 7) / 8;
   if (grid > 148 * 16) grid = 148 * 16;
-  attn_keep_bits_kernel<<<grid, 256, 0, st>>>(plan.keep, rows, plan.shape.S, wpr, drop);
+  attn_keep_bits_kernel<<<static_cast<int>(grid), 256, 0, st>>>(plan.keep, BH, plan.shape.S, W, drop);
   return check_launch("attn_keep_bits");
 }
 

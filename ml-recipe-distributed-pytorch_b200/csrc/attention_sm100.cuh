@@ -27,14 +27,15 @@ struct AttnPlan {
   const bf16* dctx;
   float* dsum;   // [B][A][S] rowsum(dO * O)
   bf16* dqkv;    // [B*S][3H]
-  uint32_t* keep;  // [B][A][S][4 * nchunk] dropout keep bits (forward writes, backward reads) or null
+  uint32_t* keep;  // [B][A][S][attn_keep_words(S)] dropout keep bits (forward writes, backward reads) or null
 };
 
 // qkv/ctx/dctx/dqkv may be null when only the forward (or only a plan for it) is needed.
 int attn_plan(AttnPlan* plan, const AttnShape& s, const void* qkv, void* ctx, float* lse2, const void* dctx,
               float* dsum, void* dqkv, uint32_t* keep);
-// 32-bit words of keep bits per (batch, head, query) row for sequence length S
-inline int attn_keep_words(int S) { return 4 * ((S + 127) / 128); }
+// 32-bit words of keep bits per (batch, head, position) row for sequence length S: the decisions of
+// query r over all keys, then those of key r over all queries (attention_sm100.cu: attn_keep_bits_kernel)
+inline int attn_keep_words(int S) { return 8 * ((S + 127) / 128); }
 // Writes the dropout keep bits of one attention call (plan.keep).  The decisions depend only on the
 // key, so this can run ahead of / concurrently with whatever produces qkv.
 int attn_make_keep_bits(const AttnPlan& plan, DropKey drop, cudaStream_t st);
