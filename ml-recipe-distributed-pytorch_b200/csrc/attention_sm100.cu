@@ -33,9 +33,14 @@ constexpr int CH = 16384;  // bytes of one 128 x 64 bf16 tile
 constexpr int ROW_THREADS = 512;               // 16 warps: 4 threads per tile row (column quarters)
 constexpr int ATT_THREADS = ROW_THREADS + 32;  // + 1 control warp (TMA + MMA issue, TMEM alloc)
 constexpr int CTRL_WARP = ROW_THREADS / 32;
+// dK/dV kernel: two CTAs per SM, 8 row warps (2 threads per tile row) + 1 control warp each
+constexpr int HC = 8192;  // bytes of one 64 x 64 bf16 tile
+constexpr int BW_ROW_THREADS = 256;
+constexpr int BW_THREADS = BW_ROW_THREADS + 32;
+constexpr int BW_CTRL_WARP = BW_ROW_THREADS / 32;
 
 struct AttnArgs {
-  int B, S, A, H, nchunk, tmem_cols;
+  int B, S, A, H, nchunk, nchunk64, tmem_cols;
   float scale, scale_log2;
   const uint8_t* key_mask;
   bf16* ctx;
@@ -53,8 +58,26 @@ __device__ unsigned long long g_attn_trace[4096 * 16];
     const unsigned bl = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);                     \
     if (bl < 4096) g_attn_trace[bl * 16 + (slot)] = clock64();                                              \
   } while (0)
+// accumulated phase durations of one thread over the CTA's life: ATACC(k) adds the time since the
+// previous ATACC to bucket k, ATACC_WRITE stores buckets 1..8 next to the ATRACE slots 0 and 9
+#define ATACC_DECL long long tacc_[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}; long long tprev_ = clock64()
+#define ATACC(k)                                                                                             \
+  do {                                                                                                      \
+    const long long now_ = clock64();                                                                       \
+    tacc_[k] += now_ - tprev_;                                                                              \
+    tprev_ = now_;                                                                                          \
+  } while (0)
+#define ATACC_WRITE()                                                                                        \
+  do {                                                                                                      \
+    const unsigned bl = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);                     \
+    if (bl < 4096)                                                                                          \
+      for (int k_ = 1; k_ < 9; ++k_) g_attn_trace[bl * 16 + k_] = tacc_[k_];                                \
+  } while (0)
 #else
 #define ATRACE(slot) do {} while (0)
+#define ATACC_DECL do {} while (0)
+#define ATACC(k) do {} while (0)
+#define ATACC_WRITE() do {} while (0)
 #endif
 
 __device__ __forceinline__ float fast_exp2(float x) {
@@ -77,6 +100,15 @@ __device__ __forceinline__ void mma_k128_mn(uint32_t tmem_d, uint32_t a_addr, ui
   for (int k = 0; k < 8; ++k)
     umma_bf16(tmem_d, umma_desc_kmajor(a_addr + (k >> 2) * CH + (k & 3) * 32),
               umma_desc_mnmajor(b_addr + k * 2048, CH), idesc, (accumulate_first || k > 0) ? 1u : 0u);
+}
+
+// D[128 x 64] (+)= A[128 x 64] * B[64 x 64]; A = one K-major atom column, B = MN-major tile of 64 rows
+__device__ __forceinline__ void mma_k64_mn(uint32_t tmem_d, uint32_t a_addr, uint32_t b_addr, uint32_t idesc,
+                                           bool accumulate_first) {
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    umma_bf16(tmem_d, umma_desc_kmajor(a_addr + k * 32), umma_desc_mnmajor(b_addr + k * 2048, CH), idesc,
+              (accumulate_first || k > 0) ? 1u : 0u);
 }
 
 // 8 consecutive bf16 of row r, 16-byte chunk c16 (0..15) of a [128 x 128] K-major operand tile
@@ -705,23 +737,25 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
 // =========================================================================================
 // backward, dK and dV (rows = keys)
 // =========================================================================================
-// Persistent: contiguous (batch, head, key-tile) ranges per CTA.  The Q / dO chunks stream through a
-// 2-stage ring that keeps running across tile boundaries (chunk counter g = it * N + i), the next
-// tile's K / V are fetched once the current tile's last score MMAs have completed.
-__global__ void __launch_bounds__(ATT_THREADS, 1)
-attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_dctx,
-                    const __grid_constant__ CUtensorMap tm_dqkv, const AttnArgs a) {
+// Two CTAs per SM (288 threads, half of TMEM and of shared memory each), so that one CTA's TMEM loads,
+// operand stores and barrier waits overlap the other's arithmetic.  Persistent: contiguous (batch, head,
+// key-tile) ranges per CTA.  The Q / dO rows stream through a 2-stage ring in chunks of 64 queries that
+// keeps running across tile boundaries (chunk counter g = it * M + i, M = ceil(S / 64)); the next tile's
+// K / V are fetched once the current tile's last score MMAs have completed.
+__global__ void __launch_bounds__(BW_THREADS, 2)
+attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_q64,
+                    const __grid_constant__ CUtensorMap tm_do64, const __grid_constant__ CUtensorMap tm_dqkv,
+                    const AttnArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
-  const int N = a.nchunk;
+  const int N = a.nchunk, M = a.nchunk64;
   uint8_t* sK = smem;
   uint8_t* sV = sK + CH;
-  uint8_t* sQ = sV + CH;     // 2 stages
-  uint8_t* sdO = sQ + 2 * CH;  // 2 stages
-  uint8_t* sPt = sdO + 2 * CH;   // 2 * CH
-  uint8_t* sdSt = sPt + 2 * CH;  // 2 * CH
-  uint8_t* sOut = sdSt + 2 * CH;  // 2 * CH: dV and dK tiles staged for the TMA stores
-  float* s_lse = reinterpret_cast<float*>(sOut + 2 * CH);
+  uint8_t* sQ = sV + CH;       // 2 stages of 64 queries
+  uint8_t* sdO = sQ + 2 * HC;  // 2 stages
+  uint8_t* sPt = sdO + 2 * HC;  // [128 keys][64 queries] bf16; staging of the dV tile at the end of a tile
+  uint8_t* sdSt = sPt + CH;     // same for dS^T / dK
+  float* s_lse = reinterpret_cast<float*>(sdSt + CH);
   float* s_dsum = s_lse + 512;
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_dsum + 512);
   uint64_t* bar_kv = bars + 0;
@@ -734,21 +768,21 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
 
   const int tid = threadIdx.x, warp = tid >> 5;
-  const int S = a.S, Sp = N * 128;
+  const int S = a.S;
   const int tiles = a.B * a.A * N;
   const int t0 = static_cast<int>(static_cast<long long>(blockIdx.x) * tiles / gridDim.x);
   const int t1 = static_cast<int>(static_cast<long long>(blockIdx.x + 1) * tiles / gridDim.x);
-  const uint32_t chunks = static_cast<uint32_t>(t1 - t0) * N;  // Q / dO chunks this CTA streams
+  const uint32_t chunks = static_cast<uint32_t>(t1 - t0) * M;  // Q / dO chunks this CTA streams
   if (tid == 0) ATRACE(0);
 
   // chunk g of this CTA's stream -> TMA coordinates of its Q / dO rows
   auto load_chunk = [&](uint32_t g) {
-    const int t = t0 + static_cast<int>(g) / N, i = static_cast<int>(g) % N;
+    const int t = t0 + static_cast<int>(g) / M, i = static_cast<int>(g) % M;
     const int bh = t / N, b = bh / a.A, h = bh - b * a.A;
     const int st = g & 1;
-    mbar_arrive_expect_tx(&bar_ld[st], 2 * CH);
-    tma_load_3d(sQ + st * CH, &tm_qkv, h * 64, i * 128, b, &bar_ld[st]);
-    tma_load_3d(sdO + st * CH, &tm_dctx, h * 64, i * 128, b, &bar_ld[st]);
+    mbar_arrive_expect_tx(&bar_ld[st], 2 * HC);
+    tma_load_3d(sQ + st * HC, &tm_q64, h * 64, i * 64, b, &bar_ld[st]);
+    tma_load_3d(sdO + st * HC, &tm_do64, h * 64, i * 64, b, &bar_ld[st]);
   };
   auto load_kv = [&](int t) {
     const int bh = t / N, kt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
@@ -757,15 +791,16 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
     tma_load_3d(sV, &tm_qkv, 2 * a.H + h * 64, kt * 128, b, bar_kv);
   };
 
-  if (tid == ROW_THREADS) {
+  if (tid == BW_ROW_THREADS) {
     tma_prefetch_desc(&tm_qkv);
-    tma_prefetch_desc(&tm_dctx);
+    tma_prefetch_desc(&tm_q64);
+    tma_prefetch_desc(&tm_do64);
     mbar_init(bar_kv, 1);
     mbar_init(&bar_ld[0], 1);
     mbar_init(&bar_ld[1], 1);
     mbar_init(bar_s, 1);
-    mbar_init(bar_sfree, ROW_THREADS);
-    mbar_init(bar_pt, ROW_THREADS);
+    mbar_init(bar_sfree, BW_ROW_THREADS);
+    mbar_init(bar_pt, BW_ROW_THREADS);
     mbar_init(bar_ptfree, 1);
     mbar_init(bar_out, 1);
     fence_mbar_init();
@@ -775,134 +810,140 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
       for (uint32_t g = 0; g < 2 && g < chunks; ++g) load_chunk(g);
     }
   }
-  if (warp == CTRL_WARP) {
-    tmem_alloc(tmem_slot, 512);
+  if (warp == BW_CTRL_WARP) {
+    tmem_alloc(tmem_slot, 256);
     tmem_relinquish();
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  constexpr uint32_t COL_S = 0, COL_DP = 128, COL_DV = 256, COL_DK = 320;
+  constexpr uint32_t COL_S = 0, COL_DP = 64, COL_DV = 128, COL_DK = 192;
 
-  if (tid == ROW_THREADS) {
-    constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
+  if (uniform_warp_idx() == BW_CTRL_WARP) {
+    // The whole control warp walks the loop (warp-uniform control flow and operands); one elected lane
+    // issues the MMAs and TMA loads.  i and t follow the chunk counter without divisions.
+    constexpr uint32_t idesc_s = umma_idesc_bf16(128, 64, 0, 0);
     constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
-    // score MMAs of chunk g: S^T = K Q^T and dP^T = V dO^T into the single-buffered TMEM columns
-    auto issue_scores = [&](uint32_t g) {
+    const bool leader = elect_one();
+    // score MMAs of chunk g (first chunk of a tile if `first`): S^T = K Q^T and dP^T = V dO^T into the
+    // single-buffered TMEM columns
+    auto issue_scores = [&](uint32_t g, bool first, uint32_t tile_it) {
       const int st = g & 1;
-      if (g % N == 0) mbar_wait(bar_kv, (g / N) & 1);
+      if (first) mbar_wait(bar_kv, tile_it & 1);
       mbar_wait(&bar_ld[st], (g >> 1) & 1);
       if (g > 0) mbar_wait(bar_sfree, (g - 1) & 1);
       tc_fence_after();
-      mma_k64(tmem + COL_S, smem_u32(sK), smem_u32(sQ + st * CH), idesc_s);
-      mma_k64(tmem + COL_DP, smem_u32(sV), smem_u32(sdO + st * CH), idesc_s);
-      umma_commit(bar_s);
+      if (leader) {
+        mma_k64(tmem + COL_S, smem_u32(sK), smem_u32(sQ + st * HC), idesc_s);
+        mma_k64(tmem + COL_DP, smem_u32(sV), smem_u32(sdO + st * HC), idesc_s);
+        umma_commit(bar_s);
+      }
+      __syncwarp();
     };
-    if (chunks > 0) issue_scores(0);
+    if (chunks > 0) issue_scores(0, true, 0);
+    int i = 0, t = t0;
+    uint32_t it = 0;
     for (uint32_t g = 0; g < chunks; ++g) {
-      const int i = static_cast<int>(g % N), st = g & 1;
-      const int t = t0 + static_cast<int>(g / N);
-      if (i == N - 1 && t + 1 < t1) {
+      const int st = g & 1;
+      const bool last = i == M - 1;
+      if (last && t + 1 < t1) {
         // the tile's last score MMAs have completed: K and V can be replaced
         mbar_wait(bar_s, g & 1);
-        load_kv(t + 1);
+        if (leader) load_kv(t + 1);
+        __syncwarp();
       }
       // the next chunk's scores are issued before this chunk's P^T / dS^T are waited for, so that they
       // run while the row threads are still busy with this chunk
-      if (g + 1 < chunks) issue_scores(g + 1);
+      if (g + 1 < chunks) issue_scores(g + 1, last, it + 1);
       mbar_wait(bar_pt, g & 1);
       tc_fence_after();
-      const uint32_t acc = tmem + ((g / N) & 1u) * 128;  // the tile's accumulator buffer
-      mma_k128_mn(acc + COL_DV, smem_u32(sPt), smem_u32(sdO + st * CH), idesc_o, i > 0);
-      mma_k128_mn(acc + COL_DK, smem_u32(sdSt), smem_u32(sQ + st * CH), idesc_o, i > 0);
-      umma_commit(bar_ptfree);
-      if (i == N - 1) umma_commit(bar_out);
+      if (leader) {
+        mma_k64_mn(tmem + COL_DV, smem_u32(sPt), smem_u32(sdO + st * HC), idesc_o, i > 0);
+        mma_k64_mn(tmem + COL_DK, smem_u32(sdSt), smem_u32(sQ + st * HC), idesc_o, i > 0);
+        umma_commit(bar_ptfree);
+        if (last) umma_commit(bar_out);
+      }
+      __syncwarp();
       if (g + 2 < chunks) {
         // stage `st` is re-filled only after every MMA that reads it has completed
         mbar_wait(bar_ptfree, g & 1);
-        load_chunk(g + 2);
+        if (leader) load_chunk(g + 2);
+        __syncwarp();
+      }
+      if (last) {
+        i = 0;
+        ++t;
+        ++it;
+      } else {
+        ++i;
       }
     }
-  } else if (tid < ROW_THREADS) {
-    const int r = tid & 127, qd = tid >> 7;
-    const uint32_t lane_base = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+  } else if (tid < BW_ROW_THREADS) {
+    // thread (r, hq): key row r of the tile, queries [32 hq, 32 hq + 32) of every 64-query chunk
+    const int r = tid & 127, hq = tid >> 7, ew = warp & 3;
+    const uint32_t lane_base = tmem + (static_cast<uint32_t>(ew * 32) << 16);
     const float sl2 = a.scale_log2;
     const bool dropping = a.drop.thresh != 0u;
-    // dV and dK of this CTA's tile `it` (accumulator buffer it & 1) -> bf16 -> swizzled smem -> TMA stores
-    auto drain = [&](int it) {
-      const int t = t0 + it;
-      const int bh = t / N, kt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
-      // rows of masked keys hold garbage (their probabilities are not forced to zero in the loop): they
-      // get exact zeros here.  P^T was accumulated without the dropout scale: dV takes it here.
+    const float c1 = a.drop.scale * a.scale;
+    ATACC_DECL;
+    // Inputs are fetched ahead of their use so that their global-memory latency hides behind the arithmetic:
+    // the key's keep decisions over the chunk's queries (key-major layout, word 2 i + hq) one chunk ahead,
+    // and the row statistics -lse2 and -D * scale of queries tid, tid + 256 one (batch, head) ahead.
+    auto fetch_keep = [&](uint32_t g) -> uint32_t {
+      if (!dropping || g >= chunks) return 0xffffffffu;
+      const int t = t0 + static_cast<int>(g / M), i = static_cast<int>(g % M);
+      const int bh = t / N, kt = t - bh * N;
       const int key = kt * 128 + r;
-      const bool key_ok = key < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + key] != 0);
-      mbar_wait(bar_out, it & 1);
-      tc_fence_after();
-      // the previous stores must have finished reading the staging buffers
-      if (tid == 0) tma_wait_group_read<0>();
-      named_bar_sync(1, ROW_THREADS);
+      if (key >= S) return 0xffffffffu;
+      return ldg_issue_u32(a.keep + (static_cast<size_t>(bh) * S + key) * (8 * N) + 4 * N + 2 * i + hq);
+    };
+    float nlse_next[2] = {-INFINITY, -INFINITY}, nds_next[2] = {0.0f, 0.0f};
+    auto fetch_stats = [&](int t) {
+      const size_t stat = static_cast<size_t>(t / N) * S;
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {  // c = 0: dV, c = 1: dK (COL_DK = COL_DV + 64); 16 columns per thread
-        uint32_t v[16];
-        tmem_ld_32x16(lane_base + (it & 1) * 128 + COL_DV + c * 64 + qd * 16, v);
-        tmem_wait_ld();
-        const float mul = c == 0 ? a.drop.scale : 1.0f;
-        float f[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) f[i] = key_ok ? __uint_as_float(v[i]) * mul : 0.0f;
-        st_out16(sOut + c * CH, r, qd, f);
-      }
-      tc_fence_before();
-      fence_proxy_async_smem();
-      named_bar_sync(1, ROW_THREADS);
-      if (tid == 0) {
-        // V block is the third H-wide slab of dqkv, K the second; rows beyond S are clipped by the map
-        tma_store_3d(&tm_dqkv, sOut, 2 * a.H + h * 64, kt * 128, b);
-        tma_store_3d(&tm_dqkv, sOut + CH, a.H + h * 64, kt * 128, b);
-        tma_commit_group();
+      for (int u = 0; u < 2; ++u) {
+        const int q = tid + u * BW_ROW_THREADS;
+        nlse_next[u] = q < S ? -ldg_issue_f32(a.lse2 + stat + q) : -INFINITY;
+        nds_next[u] = q < S ? -ldg_issue_f32(a.dsum + stat + q) * a.scale : 0.0f;
       }
     };
-    const float c1 = a.drop.scale * a.scale;
+    uint32_t keep_next = fetch_keep(0);
+    if (t0 < t1) fetch_stats(t0);
     int prev_bh = -1;
     for (int t = t0, it = 0; t < t1; ++t, ++it) {
-      const int bh = t / N, kt = t - bh * N;
-      const uint32_t g0 = static_cast<uint32_t>(it) * N;
-      const int key = kt * 128 + r;
-      // this key's keep decisions over the queries (key-major layout): word i * 4 + qd covers the 32
-      // queries this thread handles in chunk i
-      uint32_t kw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-      if (dropping && key < S) {
-        const uint32_t* keep_row = a.keep + (static_cast<size_t>(bh) * S + key) * (8 * N) + 4 * N + qd;
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (j < N) kw[j] = __ldg(keep_row + j * 4);
-      }
+      const int bh = t / N, kt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
+      const uint32_t g0 = static_cast<uint32_t>(it) * M;
       if (bh != prev_bh) {
-        // row statistics of every query of this (batch, head), once nobody still reads the old ones:
-        // -lse2 and -D * scale, so that p = exp2(s * sl2 + nlse) and ds = p * (dp * c1 + nds)
-        if (it > 0) named_bar_sync(1, ROW_THREADS);
-        const size_t stat = static_cast<size_t>(bh) * S;
-        for (int kq = tid; kq < Sp; kq += ROW_THREADS) {
-          s_lse[kq] = kq < S ? -a.lse2[stat + kq] : -INFINITY;
-          s_dsum[kq] = kq < S ? -a.dsum[stat + kq] * a.scale : 0.0f;
+        // p = exp2(s * sl2 + nlse) and ds = p * (dp * c1 + nds); nobody may still read the old statistics
+        if (it > 0) named_bar_sync(1, BW_ROW_THREADS);
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          s_lse[tid + u * BW_ROW_THREADS] = nlse_next[u];
+          s_dsum[tid + u * BW_ROW_THREADS] = nds_next[u];
         }
-        named_bar_sync(1, ROW_THREADS);
+        named_bar_sync(1, BW_ROW_THREADS);
         prev_bh = bh;
+        // the next (batch, head) this CTA will meet, if any
+        const int tn = (bh + 1) * N;
+        if (tn < t1) fetch_stats(tn);
       }
-      for (int i = 0; i < N; ++i) {
+      ATACC(7);
+      for (int i = 0; i < M; ++i) {
         const uint32_t g = g0 + i;
+        const uint32_t bits = keep_next;
+        keep_next = fetch_keep(g + 1);
         mbar_wait(bar_s, g & 1);
-        if (tid == 0 && i == 0) ATRACE(4);
+        ATACC(1);
         tc_fence_after();
         uint32_t vs[32], vd[32];
-        tmem_ld_32x32(lane_base + COL_S + qd * 32, vs);
-        tmem_ld_32x32(lane_base + COL_DP + qd * 32, vd);
+        tmem_ld_32x32(lane_base + COL_S + hq * 32, vs);
+        tmem_ld_32x32(lane_base + COL_DP + hq * 32, vd);
         tmem_wait_ld();
         tc_fence_before();
         mbar_arrive(bar_sfree);
-        const int q0 = i * 128 + qd * 32;
-        const uint32_t bits = kw[i & 3];
+        ATACC(2);
+        const int q0 = i * 64 + hq * 32;
         uint4 ppk[4], dpk[4];
 #pragma unroll
         for (int gq = 0; gq < 4; ++gq) {
@@ -926,39 +967,74 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
           dpk[gq] = make_uint4(pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]), pack_bf16x2(ds[4], ds[5]),
                                pack_bf16x2(ds[6], ds[7]));
         }
+        ATACC(3);
         // the operand buffers are needed only now: the previous chunk's dV / dK MMAs have had the whole
         // computation to finish
         if (g >= 1) mbar_wait(bar_ptfree, (g - 1) & 1);
-        if (tid == 0 && i == 1) ATRACE(5);
+        ATACC(4);
 #pragma unroll
         for (int gq = 0; gq < 4; ++gq) {
-          st_tile16p(sPt, r, qd * 4 + gq, ppk[gq]);
-          st_tile16p(sdSt, r, qd * 4 + gq, dpk[gq]);
+          st_tile16p(sPt, r, hq * 4 + gq, ppk[gq]);
+          st_tile16p(sdSt, r, hq * 4 + gq, dpk[gq]);
         }
         fence_proxy_async_smem();
         tc_fence_before();
         mbar_arrive(bar_pt);
-        // the previous tile's accumulators (the other TMEM buffer) are drained here, after this tile's
-        // first chunk, so that nobody idles while that tile's last MMAs complete
-        if (i == 0 && it > 0) drain(it - 1);
+        ATACC(5);
+      }
+      // ---- drain: dV and dK of the tile -> bf16 -> swizzled smem (the operand buffers: every MMA of the
+      // tile has completed) -> TMA stores, per TMEM lane quarter (2 warps, named barrier 2 + ew, box of 32
+      // rows).  Rows of masked keys hold garbage (their probabilities are not forced to zero in the loop):
+      // they get exact zeros.  P^T was accumulated without the dropout scale: dV takes it here.
+      {
+        const int key = kt * 128 + r;
+        const bool key_ok = key < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + key] != 0);
+        mbar_wait(bar_out, it & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {  // c = 0: dV, c = 1: dK; 32 columns per thread
+          uint32_t v[32];
+          tmem_ld_32x32(lane_base + COL_DV + c * 64 + hq * 32, v);
+          tmem_wait_ld();
+          const float mul = c == 0 ? a.drop.scale : 1.0f;
+          uint8_t* tile = c == 0 ? sPt : sdSt;
+#pragma unroll
+          for (int q4 = 0; q4 < 4; ++q4) {
+            float f[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] = key_ok ? __uint_as_float(v[q4 * 8 + e]) * mul : 0.0f;
+            st_tile16(tile, r, hq * 4 + q4, f);
+          }
+        }
+        tc_fence_before();
+        fence_proxy_async_smem();
+        named_bar_sync(2 + ew, 64);
+        if (tid == ew * 32) {
+          // V block is the third H-wide slab of dqkv, K the second; rows beyond S are clipped by the map
+          tma_store_3d(&tm_dqkv, sPt + ew * 4096, 2 * a.H + h * 64, kt * 128 + ew * 32, b);
+          tma_store_3d(&tm_dqkv, sdSt + ew * 4096, a.H + h * 64, kt * 128 + ew * 32, b);
+          tma_commit_group();
+          tma_wait_group_read<0>();  // the next tile's first chunk overwrites these rows
+        }
+        named_bar_sync(2 + ew, 64);
+        ATACC(6);
       }
     }
-    if (t1 > t0) drain(t1 - t0 - 1);
-    if (tid == 0) tma_wait_group_read<0>();
+    if (tid == 0) ATACC_WRITE();
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == CTRL_WARP) {
+  if (warp == BW_CTRL_WARP) {
     tc_fence_after();
-    tmem_dealloc(tmem, 512);
+    tmem_dealloc(tmem, 256);
   }
   if (tid == 0) ATRACE(9);
 }
 
 int fwd_smem_bytes(int n) { return CH * (5 + 2 * n) + 2048 + 4096 + 256 + 1024; }
 int dq_smem_bytes(int n) { return CH * (5 + 2 * n) + 2048 + 256 + 1024; }
-int dkv_smem_bytes() { return CH * 12 + 4096 + 256 + 1024; }
+int dkv_smem_bytes() { return CH * 4 + HC * 4 + 4096 + 256 + 1024; }
 
 AttnArgs make_args(const AttnPlan& p, const uint8_t* key_mask, DropKey drop) {
   AttnArgs a;
@@ -967,6 +1043,7 @@ AttnArgs make_args(const AttnPlan& p, const uint8_t* key_mask, DropKey drop) {
   a.A = p.shape.A;
   a.H = p.shape.H;
   a.nchunk = p.nchunk;
+  a.nchunk64 = (p.shape.S + 63) / 64;
   a.tmem_cols = p.tmem_cols;
   a.scale = 0.125f;  // 1 / sqrt(64)
   a.scale_log2 = 0.125f * 1.4426950408889634f;
@@ -1009,7 +1086,13 @@ int attn_plan(AttnPlan* plan, const AttnShape& s, const void* qkv, void* ctx, fl
       encode_tmap_3d(&plan->tm_qkv, qkv, 2, 3 * H, s.S, s.B, 3 * H, static_cast<uint64_t>(s.S) * 3 * H, 64, 128, 1))
     return 1;
   if (dctx != nullptr &&
-      encode_tmap_3d(&plan->tm_dctx, dctx, 2, H, s.S, s.B, H, static_cast<uint64_t>(s.S) * H, 64, 128, 1))
+      (encode_tmap_3d(&plan->tm_dctx, dctx, 2, H, s.S, s.B, H, static_cast<uint64_t>(s.S) * H, 64, 128, 1) ||
+       encode_tmap_3d(&plan->tm_do64, dctx, 2, H, s.S, s.B, H, static_cast<uint64_t>(s.S) * H, 64, 64, 1) ||
+       encode_tmap_3d(&plan->tm_q64, qkv, 2, 3 * H, s.S, s.B, 3 * H, static_cast<uint64_t>(s.S) * 3 * H, 64, 64, 1)))
+    return 1;
+  // the dK/dV kernel stores 32-row boxes (one per TMEM lane quarter); the dQ kernel 128-row ones
+  if (dqkv != nullptr &&
+      encode_tmap_3d(&plan->tm_dqkv32, dqkv, 2, 3 * H, s.S, s.B, 3 * H, static_cast<uint64_t>(s.S) * 3 * H, 64, 32, 1))
     return 1;
   if (ctx != nullptr &&
       encode_tmap_3d(&plan->tm_ctx, ctx, 2, H, s.S, s.B, H, static_cast<uint64_t>(s.S) * H, 64, 128, 1))
@@ -1090,7 +1173,9 @@ int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, c
     attn_bwd_dq_kernel<false><<<grid, ATT_THREADS, dq_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_dctx,
                                                                                       plan.tm_dqkv, a);
   if (check_launch("attn_bwd_dq")) return 1;
-  attn_bwd_dkv_kernel<<<grid, ATT_THREADS, dkv_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_dctx, plan.tm_dqkv, a);
+  const int grid_kv = tiles < 2 * sms ? tiles : 2 * sms;  // two co-resident CTAs per SM
+  attn_bwd_dkv_kernel<<<grid_kv, BW_THREADS, dkv_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_q64, plan.tm_do64,
+                                                                     plan.tm_dqkv32, a);
   return check_launch("attn_bwd_dkv");
 }
 

@@ -16,6 +16,9 @@ struct AttnShape {
 struct AttnPlan {
   CUtensorMap tm_qkv;   // [B][S][3H] bf16, box {64,128,1}
   CUtensorMap tm_dctx;  // [B][S][H]  bf16, box {64,128,1}
+  CUtensorMap tm_q64;   // qkv with box {64,64,1}: 64-row Q chunks of the dK/dV kernel
+  CUtensorMap tm_do64;  // dctx with box {64,64,1}
+  CUtensorMap tm_dqkv32;  // dqkv with box {64,32,1}: dK/dV stores, one per TMEM lane quarter
   CUtensorMap tm_ctx;   // [B][S][H]  bf16 (forward output, TMA store)
   CUtensorMap tm_dqkv;  // [B][S][3H] bf16 (backward output, TMA store)
   AttnShape shape;

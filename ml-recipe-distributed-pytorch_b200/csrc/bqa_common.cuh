@@ -85,6 +85,36 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// Read-only global loads that the compiler may not move: used for prefetches that must be ISSUED at a
+// given point of a barrier-synchronised loop (a plain load may be sunk to its first use).
+__device__ __forceinline__ uint32_t ldg_issue_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ float ldg_issue_f32(const float* p) {
+  float v;
+  asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+
+// One lane of a converged warp (the others get false).  Code that issues tcgen05.mma / TMA from inside
+// `if (elect_one())` within warp-uniform control flow keeps descriptors in uniform registers; issuing from
+// a `threadIdx.x == k` branch instead makes the compiler wrap every instruction in an election loop.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(pred));
+  return pred != 0;
+}
+// warp index as a value the compiler knows to be warp-uniform
+__device__ __forceinline__ int uniform_warp_idx() { return __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0); }
+
 // generic-proxy writes to shared memory -> visible to the async proxy (TMA store, UMMA reads)
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
