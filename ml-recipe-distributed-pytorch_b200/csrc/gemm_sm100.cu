@@ -69,7 +69,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
   uint64_t* bar_tempty = bar_tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_tempty + 2);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = uniform_warp_idx();  // warp-uniform value: role branches below are uniform control flow
   const int lane = threadIdx.x & 31;
   const uint32_t rank = NCTA == 2 ? cluster_ctarank() : 0u;  // 0 = the CTA that issues the MMAs
 
@@ -106,8 +106,10 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
   const int num_tiles = tiles_mn * args.k_splits;
   const int tile0 = blockIdx.x / NCTA, tile_step = gridDim.x / NCTA;
 
-  if (warp == 0 && lane == 0) {
+  if (warp == 0) {
     // ------------------------------ TMA producer (every CTA) ------------------------------
+    // the whole warp walks the loop (uniform control flow and operands); one elected lane issues
+    const bool leader = elect_one();
     int stage = 0;
     uint32_t phase = 0;
     for (int tile = tile0; tile < num_tiles; tile += tile_step) {
@@ -119,6 +121,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       const int kb1 = min(kb0 + args.kb_per_split, args.kb_total);
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(&bar_empty[stage], phase ^ 1u);
+        if (leader) {
         const int k0 = kb * BLOCK_K;
         uint8_t* a_dst = sA + stage * A_STAGE_BYTES;
         uint8_t* b_dst = sB + stage * B_STAGE_BYTES;
@@ -144,15 +147,18 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           if (rank == 0) mbar_arrive_expect_tx(fb, 2 * (A_STAGE_BYTES + B_STAGE_BYTES));
           else mbar_arrive_cluster(fb, 0);
         }
+        }
+        __syncwarp();
         if (++stage == STAGES) {
           stage = 0;
           phase ^= 1u;
         }
       }
     }
-  } else if (warp == 1 && lane == 0 && rank == 0) {
+  } else if (warp == 1 && rank == 0) {
     // ------------------------------ MMA issuer (even CTA only) ------------------------------
     constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BLOCK_N, A_MN, B_MN);
+    const bool leader = elect_one();
     int stage = 0;
     uint32_t phase = 0;
     uint32_t it = 0;
@@ -168,6 +174,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(&bar_full[stage], phase);
         tc_fence_after();
+        if (leader) {
         const uint32_t a_addr = smem_u32(sA + stage * A_STAGE_BYTES);
         const uint32_t b_addr = smem_u32(sB + stage * B_STAGE_BYTES);
 #pragma unroll
@@ -186,6 +193,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           umma_commit(&bar_empty[stage]);
           if (kb == kb1 - 1) umma_commit(&bar_tfull[as]);
         }
+        }
+        __syncwarp();
         if (++stage == STAGES) {
           stage = 0;
           phase ^= 1u;
