@@ -284,37 +284,70 @@ pooled_bwd_kernel(const float* __restrict__ pooled, const float* __restrict__ re
   }
 }
 
-// dx0[b][i] = sum_j dpre[b][j] * Wp[j][i];  grid (ceil(H/256), B)
+// dx0[b][i] += sum_{j in slice} dpre[b][j] * Wp[j][i] for every batch row b at once, so that Wp is read once.
+// grid (ceil(H/256), ceil(H/PJ)); dx0 is zeroed by the caller; batch rows are taken PB at a time.
+constexpr int PJ = 32;  // j rows of Wp per block
+constexpr int PB = 32;  // batch rows per pass
 __global__ void __launch_bounds__(256)
-pooler_dx_kernel(const float* __restrict__ dpre, const float* __restrict__ Wp, float* __restrict__ dx0, int H) {
-  __shared__ float s_d[1024];
-  const int b = blockIdx.y;
-  for (int j = threadIdx.x; j < H; j += blockDim.x) s_d[j] = dpre[static_cast<size_t>(b) * H + j];
-  __syncthreads();
+pooler_dx_kernel(const float* __restrict__ dpre, const float* __restrict__ Wp, float* __restrict__ dx0, int B,
+                 int H) {
+  __shared__ float s_d[PB][PJ];
   const int i = blockIdx.x * 256 + threadIdx.x;
-  if (i >= H) return;
-  float acc = 0.0f;
-#pragma unroll 8
-  for (int j = 0; j < H; ++j) acc += s_d[j] * __ldg(Wp + static_cast<size_t>(j) * H + i);
-  dx0[static_cast<size_t>(b) * H + i] = acc;
+  const int j0 = blockIdx.y * PJ;
+  float w[PJ];
+#pragma unroll
+  for (int j = 0; j < PJ; ++j) w[j] = (i < H && j0 + j < H) ? __ldg(Wp + static_cast<size_t>(j0 + j) * H + i) : 0.0f;
+  for (int b0 = 0; b0 < B; b0 += PB) {
+    __syncthreads();
+    for (int e = threadIdx.x; e < PB * PJ; e += 256) {
+      const int b = b0 + e / PJ, j = j0 + e % PJ;
+      s_d[e / PJ][e % PJ] = (b < B && j < H) ? dpre[static_cast<size_t>(b) * H + j] : 0.0f;
+    }
+    __syncthreads();
+    if (i < H) {
+      for (int b = 0; b < PB && b0 + b < B; ++b) {
+        float acc = 0.0f;
+#pragma unroll
+        for (int j = 0; j < PJ; ++j) acc += s_d[b][j] * w[j];
+        atomicAdd(dx0 + static_cast<size_t>(b0 + b) * H + i, acc);
+      }
+    }
+  }
 }
 
-// dWp[j][i] += sum_b dpre[b][j] * x0[b][i], dbp[j] += sum_b dpre[b][j];  grid H (one j per block)
+// dWp[j][i] += sum_b dpre[b][j] * x0[b][i], dbp[j] += sum_b dpre[b][j], x0[b] = [CLS] row of batch b.
+// grid (ceil(H/256), ceil(H/PJ)): the block keeps its 256 columns of the [CLS] rows in registers-by-batch
+// through shared memory and produces PJ rows of dWp.
 __global__ void __launch_bounds__(256)
 pooler_wgrad_kernel(const float* __restrict__ dpre, const bf16* __restrict__ y, float* __restrict__ dWp,
                     float* __restrict__ dbp, int B, int S, int H) {
-  const int j = blockIdx.x;
-  for (int i = threadIdx.x; i < H; i += blockDim.x) {
-    float acc = 0.0f;
-    for (int b = 0; b < B; ++b)
-      acc += dpre[static_cast<size_t>(b) * H + j] * __bfloat162float(y[static_cast<size_t>(b) * S * H + i]);
-    dWp[static_cast<size_t>(j) * H + i] += acc;
+  __shared__ float s_d[PB][PJ];
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  const int j0 = blockIdx.y * PJ;
+  float acc[PJ];
+#pragma unroll
+  for (int j = 0; j < PJ; ++j) acc[j] = 0.0f;
+  float bsum = 0.0f;  // thread j < PJ of the first column block: bias gradient of row j0 + j
+  for (int b0 = 0; b0 < B; b0 += PB) {
+    __syncthreads();
+    for (int e = threadIdx.x; e < PB * PJ; e += 256) {
+      const int b = b0 + e / PJ, j = j0 + e % PJ;
+      s_d[e / PJ][e % PJ] = (b < B && j < H) ? dpre[static_cast<size_t>(b) * H + j] : 0.0f;
+    }
+    __syncthreads();
+    for (int b = 0; b < PB && b0 + b < B; ++b) {
+      const float x = i < H ? __bfloat162float(y[static_cast<size_t>(b0 + b) * S * H + i]) : 0.0f;
+#pragma unroll
+      for (int j = 0; j < PJ; ++j) acc[j] += s_d[b][j] * x;
+      if (blockIdx.x == 0 && threadIdx.x < PJ) bsum += s_d[b][threadIdx.x];
+    }
   }
-  if (threadIdx.x == 0) {
-    float acc = 0.0f;
-    for (int b = 0; b < B; ++b) acc += dpre[static_cast<size_t>(b) * H + j];
-    dbp[j] += acc;
+  if (i < H) {
+#pragma unroll
+    for (int j = 0; j < PJ; ++j)
+      if (j0 + j < H) dWp[static_cast<size_t>(j0 + j) * H + i] += acc[j];  // single writer per element
   }
+  if (blockIdx.x == 0 && threadIdx.x < PJ && j0 + threadIdx.x < H) dbp[j0 + threadIdx.x] += bsum;
 }
 
 // dy[t][:] = ds[t] * Ws[0][:] + de[t] * Ws[1][:] (+ dx0[b][:] on the [CLS] row)   -> bf16
@@ -492,10 +525,11 @@ int launch_heads_bwd(const bf16* y, const float* pooled, const float* reg_s, con
   pooled_bwd_kernel<<<B, 256, 0, st>>>(pooled, reg_s, reg_e, d_cls, d_reg_s, d_reg_e, hp, hg, dpre_scratch, H, C,
                                        cls_drop);
   if (check_launch("pooled_bwd")) return 1;
-  dim3 g2((H + 255) / 256, B);
-  pooler_dx_kernel<<<g2, 256, 0, st>>>(dpre_scratch, hp.pool_w, dx0_scratch, H);
+  dim3 g2((H + 255) / 256, (H + PJ - 1) / PJ);
+  BQA_CUDA_CHECK(cudaMemsetAsync(dx0_scratch, 0, sizeof(float) * B * H, st));
+  pooler_dx_kernel<<<g2, 256, 0, st>>>(dpre_scratch, hp.pool_w, dx0_scratch, B, H);
   if (check_launch("pooler_dx")) return 1;
-  pooler_wgrad_kernel<<<H, 256, 0, st>>>(dpre_scratch, y, hg.pool_w, hg.pool_b, B, S, H);
+  pooler_wgrad_kernel<<<g2, 256, 0, st>>>(dpre_scratch, y, hg.pool_w, hg.pool_b, B, S, H);
   if (check_launch("pooler_wgrad")) return 1;
   const int T = B * S;
   int grid = num_sms * 4;
