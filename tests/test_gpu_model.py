@@ -26,6 +26,8 @@ DEV = "cuda"
 TINY = dict(num_layers=2, hidden=128, heads=2, intermediate=512, vocab=1000, max_pos=512, type_vocab=2)
 GOLD = dict(num_layers=2, hidden=64, heads=1, intermediate=128, vocab=200, max_pos=128, type_vocab=2)
 BASE = dict(num_layers=12, hidden=768, heads=12, intermediate=3072, vocab=30522, max_pos=512, type_vocab=2)
+# two layers at the BERT-large widths (BASELINE configs[3]: S = 512, 16 heads, H = 1024, I = 4096)
+LARGE2 = dict(num_layers=2, hidden=1024, heads=16, intermediate=4096, vocab=2000, max_pos=512, type_vocab=2)
 OUT_KEYS = ("start_class", "end_class", "cls", "start_reg", "end_reg")
 
 
@@ -66,7 +68,8 @@ def check_grads(eng, grads, glob_tol=2e-2, tensor_tol=5e-2):
 
 
 @pytest.mark.parametrize("shape,B,S,p_drop,use_mask", [(TINY, 4, 128, 0.0, False), (TINY, 4, 128, 0.1, False),
-                                                       (TINY, 3, 200, 0.1, True), (BASE, 4, 384, 0.0, False)])
+                                                       (TINY, 3, 200, 0.1, True), (BASE, 4, 384, 0.0, False),
+                                                       (LARGE2, 12, 512, 0.1, True)])
 def test_step_matches_oracle(pkg, shape, B, S, p_drop, use_mask):
     E = pkg.engine
     cfgo = O.OracleConfig(hidden_dropout=p_drop, attn_dropout=p_drop, **shape)
