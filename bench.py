@@ -100,6 +100,18 @@ def make_params(batch, seq):
     return p, m
 
 
+def load_traffic():
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (null if absent)."""
+    path = os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")
+    try:
+        with open(path) as f:
+            t = json.load(f)
+        return {"value": t["mean_bytes_per_launch"], "unit": "bytes per launch (DRAM read + write), mean of the "
+                "five FFN-shaped GEMM variants; algorithmic 103.8-174.6 MB", "source": "profiles/r01_ncu_traffic.json"}
+    except (OSError, KeyError, ValueError):
+        return {"value": None, "unit": None, "source": None}
+
+
 def host_batches(n, batch, seq, seed, tokenizer):
     """n collated DummyDataset batches in pinned host memory (the reference's input ABI)."""
     import importlib
@@ -214,10 +226,12 @@ def run_native(args):
     gemm_fl = sum(prof[k][1] for k in ("gemm_fwd", "gemm_dgrad", "gemm_wgrad"))
     gemm_n = sum(prof[k][2] for k in ("gemm_fwd", "gemm_dgrad", "gemm_wgrad"))
     achieved = gemm_fl / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
+    traffic = load_traffic()
     peak = peaks["bf16_tflops_sustained"]
     roofline = {"bound": "tensor", "kernel": "bqa::gemm_kernel<A_MN,B_MN,EPI> (tcgen05, all Linear fwd/dgrad/wgrad)",
                 "achieved": round(achieved, 1), "peak": peak, "unit": "TFLOP/s", "frac": round(achieved / peak, 4),
-                "peak_source": f"bf16_tflops_sustained, {peaks['source']}", "traffic": None,
+                "peak_source": f"bf16_tflops_sustained, {peaks['source']}", "traffic": traffic["value"],
+                "traffic_unit": traffic["unit"], "traffic_source": traffic["source"],
                 "launches_per_step": gemm_n // max(1, args.steps),
                 "share_of_step": round(gemm_ms / max(1e-9, ms_total), 4),
                 "by_kind": {k: {"ms_per_step": round(v[0] / args.steps, 4),

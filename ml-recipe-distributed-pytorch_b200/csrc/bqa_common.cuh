@@ -98,6 +98,44 @@ __device__ __forceinline__ float ldg_issue_f32(const float* p) {
   return v;
 }
 
+// ----------------------------------------------------------------------------------------
+// Cluster launch control: a running cluster asks the hardware to cancel a cluster of the same grid
+// that has not started yet and takes over its work (its blockIdx) — dynamic tile scheduling without
+// a software queue.  The 16-byte response lands in shared memory (of every CTA of the cluster when
+// `multicast`) and completes 16 bytes on the mbarrier at the same offset.
+// ----------------------------------------------------------------------------------------
+__device__ __forceinline__ void clc_try_cancel(void* response, uint64_t* bar, bool multicast) {
+  if (multicast)
+    asm volatile(
+        "clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.multicast::cluster::all.b128 "
+        "[%0], [%1];" ::"r"(smem_u32(response)), "r"(smem_u32(bar))
+        : "memory");
+  else
+    asm volatile("clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.b128 [%0], [%1];" ::"r"(
+                     smem_u32(response)),
+                 "r"(smem_u32(bar))
+                 : "memory");
+}
+// true + blockIdx.x of the first CTA of the cancelled cluster, or false when no cluster was left
+__device__ __forceinline__ bool clc_decode(const void* response, uint32_t& ctaid_x) {
+  uint32_t valid, x, y, z;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p1;\n\t"
+      ".reg .b128 r;\n\t"
+      "ld.shared.b128 r, [%4];\n\t"
+      "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p1, r;\n\t"
+      "selp.u32 %3, 1, 0, p1;\n\t"
+      "mov.u32 %0, 0; mov.u32 %1, 0; mov.u32 %2, 0;\n\t"
+      "@p1 clusterlaunchcontrol.query_cancel.get_first_ctaid.v4.b32.b128 {%0, %1, %2, _}, r;\n\t"
+      "}"
+      : "=r"(x), "=r"(y), "=r"(z), "=r"(valid)
+      : "r"(smem_u32(response))
+      : "memory");
+  ctaid_x = x;
+  return valid != 0;
+}
+
 // One lane of a converged warp (the others get false).  Code that issues tcgen05.mma / TMA from inside
 // `if (elect_one())` within warp-uniform control flow keeps descriptors in uniform registers; issuing from
 // a `threadIdx.x == k` branch instead makes the compiler wrap every instruction in an election loop.

@@ -32,6 +32,7 @@ constexpr int NUM_THREADS = 384;
 constexpr int EPI_THREADS = 256;
 constexpr int W_STAGE_BYTES = 32 * 128;  // one epilogue warp's staging buffer: 32 rows x 128 B (64 bf16 or 32 fp32)
 constexpr int SMEM_BARRIER_BYTES = 256;
+constexpr int QD = 2;  // tile-scheduler response ring depth
 
 // NCTA = 1: one CTA computes a 128 x 256 tile.  NCTA = 2: a CTA pair (cluster of 2, cta_group::2)
 // computes a 256 x 256 tile; each CTA stages its own 128 rows of A and 128 of the 256 rows of B,
@@ -68,6 +69,11 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
   uint64_t* bar_tfull = bar_empty + STAGES;
   uint64_t* bar_tempty = bar_tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_tempty + 2);
+  // dynamic tile scheduling (cluster launch control): response ring + barriers
+  uint64_t* bar_qfull = bar_tempty + 4;   // [QD] response landed (16 bytes), armed by each CTA's scheduler warp
+  uint64_t* bar_qempty = bar_qfull + QD;  // [QD] on the even CTA: every consumer warp of the cluster has read it
+  uint64_t* bar_qgo = bar_qempty + QD;    // on the even CTA: its producer has started another tile
+  uint4* clc_resp = reinterpret_cast<uint4*>((reinterpret_cast<uintptr_t>(bar_qgo + 1) + 15) & ~uintptr_t(15));  // [QD]
 
   const int warp = uniform_warp_idx();  // warp-uniform value: role branches below are uniform control flow
   const int lane = threadIdx.x & 31;
@@ -86,6 +92,11 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       mbar_init(&bar_tfull[i], 1);
       mbar_init(&bar_tempty[i], NCTA * EPI_THREADS);  // pair: both CTAs' epilogues arrive on the even CTA
     }
+    for (int i = 0; i < QD; ++i) {
+      mbar_init(&bar_qfull[i], 1);
+      mbar_init(&bar_qempty[i], NCTA * 9 + 1);  // producer + 8 epilogue warps per CTA, one MMA warp
+    }
+    mbar_init(bar_qgo, 1);
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -103,8 +114,27 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
   const uint32_t tmem_base = *tmem_slot;
 
   const int tiles_mn = args.m_tiles * args.n_tiles;
-  const int num_tiles = tiles_mn * args.k_splits;
-  const int tile0 = blockIdx.x / NCTA, tile_step = gridDim.x / NCTA;
+  // One cluster is launched per tile; the clusters that get to run take over the tiles of clusters that
+  // have not started (cluster launch control), so the grid behaves like a persistent one with dynamic
+  // scheduling: an SM that becomes free late (another kernel was running on it) simply joins in.
+  // Every consumer warp walks the same sequence of responses: response k of the cluster is in slot k % QD.
+  uint32_t qk = 0;  // responses consumed by this warp
+  auto next_tile = [&](int& tile) -> bool {
+    const uint32_t slot = qk % QD, ph = (qk / QD) & 1u;
+    mbar_wait(&bar_qfull[slot], ph);
+    uint32_t cta_x;
+    const bool valid = clc_decode(&clc_resp[slot], cta_x);
+    fence_proxy_async_smem();  // the slot is overwritten by the async proxy once released
+    __syncwarp();
+    if (lane == 0) {
+      if (NCTA == 2 && rank != 0) mbar_arrive_cluster(&bar_qempty[slot], 0);
+      else mbar_arrive(&bar_qempty[slot]);
+    }
+    ++qk;
+    tile = static_cast<int>(cta_x) / NCTA;
+    return valid;
+  };
+  const int tile0 = blockIdx.x / NCTA;
 
   if (warp == 0) {
     // ------------------------------ TMA producer (every CTA) ------------------------------
@@ -112,7 +142,10 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     const bool leader = elect_one();
     int stage = 0;
     uint32_t phase = 0;
-    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+    for (int tile = tile0;;) {
+      // starting a tile lets the scheduler ask for the one after it (look-ahead of one tile: a cluster never
+      // holds more than one tile it has not started, which keeps short grids balanced)
+      if (rank == 0 && leader) mbar_arrive(bar_qgo);
       const int split = tile / tiles_mn;
       const int mn = tile - split * tiles_mn;
       const int m0 = (mn / args.n_tiles) * BLOCK_M + static_cast<int>(rank) * 128;      // own A rows
@@ -154,6 +187,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           phase ^= 1u;
         }
       }
+      if (!next_tile(tile)) break;
     }
   } else if (warp == 1 && rank == 0) {
     // ------------------------------ MMA issuer (even CTA only) ------------------------------
@@ -162,7 +196,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     int stage = 0;
     uint32_t phase = 0;
     uint32_t it = 0;
-    for (int tile = tile0; tile < num_tiles; tile += tile_step, ++it) {
+    for (int tile = tile0;; ++it) {
       const int split = tile / tiles_mn;
       const int kb0 = split * args.kb_per_split;
       const int kb1 = min(kb0 + args.kb_per_split, args.kb_total);
@@ -200,6 +234,28 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           phase ^= 1u;
         }
       }
+      if (!next_tile(tile)) break;
+    }
+  } else if (warp == 3) {
+    // ------------------------------ tile scheduler (every CTA) ------------------------------
+    // Each CTA's scheduler warp arms its own response barrier; the even CTA issues the cancellation
+    // request, whose response is multicast to the pair.  A slot is reused only after every consumer warp
+    // of the cluster has released it (they arrive on the even CTA's barrier).
+    const bool leader = elect_one();
+    for (uint32_t k = 0;; ++k) {
+      const uint32_t slot = k % QD, ph = (k / QD) & 1u;
+      if (rank == 0) {
+        mbar_wait(bar_qgo, k & 1u);
+        if (k >= QD) mbar_wait(&bar_qempty[slot], ((k / QD) - 1u) & 1u);
+      }
+      if (leader) {
+        mbar_arrive_expect_tx(&bar_qfull[slot], 16);
+        if (rank == 0) clc_try_cancel(&clc_resp[slot], &bar_qfull[slot], NCTA == 2);
+      }
+      __syncwarp();
+      mbar_wait(&bar_qfull[slot], ph);
+      uint32_t cta_x;
+      if (!clc_decode(&clc_resp[slot], cta_x)) break;  // no cluster left: the consumers see the same and stop
     }
   } else if (warp >= 4) {
     // ------------------------------ epilogue ------------------------------
@@ -216,7 +272,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     uint8_t* srow = stage0 + lane * 128;
     const int sw = lane & 7;                  // SWIZZLE_128B: 16-byte unit j of row r lives at unit j ^ (r & 7)
     uint32_t it = 0;
-    for (int tile = tile0; tile < num_tiles; tile += tile_step, ++it) {
+    for (int tile = tile0;; ++it) {
       const int split = tile / tiles_mn;
       const int mn = tile - split * tiles_mn;
       const int m0 = (mn / args.n_tiles) * BLOCK_M + static_cast<int>(rank) * 128;  // rows held in this CTA's TMEM
@@ -390,6 +446,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           for (int q = 0; q < 4; ++q) side[q] = nside[q];
         }
       }
+      if (!next_tile(tile)) break;
     }
     if (lane == 0) tma_wait_group<0>();
   }
@@ -607,7 +664,8 @@ int gemm_plan(GemmPlan* plan, const GemmProblem& p, int num_sms) {
   }
   plan->variant = a_mn | (b_mn << 1) | (p.epilogue << 2);
   const long tiles = static_cast<long>(a.m_tiles) * a.n_tiles * a.k_splits;
-  plan->grid = static_cast<int>(tiles < units ? tiles : units) * (pair ? 2 : 1);
+  (void)units;
+  plan->grid = static_cast<int>(tiles) * (pair ? 2 : 1);  // one cluster per tile; running clusters take over the rest
   return 0;
 }
 
