@@ -112,8 +112,9 @@ def load_traffic():
         return {"value": None, "unit": None, "source": None}
 
 
-def host_batches(n, batch, seq, seed, tokenizer):
-    """n collated DummyDataset batches in pinned host memory (the reference's input ABI)."""
+def host_batches(n, batch, seq, seed, tokenizer, compact=False):
+    """n collated DummyDataset batches in pinned host memory (the reference's input ABI; compact=True: int32
+    ids only, token types and mask are rebuilt on the GPU by bqa_prepare_inputs)."""
     import importlib
 
     import numpy as np
@@ -122,7 +123,7 @@ def host_batches(n, batch, seq, seed, tokenizer):
     ds = ds_mod.DummyDataset(tokenizer, max_seq_len=seq, max_question_len=64)
     out = []
     for _ in range(n):
-        out.append(ds_mod.collate_fun([ds[i] for i in range(batch)], tokenizer, pin_memory=True))
+        out.append(ds_mod.collate_fun([ds[i] for i in range(batch)], tokenizer, pin_memory=True, compact=compact))
     return out
 
 
@@ -155,7 +156,7 @@ def run_native(args):
     trainer.set_train()
     eng = model.engine
     B, S = args.batch, args.seq
-    hb = host_batches(4, B, S, 1234 + rank, tokenizer)
+    hb = host_batches(4, B, S, 1234 + rank, tokenizer, compact=True)
     db = [trainer._to_device(b) for b in hb]
     torch.cuda.synchronize()
 
@@ -239,7 +240,7 @@ def run_native(args):
                             for k, v in prof.items()},
                 "step_model_frac": round(value / world * FLOP_PER_SAMPLE_BASE_384 / 1e12 / peak, 4)
                 if S == 384 else None}
-    h2d = sum(t.numel() * t.element_size() for d in hb[0] for t in d.values())
+    h2d = sum(t.numel() * t.element_size() for d in hb[0] for t in d.values() if hasattr(t, "numel"))
     out = {"metric": METRIC, "value": round(value, 2), "unit": "samples/s", "n_gpus": world, "steps": args.steps,
            "warmup": max(args.warmup, 3), "ms_per_step": round(ms_total / args.steps, 4), "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",

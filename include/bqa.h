@@ -146,6 +146,19 @@ BQA_API int bqa_clip_adamw(float* p, float* g, float* m, float* v, void* p_bf16,
 BQA_API int bqa_f32_to_bf16(const float* src, void* dst, uint64_t n, void* stream);
 
 /* ------------------------------------------------------------------------------------
+ * Model inputs from compact token ids, on the device.  Replaces the host loops of collate_fun
+ * (modules/model/dataset/split_dataset.py:480-499) and two of the three host-to-device copies of
+ * Trainer._to_device (trainer.py:239-249): the host ships int32 ids only.
+ *   input_ids = ids, attention_mask = ids > 0 (uint8), token_type_ids = 0 up to and including the
+ *   first [SEP] of a row and 1 after it, padding included (all 0 when type_coef == 0: RoBERTa).
+ *   *missing_sep (may be NULL) is set to 1 if a row has no [SEP] and type_coef != 0; the reference
+ *   raises ValueError there (list.index), and so does the host-side collate of this package.
+ * ------------------------------------------------------------------------------------ */
+BQA_API int bqa_prepare_inputs(const int32_t* ids32, int32_t B, int32_t S, int32_t sep_token_id, int32_t type_coef,
+                               int64_t* input_ids, int64_t* token_type_ids, uint8_t* attention_mask,
+                               int32_t* missing_sep, void* stream);
+
+/* ------------------------------------------------------------------------------------
  * Span decoding (modules/model/inference/predictor.py:114-120): per row, first-index arg max
  * and max of the start and end logits, arg max / max probability of softmax(cls), and
  * score = max_start + max_end - (start[0] + end[0]).

@@ -80,6 +80,7 @@ SIGNATURES = {
                                       c_f32, c_f32, c_f32, c_i32, vp]),
     "bqa_f32_to_bf16": (ctypes.c_int, [vp, vp, c_u64, vp]),
     "bqa_decode": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, c_i32, c_i32, c_i32, vp]),
+    "bqa_prepare_inputs": (ctypes.c_int, [vp, c_i32, c_i32, c_i32, c_i32, vp, vp, vp, vp, vp]),
     "bqa_param_layout": (ctypes.c_int, [ctypes.POINTER(Config), ctypes.POINTER(Layout)]),
     "bqa_workspace_bytes": (ctypes.c_int, [ctypes.POINTER(Config), c_i32, c_i32, c_i32, ctypes.POINTER(c_u64)]),
     "bqa_create": (ctypes.c_int, [ctypes.POINTER(Config), ctypes.POINTER(vp)]),

@@ -149,4 +149,15 @@ int bqa_decode(const float* start, const float* end, const float* cls, int64_t* 
                        reinterpret_cast<cudaStream_t>(stream));
 }
 
+int bqa_prepare_inputs(const int32_t* ids32, int32_t B, int32_t S, int32_t sep_token_id, int32_t type_coef,
+                       int64_t* input_ids, int64_t* token_type_ids, uint8_t* attention_mask, int32_t* missing_sep,
+                       void* stream) {
+  if (B < 1 || S < 1) {
+    set_error("bqa_prepare_inputs: empty input (B=%d S=%d)", B, S);
+    return 1;
+  }
+  return launch_prepare_inputs(ids32, input_ids, token_type_ids, attention_mask, B, S, sep_token_id, type_coef,
+                               missing_sep, reinterpret_cast<cudaStream_t>(stream));
+}
+
 }  // extern "C"

@@ -29,6 +29,8 @@ int launch_ln_bwd(const bf16* dy, const bf16* z, const float* gamma, bf16* dz, b
                   float* dbeta, float* dbias, int T, int H, float eps, DropKey drop_in, DropKey drop_out,
                   int num_sms, cudaStream_t st);
 int launch_colsum(const bf16* X, int ld, float* out, int T, int N, int num_sms, cudaStream_t st);
+int launch_prepare_inputs(const int32_t* ids32, int64_t* ids, int64_t* token_type, uint8_t* mask, int B, int S,
+                          int sep_id, int type_coef, int* missing_sep, cudaStream_t st);
 int launch_embed_bwd(const bf16* dz0, const int64_t* ids, const int64_t* token_type, float* dword, float* dpos,
                      float* dtype, int T, int S, int H, int pad_id, cudaStream_t st);
 

@@ -536,6 +536,38 @@ embed_pos_type_bwd_kernel(const bf16* __restrict__ dz0, const int64_t* __restric
     }
 }
 
+// Model inputs from compact token ids (collate_fun, split_dataset.py:480-499, done on the device):
+//   input_ids = ids (widened), attention_mask = ids > 0,
+//   token_type_ids = 0 up to and including the first [SEP] of the row, 1 after it (and on the padding);
+//   all zeros when type_coef == 0 (RoBERTa).  A row without [SEP] gets token type 0 everywhere and sets
+//   *missing_sep (the host-side collate raises for it like the reference's list.index).
+__global__ void __launch_bounds__(128)
+prepare_inputs_kernel(const int32_t* __restrict__ ids32, int64_t* __restrict__ ids, int64_t* __restrict__ token_type,
+                      uint8_t* __restrict__ mask, int S, int sep_id, int type_coef, int* __restrict__ missing_sep) {
+  __shared__ int s_first[4];
+  const int b = blockIdx.x;
+  const int32_t* row = ids32 + static_cast<size_t>(b) * S;
+  int first = S;
+  for (int j = threadIdx.x; j < S; j += blockDim.x)
+    if (row[j] == sep_id) {
+      first = j;
+      break;  // this thread's positions are increasing
+    }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) first = min(first, __shfl_xor_sync(0xffffffffu, first, o));
+  if ((threadIdx.x & 31) == 0) s_first[threadIdx.x >> 5] = first;
+  __syncthreads();
+  first = min(min(s_first[0], s_first[1]), min(s_first[2], s_first[3]));
+  if (first == S && type_coef != 0 && threadIdx.x == 0 && missing_sep != nullptr) *missing_sep = 1;
+  for (int j = threadIdx.x; j < S; j += blockDim.x) {
+    const int32_t id = row[j];
+    const size_t o = static_cast<size_t>(b) * S + j;
+    ids[o] = id;
+    mask[o] = id > 0 ? 1 : 0;
+    token_type[o] = (type_coef != 0 && j > first) ? 1 : 0;
+  }
+}
+
 }  // namespace
 
 static inline int row_blocks(int T) { return (T + ROW_WARPS - 1) / ROW_WARPS; }
@@ -623,6 +655,12 @@ int launch_embed_bwd(const bf16* dz0, const int64_t* ids, const int64_t* token_t
   if (check_launch("embed_word_bwd")) return 1;
   embed_pos_type_bwd_kernel<<<S, 128 * PT_GROUPS, 0, st>>>(dz0, token_type, dpos, dtype, T / S, S, H);
   return check_launch("embed_pos_type_bwd");
+}
+
+int launch_prepare_inputs(const int32_t* ids32, int64_t* ids, int64_t* token_type, uint8_t* mask, int B, int S,
+                          int sep_id, int type_coef, int* missing_sep, cudaStream_t st) {
+  prepare_inputs_kernel<<<B, 128, 0, st>>>(ids32, ids, token_type, mask, S, sep_id, type_coef, missing_sep);
+  return check_launch("prepare_inputs");
 }
 
 }  // namespace bqa

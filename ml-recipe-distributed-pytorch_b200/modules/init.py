@@ -123,5 +123,6 @@ def init_datasets(params, *, tokenizer=None, clear=False):
     return train_dataset, test_dataset, weights
 
 
-def init_collate_fun(tokenizer, return_items=False):
-    return functools.partial(collate_fun, tokenizer=tokenizer, return_items=return_items)
+def init_collate_fun(tokenizer, return_items=False, compact=False):
+    """compact=True: batches carry int32 ids only and Trainer._to_device builds the model inputs on the GPU."""
+    return functools.partial(collate_fun, tokenizer=tokenizer, return_items=return_items, compact=compact)

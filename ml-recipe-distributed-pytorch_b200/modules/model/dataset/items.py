@@ -59,11 +59,18 @@ class ChunkItem:
     t2o: List[int] = field(default_factory=list)
 
 
-def collate_fun(items, tokenizer, return_items=False, pin_memory=False):
+def collate_fun(items, tokenizer, return_items=False, pin_memory=False, compact=False):
     """Pads to the batch maximum; token_type 0 up to and including the first [SEP], 1 after
-    (BERT only); attention_mask = ids > 0; labels as int64 / fp32 vectors."""
+    (BERT only); attention_mask = ids > 0; labels as int64 / fp32 vectors.
+
+    compact=True ships only int32 token ids (`input_ids_i32`, plus the two scalars the device needs):
+    `expand_compact_inputs` / `Trainer._to_device` rebuild input_ids, token_type_ids and
+    attention_mask on the GPU (bqa_prepare_inputs), a quarter of the host-to-device bytes and no
+    per-row Python loop over positions."""
     n = len(items)
     max_len = max(len(it.input_ids) for it in items)
+    if compact:
+        return _collate_compact(items, tokenizer, n, max_len, return_items, pin_memory)
     tokens = np.full((n, max_len), tokenizer.pad_token_id, dtype=np.int64)
     bert = tokenizer.model_name == 'bert'
     token_type = np.full((n, max_len), 1 if bert else 0, dtype=np.int64)
@@ -88,3 +95,50 @@ def collate_fun(items, tokenizer, return_items=False, pin_memory=False):
     if return_items:
         return [inputs, labels, items]
     return [inputs, labels]
+
+
+def _labels(items):
+    return {'start_class': torch.tensor([it.start_id for it in items], dtype=torch.int64),
+            'end_class': torch.tensor([it.end_id for it in items], dtype=torch.int64),
+            'start_reg': torch.tensor([it.start_position for it in items], dtype=torch.float32),
+            'end_reg': torch.tensor([it.end_position for it in items], dtype=torch.float32),
+            'cls': torch.tensor([it.label_id for it in items], dtype=torch.int64)}
+
+
+def _collate_compact(items, tokenizer, n, max_len, return_items, pin_memory):
+    bert = tokenizer.model_name == 'bert'
+    sep = tokenizer.sep_token_id
+    tokens = np.full((n, max_len), tokenizer.pad_token_id, dtype=np.int32)
+    for i, it in enumerate(items):
+        row = np.asarray(it.input_ids, dtype=np.int32)
+        if bert and not (row == sep).any():
+            raise ValueError(f'{sep} is not in list')  # the reference's row.index(sep_token_id)
+        tokens[i, :len(row)] = row
+    inputs = {'input_ids_i32': torch.from_numpy(tokens), 'sep_token_id': int(sep), 'type_coef': 1 if bert else 0}
+    labels = _labels(items)
+    if pin_memory and torch.cuda.is_available():
+        inputs['input_ids_i32'] = inputs['input_ids_i32'].pin_memory()
+        labels = {k: v.pin_memory() for k, v in labels.items()}
+    if return_items:
+        return [inputs, labels, items]
+    return [inputs, labels]
+
+
+def expand_compact_inputs(inputs, device):
+    """{'input_ids_i32', 'sep_token_id', 'type_coef'} -> the model's input dict on `device`, built by
+    bqa_prepare_inputs (collate_fun's token-type / mask rules, include/bqa.h)."""
+    import ctypes
+
+    from .... import _lib as L
+    ids32 = inputs['input_ids_i32'].to(device, non_blocking=True)
+    if ids32.device.type != 'cuda':
+        raise RuntimeError('compact inputs are expanded by a CUDA kernel: there is no CPU path')
+    B, S = ids32.shape
+    ids = torch.empty(B, S, dtype=torch.int64, device=device)
+    tt = torch.empty(B, S, dtype=torch.int64, device=device)
+    mask = torch.empty(B, S, dtype=torch.bool, device=device)
+    with torch.cuda.device(ids32.device):
+        L.check(L.lib.bqa_prepare_inputs(ids32.data_ptr(), B, S, int(inputs['sep_token_id']), int(inputs['type_coef']),
+                                         ids.data_ptr(), tt.data_ptr(), mask.data_ptr(), None,
+                                         L.current_stream_ptr()), 'bqa_prepare_inputs')
+    return {'input_ids': ids, 'attention_mask': mask, 'token_type_ids': tt}

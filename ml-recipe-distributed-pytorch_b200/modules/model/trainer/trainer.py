@@ -27,6 +27,7 @@ import torch
 import torch.nn as nn
 from torch.utils.data import DataLoader, DistributedSampler, RandomSampler, WeightedRandomSampler
 
+from ..dataset import expand_compact_inputs
 from .callback import TestCallback
 from .meters import AverageMeter
 from .reducer import GradReducer
@@ -233,6 +234,8 @@ class Trainer:
         if isinstance(data, torch.Tensor):
             return data.to(self.device, non_blocking=True)
         if isinstance(data, dict):
+            if 'input_ids_i32' in data:  # collate_fun(compact=True): int32 ids only, the rest is built on the GPU
+                return expand_compact_inputs(data, self.device)
             return {k: self._to_device(v) for k, v in data.items()}
         if data is None:
             return data

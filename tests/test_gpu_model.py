@@ -315,3 +315,32 @@ def test_bad_inputs_fail_loudly(pkg):
             model(torch.zeros(1, 600, dtype=torch.int64, device=DEV))
     with pytest.raises(NotImplementedError):
         model(torch.zeros(1, 8, dtype=torch.int64, device=DEV), head_mask=torch.ones(2))
+
+
+def test_inputs_built_on_device_equal_collate_fun(pkg):
+    """bqa_prepare_inputs (token types up to the first [SEP], mask = ids > 0, padding rules) against the
+    host collate_fun on ragged rows, through Trainer._to_device's compact path."""
+    ds = importlib.import_module("bqa_b200.modules.model.dataset")
+    rng = np.random.default_rng(3)
+    tok = types.SimpleNamespace(pad_token_id=0, sep_token_id=102, cls_token_id=101, model_name='bert')
+    items = []
+    for i in range(37):
+        q = rng.integers(1, 60)
+        d = rng.integers(1, 300)
+        row = [101] + rng.integers(103, 30000, q).tolist() + [102] + rng.integers(103, 30000, d).tolist() + [102]
+        items.append(ds.DatasetItem(example_id=str(i), input_ids=row, start_id=0, end_id=len(row) - 1, label_id=0,
+                                    start_position=0.0, end_position=1.0))
+    items.append(ds.DatasetItem(example_id='sep-first', input_ids=[102, 7, 8], start_id=0, end_id=1, label_id=0,
+                                start_position=0.0, end_position=1.0))
+    full, _ = ds.collate_fun(items, tok)
+    compact, _ = ds.collate_fun(items, tok, compact=True, pin_memory=True)
+    got = ds.expand_compact_inputs(compact, torch.device(DEV))
+    torch.cuda.synchronize()
+    for k in ("input_ids", "token_type_ids", "attention_mask"):
+        assert got[k].dtype == full[k].dtype, k
+        assert torch.equal(got[k].cpu(), full[k]), k
+    # RoBERTa rule: type_coef = 0 -> all token types 0
+    tok_r = types.SimpleNamespace(pad_token_id=0, sep_token_id=102, cls_token_id=101, model_name='roberta')
+    full_r, _ = ds.collate_fun(items, tok_r)
+    got_r = ds.expand_compact_inputs(ds.collate_fun(items, tok_r, compact=True)[0], torch.device(DEV))
+    assert torch.equal(got_r["token_type_ids"].cpu(), full_r["token_type_ids"])

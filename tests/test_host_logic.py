@@ -191,3 +191,27 @@ def test_model_skeleton_has_reference_state_dict_keys(mods):
     assert m.transformer.config.hidden_size == 64 and m.transformer.config.num_labels == 5
     with pytest.raises(RuntimeError, match="CUDA"):
         m(torch.zeros(1, 8, dtype=torch.int64))
+
+
+def test_compact_collate_matches_reference_layout_and_raises_without_sep():
+    """collate_fun(compact=True) ships the same ids as int32 and keeps the reference's ValueError
+    (row.index(sep_token_id), split_dataset.py:495) for a row without [SEP]."""
+    import importlib
+    import types
+    ds = importlib.import_module("bqa_b200.modules.model.dataset")
+    tok = types.SimpleNamespace(pad_token_id=0, sep_token_id=102, cls_token_id=101, model_name='bert')
+    items = [ds.DatasetItem(example_id='a', input_ids=[101, 5, 6, 102, 7, 8, 9, 102], start_id=4, end_id=6, label_id=1,
+                            start_position=0.5, end_position=0.75),
+             ds.DatasetItem(example_id='b', input_ids=[101, 5, 102, 7, 102], start_id=-1, end_id=-1, label_id=0,
+                            start_position=0.0, end_position=1.0)]
+    full, labels = ds.collate_fun(items, tok)
+    compact, labels_c = ds.collate_fun(items, tok, compact=True)
+    assert compact['input_ids_i32'].dtype == torch.int32
+    assert torch.equal(compact['input_ids_i32'].long(), full['input_ids'])
+    assert compact['sep_token_id'] == 102 and compact['type_coef'] == 1
+    for k in labels:
+        assert torch.equal(labels[k], labels_c[k])
+    bad = [ds.DatasetItem(example_id='c', input_ids=[101, 5, 6], start_id=0, end_id=0, label_id=0,
+                          start_position=0.0, end_position=1.0)]
+    with pytest.raises(ValueError):
+        ds.collate_fun(bad, tok, compact=True)
