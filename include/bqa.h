@@ -143,6 +143,14 @@ BQA_API int bqa_clip_adamw(float* p, float* g, float* m, float* v, void* p_bf16,
                            int32_t n_chunks, const double* sumsq, float max_grad_norm, const float* host_lr,
                            int32_t n_groups, float beta1, float beta2, float eps, int32_t zero_grad,
                            void* stream);
+/* AdaMod (modules/model/trainer/optim.py:42-100, params.optimizer == 'adamod') in the same fused form:
+ * clip, Adam moments with bias correction (step = 1-based step count of this update), decoupled
+ * weight decay applied before the update, the moving average `s` (exp_avg_lr, beta3) of the
+ * per-element learning rates and the momental bound min(eta, s). */
+BQA_API int bqa_clip_adamod(float* p, float* g, float* m, float* v, float* s, void* p_bf16,
+                            const bqa_adamw_chunk* chunks, int32_t n_chunks, const double* sumsq,
+                            float max_grad_norm, const float* host_lr, int32_t n_groups, float beta1, float beta2,
+                            float beta3, float eps, int64_t step, int32_t zero_grad, void* stream);
 BQA_API int bqa_f32_to_bf16(const float* src, void* dst, uint64_t n, void* stream);
 
 /* ------------------------------------------------------------------------------------
@@ -211,13 +219,14 @@ BQA_API int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* 
                         uint64_t step, float* start, float* end, float* cls, float* reg_start, float* reg_end,
                         void* stream);
 
-enum bqa_cls_loss { BQA_CLS_SMOOTH = 0, BQA_CLS_CE = 1 };
+enum bqa_cls_loss { BQA_CLS_SMOOTH = 0, BQA_CLS_CE = 1, BQA_CLS_FOCAL = 2 };
 typedef struct bqa_loss_config {
   float w_start, w_end, w_start_reg, w_end_reg, w_cls; /* init.py:19-38                       */
-  int32_t cls_loss;                                    /* params.loss: 'smooth' | 'ce'        */
+  int32_t cls_loss;                                    /* params.loss: 'smooth' | 'ce' | 'focal' */
   float smooth_alpha;
   const float* cls_weight; /* DEVICE [num_labels] fp32 or NULL (loss='ce' label weights)       */
   float loss_scale;        /* 1 / batch_split (trainer.py:198); scales gradients only          */
+  float focal_alpha, focal_gamma; /* FocalLossWithLogits(alpha, gamma) (loss.py:57-71), loss='focal'    */
 } bqa_loss_config;
 
 /* Loss of the last bqa_forward outputs against labels (int64 / fp32 [B]).  losses: DEVICE

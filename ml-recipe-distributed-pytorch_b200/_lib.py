@@ -9,10 +9,10 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbqa.so")
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 EPI_LINEAR, EPI_GELU_FWD, EPI_GELU_BWD, EPI_F32_ADD = 0, 1, 2, 3
-CLS_SMOOTH, CLS_CE = 0, 1
+CLS_SMOOTH, CLS_CE, CLS_FOCAL = 0, 1, 2
 
 c_i32, c_i64, c_u32, c_u64, c_f32 = ctypes.c_int32, ctypes.c_int64, ctypes.c_uint32, ctypes.c_uint64, ctypes.c_float
 vp = ctypes.c_void_p
@@ -53,7 +53,7 @@ class Layout(ctypes.Structure):
 class LossConfig(ctypes.Structure):
     _fields_ = [("w_start", c_f32), ("w_end", c_f32), ("w_start_reg", c_f32), ("w_end_reg", c_f32),
                 ("w_cls", c_f32), ("cls_loss", c_i32), ("smooth_alpha", c_f32), ("cls_weight", vp),
-                ("loss_scale", c_f32)]
+                ("loss_scale", c_f32), ("focal_alpha", c_f32), ("focal_gamma", c_f32)]
 
 
 class AdamWChunk(ctypes.Structure):
@@ -78,6 +78,8 @@ SIGNATURES = {
     "bqa_grad_sumsq_noalloc": (ctypes.c_int, [vp, c_u64, vp, vp]),
     "bqa_clip_adamw": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, c_i32, vp, c_f32, ctypes.POINTER(c_f32), c_i32,
                                       c_f32, c_f32, c_f32, c_i32, vp]),
+    "bqa_clip_adamod": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, c_i32, vp, c_f32, ctypes.POINTER(c_f32), c_i32,
+                                       c_f32, c_f32, c_f32, c_f32, c_i64, c_i32, vp]),
     "bqa_f32_to_bf16": (ctypes.c_int, [vp, vp, c_u64, vp]),
     "bqa_decode": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, c_i32, c_i32, c_i32, vp]),
     "bqa_prepare_inputs": (ctypes.c_int, [vp, c_i32, c_i32, c_i32, c_i32, vp, vp, vp, vp, vp]),

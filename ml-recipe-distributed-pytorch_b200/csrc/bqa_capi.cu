@@ -1,6 +1,8 @@
 // bqa_capi.cu — extern "C" surface of libbqa (declared in include/bqa.h).
 #include "../../include/bqa.h"
 
+#include <math.h>
+
 #include "bqa_host.cuh"
 #include "gemm_sm100.cuh"
 
@@ -10,7 +12,7 @@ extern "C" {
 
 const char* bqa_last_error(void) { return bqa::last_error(); }
 
-int bqa_abi_version(void) { return 1; }
+int bqa_abi_version(void) { return 2; }
 
 int bqa_gemm_bf16(const bqa_gemm_desc* d, void* stream) {
   if (d == nullptr) {
@@ -130,6 +132,33 @@ int bqa_clip_adamw(float* p, float* g, float* m, float* v, void* p_bf16, const b
   return launch_clip_adamw(p, g, m, v, reinterpret_cast<bf16*>(p_bf16), reinterpret_cast<const AdamWChunk*>(chunks),
                            n_chunks, sumsq, max_grad_norm, t, beta1, beta2, eps, zero_grad,
                            reinterpret_cast<cudaStream_t>(stream));
+}
+
+int bqa_clip_adamod(float* p, float* g, float* m, float* v, float* s, void* p_bf16, const bqa_adamw_chunk* chunks,
+                    int32_t n_chunks, const double* sumsq, float max_grad_norm, const float* host_lr,
+                    int32_t n_groups, float beta1, float beta2, float beta3, float eps, int64_t step,
+                    int32_t zero_grad, void* stream) {
+  if (n_groups < 1 || n_groups > 8 || host_lr == nullptr) {
+    set_error("bqa_clip_adamod: need 1..8 parameter groups");
+    return 1;
+  }
+  if (max_grad_norm > 0.0f && sumsq == nullptr) {
+    set_error("bqa_clip_adamod: clipping needs the sum of squares");
+    return 1;
+  }
+  if (step < 1 || s == nullptr) {
+    set_error("bqa_clip_adamod: step must be >= 1 and the exp_avg_lr buffer non-null");
+    return 1;
+  }
+  LrTable t{};
+  for (int i = 0; i < n_groups; ++i) t.lr[i] = host_lr[i];
+  // step_size = lr * sqrt(1 - beta2^t) / (1 - beta1^t)   (optim.py:83-85), in double on the host
+  const double bc1 = 1.0 - pow(static_cast<double>(beta1), static_cast<double>(step));
+  const double bc2 = 1.0 - pow(static_cast<double>(beta2), static_cast<double>(step));
+  const float bias_mul = static_cast<float>(sqrt(bc2) / bc1);
+  return launch_clip_adamod(p, g, m, v, s, reinterpret_cast<bf16*>(p_bf16),
+                            reinterpret_cast<const AdamWChunk*>(chunks), n_chunks, sumsq, max_grad_norm, t, beta1,
+                            beta2, beta3, eps, bias_mul, zero_grad, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int bqa_f32_to_bf16(const float* src, void* dst, uint64_t n, void* stream) {

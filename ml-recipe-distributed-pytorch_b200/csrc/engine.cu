@@ -615,13 +615,15 @@ static int to_loss_config(const bqa_loss_config* lc, LossConfig* k) {
     set_error("loss: null configuration");
     return 1;
   }
-  if (lc->cls_loss != BQA_CLS_SMOOTH && lc->cls_loss != BQA_CLS_CE) {
-    set_error("loss: unsupported class loss %d (focal loss is not implemented)", lc->cls_loss);
+  if (lc->cls_loss != BQA_CLS_SMOOTH && lc->cls_loss != BQA_CLS_CE && lc->cls_loss != BQA_CLS_FOCAL) {
+    set_error("loss: unsupported class loss %d", lc->cls_loss);
     return 1;
   }
   k->w_start = lc->w_start; k->w_end = lc->w_end;
   k->w_start_reg = lc->w_start_reg; k->w_end_reg = lc->w_end_reg; k->w_cls = lc->w_cls;
-  k->cls_kind = lc->cls_loss == BQA_CLS_CE ? CLS_LOSS_CE : CLS_LOSS_SMOOTH;
+  k->cls_kind = lc->cls_loss == BQA_CLS_CE ? CLS_LOSS_CE : (lc->cls_loss == BQA_CLS_FOCAL ? CLS_LOSS_FOCAL : CLS_LOSS_SMOOTH);
+  k->focal_alpha = lc->focal_alpha;
+  k->focal_gamma = lc->focal_gamma;
   k->smooth_alpha = lc->smooth_alpha;
   k->cls_weight = lc->cls_weight;
   k->grad_scale = lc->loss_scale;

@@ -137,9 +137,12 @@ loss_rows_kernel(const float* __restrict__ start, const float* __restrict__ end,
       if (threadIdx.x == 1) cnt += (y_end[i] != -1) ? 1.0f : 0.0f;
       if (threadIdx.x == 2) {
         const long long yc = y_cls[i];
-        if (yc != -100) cnt += (lc.cls_kind == CLS_LOSS_CE && lc.cls_weight != nullptr && yc >= 0 && yc < C)
-                                   ? lc.cls_weight[yc]
-                                   : 1.0f;
+        if (lc.cls_kind == CLS_LOSS_FOCAL) {
+          if (yc != -1) cnt += 1.0f;  // NLLLoss(ignore_index=-1)
+        } else if (yc != -100) {
+          cnt += (lc.cls_kind == CLS_LOSS_CE && lc.cls_weight != nullptr && yc >= 0 && yc < C) ? lc.cls_weight[yc]
+                                                                                                 : 1.0f;
+        }
       }
     }
     s_cnt[threadIdx.x] = cnt;
@@ -213,6 +216,27 @@ loss_rows_kernel(const float* __restrict__ start, const float* __restrict__ end,
           d_cls[static_cast<size_t>(b) * C + c] =
               lc.w_cls * lc.grad_scale * (__expf(z[c] - lse) * tsum - t) / static_cast<float>(B);
         }
+    } else if (lc.cls_kind == CLS_LOSS_FOCAL) {
+      // FocalLossWithLogits (loss.py:57-71): NLLLoss(ignore_index=-1, mean) of alpha (1 - p)^gamma log p
+      //   f(p_y) = -alpha (1 - p_y)^gamma log p_y ;  d f / d z_c = f'(p_y) p_y (delta_cy - p_c)
+      const bool valid = (y != -1) && y >= 0 && y < C;
+      const float den = s_cnt[2];
+      float fprime_p = 0.0f;
+      if (valid) {
+        const float logp = z[y] - lse;
+        const float py = __expf(logp);
+        const float om = fmaxf(1.0f - py, 0.0f);
+        const float pw = __powf(om, lc.focal_gamma);             // (1 - p)^gamma
+        const float pw1 = lc.focal_gamma == 0.0f ? 0.0f : lc.focal_gamma * __powf(om, lc.focal_gamma - 1.0f);
+        l = -lc.focal_alpha * pw * logp / den;
+        // f'(p) p = alpha (gamma (1 - p)^(gamma - 1) p log p - (1 - p)^gamma)
+        fprime_p = lc.focal_alpha * (pw1 * py * logp - pw);
+      }
+      if (den == 0.0f) l = __int_as_float(0x7fc00000);
+      if (with_grad)
+        for (int c = 0; c < C; ++c)
+          d_cls[static_cast<size_t>(b) * C + c] =
+              valid ? lc.w_cls * lc.grad_scale * fprime_p * ((c == y ? 1.0f : 0.0f) - __expf(z[c] - lse)) / den : 0.0f;
     } else {
       // nn.CrossEntropyLoss(weight) / NLLLoss(ignore_index=-100): weighted mean over valid rows
       const bool valid = (y != -100) && y >= 0 && y < C;

@@ -51,13 +51,14 @@ int launch_span_head_fwd(const bf16* y, const float* span_w, const float* span_b
 int launch_pooler_heads_fwd(const bf16* y, const HeadParams& hp, float* pooled, float* cls, float* reg_s,
                             float* reg_e, int B, int S, int H, int C, DropKey cls_drop, cudaStream_t st);
 
-enum ClsLossKind : int { CLS_LOSS_SMOOTH = 0, CLS_LOSS_CE = 1 };
+enum ClsLossKind : int { CLS_LOSS_SMOOTH = 0, CLS_LOSS_CE = 1, CLS_LOSS_FOCAL = 2 };
 struct LossConfig {
   float w_start, w_end, w_start_reg, w_end_reg, w_cls;
   int cls_kind;
   float smooth_alpha;
   const float* cls_weight;  // [C] fp32 or null (CrossEntropyLoss(weight=...))
   float grad_scale;         // 1 / batch_split (trainer.py:198)
+  float focal_alpha, focal_gamma;  // FocalLossWithLogits (loss.py:57-71)
 };
 // losses_out[6] = {start_class, end_class, start_reg, end_reg, cls, total}
 // d_reg_s / d_reg_e are gradients w.r.t. the sigmoid OUTPUTS (what autograd would hand back)
@@ -92,6 +93,9 @@ int launch_clip_adamw(float* p, float* g, float* m, float* v, bf16* p_bf16, cons
                       int n_chunks, const double* sumsq, float max_grad_norm, LrTable lrs, float beta1,
                       float beta2, float eps, int zero_grad, cudaStream_t st);
 int sumsq_scratch_floats(int num_sms);
+int launch_clip_adamod(float* p, float* g, float* m, float* v, float* s, bf16* p_bf16, const AdamWChunk* chunks_dev,
+                       int n_chunks, const double* sumsq, float max_grad_norm, LrTable lrs, float beta1,
+                       float beta2, float beta3, float eps, float bias_mul, int zero_grad, cudaStream_t st);
 int launch_f32_to_bf16(const float* src, bf16* dst, size_t n, int num_sms, cudaStream_t st);
 
 // ---- attention_sm100.cu ------------------------------------------------------------------

@@ -100,6 +100,59 @@ clip_adamw_kernel(float* __restrict__ p, float* __restrict__ g, float* __restric
   }
 }
 
+// AdaMod (reference optim.py:42-100) with the same chunk table, clip coefficient, zero_grad and bf16
+// shadow refresh as clip_adamw_kernel.  ss = lr * sqrt(1 - beta2^t) / (1 - beta1^t) per group.
+__global__ void __launch_bounds__(256)
+clip_adamod_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                   float* __restrict__ s, bf16* __restrict__ pb, const AdamWChunk* __restrict__ chunks,
+                   const double* __restrict__ sumsq, float max_grad_norm, LrTable lrs, float beta1, float beta2,
+                   float beta3, float eps, float bias_mul, int zero_grad) {
+  const AdamWChunk ch = chunks[blockIdx.x];
+  const float lr = lrs.lr[ch.group & 7];
+  float coef = 1.0f;
+  if (max_grad_norm > 0.0f) {
+    const float total = sqrtf(static_cast<float>(*sumsq));
+    coef = fminf(max_grad_norm / (total + 1e-6f), 1.0f);
+  }
+  const float ss = lr * bias_mul;                    // step_size before the division by denom
+  const float wd_mul = 1.0f - lr * ch.weight_decay;  // p.data.add_(-weight_decay * lr, p.data), before the update
+  for (uint64_t i = ch.begin + threadIdx.x * 4ull; i < ch.end; i += blockDim.x * 4ull) {
+    float4 gg = *reinterpret_cast<const float4*>(g + i);
+    float4 pp = *reinterpret_cast<const float4*>(p + i);
+    float4 mm = *reinterpret_cast<const float4*>(m + i);
+    float4 vv = *reinterpret_cast<const float4*>(v + i);
+    float4 sv = *reinterpret_cast<const float4*>(s + i);
+    float* gp = reinterpret_cast<float*>(&gg);
+    float* ppp = reinterpret_cast<float*>(&pp);
+    float* mp = reinterpret_cast<float*>(&mm);
+    float* vp = reinterpret_cast<float*>(&vv);
+    float* sp = reinterpret_cast<float*>(&sv);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float gk = gp[k] * coef;
+      mp[k] = beta1 * mp[k] + (1.0f - beta1) * gk;
+      vp[k] = beta2 * vp[k] + (1.0f - beta2) * gk * gk;
+      float x = ppp[k];
+      if (ch.weight_decay != 0.0f) x *= wd_mul;
+      float eta = ss / (sqrtf(vp[k]) + eps);
+      sp[k] = beta3 * sp[k] + (1.0f - beta3) * eta;
+      eta = fminf(eta, sp[k]);
+      ppp[k] = x - eta * mp[k];
+    }
+    *reinterpret_cast<float4*>(p + i) = pp;
+    *reinterpret_cast<float4*>(m + i) = mm;
+    *reinterpret_cast<float4*>(v + i) = vv;
+    *reinterpret_cast<float4*>(s + i) = sv;
+    if (pb != nullptr) {
+      uint2 o;
+      o.x = pack_bf16x2(ppp[0], ppp[1]);
+      o.y = pack_bf16x2(ppp[2], ppp[3]);
+      *reinterpret_cast<uint2*>(pb + i) = o;
+    }
+    if (zero_grad) *reinterpret_cast<float4*>(g + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
 __global__ void __launch_bounds__(256)
 f32_to_bf16_kernel(const float* __restrict__ src, bf16* __restrict__ dst, size_t n) {
   const size_t n4 = n / 4;
@@ -140,6 +193,15 @@ int launch_clip_adamw(float* p, float* g, float* m, float* v, bf16* p_bf16, cons
   clip_adamw_kernel<<<n_chunks, 256, 0, st>>>(p, g, m, v, p_bf16, chunks_dev, sumsq, max_grad_norm, lrs, beta1,
                                               beta2, eps, zero_grad);
   return check_launch("clip_adamw");
+}
+
+int launch_clip_adamod(float* p, float* g, float* m, float* v, float* s, bf16* p_bf16, const AdamWChunk* chunks_dev,
+                       int n_chunks, const double* sumsq, float max_grad_norm, LrTable lrs, float beta1,
+                       float beta2, float beta3, float eps, float bias_mul, int zero_grad, cudaStream_t st) {
+  if (n_chunks <= 0) return 0;
+  clip_adamod_kernel<<<n_chunks, 256, 0, st>>>(p, g, m, v, s, p_bf16, chunks_dev, sumsq, max_grad_norm, lrs, beta1,
+                                               beta2, beta3, eps, bias_mul, zero_grad);
+  return check_launch("clip_adamod");
 }
 
 int launch_f32_to_bf16(const float* src, bf16* dst, size_t n, int num_sms, cudaStream_t st) {

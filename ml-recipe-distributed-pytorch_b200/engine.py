@@ -206,15 +206,18 @@ class Engine:
 
 
 def make_loss_config(*, w_start=1.0, w_end=1.0, w_start_reg=1.0, w_end_reg=1.0, w_cls=1.0, loss="smooth",
-                     smooth_alpha=0.01, cls_weight=None, loss_scale=1.0):
+                     smooth_alpha=0.01, cls_weight=None, loss_scale=1.0, focal_alpha=1.0, focal_gamma=2.0):
     lc = L.LossConfig()
     lc.w_start, lc.w_end, lc.w_start_reg, lc.w_end_reg, lc.w_cls = w_start, w_end, w_start_reg, w_end_reg, w_cls
     if loss == "smooth":
         lc.cls_loss = L.CLS_SMOOTH
     elif loss == "ce":
         lc.cls_loss = L.CLS_CE
+    elif loss == "focal":
+        lc.cls_loss = L.CLS_FOCAL
     else:
-        raise NotImplementedError(f"class loss {loss!r} has no kernel (reference init.py:22-31 also offers 'focal')")
+        raise NotImplementedError(f"class loss {loss!r} (reference init.py:22-31 offers 'smooth', 'ce', 'focal')")
+    lc.focal_alpha, lc.focal_gamma = float(focal_alpha), float(focal_gamma)
     lc.smooth_alpha = smooth_alpha
     lc.cls_weight = cls_weight.data_ptr() if cls_weight is not None else None
     lc.loss_scale = loss_scale

@@ -104,7 +104,7 @@ def init_optimizer(params, model):
     if params.optimizer == 'adam':
         optimizer = FusedAdamW(groups, model, lr=params.lr, correct_bias=False)
     else:
-        optimizer = AdaMod(groups, lr=params.lr)
+        optimizer = AdaMod(groups, model, lr=params.lr)
     logger.info(f'Used optimizer: {type(optimizer).__name__}.')
     if modules is not None:
         model.list_of_trainable_modules = modules

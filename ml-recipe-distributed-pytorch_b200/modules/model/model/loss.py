@@ -30,9 +30,14 @@ class LabelSmoothingLossWithLogits(nn.Module):
 
 
 class FocalLossWithLogits(nn.Module):
-    def __init__(self, *a, **k):
+    """Configuration holder: NLLLoss(ignore_index=-1, mean) of alpha (1 - p)^gamma log p (loss.py:57-71)."""
+
+    def __init__(self, alpha=1, gamma=2, *, ignore_index=-1, reduction='mean'):
         super().__init__()
-        raise NotImplementedError("loss=focal (reference loss.py:57-71) has no kernel yet; use 'smooth' or 'ce'")
+        if ignore_index != -1 or reduction != 'mean':
+            raise NotImplementedError("the fused loss kernel implements the reference's only use: "
+                                      "ignore_index=-1, reduction='mean'")
+        self.alpha, self.gamma = alpha, gamma
 
 
 def _run_loss_kernel(outs, targets, lc, with_grad):
@@ -98,6 +103,8 @@ class WeightedLoss:
             if w is not None:
                 self._cls_weight = w.detach().to(device=device or w.device, dtype=torch.float32).contiguous()
             kw.update(loss='ce', cls_weight=self._cls_weight)
+        elif isinstance(cls_fn, FocalLossWithLogits):
+            kw.update(loss='focal', focal_alpha=float(cls_fn.alpha), focal_gamma=float(cls_fn.gamma))
         else:
             raise NotImplementedError(f"class loss {type(cls_fn).__name__} has no kernel")
         return _engine.make_loss_config(**kw)

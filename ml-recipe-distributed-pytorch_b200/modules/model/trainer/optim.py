@@ -1,8 +1,9 @@
 """Optimizer of the recipe: HF AdamW(correct_bias=False) as constructed by the reference in
 modules/init.py:125-138, fused with the global-norm clip of trainer.py:221-225 and
 `optimizer.zero_grad()` (trainer.py:287) into two kernel passes over the model's flat buffers
-(csrc/optimizer.cu).  The reference file of this name holds AdaMod (optim.py:42-100), which no
-BASELINE config uses and which has no kernel here.
+(csrc/optimizer.cu).  The reference file of this name holds AdaMod (optim.py:42-100, selected by
+`optimizer=adamod`): it is fused the same way (bqa_clip_adamod), with its third state tensor
+`exp_avg_lr`.
 
 The object is a real `torch.optim.Optimizer`: `param_groups[i]['lr']` is what LambdaLR rewrites
 and what `Trainer._get_lr` reads (trainer.py:194-195), and `state_dict()` / `load_state_dict()`
@@ -18,17 +19,18 @@ from .... import _lib as L
 CHUNK_ELEMS = 65536
 
 
-class AdaMod(torch.optim.Optimizer):
-    def __init__(self, *a, **k):
-        raise NotImplementedError("optimizer=adamod (reference optim.py:42-100) has no kernel; use optimizer=adam")
-
-
 class FusedAdamW(torch.optim.Optimizer):
+    # per-parameter state tensors (checkpoint names) and the flat buffers they are views of
+    _STATE = (('exp_avg', '_m'), ('exp_avg_sq', '_v'))
+
     def __init__(self, params, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.0, correct_bias=False):
         if correct_bias:
             raise NotImplementedError("the reference always passes correct_bias=False (init.py:137); "
                                       "bias correction has no kernel")
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
+        self._init_fused(model)
+
+    def _init_fused(self, model):
         if len(self.param_groups) > 8:
             raise ValueError("at most 8 parameter groups")
         self._model = model
@@ -42,9 +44,9 @@ class FusedAdamW(torch.optim.Optimizer):
         if self._built_for is eng:
             return eng
         dev = eng.device
-        old_m = getattr(self, "_m", None)
-        self._m = torch.zeros(eng.total, dtype=torch.float32, device=dev)
-        self._v = torch.zeros(eng.total, dtype=torch.float32, device=dev)
+        rebuilt = getattr(self, "_m", None) is not None
+        for _, attr in self._STATE:
+            setattr(self, attr, torch.zeros(eng.total, dtype=torch.float32, device=dev))
         self._sumsq = torch.zeros(1, dtype=torch.float64, device=dev)
         self._scratch = torch.empty(L.lib.bqa_sumsq_scratch_floats(), dtype=torch.float32, device=dev)
         key_of = {id(p): k for k, p in self._model.named_parameters()}
@@ -71,13 +73,13 @@ class FusedAdamW(torch.optim.Optimizer):
         # expose the moments through the standard optimizer state (checkpoint compatibility)
         for p, key in self._keys:
             st = self.state[p]
-            prev_m, prev_v = st.get('exp_avg'), st.get('exp_avg_sq')
-            m_view, v_view = eng.view(self._m, key), eng.view(self._v, key)
-            if prev_m is not None and old_m is not None:
-                m_view.copy_(prev_m)
-                v_view.copy_(prev_v)
+            for name, attr in self._STATE:
+                prev = st.get(name)
+                view = eng.view(getattr(self, attr), key)
+                if prev is not None and rebuilt:
+                    view.copy_(prev)
+                st[name] = view
             st.setdefault('step', 0)
-            st['exp_avg'], st['exp_avg_sq'] = m_view, v_view
         self._built_for = eng
         return eng
 
@@ -86,8 +88,8 @@ class FusedAdamW(torch.optim.Optimizer):
         eng = self._build()
         for p, key in self._keys:
             st = self.state[p]
-            for name, flat in (('exp_avg', self._m), ('exp_avg_sq', self._v)):
-                view = eng.view(flat, key)
+            for name, attr in self._STATE:
+                view = eng.view(getattr(self, attr), key)
                 if name in st and st[name].data_ptr() != view.data_ptr():
                     view.copy_(st[name])
                 st[name] = view
@@ -116,11 +118,7 @@ class FusedAdamW(torch.optim.Optimizer):
         g0 = self.param_groups[0]
         lrs = (ctypes.c_float * len(self.param_groups))(*[float(g['lr']) for g in self.param_groups])
         b1, b2 = g0['betas']
-        L.check(L.lib.bqa_clip_adamw(eng.params.data_ptr(), eng.grads.data_ptr(), self._m.data_ptr(),
-                                     self._v.data_ptr(), eng.shadow.data_ptr(), self._chunks.data_ptr(),
-                                     self._n_chunks, self._sumsq.data_ptr(), self._max_grad_norm, lrs,
-                                     len(self.param_groups), b1, b2, g0['eps'], 1, L.current_stream_ptr()),
-                "bqa_clip_adamw")
+        self._launch_update(eng, g0, lrs, b1, b2)
         for p, _ in self._keys:
             self.state[p]['step'] += 1
         self._max_grad_norm = 0.0
@@ -136,3 +134,40 @@ class FusedAdamW(torch.optim.Optimizer):
         self._grads_clean = True
         self._model.grads_dirty = False
         self._model.restore_grad_views()
+
+    def _launch_update(self, eng, g0, lrs, b1, b2):
+        L.check(L.lib.bqa_clip_adamw(eng.params.data_ptr(), eng.grads.data_ptr(), self._m.data_ptr(),
+                                     self._v.data_ptr(), eng.shadow.data_ptr(), self._chunks.data_ptr(),
+                                     self._n_chunks, self._sumsq.data_ptr(), self._max_grad_norm, lrs,
+                                     len(self.param_groups), b1, b2, g0['eps'], 1, L.current_stream_ptr()),
+                "bqa_clip_adamw")
+
+
+class AdaMod(FusedAdamW):
+    """AdaMod (reference modules/model/trainer/optim.py:6-100) over the model's flat buffers: the
+    reference's constructor arguments plus the model whose parameters are optimised (init.py passes
+    it).  State per parameter: {step, exp_avg, exp_avg_sq, exp_avg_lr}, as in the reference."""
+    _STATE = (('exp_avg', '_m'), ('exp_avg_sq', '_v'), ('exp_avg_lr', '_s'))
+
+    def __init__(self, params, model, lr=1e-3, betas=(0.9, 0.999), beta3=0.999, eps=1e-8, weight_decay=0):
+        if not 0.0 <= lr:
+            raise ValueError("Invalid learning rate: {}".format(lr))
+        if not 0.0 <= eps:
+            raise ValueError("Invalid epsilon value: {}".format(eps))
+        if not 0.0 <= betas[0] < 1.0:
+            raise ValueError("Invalid beta parameter at index 0: {}".format(betas[0]))
+        if not 0.0 <= betas[1] < 1.0:
+            raise ValueError("Invalid beta parameter at index 1: {}".format(betas[1]))
+        if not 0.0 <= beta3 < 1.0:
+            raise ValueError("Invalid beta3 parameter: {}".format(beta3))
+        torch.optim.Optimizer.__init__(self, params, dict(lr=lr, betas=betas, beta3=beta3, eps=eps,
+                                                          weight_decay=weight_decay))
+        self._init_fused(model)
+
+    def _launch_update(self, eng, g0, lrs, b1, b2):
+        step = self.state[self._keys[0][0]]['step'] + 1  # every parameter is updated on every step
+        L.check(L.lib.bqa_clip_adamod(eng.params.data_ptr(), eng.grads.data_ptr(), self._m.data_ptr(),
+                                      self._v.data_ptr(), self._s.data_ptr(), eng.shadow.data_ptr(),
+                                      self._chunks.data_ptr(), self._n_chunks, self._sumsq.data_ptr(),
+                                      self._max_grad_norm, lrs, len(self.param_groups), b1, b2, g0['beta3'],
+                                      g0['eps'], int(step), 1, L.current_stream_ptr()), "bqa_clip_adamod")

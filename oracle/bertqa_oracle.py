@@ -223,9 +223,11 @@ class LossConfig:
     w_start_reg: float = 1.0
     w_end_reg: float = 1.0
     w_cls: float = 1.0
-    loss: str = "smooth"          # 'smooth' | 'ce'
+    loss: str = "smooth"          # 'smooth' | 'ce' | 'focal'
     smooth_alpha: float = 0.01
     label_weights: Optional[torch.Tensor] = None
+    focal_alpha: float = 1.0
+    focal_gamma: float = 2.0
 
 
 def class_loss(logits, target, lc: LossConfig):
@@ -241,6 +243,10 @@ def class_loss(logits, target, lc: LossConfig):
         return F.nll_loss(logp, target, ignore_index=-100)
     if lc.loss == "ce":
         return F.cross_entropy(logits, target, weight=lc.label_weights)
+    if lc.loss == "focal":
+        # FocalLossWithLogits (loss.py:57-71): NLLLoss(ignore_index=-1) of alpha (1 - p)^gamma log p
+        probs = torch.exp(logp)
+        return F.nll_loss(lc.focal_alpha * (1 - probs) ** lc.focal_gamma * logp, target, ignore_index=-1)
     raise NotImplementedError(lc.loss)
 
 
@@ -299,6 +305,28 @@ def hf_adamw_step(P, grads, state, lr, weight_decay, betas=(0.9, 0.999), eps=1e-
         wd = 0.0 if any(nd in name for nd in NO_DECAY) else weight_decay
         if wd > 0.0:
             p.add_(p, alpha=-lr * wd)
+
+
+def adamod_step(P, grads, state, lr, weight_decay, betas=(0.9, 0.999), beta3=0.999, eps=1e-8):
+    """AdaMod.step (modules/model/trainer/optim.py:42-100) with the two groups of init.py:125-129.
+    Pinned by tests/golden/ref_adamod.npz (the reference class itself run for several steps)."""
+    b1, b2 = betas
+    for name, p in P.items():
+        g = grads[name]
+        st = state.setdefault(name, {"step": 0, "exp_avg": torch.zeros_like(p), "exp_avg_sq": torch.zeros_like(p),
+                                     "exp_avg_lr": torch.zeros_like(p)})
+        st["step"] += 1
+        st["exp_avg"].mul_(b1).add_(g, alpha=1.0 - b1)
+        st["exp_avg_sq"].mul_(b2).addcmul_(g, g, value=1.0 - b2)
+        denom = st["exp_avg_sq"].sqrt().add_(eps)
+        step_size = lr * math.sqrt(1.0 - b2 ** st["step"]) / (1.0 - b1 ** st["step"])
+        wd = 0.0 if any(nd in name for nd in NO_DECAY) else weight_decay
+        if wd != 0.0:
+            p.add_(p, alpha=-wd * lr)
+        eta = torch.full_like(denom, step_size).div_(denom)
+        st["exp_avg_lr"].mul_(beta3).add_(eta, alpha=1.0 - beta3)
+        eta = torch.min(eta, st["exp_avg_lr"])
+        p.add_(-eta * st["exp_avg"])
 
 
 def linear_schedule_lambda(step, num_warmup_steps, num_training_steps):

@@ -161,6 +161,45 @@ def main():
         sch.step()
     np.savez_compressed(os.path.join(OUT, "ref_schedule.npz"), lr=np.asarray(vals), warmup=np.int64(6),
                         total=np.int64(20))
+    # ---- (5) AdaMod (reference optim.py) and the focal class loss (reference loss.py), run as they are
+    import model.trainer.optim as ref_optim
+    torch.manual_seed(11)
+    names = ["transformer.w.weight", "transformer.w.bias", "classifier.weight", "x.LayerNorm.weight"]
+    shapes = [(7, 5), (7,), (3, 7), (7,)]
+    params = [torch.nn.Parameter(torch.randn(*sh)) for sh in shapes]
+    p0 = [p.detach().clone() for p in params]
+    no_decay = ['bias', 'LayerNorm.bias', 'LayerNorm.weight']
+    groups = [{'params': [p for n, p in zip(names, params) if not any(nd in n for nd in no_decay)], 'weight_decay': 0.01},
+              {'params': [p for n, p in zip(names, params) if any(nd in n for nd in no_decay)], 'weight_decay': 0.0}]
+    opt = ref_optim.AdaMod(groups, lr=1e-2)
+    grads, traj = [], []
+    for step in range(6):
+        gs = [torch.randn(*sh) * (0.1 + step) for sh in shapes]
+        for p, g in zip(params, gs):
+            p.grad = g.clone()
+        opt.step()
+        grads.append(gs)
+        traj.append([p.detach().clone() for p in params])
+    fx5 = {"names": np.array(names), "lr": np.float64(1e-2), "weight_decay": np.float64(0.01)}
+    for i, n in enumerate(names):
+        fx5[f"p0/{n}"] = p0[i].numpy()
+        for t in range(6):
+            fx5[f"g{t}/{n}"] = grads[t][i].numpy()
+            fx5[f"p{t + 1}/{n}"] = traj[t][i].numpy()
+        fx5[f"exp_avg_lr/{n}"] = opt.state[params[i]]['exp_avg_lr'].numpy()
+    np.savez_compressed(os.path.join(OUT, "ref_adamod.npz"), **fx5)
+
+    torch.manual_seed(12)
+    logits = (torch.randn(9, 5) * 2).requires_grad_(True)
+    target = torch.tensor([0, 4, 2, -1, 1, 3, -1, 0, 2])
+    fx6 = {"logits": logits.detach().numpy(), "target": target.numpy()}
+    for alpha, gamma in ((1, 2), (0.25, 3), (2, 0), (1, 1)):
+        fl = ref.loss.FocalLossWithLogits(alpha=alpha, gamma=gamma)
+        val = fl(logits, target)
+        (g,) = torch.autograd.grad(val, logits)
+        fx6[f"loss/{alpha}/{gamma}"] = val.detach().numpy()
+        fx6[f"grad/{alpha}/{gamma}"] = g.numpy()
+    np.savez_compressed(os.path.join(OUT, "ref_focal.npz"), **fx6)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

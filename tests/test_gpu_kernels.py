@@ -2,7 +2,9 @@
 bf16 inputs.  Tolerances: outputs are bf16 (relative rounding 2^-9 = 2e-3 per element), fp32
 accumulation; the bounds below are a few times the expected bf16 rounding error."""
 import ctypes
+import importlib
 
+import numpy as np
 import pytest
 import torch
 
@@ -273,3 +275,73 @@ def test_optimizer_kernels_match_oracle(pkg):
     torch.testing.assert_close(m, torch.cat([state["w.weight"]["exp_avg"], state["w.bias"]["exp_avg"]]), rtol=1e-5, atol=1e-7)
     torch.testing.assert_close(shadow.float(), want.to(torch.bfloat16).float(), rtol=0, atol=0)
     assert (g == 0).all()
+
+
+def test_adamod_kernel_matches_reference_golden(pkg):
+    """bqa_clip_adamod over a flat buffer against six steps of the reference's AdaMod class
+    (tests/golden/ref_adamod.npz): parameters after every step and the final exp_avg_lr state."""
+    from conftest import load_npz
+    L = pkg._lib
+    fx = load_npz("ref_adamod.npz")
+    names = [str(n) for n in fx["names"]]
+    no_decay = ("bias", "LayerNorm.bias", "LayerNorm.weight")
+    offs, total = {}, 0
+    for n in names:
+        offs[n] = total
+        total += (fx[f"p0/{n}"].size + 127) // 128 * 128
+    p = torch.zeros(total, device=DEV)
+    m, v, s = torch.zeros_like(p), torch.zeros_like(p), torch.zeros_like(p)
+    g = torch.zeros_like(p)
+    shadow = torch.zeros(total, dtype=torch.bfloat16, device=DEV)
+    for n in names:
+        t = torch.from_numpy(np.asarray(fx[f"p0/{n}"])).flatten()
+        p[offs[n]:offs[n] + t.numel()] = t.to(DEV)
+    chunks = (L.AdamWChunk * len(names))()
+    for i, n in enumerate(names):
+        size = fx[f"p0/{n}"].size
+        decay = not any(nd in n for nd in no_decay)
+        chunks[i].begin, chunks[i].end = offs[n], offs[n] + (size + 3) // 4 * 4
+        chunks[i].weight_decay, chunks[i].group = (float(fx["weight_decay"]) if decay else 0.0), (0 if decay else 1)
+    cd = torch.frombuffer(bytearray(bytes(chunks)), dtype=torch.uint8).to(DEV)
+    lrs = (ctypes.c_float * 2)(float(fx["lr"]), float(fx["lr"]))
+    st = L.current_stream_ptr()
+    for t in range(6):
+        for n in names:
+            gt = torch.from_numpy(np.asarray(fx[f"g{t}/{n}"])).flatten()
+            g[offs[n]:offs[n] + gt.numel()] = gt.to(DEV)
+        L.check(L.lib.bqa_clip_adamod(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), s.data_ptr(),
+                                      shadow.data_ptr(), cd.data_ptr(), len(names), None, 0.0, lrs, 2, 0.9, 0.999,
+                                      0.999, 1e-8, t + 1, 1, st), "adamod")
+        torch.cuda.synchronize()
+        assert (g == 0).all()
+        for n in names:
+            want = torch.from_numpy(np.asarray(fx[f"p{t + 1}/{n}"])).flatten().to(DEV)
+            torch.testing.assert_close(p[offs[n]:offs[n] + want.numel()], want, rtol=2e-5, atol=1e-6,
+                                       msg=lambda msg, n=n, t=t: f"step {t} {n}: {msg}")
+    for n in names:
+        want = torch.from_numpy(np.asarray(fx[f"exp_avg_lr/{n}"])).flatten().to(DEV)
+        torch.testing.assert_close(s[offs[n]:offs[n] + want.numel()], want, rtol=2e-5, atol=1e-9)
+    torch.testing.assert_close(shadow.float(), p.to(torch.bfloat16).float(), rtol=0, atol=0)
+
+
+def test_focal_loss_kernel_matches_reference_golden(pkg):
+    """The fused loss kernel with cls_loss = focal against the reference's FocalLossWithLogits: value and
+    gradient w.r.t. the class logits (the other four losses get dummy inputs)."""
+    from conftest import load_npz
+    E = pkg.engine
+    loss_mod = importlib.import_module("bqa_b200.modules.model.model.loss")
+    fx = load_npz("ref_focal.npz")
+    logits = torch.from_numpy(np.asarray(fx["logits"])).to(DEV)
+    target = torch.from_numpy(np.asarray(fx["target"])).to(DEV)
+    B, S = logits.shape[0], 16
+    outs = (torch.zeros(B, S, device=DEV), torch.zeros(B, S, device=DEV), torch.full((B,), 0.5, device=DEV),
+            torch.full((B,), 0.5, device=DEV), logits)
+    targets = {"start_class": torch.zeros(B, dtype=torch.int64), "end_class": torch.zeros(B, dtype=torch.int64),
+               "start_reg": torch.full((B,), 0.5), "end_reg": torch.full((B,), 0.5), "cls": target}
+    for alpha, gamma in ((1, 2), (0.25, 3), (2, 0), (1, 1)):
+        lc = E.make_loss_config(loss="focal", focal_alpha=alpha, focal_gamma=gamma)
+        losses, grads = loss_mod._run_loss_kernel(outs, targets, lc, True)
+        torch.cuda.synchronize()
+        assert abs(losses[4].item() - float(fx[f"loss/{alpha}/{gamma}"])) < 2e-5
+        torch.testing.assert_close(grads[4].cpu(), torch.from_numpy(np.asarray(fx[f"grad/{alpha}/{gamma}"])),
+                                   rtol=2e-4, atol=2e-6)

@@ -193,16 +193,18 @@ def test_dropin_autograd_path_equals_fused_path(pkg):
     assert all(torch.equal(a[k], b[k]) for k in a)
 
 
-def test_training_trajectory_matches_oracle(pkg):
+@pytest.mark.parametrize("optimizer", ["adam", "adamod"])
+def test_training_trajectory_matches_oracle(pkg, optimizer):
     """4 optimizer steps through the package's Trainer (grad accumulation over 2 micro-batches, clip,
-    fused AdamW with the two decay groups, warm-up schedule) vs the oracle loop on the same batches."""
+    fused AdamW / AdaMod with the two decay groups, warm-up schedule) vs the oracle loop on the same batches."""
     I = importlib.import_module("bqa_b200.modules.init")
     T = importlib.import_module("bqa_b200.modules.model.trainer.trainer")
     shape = TINY
     model = _model(pkg, shape)
     P = {k: v.detach().clone() for k, v in model.state_dict().items()}
-    hp = types.SimpleNamespace(lr=1e-3, weight_decay=1e-2, optimizer="adam", finetune=False, apex_level=None)
+    hp = types.SimpleNamespace(lr=1e-3, weight_decay=1e-2, optimizer=optimizer, finetune=False, apex_level=None)
     opt = I.init_optimizer(hp, model)
+    assert type(opt).__name__ == ("FusedAdamW" if optimizer == "adam" else "AdaMod")
     tr = T.Trainer(model=model, loss=_loss_obj(), collate_fun=None, optimizer=opt, device=torch.device(DEV), n_epochs=1,
                    train_batch_size=4, batch_split=2, n_jobs=0, warmup_coef=0.0, max_grad_norm=0.5)
     steps, warmup = 4, 2
@@ -222,7 +224,10 @@ def test_training_trajectory_matches_oracle(pkg):
         lr = 1e-3 * O.linear_schedule_lambda(s, warmup, steps)
         assert abs(opt.param_groups[0]["lr"] - lr) < 1e-12
         norms.append(O.clip_grad_norm_(acc, 0.5).item())
-        O.hf_adamw_step(P, acc, state, lr, 1e-2)
+        if optimizer == "adam":
+            O.hf_adamw_step(P, acc, state, lr, 1e-2)
+        else:
+            O.adamod_step(P, acc, state, lr, 1e-2)
         tr.optimizer_step()
         assert abs(opt.grad_norm() - norms[-1]) < 2e-2 * norms[-1]
     torch.cuda.synchronize()
@@ -234,6 +239,10 @@ def test_training_trajectory_matches_oracle(pkg):
         assert (sd[k] - P[k]).abs().max().item() < 2e-3, k
     assert (model.engine.grads == 0).all()      # optimizer.zero_grad() semantics
     assert all(opt.state[p]["step"] == steps for p in model.parameters())
+    if optimizer == "adamod":
+        k0 = "transformer.encoder.layer.0.attention.self.query.weight"
+        got = opt.state[dict(model.named_parameters())[k0]]["exp_avg_lr"]
+        assert rel(got, state[k0]["exp_avg_lr"]) < 5e-2
 
 
 def test_checkpoint_roundtrip_and_state_dict_layout(pkg, tmp_path):

@@ -165,13 +165,18 @@ def test_warmup_lambda_matches_oracle(mods):
 def test_unsupported_options_fail_loudly(mods):
     import types
     I = mods["init"]
-    with pytest.raises(NotImplementedError, match="focal"):
-        I.init_loss(types.SimpleNamespace(loss="focal", focal_alpha=1, focal_gamma=2, smooth_alpha=0.01), {})
+    with pytest.raises(NotImplementedError):
+        I.init_loss(types.SimpleNamespace(loss="hinge", smooth_alpha=0.01), {})
     mp = types.SimpleNamespace(model="roberta-base", vocab_file=None)
     with pytest.raises(NotImplementedError):
         I.init_model(mp)
-    with pytest.raises(NotImplementedError, match="adamod"):
-        mods["optim"].AdaMod([])
+    # loss=focal and optimizer=adamod are configuration holders on the host (kernels: tests -m gpu)
+    wl = I.init_loss(types.SimpleNamespace(loss="focal", focal_alpha=0.5, focal_gamma=3, smooth_alpha=0.01), {})
+    assert type(wl._losses['cls'][0]).__name__ == "FocalLossWithLogits"
+    with pytest.raises(NotImplementedError):
+        mods["model"].FocalLossWithLogits(ignore_index=-100)
+    with pytest.raises(ValueError, match="beta3"):
+        mods["optim"].AdaMod([torch.nn.Parameter(torch.zeros(2))], None, beta3=1.5)
 
 
 def test_model_skeleton_has_reference_state_dict_keys(mods):

@@ -99,3 +99,34 @@ def test_bf16_mode_stays_close_to_fp32():
     b = O.forward(P, TINY, inp["input_ids"], inp["attention_mask"], inp["token_type_ids"], bf16=True)
     for k in a:
         assert (a[k] - b[k]).abs().max() < 0.05
+
+
+def test_adamod_matches_reference_class():
+    """oracle.adamod_step against six steps of the reference's own AdaMod (optim.py:42-100), two
+    weight-decay groups as built by init.py:121-129."""
+    fx = load_npz("ref_adamod.npz")
+    names = [str(n) for n in fx["names"]]
+    P = {n: torch.from_numpy(np.asarray(fx[f"p0/{n}"])).clone() for n in names}
+    state = {}
+    for t in range(6):
+        G = {n: torch.from_numpy(np.asarray(fx[f"g{t}/{n}"])) for n in names}
+        O.adamod_step(P, G, state, lr=float(fx["lr"]), weight_decay=float(fx["weight_decay"]))
+        for n in names:
+            torch.testing.assert_close(P[n], torch.from_numpy(np.asarray(fx[f"p{t + 1}/{n}"])), rtol=1e-6, atol=1e-7,
+                                       msg=lambda m, n=n, t=t: f"step {t} {n}: {m}")
+    for n in names:
+        torch.testing.assert_close(state[n]["exp_avg_lr"], torch.from_numpy(np.asarray(fx[f"exp_avg_lr/{n}"])),
+                                   rtol=1e-6, atol=1e-9)
+
+
+def test_focal_class_loss_matches_reference_class():
+    """oracle.class_loss(loss='focal') and its autograd gradient against the reference's
+    FocalLossWithLogits (loss.py:57-71), including ignored rows (target -1) and gamma = 0."""
+    fx = load_npz("ref_focal.npz")
+    target = torch.from_numpy(np.asarray(fx["target"]))
+    for alpha, gamma in ((1, 2), (0.25, 3), (2, 0), (1, 1)):
+        logits = torch.from_numpy(np.asarray(fx["logits"])).clone().requires_grad_(True)
+        val = O.class_loss(logits, target, O.LossConfig(loss="focal", focal_alpha=alpha, focal_gamma=gamma))
+        (g,) = torch.autograd.grad(val, logits)
+        assert abs(val.item() - float(fx[f"loss/{alpha}/{gamma}"])) < 1e-6
+        torch.testing.assert_close(g, torch.from_numpy(np.asarray(fx[f"grad/{alpha}/{gamma}"])), rtol=1e-5, atol=1e-7)
