@@ -213,7 +213,10 @@ BQA_API int bqa_bind(bqa_handle* h, float* params, float* grads, void* params_bf
  * uint8/bool [B][S] or NULL (= all ones), as produced by collate_fun
  * (modules/model/dataset/split_dataset.py:480-520).  Outputs fp32: start/end [B][S],
  * cls [B][num_labels], reg_start/reg_end [B] (after the sigmoid).  training != 0 applies
- * dropout (streams derived from seed and step) and keeps activations for bqa_backward. */
+ * dropout (streams derived from seed and step) and keeps activations for bqa_backward.
+ * training is a bit set: 1 = training forward; | 2 = no dropout inside the encoder; | 4 = no
+ * dropout in front of the classifier (the reference's fine-tuning mode, init.py:86-119 +
+ * trainer.py:226-233, puts only the selected sub-modules into train mode). */
 BQA_API int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_type_ids,
                         const uint8_t* attention_mask, int32_t B, int32_t S, int32_t training, uint64_t seed,
                         uint64_t step, float* start, float* end, float* cls, float* reg_start, float* reg_end,

@@ -207,6 +207,8 @@ struct bqa_handle {
   // state of the last forward
   uint64_t seed = 0, step = 0;
   bool last_training = false;
+  bool enc_dropout_off = false, cls_dropout_off = false;  // bqa_forward training bits 2 / 4
+  uint32_t cls_site = 0;
   bool has_mask = false;
   int64_t launches = 0;
   // optional per-launch timing of the tensor-core kernels (bench.py's roofline leg)
@@ -250,6 +252,7 @@ struct bqa_handle {
   int64_t layer_off(int l) const { return lay.layer0 + lay.layer_stride * l; }
   DropKey key(uint32_t site, float p) const {
     if (!last_training || p <= 0.0f) return make_drop_key(0, 0, 0.0f);
+    if (site == cls_site ? cls_dropout_off : enc_dropout_off) return make_drop_key(0, 0, 0.0f);
     return make_drop_key(seed ^ splitmix64(step + 0x51ed270b9f3a6c1dull), site, p);
   }
 };
@@ -533,6 +536,9 @@ int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_ty
   h->seed = seed;
   h->step = step;
   h->last_training = tr;
+  h->enc_dropout_off = (training & 2) != 0;
+  h->cls_dropout_off = (training & 4) != 0;
+  h->cls_site = site_cls(h->cfg.num_layers);
   const bqa_config& c = h->cfg;
   const bqa_layout& Y = h->lay;
   Workspace& w = h->plan.ws;
@@ -553,7 +559,7 @@ int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_ty
   h->has_mask = mask != nullptr;
   BQA_CUDA_CHECK(cudaMemsetAsync(w.err_flag, 0, sizeof(int), st));
 
-  const bool attn_drop = tr && c.attn_dropout > 0.0f;
+  const bool attn_drop = tr && c.attn_dropout > 0.0f && !h->enc_dropout_off;
   if (attn_drop) {
     if (h->side == nullptr) {
       BQA_CUDA_CHECK(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));

@@ -207,6 +207,10 @@ class BertForQuestionAnswering(nn.Module):
             self._step += 1
             self._step_token += 1
             self.grads_dirty = True
+        if training:
+            # bqa_forward's training bit set: the reference's dropouts belong to self.transformer and to
+            # self.classifier[0]; they fire only if their owner is in train mode
+            training = 1 | (0 if self.transformer.training else 2) | (0 if self.classifier.training else 4)
         return self._engine.forward(input_ids, token_type_ids, attention_mask, training=training,
                                     seed=self._seed, step=self._step)
 
@@ -215,7 +219,11 @@ class BertForQuestionAnswering(nn.Module):
         if position_ids is not None or head_mask is not None:
             raise NotImplementedError("position_ids / head_mask are always None in the reference's call sites "
                                       "(trainer.py:278, predictor.py:109) and have no kernel path")
-        needs_grad = self.training and torch.is_grad_enabled()
+        # The reference's graph exists whenever autograd is on; which dropouts fire depends on the train flag
+        # of the sub-module that owns them (fine-tuning keeps the top-level module in eval mode, init.py:92).
+        needs_grad = torch.is_grad_enabled() and (self.training or self.transformer.training or
+                                                  self.classifier.training or self.position_outputs.training or
+                                                  self.reg_start.training or self.reg_end.training)
         if needs_grad:
             if not self._engine_ready():
                 self._attach()

@@ -223,7 +223,14 @@ class Trainer:
             torch.nn.utils.clip_grad_norm_(self.model.parameters(), self.max_grad_norm)
 
     def set_train(self):
-        self.model.train()
+        # trainer.py:226-233: in fine-tuning mode only the selected sub-modules go to train mode
+        trainable = getattr(self.model, 'list_of_trainable_modules', None)
+        if self.apex_level is None and trainable is not None:
+            assert isinstance(trainable, list) and all(isinstance(m, nn.Module) for m in trainable)
+            for module in trainable:
+                module.train()
+        else:
+            self.model.train()
 
     def set_eval(self):
         self.model.eval()

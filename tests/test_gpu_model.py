@@ -353,3 +353,39 @@ def test_inputs_built_on_device_equal_collate_fun(pkg):
     full_r, _ = ds.collate_fun(items, tok_r)
     got_r = ds.expand_compact_inputs(ds.collate_fun(items, tok_r, compact=True)[0], torch.device(DEV))
     assert torch.equal(got_r["token_type_ids"].cpu(), full_r["token_type_ids"])
+
+
+def test_finetune_mode_trains_only_selected_modules(pkg):
+    """params.finetune with finetune_class only (init.py:86-119, trainer.py:226-233): the model stays in eval
+    mode except the classifier, so the encoder runs without dropout, the classifier's dropout fires, and only
+    the classifier's parameters move."""
+    I = importlib.import_module("bqa_b200.modules.init")
+    T = importlib.import_module("bqa_b200.modules.model.trainer.trainer")
+    model = _model(pkg, TINY, p_drop=0.5)
+    hp = types.SimpleNamespace(lr=1e-2, weight_decay=0.0, optimizer="adam", finetune=True, finetune_transformer=False,
+                               finetune_position=False, finetune_position_reg=False, finetune_class=True,
+                               apex_level=None)
+    opt = I.init_optimizer(hp, model)
+    tr = T.Trainer(model=model, loss=_loss_obj(), collate_fun=None, optimizer=opt, device=torch.device(DEV), n_epochs=1,
+                   train_batch_size=4, batch_split=1, n_jobs=0, warmup_coef=0.0, max_grad_norm=1.0)
+    tr.set_train()
+    assert not model.training and not model.transformer.training and model.classifier.training
+    sd0 = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    inputs, labels = O.dummy_batch(4, 128, vocab=1000, seed=5, device=DEV)
+    spans, clss = [], []
+    for _ in range(2):
+        outs, _ = model.forward_loss_backward(inputs, labels, tr.loss.loss_config(device=torch.device(DEV)))
+        spans.append(outs["start_class"].clone())
+        clss.append(outs["cls"].clone())
+        model.engine.grads.zero_()
+    assert torch.equal(spans[0], spans[1])        # encoder: no dropout although hidden_dropout_prob = 0.5
+    assert not torch.equal(clss[0], clss[1])      # classifier dropout: a new mask every step
+    for s in range(2):
+        tr.train_micro_batch(inputs, labels, last_of_step=True)
+        tr.optimizer_step()
+    torch.cuda.synchronize()
+    for k, v in model.state_dict().items():
+        if k.startswith("classifier."):
+            assert not torch.equal(v, sd0[k]), k
+        else:
+            assert torch.equal(v, sd0[k]), k
