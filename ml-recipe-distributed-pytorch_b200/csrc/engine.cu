@@ -208,6 +208,11 @@ struct bqa_handle {
   uint64_t seed = 0, step = 0;
   bool last_training = false;
   bool enc_dropout_off = false, cls_dropout_off = false;  // bqa_forward training bits 2 / 4
+  // attention keep bits generated ahead of time (at the end of a backward, for the next step): valid for
+  // this (seed, step, B, S) if bits_ahead
+  bool bits_ahead = false;
+  uint64_t bits_seed = 0, bits_step = 0;
+  int bits_B = 0, bits_S = 0;
   uint32_t cls_site = 0;
   bool has_mask = false;
   int64_t launches = 0;
@@ -250,6 +255,10 @@ struct bqa_handle {
   float* G(int64_t off) const { return grads + off; }
   const bf16* W(int64_t off) const { return params_bf16 + off; }
   int64_t layer_off(int l) const { return lay.layer0 + lay.layer_stride * l; }
+  DropKey key_at(uint64_t seed_, uint64_t step_, uint32_t site, float p) const {
+    if (p <= 0.0f) return make_drop_key(0, 0, 0.0f);
+    return make_drop_key(seed_ ^ splitmix64(step_ + 0x51ed270b9f3a6c1dull), site, p);
+  }
   DropKey key(uint32_t site, float p) const {
     if (!last_training || p <= 0.0f) return make_drop_key(0, 0, 0.0f);
     if (site == cls_site ? cls_dropout_off : enc_dropout_off) return make_drop_key(0, 0, 0.0f);
@@ -260,6 +269,7 @@ struct bqa_handle {
 namespace {
 
 int build_plan(bqa_handle* h, int B, int S, bool training) {
+  h->bits_ahead = false;  // the keep-bit buffers move with the plan
   const bqa_config& c = h->cfg;
   Plan& p = h->plan;
   h->plan_valid = false;
@@ -567,14 +577,18 @@ int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_ty
       h->ev_bits.resize(c.num_layers);
       for (auto& e : h->ev_bits) BQA_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     }
-    BQA_CUDA_CHECK(cudaEventRecord(h->ev_fork, st));  // everything that read last step's bits is behind us
-    BQA_CUDA_CHECK(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
-    for (int l = 0; l < c.num_layers; ++l) {
-      if (attn_make_keep_bits(h->plan.layer[l].attn, h->key(site_attn(l), c.attn_dropout), h->side)) return 1;
-      BQA_CUDA_CHECK(cudaEventRecord(h->ev_bits[l], h->side));
+    const bool ahead = h->bits_ahead && h->bits_seed == seed && h->bits_step == step && h->bits_B == B && h->bits_S == S;
+    if (!ahead) {
+      BQA_CUDA_CHECK(cudaEventRecord(h->ev_fork, st));  // everything that read last step's bits is behind us
+      BQA_CUDA_CHECK(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+      for (int l = 0; l < c.num_layers; ++l) {
+        if (attn_make_keep_bits(h->plan.layer[l].attn, h->key(site_attn(l), c.attn_dropout), h->side)) return 1;
+        BQA_CUDA_CHECK(cudaEventRecord(h->ev_bits[l], h->side));
+      }
+      h->launches += c.num_layers;
     }
-    h->launches += c.num_layers;
   }
+  h->bits_ahead = false;
   if (launch_embed_ln_fwd(w.ids, w.tt, h->P(Y.word_emb), h->P(Y.pos_emb), h->P(Y.type_emb), h->P(Y.emb_ln_g),
                           h->P(Y.emb_ln_b), w.z0, w.x0, T, S, H, c.vocab, c.type_vocab, c.ln_eps,
                           h->key(site_embed(), c.hidden_dropout), w.err_flag, st))
@@ -782,6 +796,27 @@ int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* s
         return 1;
       h->launches += 2;
     }
+  }
+  // The attention-dropout decisions depend only on (seed, step, site): once layer 0's attention backward
+  // has read this step's bits, the next step's are generated on the side stream, where they overlap the
+  // rest of this step (embedding backward, gradient exchange, clip + AdamW: HBM-bound work that leaves the
+  // issue slots idle) instead of the next forward's GEMMs.  bqa_forward uses them if it is called with the
+  // predicted (seed, step + 1, B, S) and generates its own otherwise.
+  if (last_phase >= L && first_phase <= L && c.attn_dropout > 0.0f && !h->enc_dropout_off && h->side != nullptr) {
+    BQA_CUDA_CHECK(cudaEventRecord(h->ev_fork, st));
+    BQA_CUDA_CHECK(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+    for (int l = 0; l < L; ++l) {
+      if (attn_make_keep_bits(h->plan.layer[l].attn, h->key_at(h->seed, h->step + 1, site_attn(l), c.attn_dropout),
+                              h->side))
+        return 1;
+      BQA_CUDA_CHECK(cudaEventRecord(h->ev_bits[l], h->side));
+    }
+    h->launches += L;
+    h->bits_ahead = true;
+    h->bits_seed = h->seed;
+    h->bits_step = h->step + 1;
+    h->bits_B = B;
+    h->bits_S = S;
   }
   return 0;
 }
