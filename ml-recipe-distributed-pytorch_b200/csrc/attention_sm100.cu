@@ -298,6 +298,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  pdl_trigger();  // the next kernel may start its prologue; it waits for this grid before reading
 
   if (tid == ROW_THREADS) {
     // ---------------- control thread: TMA + MMA issue ----------------
@@ -476,6 +477,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
 __global__ void __launch_bounds__(128)
 attn_dsum_kernel(const bf16* __restrict__ ctx, const bf16* __restrict__ dctx, float* __restrict__ dsum, int B, int S,
                  int A, int H) {
+  pdl_trigger();  // the next kernel (a GEMM) may start its prologue now; it waits for this grid before reading
   const int lane = threadIdx.x & 31;
   const int t = blockIdx.x * 4 + (threadIdx.x >> 5);
   if (t >= B * S) return;
@@ -569,6 +571,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  pdl_trigger();  // the next kernel may start its prologue; it waits for this grid before reading
   constexpr uint32_t COL_S = 0, COL_DP = 128, COL_DQ = 256;
 
   if (tid == ROW_THREADS) {
@@ -818,6 +821,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  pdl_trigger();  // the next kernel may start its prologue; it waits for this grid before reading
   constexpr uint32_t COL_S = 0, COL_DP = 64, COL_DV = 128, COL_DK = 192;
 
   if (uniform_warp_idx() == BW_CTRL_WARP) {

@@ -136,6 +136,15 @@ __device__ __forceinline__ bool clc_decode(const void* response, uint32_t& ctaid
   return valid != 0;
 }
 
+// Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization attribute may
+// start while its predecessor in the stream is still running; everything it does before pdl_wait() (barrier
+// init, TMEM allocation, descriptor prefetch) overlaps the predecessor's tail.  pdl_wait() returns once the
+// predecessor has completed and its writes are visible; pdl_trigger() lets the successor start as soon as
+// resources free up.  Both are no-ops for a normally launched kernel.  Nothing the predecessor may have
+// written is touched before pdl_wait(), and the trigger comes after the wait, so completion is transitive.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // One lane of a converged warp (the others get false).  Code that issues tcgen05.mma / TMA from inside
 // `if (elect_one())` within warp-uniform control flow keeps descriptors in uniform registers; issuing from
 // a `threadIdx.x == k` branch instead makes the compiler wrap every instruction in an election loop.

@@ -112,6 +112,9 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
   if (NCTA == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // the prologue above overlapped the previous kernel's tail (programmatic dependent launch)
+  pdl_wait();
+  pdl_trigger();
 
   const int tiles_mn = args.m_tiles * args.n_tiles;
   // One cluster is launched per tile; the clusters that get to run take over the tiles of clusters that
@@ -506,11 +509,19 @@ int launch_variant(const GemmPlan& plan, cudaStream_t stream) {
     }
     configured = true;
   }
-  if (plan.pair)
-    k2<<<plan.grid, NUM_THREADS, Cfg<2, EPI>::SMEM_ALLOC, stream>>>(plan.tmA, plan.tmB, plan.tmC, plan.tmC2, plan.args);
-  else
-    k1<<<plan.grid, NUM_THREADS, Cfg<1, EPI>::SMEM_ALLOC, stream>>>(plan.tmA, plan.tmB, plan.tmC, plan.tmC2, plan.args);
-  cudaError_t e = cudaGetLastError();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(plan.grid);
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = plan.pair ? Cfg<2, EPI>::SMEM_ALLOC : Cfg<1, EPI>::SMEM_ALLOC;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // see pdl_wait() in the kernel
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = plan.pair ? cudaLaunchKernelEx(&cfg, k2, plan.tmA, plan.tmB, plan.tmC, plan.tmC2, plan.args)
+                            : cudaLaunchKernelEx(&cfg, k1, plan.tmA, plan.tmB, plan.tmC, plan.tmC2, plan.args);
+  if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("gemm: launch failed: %s", cudaGetErrorString(e));
     return 1;

@@ -144,6 +144,7 @@ template <int NV>
 __global__ void __launch_bounds__(ROW_WARPS * 32)
 ln_fwd_kernel(const bf16* __restrict__ z, const float* __restrict__ gamma, const float* __restrict__ beta,
               bf16* __restrict__ y, int T, int H, float eps) {
+  pdl_trigger();  // the next kernel (a GEMM) may start its prologue now; it waits for this grid before reading
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * ROW_WARPS + (threadIdx.x >> 5);
   if (row >= T) return;
@@ -201,6 +202,7 @@ embed_ln_fwd_kernel(const int64_t* __restrict__ ids, const int64_t* __restrict__
                     const float* __restrict__ gamma, const float* __restrict__ beta, bf16* __restrict__ z0,
                     bf16* __restrict__ x0, int T, int S, int H, int V, int TV, float eps, DropKey drop,
                     int* __restrict__ err_flag) {
+  pdl_trigger();  // the next kernel (a GEMM) may start its prologue now; it waits for this grid before reading
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * ROW_WARPS + (threadIdx.x >> 5);
   if (row >= T) return;
@@ -246,6 +248,7 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
               bf16* __restrict__ dz, bf16* __restrict__ dz_masked, float* __restrict__ dgamma,
               float* __restrict__ dbeta, float* __restrict__ dbias, int T, int H, float eps, DropKey drop_in,
               DropKey drop_out) {
+  pdl_trigger();  // the next kernel (a GEMM) may start its prologue now; it waits for this grid before reading
   extern __shared__ float ln_smem[];
   constexpr int W = NV * 256;           // padded row width
   float* s_gamma = ln_smem;             // [W]
@@ -415,6 +418,7 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
 // out[n] += sum_t X[t][n]  (bias gradients of the fused QKV and intermediate projections)
 __global__ void __launch_bounds__(256)
 colsum_kernel(const bf16* __restrict__ X, int ld, float* __restrict__ out, int T, int N) {
+  pdl_trigger();  // the next kernel (a GEMM) may start its prologue now; it waits for this grid before reading
   __shared__ float red[8][32 * 8 + 1];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int c = (blockIdx.x * 32 + tx) * 8;
