@@ -248,7 +248,7 @@ def run_native(args):
     achieved = gemm_fl / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
     traffic = load_traffic()
     peak = peaks["bf16_tflops_sustained"]
-    roofline = {"bound": "tensor", "kernel": "bqa::gemm_kernel<A_MN,B_MN,EPI> (tcgen05, all Linear fwd/dgrad/wgrad)",
+    roofline = {"bound": "tensor", "kernel": "bqa::gemm_pair_kernel<A_MN,B_MN,EPI> (tcgen05 cta_group::2, all Linear fwd/dgrad/wgrad)",
                 "achieved": round(achieved, 1), "peak": peak, "unit": "TFLOP/s", "frac": round(achieved / peak, 4),
                 "peak_source": f"bf16_tflops_sustained, {peaks['source']}", "traffic": traffic["value"],
                 "traffic_unit": traffic["unit"], "traffic_source": traffic["source"],
