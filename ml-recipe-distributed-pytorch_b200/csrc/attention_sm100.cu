@@ -6,15 +6,15 @@
 // and its autograd backward.  The reference materialises the [B,A,S,S] score tensor in HBM
 // several times per layer; here scores live only in tensor memory:
 //
-//   forward  (CTA = one (batch, head, 128-query tile)):
+//   forward  (persistent; a CTA walks a contiguous range of (batch, head, 128-query tile) tiles):
 //     TMA -> smem Q, K, V | tcgen05.mma S = Q K^T into TMEM (128 lanes x S columns, fp32)
-//     | 128 softmax threads, one per query row: row max, exp2, row sum straight out of TMEM
-//     | P (bf16, dropped) -> 128B-swizzled smem | tcgen05.mma O += P V (V is the MN-major operand)
-//     | O / rowsum -> ctx, log-sum-exp -> lse2.
+//     | 512 softmax threads, four per query row: row max, exp2, row sum straight out of TMEM
+//     | P (bf16, unscaled, dropped) -> 128B-swizzled smem | tcgen05.mma O += P V (V is the MN-major operand)
+//     | O * (dropout scale / rowsum) -> ctx, log-sum-exp -> lse2.
 //   backward = two kernels with the same structure, each recomputing its score tile:
-//     dQ  kernel (CTA = 128-query tile):  S, dP = dO V^T ; dS = P (dP - D) ; dQ += dS K
-//     dKV kernel (CTA = 128-key tile), transposed problem so that rows are keys:
-//                S^T = K Q^T, dP^T = V dO^T ; dV += P^T dO ; dK += dS^T Q
+//     dQ  kernel (persistent, CTA = 128-query tile): S, dP = dO V^T ; dS = P (dP - D) ; dQ += dS K
+//     dKV kernel (two CTAs per SM, CTA = 128-key tile, 64-query chunks), transposed problem so that
+//                rows are keys: S^T = K Q^T, dP^T = V dO^T ; dV += P^T dO ; dK += dS^T Q
 //   with D = rowsum(dO * O) from a small HBM-bound pre-pass.
 // Dropout decisions are the stateless hash of (batch, head, query, key), identical in all kernels.
 #include "attention_sm100.cuh"

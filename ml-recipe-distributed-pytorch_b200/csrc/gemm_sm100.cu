@@ -1,18 +1,24 @@
-// gemm_sm100.cu — persistent, warp-specialised bf16 GEMM on tcgen05 tensor cores (sm_100a).
+// gemm_sm100.cu — warp-specialised, dynamically scheduled bf16 GEMM on tcgen05 tensor cores (sm_100a).
 //
 // Replaces the cuBLAS GEMMs the reference reaches through torch.nn.Linear in
 // transformers' BertSelfAttention / BertSelfOutput / BertIntermediate / BertOutput
 // (site-packages/transformers/models/bert/modeling_bert.py:179-181,294-298,339-342,352-356)
 // and their autograd backward (reference trainer.py:197-204).
 //
-// CTA = 384 threads, one CTA per SM, static round-robin tile schedule; large problems run as CTA pairs
-// (cluster of 2, tcgen05 cta_group::2, 256 x 256 tiles, 6-stage ring), small ones as single CTAs
-// (128 x 256 tiles, 4-stage ring):
-//   warp 0 (1 thread)  TMA producer: 3-stage ring of {A 128x64, B 256x64} bf16 tiles, 128B swizzle
-//   warp 1 (1 thread)  MMA issuer  : tcgen05.mma cta_group::1 kind::f16, M=128 N=256 K=16, fp32 in TMEM
-//   warp 2             TMEM allocator (512 columns = two 128x256 fp32 accumulators, double-buffered)
-//   warps 4-11         epilogue    : tcgen05.ld -> registers -> fused op -> swizzled smem -> TMA store
-//                      (two warps per TMEM lane quarter, each draining half of every column chunk)
+// CTA = 384 threads, one CTA per SM.  Large problems run as CTA pairs (cluster of 2, tcgen05
+// cta_group::2, 256 x 256 tiles, 6-stage ring; 5 stages with the two-output epilogue), small ones
+// as single CTAs (128 x 256 tiles, 4-stage ring).  One cluster is launched per tile; a cluster that
+// runs asks the hardware to cancel a pending cluster and takes over its tile (cluster launch
+// control), so the grid behaves like a persistent one whose tile list is dynamic.
+//   warp 0             TMA producer: ring of {A 128x64, B 128x64 (pair) / 256x64} bf16 tiles, 128B swizzle
+//   warp 1             MMA issuer  : tcgen05.mma kind::f16, N=256 K=16, fp32 accumulators in TMEM
+//                      (warps 0/1 walk their loops warp-uniformly; one elected lane issues)
+//   warp 2             TMEM allocator (512 columns = two 256-column accumulators, double-buffered)
+//   warp 3             tile scheduler: clusterlaunchcontrol.try_cancel, look-ahead of one tile
+//   warps 4-11         epilogue    : tcgen05.ld -> registers -> fused op -> own swizzled smem staging ->
+//                      own TMA store / reduce-add (two warps per TMEM lane quarter, one column half each)
+// The prologue (barrier init, TMEM allocation, descriptor prefetch) overlaps the previous kernel's
+// tail through programmatic dependent launch.
 // Operands may be K-major or MN-major (instruction-descriptor major bits + smem descriptor
 // strides), so forward, dgrad and wgrad all read the tensors in the layout PyTorch gives them.
 #include "gemm_sm100.cuh"
