@@ -1145,7 +1145,7 @@ int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cu
   return check_launch("attn_fwd");
 }
 
-int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st) {
+int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st, bool dsum_ready) {
   static bool configured = false;
   if (!configured) {
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1162,9 +1162,11 @@ int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, c
     return 1;
   }
   const int T = plan.shape.B * plan.shape.S;
-  attn_dsum_kernel<<<(T + 3) / 4, 128, 0, st>>>(plan.ctx, plan.dctx, plan.dsum, plan.shape.B, plan.shape.S,
-                                               plan.shape.A, plan.shape.H);
-  if (check_launch("attn_dsum")) return 1;
+  if (!dsum_ready) {
+    attn_dsum_kernel<<<(T + 3) / 4, 128, 0, st>>>(plan.ctx, plan.dctx, plan.dsum, plan.shape.B, plan.shape.S,
+                                                 plan.shape.A, plan.shape.H);
+    if (check_launch("attn_dsum")) return 1;
+  }
   int sms = 0;
   if (device_sm_count(&sms)) return 1;
   const int tiles = plan.nchunk * plan.shape.A * plan.shape.B;

@@ -46,6 +46,9 @@ int attn_make_keep_bits(const AttnPlan& plan, DropKey drop, cudaStream_t st);
 // must already hold this call's keep bits (bits_ready) or they are generated first on `st`.
 int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st,
                  bool bits_ready = false);
-int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st);
+// dsum_ready: plan.dsum already holds D = rowsum(dO * O) (written by the epilogue of the GEMM that produced
+// dctx); otherwise a small pre-pass computes it.
+int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st,
+                  bool dsum_ready = false);
 
 }  // namespace bqa

@@ -351,7 +351,20 @@ int build_plan(bqa_handle* h, int B, int S, bool training) {
               nullptr))
       return 1;
     if (wgrad(&lp.w_ffn1, w.du, I, act.a, H, h->G(lo + Y.i_w))) return 1;
-    if (dgrad(&lp.d_ao, dgm, H, h->W(lo + Y.ao_w), H, w.dctx, EPI_LINEAR, nullptr, nullptr)) return 1;
+    {
+      // dctx = dgm . Wo; its epilogue also emits D = rowsum(dctx * ctx) per (batch, head, query), which the
+      // attention backward needs (no separate pass over dctx and ctx)
+      GemmProblem g{};
+      g.M = T; g.N = H; g.K = H;
+      g.A = dgm; g.lda = H; g.a_mn_major = 0;
+      g.B = h->W(lo + Y.ao_w); g.ldb = H; g.b_mn_major = 1;
+      g.C = w.dctx; g.ldc = H;
+      g.epilogue = EPI_LINEAR;
+      g.k_splits = 1;
+      g.drop = make_drop_key(0, 0, 0.0f);
+      g.dot_with = act.ctx; g.ld_dot = H; g.dot_out = w.dsum; g.dot_rows = S;
+      if (gemm_plan(&lp.d_ao, g, h->num_sms)) return 1;
+    }
     if (wgrad(&lp.w_ao, dgm, H, act.ctx, H, h->G(lo + Y.ao_w))) return 1;
     if (dgrad(&lp.d_qkv, w.dqkv, 3 * H, h->W(lo + Y.qkv_w), H, dy_out, EPI_LINEAR, w.dres, nullptr)) return 1;
     if (wgrad(&lp.w_qkv, w.dqkv, 3 * H, x_in, H, h->G(lo + Y.qkv_w))) return 1;
@@ -779,7 +792,7 @@ int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* s
       if (launch_gemm(h, lp.w_ao, nodrop, st)) return 1;
       if (launch_gemm(h, lp.d_ao, nodrop, st)) return 1;  // dctx = dgm . Wo
       h->time_begin(4, attn_flops(h, B, S, true), st);
-      if (attn_backward(lp.attn, mask, h->key(site_attn(l), c.attn_dropout), st)) return 1;
+      if (attn_backward(lp.attn, mask, h->key(site_attn(l), c.attn_dropout), st, /*dsum_ready=*/true)) return 1;
       h->time_end(st);
       if (launch_colsum(w.dqkv, 3 * H, h->G(lo + Y.qkv_b), T, 3 * H, h->num_sms, st)) return 1;
       if (launch_gemm(h, lp.w_qkv, nodrop, st)) return 1;

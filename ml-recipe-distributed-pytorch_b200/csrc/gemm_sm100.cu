@@ -294,6 +294,9 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       // piece before the accumulator is waited for
       const bf16* side_row = nullptr;
       if (EPI == EPI_LINEAR && args.residual != nullptr && row_ok) side_row = args.residual + static_cast<size_t>(m) * args.ld_res;
+      const bool dotting = EPI == EPI_LINEAR && args.dot_out != nullptr;  // side operand = dot_with, not added
+      if (dotting && row_ok) side_row = args.dot_with + static_cast<size_t>(m) * args.ld_dot;
+      float dot_acc = 0.0f;
       if (EPI == EPI_GELU_BWD && row_ok) side_row = args.aux + static_cast<size_t>(m) * args.ld_aux;
       uint4 side[4];
       bool side_ok = side_row != nullptr && n0 < args.N;
@@ -364,7 +367,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
                 f[i + 1] = k1 ? f[i + 1] * args.drop.scale : 0.0f;
               }
             }
-            if (side_ok) {
+            if (side_ok && !dotting) {
 #pragma unroll
               for (int q = 0; q < 4; ++q) {
                 const uint4 r = side[q];
@@ -435,6 +438,22 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
             o.z = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]);
             o.w = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
             *reinterpret_cast<uint4*>(srow + ((((piece & 1) * 4 + q) ^ sw) << 4)) = o;
+            if (dotting && side_ok) {
+              // dot product of the values as stored (bf16) with the side operand, 64 columns = two pieces
+              const uint4 r = side[q];
+              const float2 a0 = unpack_bf16x2(o.x), a1 = unpack_bf16x2(o.y), a2 = unpack_bf16x2(o.z), a3 = unpack_bf16x2(o.w);
+              const float2 b0 = unpack_bf16x2(r.x), b1 = unpack_bf16x2(r.y), b2 = unpack_bf16x2(r.z), b3 = unpack_bf16x2(r.w);
+              dot_acc += a0.x * b0.x + a0.y * b0.y + a1.x * b1.x + a1.y * b1.y + a2.x * b2.x + a2.y * b2.y +
+                         a3.x * b3.x + a3.y * b3.y;
+            }
+          }
+          if (dotting && (piece & 1)) {
+            if (row_ok && n < args.N) {
+              const int blk = (n - 32) >> 6;  // 64-column block of the output row
+              const int outer = m / args.dot_rows, inner = m - outer * args.dot_rows;
+              args.dot_out[(static_cast<size_t>(outer) * (args.N >> 6) + blk) * args.dot_rows + inner] = dot_acc;
+            }
+            dot_acc = 0.0f;
           }
           if (piece & 1) {
             fence_proxy_async_smem();
@@ -675,6 +694,15 @@ int gemm_plan(GemmPlan* plan, const GemmProblem& p, int num_sms) {
   a.aux = reinterpret_cast<const bf16*>(p.aux);
   a.ld_aux = p.ld_aux;
   a.drop = p.drop;
+  a.dot_with = reinterpret_cast<const bf16*>(p.dot_with);
+  a.ld_dot = p.ld_dot;
+  a.dot_out = p.dot_out;
+  a.dot_rows = p.dot_rows;
+  if (p.dot_out != nullptr &&
+      (p.epilogue != EPI_LINEAR || p.residual != nullptr || p.dot_with == nullptr || p.dot_rows < 1 || p.N % 64 != 0)) {
+    set_error("gemm: the row-dot output needs EPI_LINEAR without residual, a dot_with operand and N %% 64 == 0");
+    return 1;
+  }
   if (p.epilogue == EPI_GELU_BWD && p.aux == nullptr) {
     set_error("gemm: EPI_GELU_BWD needs aux");
     return 1;

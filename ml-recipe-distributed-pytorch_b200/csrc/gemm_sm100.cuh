@@ -43,6 +43,14 @@ struct GemmProblem {
   int k_splits;  // >= 1; > 1 only with EPI_F32_ADD; 0 = choose automatically (EPI_F32_ADD)
   int force_single;  // 1 = never use CTA pairs (tests)
   DropKey drop;  // thresh == 0 -> no dropout           (EPI_LINEAR)
+  // EPI_LINEAR without residual: also emit, per row m and 64-column block j, the dot product of the
+  // (bf16-rounded) output block with the same block of `dot_with` (bf16 [M][ld_dot]):
+  //   dot_out[((m / dot_rows) * (N / 64) + j) * dot_rows + m % dot_rows]
+  // — the attention backward's D = rowsum(dO * O) per (batch, head, query), with M = B * S, dot_rows = S.
+  const void* dot_with;
+  int ld_dot;
+  float* dot_out;
+  int dot_rows;
 };
 
 struct GemmArgs {
@@ -54,6 +62,10 @@ struct GemmArgs {
   const bf16* aux;
   int ld_aux;
   DropKey drop;
+  const bf16* dot_with;
+  int ld_dot;
+  float* dot_out;
+  int dot_rows;
 };
 
 struct GemmPlan {
