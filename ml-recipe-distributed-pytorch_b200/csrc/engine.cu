@@ -345,7 +345,21 @@ int build_plan(bqa_handle* h, int B, int S, bool training) {
     bf16* dy_out = (l & 1) ? w.dy1 : w.dy0;  // gradient w.r.t. this layer's input
     // without hidden dropout the masked gradient IS the residual gradient: read it in place
     const bf16* dgm = c.hidden_dropout > 0.0f ? w.dgm : w.dres;
-    if (dgrad(&lp.d_ffn2, dgm, H, h->W(lo + Y.o_w), I, w.du, EPI_GELU_BWD, nullptr, act.u)) return 1;
+    {
+      // du = (dgm . W2) * gelu'(u); the epilogue also accumulates the bias gradient of the intermediate
+      // projection (column sums of du) instead of a separate pass over du
+      GemmProblem g{};
+      g.M = T; g.N = I; g.K = H;
+      g.A = dgm; g.lda = H; g.a_mn_major = 0;
+      g.B = h->W(lo + Y.o_w); g.ldb = I; g.b_mn_major = 1;
+      g.C = w.du; g.ldc = I;
+      g.epilogue = EPI_GELU_BWD;
+      g.aux = act.u; g.ld_aux = I;
+      g.k_splits = 1;
+      g.drop = make_drop_key(0, 0, 0.0f);
+      g.colsum_out = h->G(lo + Y.i_b);
+      if (gemm_plan(&lp.d_ffn2, g, h->num_sms)) return 1;
+    }
     if (wgrad(&lp.w_ffn2, dgm, H, act.g, I, h->G(lo + Y.o_w))) return 1;
     if (dgrad(&lp.d_ffn1, w.du, I, h->W(lo + Y.i_w), H, w.dctx /* da, reuses dctx slab */, EPI_LINEAR, w.dres,
               nullptr))
@@ -781,7 +795,6 @@ int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* s
         return 1;
       if (launch_gemm(h, lp.w_ffn2, nodrop, st)) return 1;
       if (launch_gemm(h, lp.d_ffn2, nodrop, st)) return 1;  // du = (dgm . W2) * gelu'(u)
-      if (launch_colsum(w.du, I, h->G(lo + Y.i_b), T, I, h->num_sms, st)) return 1;
       if (launch_gemm(h, lp.w_ffn1, nodrop, st)) return 1;
       if (launch_gemm(h, lp.d_ffn1, nodrop, st)) return 1;  // da = du . W1 + dres   (into the dctx slab)
       // LN1 backward on da
@@ -797,7 +810,7 @@ int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* s
       if (launch_colsum(w.dqkv, 3 * H, h->G(lo + Y.qkv_b), T, 3 * H, h->num_sms, st)) return 1;
       if (launch_gemm(h, lp.w_qkv, nodrop, st)) return 1;
       if (launch_gemm(h, lp.d_qkv, nodrop, st)) return 1;  // dx = dqkv . Wqkv + dres
-      h->launches += 7;
+      h->launches += 5;  // 2 LayerNorm backward, 1 column sum, 2 attention backward (GEMMs count themselves)
     } else {
       // embeddings: x0 = dropout(LN(z0)); dz0 scattered into the three tables
       const bf16* dy_in = w.dy0;  // layer 0 wrote its input gradient into dy[0 & 1]

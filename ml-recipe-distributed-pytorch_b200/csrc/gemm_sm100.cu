@@ -403,6 +403,25 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
               }
             }
           }
+          if (EPI == EPI_GELU_BWD && args.colsum_out != nullptr) {
+            // Column sums of this 32 x 32 piece over the warp's rows by a transpose-reduce: each step halves
+            // the values a lane holds and doubles the rows they cover (31 shuffles), lane c ends with column c.
+            // Rows beyond M are exact zeros (zero-filled operand rows).
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = f[i];
+#pragma unroll
+            for (int s = 16; s >= 1; s >>= 1) {
+              const bool up = (lane & s) != 0;
+#pragma unroll
+              for (int i = 0; i < s; ++i) {
+                const float send = up ? v[i] : v[i + s];
+                const float recv = __shfl_xor_sync(0xffffffffu, send, s);
+                v[i] = (up ? v[i + s] : v[i]) + recv;
+              }
+            }
+            if (n + lane < args.N) atomicAdd(args.colsum_out + n + lane, v[0]);
+          }
           // two pieces fill one 128-byte staging row; the buffer is reused once the previous store has
           // finished reading it
           if ((piece & 1) == 0) {
@@ -698,6 +717,11 @@ int gemm_plan(GemmPlan* plan, const GemmProblem& p, int num_sms) {
   a.ld_dot = p.ld_dot;
   a.dot_out = p.dot_out;
   a.dot_rows = p.dot_rows;
+  a.colsum_out = p.colsum_out;
+  if (p.colsum_out != nullptr && p.epilogue != EPI_GELU_BWD) {
+    set_error("gemm: the column-sum output is implemented for EPI_GELU_BWD only");
+    return 1;
+  }
   if (p.dot_out != nullptr &&
       (p.epilogue != EPI_LINEAR || p.residual != nullptr || p.dot_with == nullptr || p.dot_rows < 1 || p.N % 64 != 0)) {
     set_error("gemm: the row-dot output needs EPI_LINEAR without residual, a dot_with operand and N %% 64 == 0");

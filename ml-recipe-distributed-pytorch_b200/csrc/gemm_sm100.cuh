@@ -51,6 +51,9 @@ struct GemmProblem {
   int ld_dot;
   float* dot_out;
   int dot_rows;
+  // EPI_GELU_BWD: also accumulate the column sums of the output into colsum_out[N] (fp32 atomics) — the bias
+  // gradient of the layer whose pre-activation gradient this GEMM produces.
+  float* colsum_out;
 };
 
 struct GemmArgs {
@@ -66,6 +69,7 @@ struct GemmArgs {
   int ld_dot;
   float* dot_out;
   int dot_rows;
+  float* colsum_out;
 };
 
 struct GemmPlan {
