@@ -47,7 +47,8 @@ struct AttnArgs {
   float* lse2;
   float* dsum;
   bf16* dqkv;
-  uint32_t* keep;  // [B][A][S][4 * nchunk] dropout keep bits (bit k of word w = key 32 w + k), or null
+  uint32_t* keep;  // [B][A][S][attn_keep_words(S)] dropout keep bits, or null
+  float* dbias;    // [3H] fp32 or null: column sums of dqkv (gradient of the fused QKV bias), accumulated
   DropKey drop;
 };
 
@@ -150,6 +151,17 @@ __device__ __forceinline__ void st_out16(uint8_t* tile, int r, int qd, const flo
     o.w = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
     *reinterpret_cast<uint4*>(tile + r * 128 + ((((qd * 2 + q)) ^ (r & 7)) << 4)) = o;
   }
+}
+
+// sum over `rows` consecutive rows (from row0) of column `col` (0..63) of a [rows x 64] bf16 tile staged in the
+// SWIZZLE_128B layout st_out16 / st_tile16 write
+__device__ __forceinline__ float staged_colsum(const uint8_t* tile, int row0, int rows, int col) {
+  float s = 0.0f;
+  for (int rr = row0; rr < row0 + rows; ++rr) {
+    const uint16_t raw = *reinterpret_cast<const uint16_t*>(tile + rr * 128 + ((((col >> 3) ^ (rr & 7))) << 4) + (col & 7) * 2);
+    s += __uint_as_float(static_cast<uint32_t>(raw) << 16);
+  }
+  return s;
 }
 
 __device__ __forceinline__ uint8_t* align1024(uint8_t* p) { return p + ((1024u - (smem_u32(p) & 1023u)) & 1023u); }
@@ -521,7 +533,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
   uint8_t* sV = sK + N * CH;
   uint8_t* sdS = sV + N * CH;  // 2 * CH
   float* kbias = reinterpret_cast<float*>(sdS + 2 * CH);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(kbias + 512);
+  float* s_red = kbias + 512;  // [8][64] partial column sums of the drained tile
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_red + 512);
   uint64_t* bar_qo = bars + 0;
   uint64_t* bar_kv = bars + 1;
   uint64_t* bar_s = bars + 2;
@@ -654,6 +667,18 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
       if (tid == 0) {
         tma_store_3d(&tm_dqkv, sOut, h * 64, qt * 128, b);  // Q slab of dqkv; rows beyond S are clipped
         tma_commit_group();
+      }
+      if (a.dbias != nullptr) {
+        // gradient of the query bias: column sums of the staged tile (rows beyond S are exact zeros),
+        // 8 row groups -> shared memory -> 64 atomics per tile
+        s_red[(tid >> 6) * 64 + (tid & 63)] = staged_colsum(sOut, (tid >> 6) * 16, 16, tid & 63);
+        named_bar_sync(1, ROW_THREADS);
+        if (tid < 64) {
+          float sum = 0.0f;
+#pragma unroll
+          for (int g8 = 0; g8 < 8; ++g8) sum += s_red[g8 * 64 + tid];
+          atomicAdd(a.dbias + h * 64 + tid, sum);
+        }
       }
     };
     int prev_b = -1;
@@ -1018,8 +1043,15 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
           tma_store_3d(&tm_dqkv, sPt + ew * 4096, 2 * a.H + h * 64, kt * 128 + ew * 32, b);
           tma_store_3d(&tm_dqkv, sdSt + ew * 4096, a.H + h * 64, kt * 128 + ew * 32, b);
           tma_commit_group();
-          tma_wait_group_read<0>();  // the next tile's first chunk overwrites these rows
         }
+        if (a.dbias != nullptr) {
+          // gradients of the value and key biases: column sums of the quarter's 32 staged rows (rows of
+          // masked or out-of-range keys are exact zeros)
+          const int col = (r & 31) + 32 * hq;
+          atomicAdd(a.dbias + 2 * a.H + h * 64 + col, staged_colsum(sPt, ew * 32, 32, col));
+          atomicAdd(a.dbias + a.H + h * 64 + col, staged_colsum(sdSt, ew * 32, 32, col));
+        }
+        if (tid == ew * 32) tma_wait_group_read<0>();  // the next tile's first chunk overwrites these rows
         named_bar_sync(2 + ew, 64);
         ATACC(6);
       }
@@ -1037,7 +1069,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
 }
 
 int fwd_smem_bytes(int n) { return CH * (5 + 2 * n) + 2048 + 4096 + 256 + 1024; }
-int dq_smem_bytes(int n) { return CH * (5 + 2 * n) + 2048 + 256 + 1024; }
+int dq_smem_bytes(int n) { return CH * (5 + 2 * n) + 2048 + 2048 + 256 + 1024; }
 int dkv_smem_bytes() { return CH * 4 + HC * 4 + 4096 + 256 + 1024; }
 
 AttnArgs make_args(const AttnPlan& p, const uint8_t* key_mask, DropKey drop) {
@@ -1057,6 +1089,7 @@ AttnArgs make_args(const AttnPlan& p, const uint8_t* key_mask, DropKey drop) {
   a.dsum = p.dsum;
   a.dqkv = p.dqkv;
   a.keep = p.keep;
+  a.dbias = nullptr;
   a.drop = drop;
   return a;
 }
@@ -1145,7 +1178,8 @@ int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cu
   return check_launch("attn_fwd");
 }
 
-int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st, bool dsum_ready) {
+int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st, bool dsum_ready,
+                  float* dqkv_bias_grad) {
   static bool configured = false;
   if (!configured) {
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1156,7 +1190,8 @@ int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, c
                                         dkv_smem_bytes()));
     configured = true;
   }
-  const AttnArgs a = make_args(plan, key_mask, drop);
+  AttnArgs a = make_args(plan, key_mask, drop);
+  a.dbias = dqkv_bias_grad;
   if (drop.thresh != 0u && plan.keep == nullptr) {
     set_error("attention: dropout needs the keep-bit buffer written by the forward");
     return 1;

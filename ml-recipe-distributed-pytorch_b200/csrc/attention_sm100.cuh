@@ -48,7 +48,9 @@ int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cu
                  bool bits_ready = false);
 // dsum_ready: plan.dsum already holds D = rowsum(dO * O) (written by the epilogue of the GEMM that produced
 // dctx); otherwise a small pre-pass computes it.
+// dqkv_bias_grad: fp32 [3H] or null; the column sums of dqkv (gradient of the fused QKV bias) are accumulated
+// into it by the kernels' drains, so that no separate pass over dqkv is needed.
 int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st,
-                  bool dsum_ready = false);
+                  bool dsum_ready = false, float* dqkv_bias_grad = nullptr);
 
 }  // namespace bqa

@@ -805,12 +805,13 @@ int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* s
       if (launch_gemm(h, lp.w_ao, nodrop, st)) return 1;
       if (launch_gemm(h, lp.d_ao, nodrop, st)) return 1;  // dctx = dgm . Wo
       h->time_begin(4, attn_flops(h, B, S, true), st);
-      if (attn_backward(lp.attn, mask, h->key(site_attn(l), c.attn_dropout), st, /*dsum_ready=*/true)) return 1;
+      if (attn_backward(lp.attn, mask, h->key(site_attn(l), c.attn_dropout), st, /*dsum_ready=*/true,
+                        /*dqkv_bias_grad=*/h->G(lo + Y.qkv_b)))
+        return 1;
       h->time_end(st);
-      if (launch_colsum(w.dqkv, 3 * H, h->G(lo + Y.qkv_b), T, 3 * H, h->num_sms, st)) return 1;
       if (launch_gemm(h, lp.w_qkv, nodrop, st)) return 1;
       if (launch_gemm(h, lp.d_qkv, nodrop, st)) return 1;  // dx = dqkv . Wqkv + dres
-      h->launches += 5;  // 2 LayerNorm backward, 1 column sum, 2 attention backward (GEMMs count themselves)
+      h->launches += 4;  // 2 LayerNorm backward, 2 attention backward (GEMMs count themselves)
     } else {
       // embeddings: x0 = dropout(LN(z0)); dz0 scattered into the three tables
       const bf16* dy_in = w.dy0;  // layer 0 wrote its input gradient into dy[0 & 1]
