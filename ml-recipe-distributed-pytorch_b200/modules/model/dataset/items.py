@@ -114,7 +114,10 @@ def _collate_compact(items, tokenizer, n, max_len, return_items, pin_memory):
         if bert and not (row == sep).any():
             raise ValueError(f'{sep} is not in list')  # the reference's row.index(sep_token_id)
         tokens[i, :len(row)] = row
-    inputs = {'input_ids_i32': torch.from_numpy(tokens), 'sep_token_id': int(sep), 'type_coef': 1 if bert else 0}
+    # no_padding: every position holds a real token (ids > 0), so attention_mask would be all True; the model
+    # then gets attention_mask=None (same result) and the attention kernels take their mask-free variants
+    inputs = {'input_ids_i32': torch.from_numpy(tokens), 'sep_token_id': int(sep), 'type_coef': 1 if bert else 0,
+              'no_padding': bool((tokens > 0).all())}
     labels = _labels(items)
     if pin_memory and torch.cuda.is_available():
         inputs['input_ids_i32'] = inputs['input_ids_i32'].pin_memory()
@@ -141,4 +144,5 @@ def expand_compact_inputs(inputs, device):
         L.check(L.lib.bqa_prepare_inputs(ids32.data_ptr(), B, S, int(inputs['sep_token_id']), int(inputs['type_coef']),
                                          ids.data_ptr(), tt.data_ptr(), mask.data_ptr(), None,
                                          L.current_stream_ptr()), 'bqa_prepare_inputs')
-    return {'input_ids': ids, 'attention_mask': mask, 'token_type_ids': tt}
+    return {'input_ids': ids, 'attention_mask': None if inputs.get('no_padding', False) else mask,
+            'token_type_ids': tt}

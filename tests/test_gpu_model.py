@@ -343,8 +343,13 @@ def test_inputs_built_on_device_equal_collate_fun(pkg):
                                 start_position=0.0, end_position=1.0))
     full, _ = ds.collate_fun(items, tok)
     compact, _ = ds.collate_fun(items, tok, compact=True, pin_memory=True)
+    assert compact["no_padding"] is False
     got = ds.expand_compact_inputs(compact, torch.device(DEV))
     torch.cuda.synchronize()
+    # a batch without padding elides the (all-True) mask
+    same_len = [it for it in items if len(it.input_ids) == len(items[0].input_ids)] or items[:1]
+    dense = ds.expand_compact_inputs(ds.collate_fun(same_len[:1] * 3, tok, compact=True)[0], torch.device(DEV))
+    assert dense["attention_mask"] is None
     for k in ("input_ids", "token_type_ids", "attention_mask"):
         assert got[k].dtype == full[k].dtype, k
         assert torch.equal(got[k].cpu(), full[k]), k
