@@ -8,7 +8,9 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbqa.so")
+# BQA_LIB_PATH: load another build of the same library (A/B timing of kernel variants on one box); still
+# the same ABI check, still no fallback
+LIB_PATH = os.environ.get("BQA_LIB_PATH") or os.path.join(_HERE, "libbqa.so")
 ABI_VERSION = 2
 
 EPI_LINEAR, EPI_GELU_FWD, EPI_GELU_BWD, EPI_F32_ADD = 0, 1, 2, 3
