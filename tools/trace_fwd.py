@@ -1,0 +1,33 @@
+"""Accumulated phase times of the row threads of the attention forward kernel (trace build)."""
+import ctypes, os, sys
+import numpy as np
+import torch
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+lib = ctypes.CDLL(os.path.join(ROOT, "tools/_trace/libbqa_trace.so"))
+vp = ctypes.c_void_p
+lib.bqa_attention_forward.argtypes = [vp, vp, vp, vp, vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_float,
+                                      ctypes.c_uint64, ctypes.c_uint32, vp]
+lib.bqa_attention_keep_words.argtypes = [ctypes.c_int32]
+lib.bqa_trace_read.argtypes = [vp]
+B, S, A = 32, 384, 12
+H = A * 64
+dev = "cuda"
+qkv = torch.randn(B, S, 3 * H, device=dev).to(torch.bfloat16)
+ctx = torch.zeros(B, S, H, device=dev, dtype=torch.bfloat16)
+lse2 = torch.zeros(B, A, S, device=dev)
+keep = torch.zeros(B, A, S, lib.bqa_attention_keep_words(S), dtype=torch.int32, device=dev)
+st = torch.cuda.current_stream().cuda_stream
+names = {1: "wait scores", 2: "pass 1 (row max)", 3: "row-max barrier", 4: "pass 2 (exp, P stores)", 5: "row-sum barrier",
+         6: "wait O", 7: "epilogue", 8: "tile prologue"}
+for p in (0.1, 0.0):
+    for _ in range(3):
+        assert lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep.data_ptr(), None, B, S, A, p, 7, 5, st) == 0
+    torch.cuda.synchronize()
+    buf = np.zeros(4096 * 16, dtype=np.uint64)
+    assert lib.bqa_trace_read(buf.ctypes.data) == 0
+    t = buf.reshape(4096, 16)[:148].astype(np.int64)
+    total = t[:, 9] - t[:, 0]
+    tiles = 1152 / 148
+    print(f"--- forward, dropout {p}: cycles per CTA {total.mean():.0f}; per tile {total.mean() / tiles:.0f}")
+    for k in range(1, 9):
+        print(f"  {names[k]:>24s}: {t[:, k].mean() / tiles:8.0f} per tile  {t[:, k].mean() / total.mean() * 100:5.1f}%")
