@@ -73,6 +73,18 @@ typedef struct bqa_gemm_desc {
   float dropout_p;    /* 0 disables; applied to (acc + bias) before the residual             */
   uint64_t drop_seed; /* with drop_site selects the dropout stream                           */
   uint32_t drop_site;
+  /* Fused side outputs of the backward GEMMs (all optional, NULL disables; ABI version 3).
+   * colsum_out (BQA_EPI_GELU_BWD): [N] fp32, += column sums of C (the bias gradient of the
+   *   intermediate projection, modeling_bert.py:339-342, without a pass over C).
+   * dot_with / dot_out (BQA_EPI_LINEAR, N a multiple of 64): per row m and 64-column block j,
+   *   dot_out[((m / dot_rows) * (N / 64) + j) * dot_rows + m % dot_rows] = sum of C[m][64j..64j+63]
+   *   * dot_with[m][64j..64j+63] (dot_with bf16 [M][ld_dot]) — the attention backward's
+   *   D = rowsum(dO * O) per (batch, head, query) with M = B * S, dot_rows = S, written (not added). */
+  float* colsum_out;
+  const void* dot_with;
+  int32_t ld_dot;
+  float* dot_out;
+  int32_t dot_rows;
 } bqa_gemm_desc;
 
 BQA_API int bqa_gemm_bf16(const bqa_gemm_desc* desc, void* stream);
@@ -85,7 +97,8 @@ BQA_API int bqa_gemm_bf16(const bqa_gemm_desc* desc, void* stream);
  *   keep_bits [B][A][S][bqa_attention_keep_words(S)] uint32: dropout decisions written by the
  *   forward and read by the backward; opaque to the caller (per position r: the decisions of
  *   query r over the keys, then those of key r over the queries); may be NULL when dropout_p == 0
- *   backward: dctx [B*S][H] bf16 in, dqkv [B*S][3H] bf16 out, dsum [B][A][S] fp32 scratch
+ *   backward: dctx [B*S][H] bf16 in, dqkv [B*S][3H] bf16 out, dsum [B][A][S] fp32 scratch;
+ *   dqkv_bias_grad: [3H] fp32 or NULL, += column sums of dqkv (gradient of the fused Q/K/V bias)
  * ------------------------------------------------------------------------------------ */
 BQA_API int bqa_attention_keep_words(int32_t S);
 BQA_API int bqa_attention_forward(const void* qkv, void* ctx, float* lse2, uint32_t* keep_bits,
@@ -94,7 +107,7 @@ BQA_API int bqa_attention_forward(const void* qkv, void* ctx, float* lse2, uint3
 BQA_API int bqa_attention_backward(const void* qkv, const void* ctx, const float* lse2, const uint32_t* keep_bits,
                                    const void* dctx, void* dqkv, float* dsum, const uint8_t* key_mask, int32_t B,
                                    int32_t S, int32_t A, float dropout_p, uint64_t drop_seed, uint32_t drop_site,
-                                   void* stream);
+                                   float* dqkv_bias_grad, void* stream);
 
 /* ------------------------------------------------------------------------------------
  * Row kernels (HBM-bound).  LayerNorm(eps) over H of bf16 rows with fp32 affine parameters
@@ -239,6 +252,11 @@ BQA_API int bqa_loss(bqa_handle* h, const float* start, const float* end, const 
                      const float* reg_start, const float* reg_end, const int64_t* y_start, const int64_t* y_end,
                      const int64_t* y_cls, const float* y_reg_start, const float* y_reg_end,
                      const bqa_loss_config* lc, int32_t with_grad, float* losses, void* stream);
+/* *host_status = 1 if the last bqa_forward met a token id outside [0, vocab) or a token type outside
+ * [0, type_vocab) (torch's nn.Embedding raises IndexError there, modeling_bert.py:72-112; the kernels clamp
+ * the id to 0, set this flag and bqa_loss then reports NaN for all six scalars), else 0.  Synchronises
+ * `stream`.  host_status is a HOST pointer. */
+BQA_API int bqa_input_status(bqa_handle* h, int32_t* host_status, void* stream);
 /* Handle-free form of bqa_loss for callers that own every buffer (the autograd-facing
  * WeightedLoss): d_* receive d(total * loss_scale)/d(output) when with_grad != 0 (d_reg_* are
  * w.r.t. the sigmoid outputs); row_scratch: >= 5 * B floats. */

@@ -8,10 +8,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-# BQA_LIB_PATH: load another build of the same library (A/B timing of kernel variants on one box); still
-# the same ABI check, still no fallback
-LIB_PATH = os.environ.get("BQA_LIB_PATH") or os.path.join(_HERE, "libbqa.so")
-ABI_VERSION = 2
+LIB_PATH = os.path.join(_HERE, "libbqa.so")
+ABI_VERSION = 3
 
 EPI_LINEAR, EPI_GELU_FWD, EPI_GELU_BWD, EPI_F32_ADD = 0, 1, 2, 3
 CLS_SMOOTH, CLS_CE, CLS_FOCAL = 0, 1, 2
@@ -33,6 +31,7 @@ class GemmDesc(ctypes.Structure):
         ("k_splits", c_i32),
         ("dropout_p", c_f32),
         ("drop_seed", c_u64), ("drop_site", c_u32),
+        ("colsum_out", vp), ("dot_with", vp), ("ld_dot", c_i32), ("dot_out", vp), ("dot_rows", c_i32),
     ]
 
 
@@ -70,7 +69,7 @@ SIGNATURES = {
     "bqa_attention_keep_words": (ctypes.c_int, [c_i32]),
     "bqa_attention_forward": (ctypes.c_int, [vp, vp, vp, vp, vp, c_i32, c_i32, c_i32, c_f32, c_u64, c_u32, vp]),
     "bqa_attention_backward": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, c_i32, c_i32, c_i32, c_f32, c_u64,
-                                              c_u32, vp]),
+                                              c_u32, vp, vp]),
     "bqa_layernorm_forward": (ctypes.c_int, [vp, vp, vp, vp, c_i32, c_i32, c_f32, vp]),
     "bqa_layernorm_backward": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, c_i32, c_i32, c_f32, c_f32, c_u32,
                                               c_f32, c_u32, c_u64, vp]),
@@ -93,6 +92,7 @@ SIGNATURES = {
     "bqa_forward": (ctypes.c_int, [vp, vp, vp, vp, c_i32, c_i32, c_i32, c_u64, c_u64, vp, vp, vp, vp, vp, vp]),
     "bqa_loss": (ctypes.c_int, [vp] + [vp] * 10 + [ctypes.POINTER(LossConfig), c_i32, vp, vp]),
     "bqa_qa_loss": (ctypes.c_int, [vp] * 17 + [c_i32, c_i32, c_i32, ctypes.POINTER(LossConfig), c_i32, vp]),
+    "bqa_input_status": (ctypes.c_int, [vp, ctypes.POINTER(c_i32), vp]),
     "bqa_set_output_grads": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp]),
     "bqa_backward": (ctypes.c_int, [vp, c_i32, c_i32, vp]),
     "bqa_num_backward_phases": (ctypes.c_int, [vp]),
@@ -104,18 +104,18 @@ SIGNATURES = {
 }
 
 
-def _load():
-    if not os.path.exists(LIB_PATH):
+def _load(path=LIB_PATH):
+    if not os.path.exists(path):
         raise ImportError(
-            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
             "(needs nvcc; there is no fallback implementation)")
-    lib = ctypes.CDLL(LIB_PATH)
+    lib = ctypes.CDLL(path)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError here = library and binding out of sync
         fn.restype = res
         fn.argtypes = args
     if lib.bqa_abi_version() != ABI_VERSION:
-        raise ImportError(f"{LIB_PATH}: ABI version {lib.bqa_abi_version()} != expected {ABI_VERSION}; rebuild")
+        raise ImportError(f"{path}: ABI version {lib.bqa_abi_version()} != expected {ABI_VERSION}; rebuild")
     return lib
 
 
@@ -140,7 +140,7 @@ def current_stream_ptr():
 
 def gemm_bf16(A, B, C, *, a_mn_major=False, b_mn_major=False, epilogue=EPI_LINEAR, C2=None, bias=None,
               residual=None, aux=None, k_splits=1, dropout_p=0.0, drop_seed=0, drop_site=0, M=None, N=None,
-              K=None):
+              K=None, colsum_out=None, dot_with=None, dot_out=None, dot_rows=0):
     """C = epilogue(op(A) . op(B)) on the tcgen05 kernel.  Shapes follow include/bqa.h:
     A is [M,K] (K-major) or [K,M] (MN-major); B is [N,K] or [K,N]; C is [M,N]."""
     if M is None:
@@ -165,5 +165,10 @@ def gemm_bf16(A, B, C, *, a_mn_major=False, b_mn_major=False, epilogue=EPI_LINEA
     d.dropout_p = dropout_p
     d.drop_seed = drop_seed
     d.drop_site = drop_site
+    d.colsum_out = colsum_out.data_ptr() if colsum_out is not None else None
+    d.dot_with = dot_with.data_ptr() if dot_with is not None else None
+    d.ld_dot = dot_with.stride(0) if dot_with is not None else 0
+    d.dot_out = dot_out.data_ptr() if dot_out is not None else None
+    d.dot_rows = dot_rows
     check(lib.bqa_gemm_bf16(ctypes.byref(d), current_stream_ptr()), "bqa_gemm_bf16")
     return C

@@ -1156,13 +1156,13 @@ int attn_make_keep_bits(const AttnPlan& plan, DropKey drop, cudaStream_t st) {
 }
 
 int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st, bool bits_ready) {
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce once;
+  int once_dev; if (once.needs_setup(&once_dev)) {
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         fwd_smem_bytes(4)));
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         fwd_smem_bytes(4)));
-    configured = true;
+    once.mark_done(once_dev);
   }
   const AttnArgs a = make_args(plan, key_mask, drop);
   if (drop.thresh != 0u && !bits_ready && attn_make_keep_bits(plan, drop, st)) return 1;
@@ -1180,15 +1180,15 @@ int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cu
 
 int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st, bool dsum_ready,
                   float* dqkv_bias_grad) {
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce once;
+  int once_dev; if (once.needs_setup(&once_dev)) {
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         dq_smem_bytes(4)));
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         dq_smem_bytes(4)));
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dkv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         dkv_smem_bytes()));
-    configured = true;
+    once.mark_done(once_dev);
   }
   AttnArgs a = make_args(plan, key_mask, drop);
   a.dbias = dqkv_bias_grad;

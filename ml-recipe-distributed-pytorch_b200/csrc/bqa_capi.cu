@@ -12,7 +12,7 @@ extern "C" {
 
 const char* bqa_last_error(void) { return bqa::last_error(); }
 
-int bqa_abi_version(void) { return 2; }
+int bqa_abi_version(void) { return 3; }
 
 int bqa_gemm_bf16(const bqa_gemm_desc* d, void* stream) {
   if (d == nullptr) {
@@ -42,6 +42,11 @@ int bqa_gemm_bf16(const bqa_gemm_desc* d, void* stream) {
   p.ld_aux = d->ld_aux;
   p.k_splits = d->k_splits;
   p.drop = make_drop_key(d->drop_seed, d->drop_site, d->dropout_p);
+  p.colsum_out = d->colsum_out;
+  p.dot_with = d->dot_with;
+  p.ld_dot = d->ld_dot;
+  p.dot_out = d->dot_out;
+  p.dot_rows = d->dot_rows;
   GemmPlan plan;
   if (gemm_plan(&plan, p, num_sms)) return 1;
   return gemm_launch(plan, reinterpret_cast<cudaStream_t>(stream));
@@ -71,14 +76,15 @@ int bqa_attention_forward(const void* qkv, void* ctx, float* lse2, uint32_t* kee
 
 int bqa_attention_backward(const void* qkv, const void* ctx, const float* lse2, const uint32_t* keep_bits,
                            const void* dctx, void* dqkv, float* dsum, const uint8_t* key_mask, int32_t B, int32_t S,
-                           int32_t A, float dropout_p, uint64_t drop_seed, uint32_t drop_site, void* stream) {
+                           int32_t A, float dropout_p, uint64_t drop_seed, uint32_t drop_site, float* dqkv_bias_grad,
+                           void* stream) {
   AttnPlan plan;
   AttnShape s{B, S, A, A * 64};
   if (attn_plan(&plan, s, qkv, const_cast<void*>(ctx), const_cast<float*>(lse2), dctx, dsum, dqkv,
                 const_cast<uint32_t*>(keep_bits)))
     return 1;
   return attn_backward(plan, key_mask, make_drop_key(drop_seed, drop_site, dropout_p),
-                       reinterpret_cast<cudaStream_t>(stream));
+                       reinterpret_cast<cudaStream_t>(stream), /*dsum_ready=*/false, dqkv_bias_grad);
 }
 
 int bqa_layernorm_forward(const void* z, const float* gamma, const float* beta, void* y, int32_t T, int32_t H,

@@ -5,6 +5,8 @@
 #include <math.h>
 #include <stdint.h>
 
+#include <atomic>
+
 #include "bqa_common.cuh"
 
 namespace bqa {
@@ -21,17 +23,40 @@ const char* last_error();
     }                                                                                          \
   } while (0)
 
+constexpr int MAX_DEVICES = 64;
+
+// SM count of the current device; cached per device ordinal (atomics: any thread may ask)
 inline int device_sm_count(int* out) {
+  static std::atomic<int> cached[MAX_DEVICES];  // zero-initialised: 0 = not queried yet
   int dev = 0;
   BQA_CUDA_CHECK(cudaGetDevice(&dev));
-  static int cached_dev = -1, cached = 0;
-  if (cached_dev != dev) {
-    BQA_CUDA_CHECK(cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev));
-    cached_dev = dev;
+  int n = (dev >= 0 && dev < MAX_DEVICES) ? cached[dev].load(std::memory_order_relaxed) : 0;
+  if (n == 0) {
+    BQA_CUDA_CHECK(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+    if (dev >= 0 && dev < MAX_DEVICES) cached[dev].store(n, std::memory_order_relaxed);
   }
-  *out = cached;
+  *out = n;
   return 0;
 }
+
+// Function attributes (cudaFuncSetAttribute) are per device: one flag per device ordinal and call site.
+// needs_setup() is true until mark_done() has been called for the current device; running the set-up twice
+// (two threads racing) is harmless.
+struct PerDeviceOnce {
+  std::atomic<bool> done[MAX_DEVICES];
+  // true until mark_done(*dev) has been called for the current device; *dev = its ordinal (-1 if unknown:
+  // then the set-up runs on every call)
+  bool needs_setup(int* dev) {
+    if (cudaGetDevice(dev) != cudaSuccess || *dev < 0 || *dev >= MAX_DEVICES) {
+      *dev = -1;
+      return true;
+    }
+    return !done[*dev].load(std::memory_order_acquire);
+  }
+  void mark_done(int dev) {
+    if (dev >= 0) done[dev].store(true, std::memory_order_release);
+  }
+};
 
 inline uint64_t splitmix64(uint64_t x) {
   x += 0x9e3779b97f4a7c15ull;

@@ -109,7 +109,7 @@ struct LayerActs {
 struct Workspace {
   bf16 *z0, *x0;
   std::vector<LayerActs> layer;  // L slots in training, 2 in inference
-  float *pooled, *start, *end, *cls, *reg_s, *reg_e;  // internal copies of the outputs
+  float *pooled, *reg_s, *reg_e;  // pooler output and the two sigmoid outputs, kept for the backward
   float *d_start, *d_end, *d_cls, *d_reg_s, *d_reg_e;
   float *loss_rows, *dpre, *dx0;
   uint8_t* mask;
@@ -144,9 +144,6 @@ void carve(Workspace* w, uint8_t* base, const bqa_config& c, int B, int S, bool 
                  : nullptr;
   }
   w->pooled = b.take<float>(static_cast<uint64_t>(B) * H);
-  w->start = b.take<float>(T);
-  w->end = b.take<float>(T);
-  w->cls = b.take<float>(static_cast<uint64_t>(B) * c.num_labels);
   w->reg_s = b.take<float>(B);
   w->reg_e = b.take<float>(B);
   w->mask = b.take<uint8_t>(T);
@@ -226,6 +223,8 @@ struct bqa_handle {
   // stream runs the embeddings and the first GEMMs (the decisions depend only on the step's keys)
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr;
+  cudaEvent_t ev_tail = nullptr;  // end of the ahead-of-time keep-bit generation on the side stream
+  bool side_pending = false;      // that work has not been ordered before the main stream yet
   std::vector<cudaEvent_t> ev_bits;
   bool profiling = false;
   std::vector<Timed> timed;
@@ -487,6 +486,7 @@ int bqa_destroy(bqa_handle* h) {
     for (auto e : h->event_pool) cudaEventDestroy(e);
     for (auto e : h->ev_bits) cudaEventDestroy(e);
     if (h->ev_fork != nullptr) cudaEventDestroy(h->ev_fork);
+    if (h->ev_tail != nullptr) cudaEventDestroy(h->ev_tail);
     if (h->side != nullptr) cudaStreamDestroy(h->side);
   }
   delete h;
@@ -582,29 +582,30 @@ int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_ty
   const int T = B * S, H = c.hidden;
   const size_t tb = static_cast<size_t>(T);
 
-  // inputs are kept for the backward (embedding scatter, key mask)
-  BQA_CUDA_CHECK(cudaMemcpyAsync(w.ids, input_ids, tb * sizeof(int64_t), cudaMemcpyDeviceToDevice, st));
-  if (token_type_ids != nullptr)
-    BQA_CUDA_CHECK(cudaMemcpyAsync(w.tt, token_type_ids, tb * sizeof(int64_t), cudaMemcpyDeviceToDevice, st));
-  else
-    BQA_CUDA_CHECK(cudaMemsetAsync(w.tt, 0, tb * sizeof(int64_t), st));
-  const uint8_t* mask = nullptr;
-  if (attention_mask != nullptr) {
-    BQA_CUDA_CHECK(cudaMemcpyAsync(w.mask, attention_mask, tb, cudaMemcpyDeviceToDevice, st));
-    mask = w.mask;
-  }
+  // The private copies of the inputs that the backward needs (embedding scatter, key mask) are written by the
+  // embedding kernel itself; only the error flag is cleared here.
+  const uint8_t* mask = attention_mask != nullptr ? w.mask : nullptr;
   h->has_mask = mask != nullptr;
-  BQA_CUDA_CHECK(cudaMemsetAsync(w.err_flag, 0, sizeof(int), st));
 
   const bool attn_drop = tr && c.attn_dropout > 0.0f && !h->enc_dropout_off;
+  const bool ahead = attn_drop && h->bits_ahead && h->bits_seed == seed && h->bits_step == step && h->bits_B == B &&
+                     h->bits_S == S;
+  if (h->side_pending && !ahead) {
+    // keep bits generated ahead of time that this forward will not consume (other shape, plan rebuilt, eval,
+    // dropout off): those side-stream kernels may still be writing into the workspace that the kernels below
+    // are about to reuse — order them first
+    BQA_CUDA_CHECK(cudaStreamWaitEvent(st, h->ev_tail, 0));
+  }
+  h->side_pending = false;  // consumed bits are ordered by the per-layer events
+  BQA_CUDA_CHECK(cudaMemsetAsync(w.err_flag, 0, sizeof(int), st));
   if (attn_drop) {
     if (h->side == nullptr) {
       BQA_CUDA_CHECK(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
       BQA_CUDA_CHECK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+      BQA_CUDA_CHECK(cudaEventCreateWithFlags(&h->ev_tail, cudaEventDisableTiming));
       h->ev_bits.resize(c.num_layers);
       for (auto& e : h->ev_bits) BQA_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     }
-    const bool ahead = h->bits_ahead && h->bits_seed == seed && h->bits_step == step && h->bits_B == B && h->bits_S == S;
     if (!ahead) {
       BQA_CUDA_CHECK(cudaEventRecord(h->ev_fork, st));  // everything that read last step's bits is behind us
       BQA_CUDA_CHECK(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
@@ -616,9 +617,9 @@ int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_ty
     }
   }
   h->bits_ahead = false;
-  if (launch_embed_ln_fwd(w.ids, w.tt, h->P(Y.word_emb), h->P(Y.pos_emb), h->P(Y.type_emb), h->P(Y.emb_ln_g),
-                          h->P(Y.emb_ln_b), w.z0, w.x0, T, S, H, c.vocab, c.type_vocab, c.ln_eps,
-                          h->key(site_embed(), c.hidden_dropout), w.err_flag, st))
+  if (launch_embed_ln_fwd(input_ids, token_type_ids, attention_mask, h->P(Y.word_emb), h->P(Y.pos_emb),
+                          h->P(Y.type_emb), h->P(Y.emb_ln_g), h->P(Y.emb_ln_b), w.z0, w.x0, w.ids, w.tt, w.mask, T, S,
+                          H, c.vocab, c.type_vocab, c.ln_eps, h->key(site_embed(), c.hidden_dropout), w.err_flag, st))
     return 1;
   h->launches += 1;
   const int slots = static_cast<int>(w.layer.size());
@@ -641,19 +642,12 @@ int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_ty
   }
   const bf16* y = w.layer[(c.num_layers - 1) % slots].x_out;
   const HeadParams hp = head_params(h);
-  if (launch_span_head_fwd(y, hp.span_w, hp.span_b, w.start, w.end, T, H, st)) return 1;
-  if (launch_pooler_heads_fwd(y, hp, w.pooled, w.cls, w.reg_s, w.reg_e, B, S, H, c.num_labels,
+  // the outputs go straight into the caller's buffers; the backward keeps its own copy of the sigmoid outputs
+  if (launch_span_head_fwd(y, hp.span_w, hp.span_b, start, end, T, H, st)) return 1;
+  if (launch_pooler_heads_fwd(y, hp, w.pooled, cls, reg_start, reg_end, w.reg_s, w.reg_e, B, S, H, c.num_labels,
                               h->key(site_cls(c.num_layers), c.hidden_dropout), st))
     return 1;
   h->launches += 3;
-  BQA_CUDA_CHECK(cudaMemcpyAsync(start, w.start, tb * sizeof(float), cudaMemcpyDeviceToDevice, st));
-  BQA_CUDA_CHECK(cudaMemcpyAsync(end, w.end, tb * sizeof(float), cudaMemcpyDeviceToDevice, st));
-  BQA_CUDA_CHECK(cudaMemcpyAsync(cls, w.cls, static_cast<size_t>(B) * c.num_labels * sizeof(float),
-                                 cudaMemcpyDeviceToDevice, st));
-  BQA_CUDA_CHECK(cudaMemcpyAsync(reg_start, w.reg_s, static_cast<size_t>(B) * sizeof(float),
-                                 cudaMemcpyDeviceToDevice, st));
-  BQA_CUDA_CHECK(cudaMemcpyAsync(reg_end, w.reg_e, static_cast<size_t>(B) * sizeof(float),
-                                 cudaMemcpyDeviceToDevice, st));
   return 0;
 }
 
@@ -716,7 +710,21 @@ int bqa_loss(bqa_handle* h, const float* start, const float* end, const float* c
   h->launches += 2;
   return launch_loss_fwd_bwd(start, end, cls, reg_start, reg_end, y_start, y_end, y_cls, y_reg_start, y_reg_end,
                              w.d_start, w.d_end, w.d_cls, w.d_reg_s, w.d_reg_e, w.loss_rows, losses, h->plan.B,
-                             h->plan.S, h->cfg.num_labels, k, with_grad, reinterpret_cast<cudaStream_t>(stream));
+                             h->plan.S, h->cfg.num_labels, k, with_grad, reinterpret_cast<cudaStream_t>(stream),
+                             w.err_flag);
+}
+
+int bqa_input_status(bqa_handle* h, int32_t* host_status, void* stream) {
+  if (h == nullptr || host_status == nullptr || !h->plan_valid) {
+    set_error("bqa_input_status: no forward has been run on this handle");
+    return 1;
+  }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  int flag = 0;
+  BQA_CUDA_CHECK(cudaMemcpyAsync(&flag, h->plan.ws.err_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+  BQA_CUDA_CHECK(cudaStreamSynchronize(st));
+  *host_status = flag;
+  return 0;
 }
 
 int bqa_set_output_grads(bqa_handle* h, const float* d_start, const float* d_end, const float* d_cls,
@@ -819,7 +827,7 @@ int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* s
                         T, H, c.ln_eps, h->key(site_embed(), c.hidden_dropout), nodrop, h->num_sms, st))
         return 1;
       if (launch_embed_bwd(w.dres, w.ids, w.tt, h->G(Y.word_emb), h->G(Y.pos_emb), h->G(Y.type_emb), T, S, H,
-                           /*pad_token_id (BertConfig default)=*/0, st))
+                           c.vocab, c.type_vocab, /*pad_token_id (BertConfig default)=*/0, st))
         return 1;
       h->launches += 2;
     }
@@ -838,6 +846,8 @@ int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* s
         return 1;
       BQA_CUDA_CHECK(cudaEventRecord(h->ev_bits[l], h->side));
     }
+    BQA_CUDA_CHECK(cudaEventRecord(h->ev_tail, h->side));
+    h->side_pending = true;
     h->launches += L;
     h->bits_ahead = true;
     h->bits_seed = h->seed;

@@ -23,6 +23,8 @@
 // strides), so forward, dgrad and wgrad all read the tensors in the layout PyTorch gives them.
 #include "gemm_sm100.cuh"
 
+#include "bqa_host.cuh"
+
 #include <cstdarg>
 #include <cstdio>
 #include <mutex>
@@ -541,17 +543,17 @@ EncodeTiledFn get_encode_fn() {
 
 template <int A_MN, int B_MN, int EPI>
 int launch_variant(const GemmPlan& plan, cudaStream_t stream) {
-  static bool configured = false;  // per-process; the attribute is per-device but all devices share the value
+  static PerDeviceOnce once;  // the shared-memory attribute is per device
   auto k1 = gemm_kernel<A_MN, B_MN, EPI>;
   auto k2 = gemm_pair_kernel<A_MN, B_MN, EPI>;
-  if (!configured) {
+  int once_dev; if (once.needs_setup(&once_dev)) {
     cudaError_t e = cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<1, EPI>::SMEM_ALLOC);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<2, EPI>::SMEM_ALLOC);
     if (e != cudaSuccess) {
       set_error("gemm: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
       return 1;
     }
-    configured = true;
+    once.mark_done(once_dev);
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(plan.grid);

@@ -89,7 +89,8 @@ pooler_fwd_kernel(const bf16* __restrict__ y, const float* __restrict__ Wp, cons
 // cls[b][c] = dropout(pooled[b]) . Wc[c] + bc[c]; reg = sigmoid(pooled[b] . w + b);  grid B
 __global__ void __launch_bounds__(256)
 heads_fwd_kernel(const float* __restrict__ pooled, HeadParams hp, float* __restrict__ cls, float* __restrict__ reg_s,
-                 float* __restrict__ reg_e, int H, int C, DropKey drop) {
+                 float* __restrict__ reg_e, float* __restrict__ reg_s2, float* __restrict__ reg_e2, int H, int C,
+                 DropKey drop) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
   const int b = blockIdx.x;
   const float* p = pooled + static_cast<size_t>(b) * H;
@@ -109,6 +110,8 @@ heads_fwd_kernel(const float* __restrict__ pooled, HeadParams hp, float* __restr
         const float z = acc + (o == C ? hp.regs_b[0] : hp.rege_b[0]);
         const float sg = 1.0f / (1.0f + __expf(-z));
         (o == C ? reg_s : reg_e)[b] = sg;
+        float* second = o == C ? reg_s2 : reg_e2;
+        if (second != nullptr) second[b] = sg;
       }
     }
   }
@@ -254,7 +257,7 @@ loss_rows_kernel(const float* __restrict__ start, const float* __restrict__ end,
 }
 
 __global__ void loss_finalize_kernel(const float* __restrict__ row_scratch, float* __restrict__ losses, int B,
-                                     LossConfig lc) {
+                                     LossConfig lc, const int* __restrict__ err_flag) {
   if (threadIdx.x < 5) {
     float s = 0.0f;
     for (int b = 0; b < B; ++b) s += row_scratch[b * 5 + threadIdx.x];
@@ -270,6 +273,10 @@ __global__ void loss_finalize_kernel(const float* __restrict__ row_scratch, floa
     total += lc.w_end_reg * losses[3];
     total += lc.w_cls * losses[4];
     losses[5] = total;
+    if (err_flag != nullptr && *err_flag != 0) {
+#pragma unroll
+      for (int i = 0; i < 6; ++i) losses[i] = __int_as_float(0x7fc00000);
+    }
   }
 }
 
@@ -516,11 +523,12 @@ int launch_span_head_fwd(const bf16* y, const float* span_w, const float* span_b
 }
 
 int launch_pooler_heads_fwd(const bf16* y, const HeadParams& hp, float* pooled, float* cls, float* reg_s,
-                            float* reg_e, int B, int S, int H, int C, DropKey cls_drop, cudaStream_t st) {
+                            float* reg_e, float* reg_s2, float* reg_e2, int B, int S, int H, int C, DropKey cls_drop,
+                            cudaStream_t st) {
   dim3 grid((H + 31) / 32, B);
   pooler_fwd_kernel<<<grid, 256, 0, st>>>(y, hp.pool_w, hp.pool_b, pooled, S, H);
   if (check_launch("pooler_fwd")) return 1;
-  heads_fwd_kernel<<<B, 256, 0, st>>>(pooled, hp, cls, reg_s, reg_e, H, C, cls_drop);
+  heads_fwd_kernel<<<B, 256, 0, st>>>(pooled, hp, cls, reg_s, reg_e, reg_s2, reg_e2, H, C, cls_drop);
   return check_launch("heads_fwd");
 }
 
@@ -528,12 +536,12 @@ int launch_loss_fwd_bwd(const float* start, const float* end, const float* cls, 
                         const float* reg_e, const int64_t* y_start, const int64_t* y_end, const int64_t* y_cls,
                         const float* y_reg_s, const float* y_reg_e, float* d_start, float* d_end, float* d_cls,
                         float* d_reg_s, float* d_reg_e, float* row_scratch, float* losses_out, int B, int S,
-                        int C, const LossConfig& lc, int with_grad, cudaStream_t st) {
+                        int C, const LossConfig& lc, int with_grad, cudaStream_t st, const int* err_flag) {
   loss_rows_kernel<<<B, 256, 0, st>>>(start, end, cls, reg_s, reg_e, y_start, y_end, y_cls, y_reg_s, y_reg_e,
                                       d_start, d_end, d_cls, d_reg_s, d_reg_e, row_scratch, B, S, C, lc,
                                       with_grad);
   if (check_launch("loss_rows")) return 1;
-  loss_finalize_kernel<<<1, 32, 0, st>>>(row_scratch, losses_out, B, lc);
+  loss_finalize_kernel<<<1, 32, 0, st>>>(row_scratch, losses_out, B, lc, err_flag);
   return check_launch("loss_finalize");
 }
 

@@ -22,9 +22,11 @@ inline int check_launch(const char* what) {
 // ---- rowwise.cu -------------------------------------------------------------------------
 int launch_ln_fwd(const bf16* z, const float* gamma, const float* beta, bf16* y, int T, int H, float eps,
                   cudaStream_t st);
-int launch_embed_ln_fwd(const int64_t* ids, const int64_t* token_type, const float* word, const float* pos,
-                        const float* type, const float* gamma, const float* beta, bf16* z0, bf16* x0, int T, int S,
-                        int H, int V, int TV, float eps, DropKey drop, int* err_flag, cudaStream_t st);
+// ids_kept / tt_kept / mask_kept (each may be null): range-checked private copies of the inputs for the backward
+int launch_embed_ln_fwd(const int64_t* ids, const int64_t* token_type, const uint8_t* key_mask, const float* word,
+                        const float* pos, const float* type, const float* gamma, const float* beta, bf16* z0,
+                        bf16* x0, int64_t* ids_kept, int64_t* tt_kept, uint8_t* mask_kept, int T, int S, int H, int V,
+                        int TV, float eps, DropKey drop, int* err_flag, cudaStream_t st);
 int launch_ln_bwd(const bf16* dy, const bf16* z, const float* gamma, bf16* dz, bf16* dz_masked, float* dgamma,
                   float* dbeta, float* dbias, int T, int H, float eps, DropKey drop_in, DropKey drop_out,
                   int num_sms, cudaStream_t st);
@@ -32,7 +34,7 @@ int launch_colsum(const bf16* X, int ld, float* out, int T, int N, int num_sms, 
 int launch_prepare_inputs(const int32_t* ids32, int64_t* ids, int64_t* token_type, uint8_t* mask, int B, int S,
                           int sep_id, int type_coef, int* missing_sep, cudaStream_t st);
 int launch_embed_bwd(const bf16* dz0, const int64_t* ids, const int64_t* token_type, float* dword, float* dpos,
-                     float* dtype, int T, int S, int H, int pad_id, cudaStream_t st);
+                     float* dtype, int T, int S, int H, int V, int TV, int pad_id, cudaStream_t st);
 
 // ---- heads_loss.cu ----------------------------------------------------------------------
 struct HeadParams {  // fp32 master weights of the pooler and the four heads (+ their gradients)
@@ -48,8 +50,10 @@ struct HeadGrads {
 
 int launch_span_head_fwd(const bf16* y, const float* span_w, const float* span_b, float* start, float* end, int T,
                          int H, cudaStream_t st);
+// reg_s2 / reg_e2 (may be null): second copy of the two sigmoid outputs (kept for the backward)
 int launch_pooler_heads_fwd(const bf16* y, const HeadParams& hp, float* pooled, float* cls, float* reg_s,
-                            float* reg_e, int B, int S, int H, int C, DropKey cls_drop, cudaStream_t st);
+                            float* reg_e, float* reg_s2, float* reg_e2, int B, int S, int H, int C, DropKey cls_drop,
+                            cudaStream_t st);
 
 enum ClsLossKind : int { CLS_LOSS_SMOOTH = 0, CLS_LOSS_CE = 1, CLS_LOSS_FOCAL = 2 };
 struct LossConfig {
@@ -60,13 +64,14 @@ struct LossConfig {
   float grad_scale;         // 1 / batch_split (trainer.py:198)
   float focal_alpha, focal_gamma;  // FocalLossWithLogits (loss.py:57-71)
 };
-// losses_out[6] = {start_class, end_class, start_reg, end_reg, cls, total}
+// losses_out[6] = {start_class, end_class, start_reg, end_reg, cls, total}; all NaN when *err_flag != 0 (the
+// forward saw an out-of-range token / type id, where the reference raises IndexError)
 // d_reg_s / d_reg_e are gradients w.r.t. the sigmoid OUTPUTS (what autograd would hand back)
 int launch_loss_fwd_bwd(const float* start, const float* end, const float* cls, const float* reg_s,
                         const float* reg_e, const int64_t* y_start, const int64_t* y_end, const int64_t* y_cls,
                         const float* y_reg_s, const float* y_reg_e, float* d_start, float* d_end, float* d_cls,
                         float* d_reg_s, float* d_reg_e, float* row_scratch, float* losses_out, int B, int S,
-                        int C, const LossConfig& lc, int with_grad, cudaStream_t st);
+                        int C, const LossConfig& lc, int with_grad, cudaStream_t st, const int* err_flag = nullptr);
 int launch_heads_bwd(const bf16* y, const float* pooled, const float* reg_s, const float* reg_e,
                      const float* d_start, const float* d_end, const float* d_cls, const float* d_reg_s,
                      const float* d_reg_e, const HeadParams& hp, const HeadGrads& hg, float* dpre_scratch,

@@ -198,10 +198,11 @@ ln_fwd_kernel(const bf16* __restrict__ z, const float* __restrict__ gamma, const
 // x0 = dropout(LayerNorm(z0))
 __global__ void __launch_bounds__(ROW_WARPS * 32)
 embed_ln_fwd_kernel(const int64_t* __restrict__ ids, const int64_t* __restrict__ token_type,
-                    const float* __restrict__ word, const float* __restrict__ pos, const float* __restrict__ type,
-                    const float* __restrict__ gamma, const float* __restrict__ beta, bf16* __restrict__ z0,
-                    bf16* __restrict__ x0, int T, int S, int H, int V, int TV, float eps, DropKey drop,
-                    int* __restrict__ err_flag) {
+                    const uint8_t* __restrict__ key_mask, const float* __restrict__ word,
+                    const float* __restrict__ pos, const float* __restrict__ type, const float* __restrict__ gamma,
+                    const float* __restrict__ beta, bf16* __restrict__ z0, bf16* __restrict__ x0,
+                    int64_t* __restrict__ ids_kept, int64_t* __restrict__ tt_kept, uint8_t* __restrict__ mask_kept,
+                    int T, int S, int H, int V, int TV, float eps, DropKey drop, int* __restrict__ err_flag) {
   pdl_trigger();  // the next kernel (a GEMM) may start its prologue now; it waits for this grid before reading
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * ROW_WARPS + (threadIdx.x >> 5);
@@ -209,9 +210,16 @@ embed_ln_fwd_kernel(const int64_t* __restrict__ ids, const int64_t* __restrict__
   long long id = ids[row];
   long long tt = token_type != nullptr ? token_type[row] : 0;
   if (id < 0 || id >= V || tt < 0 || tt >= TV) {
-    if (lane == 0) atomicExch(err_flag, 1);  // torch raises IndexError here; surfaced by the host wrapper
+    // torch raises IndexError here; the flag turns the step's loss into NaN and bqa_input_status() reports it
+    if (lane == 0) atomicExch(err_flag, 1);
     id = 0;
     tt = 0;
+  }
+  // the backward (embedding scatter, key mask) reads these private, range-checked copies of the inputs
+  if (lane == 0) {
+    if (ids_kept != nullptr) ids_kept[row] = id;
+    if (tt_kept != nullptr) tt_kept[row] = tt;
+    if (mask_kept != nullptr && key_mask != nullptr) mask_kept[row] = key_mask[row];
   }
   const int s = row % S;
   RowVec w, p, t, g, b;
@@ -464,12 +472,12 @@ colsum_kernel(const bf16* __restrict__ X, int ld, float* __restrict__ out, int T
 //               per token and column (T-way contention on two rows was 1.1 ms per step).
 __global__ void __launch_bounds__(ROW_WARPS * 32)
 embed_word_bwd_kernel(const bf16* __restrict__ dz0, const int64_t* __restrict__ ids, float* __restrict__ dword,
-                      int T, int H, int pad_id) {
+                      int T, int H, int V, int pad_id) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * ROW_WARPS + (threadIdx.x >> 5);
   if (row >= T) return;
   const long long id = ids[row];
-  if (id == pad_id) return;
+  if (id == pad_id || id < 0 || id >= V) return;  // out-of-range ids were reported by the forward
   RowVec d;
   load_row_bf16(dz0 + static_cast<size_t>(row) * H, H, lane, d);
   float* w = dword + static_cast<size_t>(id) * H;
@@ -488,7 +496,7 @@ embed_word_bwd_kernel(const bf16* __restrict__ dz0, const int64_t* __restrict__ 
 constexpr int PT_GROUPS = 4;
 __global__ void __launch_bounds__(128 * PT_GROUPS)
 embed_pos_type_bwd_kernel(const bf16* __restrict__ dz0, const int64_t* __restrict__ token_type,
-                          float* __restrict__ dpos, float* __restrict__ dtype, int B, int S, int H) {
+                          float* __restrict__ dpos, float* __restrict__ dtype, int B, int S, int H, int TV) {
   __shared__ float s_acc[PT_GROUPS - 1][2][1024];
   __shared__ int s_any[PT_GROUPS - 1][2];
   const int s = blockIdx.x;
@@ -501,7 +509,8 @@ embed_pos_type_bwd_kernel(const bf16* __restrict__ dz0, const int64_t* __restric
   if (c < H) {
     for (int b = grp; b < B; b += PT_GROUPS) {
       const size_t row = static_cast<size_t>(b) * S + s;
-      const int tt = token_type != nullptr ? static_cast<int>(token_type[row]) & 1 : 0;
+      // two accumulators: type_vocab <= 2 (engine.cu: compute_layout); with one type row everything goes to row 0
+      const int tt = (token_type != nullptr && TV > 1 && token_type[row] == 1) ? 1 : 0;
       const uint4 u = __ldg(reinterpret_cast<const uint4*>(dz0 + row * H + c));
       const float2 a = unpack_bf16x2(u.x), bb = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
       const float v[8] = {a.x, a.y, bb.x, bb.y, cc.x, cc.y, d.x, d.y};
@@ -591,15 +600,17 @@ int launch_ln_fwd(const bf16* z, const float* gamma, const float* beta, bf16* y,
   return check_launch("ln_fwd");
 }
 
-int launch_embed_ln_fwd(const int64_t* ids, const int64_t* token_type, const float* word, const float* pos,
-                        const float* type, const float* gamma, const float* beta, bf16* z0, bf16* x0, int T, int S,
-                        int H, int V, int TV, float eps, DropKey drop, int* err_flag, cudaStream_t st) {
+int launch_embed_ln_fwd(const int64_t* ids, const int64_t* token_type, const uint8_t* key_mask, const float* word,
+                        const float* pos, const float* type, const float* gamma, const float* beta, bf16* z0,
+                        bf16* x0, int64_t* ids_kept, int64_t* tt_kept, uint8_t* mask_kept, int T, int S, int H, int V,
+                        int TV, float eps, DropKey drop, int* err_flag, cudaStream_t st) {
   if (H % 8 != 0 || H > MAXV * 256) {
     set_error("embeddings: H=%d must be a multiple of 8 and <= %d", H, MAXV * 256);
     return 1;
   }
-  embed_ln_fwd_kernel<<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(ids, token_type, word, pos, type, gamma, beta, z0,
-                                                              x0, T, S, H, V, TV, eps, drop, err_flag);
+  embed_ln_fwd_kernel<<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(ids, token_type, key_mask, word, pos, type, gamma,
+                                                              beta, z0, x0, ids_kept, tt_kept, mask_kept, T, S, H, V,
+                                                              TV, eps, drop, err_flag);
   return check_launch("embed_ln_fwd");
 }
 
@@ -616,11 +627,11 @@ int launch_ln_bwd(const bf16* dy, const bf16* z, const float* gamma, bf16* dz, b
   if (grid > row_blocks(T)) grid = row_blocks(T);
 #define BQA_LN_BWD(NV)                                                                                         \
   {                                                                                                            \
-    static bool configured = false;                                                                            \
-    if (!configured) {                                                                                         \
+    static PerDeviceOnce once;                                                                                 \
+    int once_dev; if (once.needs_setup(&once_dev)) {                                                                                  \
       BQA_CUDA_CHECK(cudaFuncSetAttribute(ln_bwd_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
                                           static_cast<int>(smem)));                                            \
-      configured = true;                                                                                       \
+      once.mark_done(once_dev);                                                                                        \
     }                                                                                                          \
     ln_bwd_kernel<NV><<<grid, ROW_WARPS * 32, smem, st>>>(dy, z, gamma, dz, dz_masked, dgamma, dbeta, dbias, T, H, \
                                                           eps, drop_in, drop_out);                             \
@@ -650,14 +661,14 @@ int launch_colsum(const bf16* X, int ld, float* out, int T, int N, int num_sms, 
 }
 
 int launch_embed_bwd(const bf16* dz0, const int64_t* ids, const int64_t* token_type, float* dword, float* dpos,
-                     float* dtype, int T, int S, int H, int pad_id, cudaStream_t st) {
+                     float* dtype, int T, int S, int H, int V, int TV, int pad_id, cudaStream_t st) {
   if (H % 8 != 0 || H > 1024) {
     set_error("embedding backward: H=%d must be a multiple of 8 and <= 1024", H);
     return 1;
   }
-  embed_word_bwd_kernel<<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(dz0, ids, dword, T, H, pad_id);
+  embed_word_bwd_kernel<<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(dz0, ids, dword, T, H, V, pad_id);
   if (check_launch("embed_word_bwd")) return 1;
-  embed_pos_type_bwd_kernel<<<S, 128 * PT_GROUPS, 0, st>>>(dz0, token_type, dpos, dtype, T / S, S, H);
+  embed_pos_type_bwd_kernel<<<S, 128 * PT_GROUPS, 0, st>>>(dz0, token_type, dpos, dtype, T / S, S, H, TV);
   return check_launch("embed_pos_type_bwd");
 }
 

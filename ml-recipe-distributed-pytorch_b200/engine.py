@@ -176,6 +176,14 @@ class Engine:
                                L.current_stream_ptr()), "bqa_loss")
         return losses
 
+    def check_inputs(self):
+        """Raises IndexError if the last forward saw a token / token-type id outside the embedding tables (what
+        torch's nn.Embedding does in the reference).  Synchronises the current stream."""
+        flag = L.c_i32(0)
+        L.check(L.lib.bqa_input_status(self.handle, ctypes.byref(flag), L.current_stream_ptr()), "bqa_input_status")
+        if flag.value:
+            raise IndexError("index out of range in self (input_ids / token_type_ids outside the embedding tables)")
+
     def set_output_grads(self, d_start, d_end, d_cls, d_reg_s, d_reg_e):
         def c(t):
             return None if t is None else t.to(device=self.device, dtype=torch.float32).contiguous()

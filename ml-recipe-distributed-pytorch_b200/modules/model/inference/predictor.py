@@ -67,6 +67,9 @@ class Predictor:
         dec = device_decode(preds)
         ints = torch.stack([dec['start_ids'], dec['end_ids'], dec['cls_ids']]).cpu().numpy()
         flts = torch.stack([dec['scores'], preds['start_reg'].float(), preds['end_reg'].float()]).cpu().numpy()
+        # the copies above synchronised the stream: reading the input-error flag costs nothing more.  The
+        # reference's nn.Embedding raises IndexError for ids outside the tables; so does this.
+        self.model.engine.check_inputs()
         return {'scores': flts[0], 'start_ids': ints[0], 'end_ids': ints[1], 'cls_ids': ints[2],
                 'start_reg': flts[1], 'end_reg': flts[2]}
 

@@ -44,7 +44,6 @@ class FusedAdamW(torch.optim.Optimizer):
         if self._built_for is eng:
             return eng
         dev = eng.device
-        rebuilt = getattr(self, "_m", None) is not None
         for _, attr in self._STATE:
             setattr(self, attr, torch.zeros(eng.total, dtype=torch.float32, device=dev))
         self._sumsq = torch.zeros(1, dtype=torch.float64, device=dev)
@@ -76,8 +75,10 @@ class FusedAdamW(torch.optim.Optimizer):
             for name, attr in self._STATE:
                 prev = st.get(name)
                 view = eng.view(getattr(self, attr), key)
-                if prev is not None and rebuilt:
-                    view.copy_(prev)
+                # moments that exist already (loaded from a checkpoint before the first build, or living in
+                # the buffers of a previous engine) move into the new flat buffers
+                if prev is not None and prev.data_ptr() != view.data_ptr():
+                    view.copy_(prev.to(device=dev, dtype=torch.float32).reshape(view.shape))
                 st[name] = view
             st.setdefault('step', 0)
         self._built_for = eng

@@ -300,6 +300,10 @@ class Trainer:
             readback.push(self.train_micro_batch(inputs, labels, last_of_step=last))
             vals = readback.pop_previous()  # one iteration late: never waits for the GPU
             if vals is not None:
+                if vals[5] != vals[5]:
+                    # NaN: either divergence (the reference trains on) or token ids outside the embedding tables,
+                    # which the kernels turn into a NaN loss where torch raises IndexError — ask and raise
+                    self.model.engine.check_inputs()
                 avg_meters.update(zip(_LOSS_KEYS, vals))
             avg_meters['lr'] = self._get_lr()
             if last:

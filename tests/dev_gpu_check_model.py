@@ -63,7 +63,7 @@ def attn_case(B, S, A, p, use_mask, bwd=True):
         dqkv = torch.zeros(B, S, 3 * H, device=dev, dtype=torch.bfloat16)
         dsum = torch.zeros(B, A, S, device=dev)
         L.check(L.lib.bqa_attention_backward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep_bits.data_ptr(), dctx.data_ptr(),
-                                             dqkv.data_ptr(), dsum.data_ptr(), L.ptr(m8), B, S, A, p, 77, 5, st),
+                                             dqkv.data_ptr(), dsum.data_ptr(), L.ptr(m8), B, S, A, p, 77, 5, None, st),
                 "attn bwd")
         torch.cuda.synchronize()
         g = x.grad

@@ -91,6 +91,38 @@ def test_gemm_variants(pkg, M, N, K, mode, ex):
         assert (C.float() - u.grad).abs().max().item() <= 8e-3
 
 
+@pytest.mark.parametrize("Bt,S,A", [(2, 200, 2), (32, 384, 12)])
+def test_gemm_fused_side_outputs(pkg, Bt, S, A):
+    """The side outputs that the backward GEMMs' epilogues produce instead of separate passes, at a ragged small
+    shape and at the BASELINE shape: (1) EPI_GELU_BWD's column sums of du (bias gradient of the intermediate
+    projection), (2) the row-dot D = rowsum(dctx * ctx) per (batch, head, query) of the dgrad GEMM that produces
+    dctx (read by the attention backward)."""
+    L = pkg._lib
+    torch.manual_seed(3)
+    H, I = A * 64, A * 256
+    M = Bt * S
+    # (1) du = (dgm . W2) * gelu'   with W2 [H, I] as the MN-major operand; colsum_out += sum_m du[m, :]
+    dgm, W2, gp = rnd(M, H), rnd(H, I, scale=0.05), rnd(M, I, scale=1.0)
+    du = torch.empty(M, I, device=DEV, dtype=torch.bfloat16)
+    cs = torch.full((I,), 0.5, device=DEV)
+    L.gemm_bf16(dgm, W2, du, b_mn_major=True, epilogue=L.EPI_GELU_BWD, aux=gp, colsum_out=cs)
+    torch.cuda.synchronize()
+    ref = (dgm.float() @ W2.float()) * gp.float()
+    assert (du.float() - ref).abs().max().item() <= 8e-3 * ref.abs().max().item()
+    want = ref.sum(0) + 0.5
+    assert (cs - want).norm().item() <= 3e-3 * want.norm().item() + 1e-3 * ref.abs().max().item() * M ** 0.5
+    # (2) dctx = dgm . Wo (MN-major Wo [H, H]); D[b, h, q] = sum_d dctx[b q, 64 h + d] * ctx[b q, 64 h + d]
+    Wo, ctx = rnd(H, H, scale=0.05), rnd(M, H)
+    dctx = torch.empty(M, H, device=DEV, dtype=torch.bfloat16)
+    D = torch.full((Bt, A, S), 7.0, device=DEV)
+    L.gemm_bf16(dgm, Wo, dctx, b_mn_major=True, dot_with=ctx, dot_out=D, dot_rows=S)
+    torch.cuda.synchronize()
+    ref = dgm.float() @ Wo.float()
+    assert (dctx.float() - ref).abs().max().item() <= 8e-3 * ref.abs().max().item()
+    wantD = (dctx.float() * ctx.float()).view(Bt, S, A, 64).sum(-1).permute(0, 2, 1)
+    assert (D - wantD).abs().max().item() <= 2e-3 * wantD.abs().max().item()
+
+
 def test_gemm_linearity_at_full_size(pkg):
     """Size-independent property at the BASELINE FFN shape: C(A1 + A2) == C(A1) + C(A2) up to rounding."""
     L = pkg._lib
@@ -146,10 +178,15 @@ def test_attention_forward_backward(pkg, B, S, A, p, use_mask):
     o.backward(dctx.float())
     dqkv = torch.zeros(B, S, 3 * H, device=DEV, dtype=torch.bfloat16)
     dsum = torch.zeros(B, A, S, device=DEV)
+    dbias = torch.zeros(3 * H, device=DEV)
     L.check(L.lib.bqa_attention_backward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep_bits.data_ptr(), dctx.data_ptr(),
-                                         dqkv.data_ptr(), dsum.data_ptr(), L.ptr(m8), B, S, A, p, 77, 5, st),
+                                         dqkv.data_ptr(), dsum.data_ptr(), L.ptr(m8), B, S, A, p, 77, 5, dbias.data_ptr(),
+                                         st),
             "attention backward")
     torch.cuda.synchronize()
+    # fused side output: gradient of the Q/K/V bias = column sums of dqkv, accumulated by the kernels' drains
+    want_b = dqkv.float().sum(dim=(0, 1))
+    assert (dbias - want_b).norm().item() <= 2e-3 * want_b.norm().item() + 1e-4 * max(1.0, dqkv.float().abs().max().item()) * (B * S) ** 0.5
     gscale = x.grad.abs().max().item()
     for i in range(3):
         got, want = dqkv[..., i * H:(i + 1) * H].float(), x.grad[..., i * H:(i + 1) * H]
@@ -203,6 +240,65 @@ def test_layernorm_and_colsum(pkg, T, H):
     L.check(L.lib.bqa_colsum_bf16(X.data_ptr(), 3 * H, cs.data_ptr(), T, 3 * H, st), "colsum")
     torch.cuda.synchronize()
     assert rel(cs, X.float().sum(0)) < 1e-5
+
+
+def test_dropout_keep_rate_per_site_on_device(pkg):
+    """Statistics of the CUDA kernels' own dropout decisions (no restatement of the hash involved): at every
+    kind of site the fraction of kept elements is 1 - p within 4 sigma of a binomial, and kept values carry
+    the 1 / (1 - p) scale.  Sites: GEMM epilogue (hidden dropout after the attention-output / FFN-output
+    projections), attention probabilities (keep bits + the context they produce), LayerNorm-backward mask."""
+    L = pkg._lib
+    p = 0.1
+    st = L.current_stream_ptr()
+
+    def check_rate(kept, n, what):
+        sigma = (p * (1 - p) / n) ** 0.5
+        assert abs(kept / n - (1 - p)) < 4 * sigma, f"{what}: keep rate {kept / n:.5f} over {n} elements"
+
+    # GEMM epilogue: A = 0, bias = 1  =>  C = dropout(1) in {0, 1/(1-p)}
+    M, N, K = 2048, 768, 64
+    A, B = torch.zeros(M, K, device=DEV, dtype=torch.bfloat16), torch.zeros(N, K, device=DEV, dtype=torch.bfloat16)
+    for site in (2, 3, 35):
+        C = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+        L.gemm_bf16(A, B, C, bias=torch.ones(N, device=DEV), dropout_p=p, drop_seed=99, drop_site=site)
+        torch.cuda.synchronize()
+        vals = C.float()
+        kept = int((vals != 0).sum())
+        check_rate(kept, M * N, f"gemm epilogue site {site}")
+        assert (vals[vals != 0] - 1 / (1 - p)).abs().max().item() < 8e-3
+    # attention: Q = K = 0 => uniform probabilities 1/S; V = 1 => ctx[q] = (#kept keys of q) / (S (1-p))
+    Bt, S, Ah = 8, 384, 4
+    H = Ah * 64
+    qkv = torch.zeros(Bt, S, 3 * H, device=DEV, dtype=torch.bfloat16)
+    qkv[..., 2 * H:] = 1.0
+    ctx = torch.zeros(Bt, S, H, device=DEV, dtype=torch.bfloat16)
+    lse2 = torch.zeros(Bt, Ah, S, device=DEV)
+    W = L.lib.bqa_attention_keep_words(S)
+    keep_bits = torch.zeros(Bt, Ah, S, W, dtype=torch.int32, device=DEV)
+    L.check(L.lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep_bits.data_ptr(), None, Bt, S,
+                                        Ah, p, 99, 4, st), "attention forward")
+    torch.cuda.synchronize()
+    words = keep_bits.view(Bt, Ah, S, 2, W // 2).to(torch.int64) & 0xFFFFFFFF
+    shifts = torch.arange(32, device=DEV, dtype=torch.int64)
+    per_layout = ((words[..., None] >> shifts) & 1).sum(dim=(-1, -2))        # [B, A, S, 2]: per query / per key
+    n = Bt * Ah * S * S
+    check_rate(int(per_layout[..., 0].sum()), n, "attention keep bits (query-major)")
+    check_rate(int(per_layout[..., 1].sum()), n, "attention keep bits (key-major)")
+    want_ctx = per_layout[..., 0].float() / (S * (1 - p))                      # [B, A, S]
+    got_ctx = ctx.float().view(Bt, S, Ah, 64).permute(0, 2, 1, 3)
+    assert (got_ctx - want_ctx[..., None]).abs().max().item() < 1e-2
+    # LayerNorm backward: dz_masked is dz where kept (scaled), 0 where dropped
+    T, Hh = 4096, 768
+    z, dy = torch.randn(T, Hh, device=DEV).to(torch.bfloat16), torch.randn(T, Hh, device=DEV).to(torch.bfloat16)
+    g = torch.ones(Hh, device=DEV)
+    dz, dzm = torch.empty_like(z), torch.empty_like(z)
+    dg, db, dbias = (torch.zeros(Hh, device=DEV) for _ in range(3))
+    L.check(L.lib.bqa_layernorm_backward(dy.data_ptr(), z.data_ptr(), g.data_ptr(), dz.data_ptr(), dzm.data_ptr(),
+                                         dg.data_ptr(), db.data_ptr(), dbias.data_ptr(), T, Hh, 1e-12, 0.0, 0, p, 6, 99,
+                                         st), "ln bwd")
+    torch.cuda.synchronize()
+    live = dz.float() != 0
+    check_rate(int(((dzm.float() != 0) & live).sum()), int(live.sum()), "layernorm backward mask")
 
 
 def test_decode_bit_exact_against_reference_golden(pkg):

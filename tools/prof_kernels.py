@@ -48,7 +48,7 @@ if "attn" in which:
         L.check(L.lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep_bits.data_ptr(), None, B, S, A, 0.1, 7, 5,
                                             st), "fwd")
         L.check(L.lib.bqa_attention_backward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep_bits.data_ptr(), dctx.data_ptr(),
-                                             dqkv.data_ptr(), dsum.data_ptr(), None, B, S, A, 0.1, 7, 5, st), "bwd")
+                                             dqkv.data_ptr(), dsum.data_ptr(), None, B, S, A, 0.1, 7, 5, None, st), "bwd")
     torch.cuda.synchronize()
 if "rows" in which:
     z, dy = rnd(T, H), rnd(T, H)

@@ -6,6 +6,8 @@ sys.path.insert(0, ROOT)
 import torch
 from __graft_entry__ import load_package
 pkg = load_package()
+from _ab import maybe_swap_library
+maybe_swap_library(pkg)
 L = pkg._lib
 dev = "cuda"
 torch.manual_seed(0)
@@ -30,7 +32,7 @@ def fwd(m, p):
 
 def bwd(m, p):
     L.check(L.lib.bqa_attention_backward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep.data_ptr(), dctx.data_ptr(),
-                                         dqkv.data_ptr(), dsum.data_ptr(), L.ptr(m), B, S, A, p, 7, 5, st), "bwd")
+                                         dqkv.data_ptr(), dsum.data_ptr(), L.ptr(m), B, S, A, p, 7, 5, None, st), "bwd")
 
 
 print("library:", L.LIB_PATH)

@@ -6,6 +6,8 @@ sys.path.insert(0, ROOT)
 import torch
 from __graft_entry__ import load_package
 pkg = load_package()
+from _ab import maybe_swap_library
+maybe_swap_library(pkg)
 L = pkg._lib
 dev = "cuda"
 torch.manual_seed(0)

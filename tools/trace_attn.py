@@ -16,7 +16,7 @@ ctx = torch.zeros(B, S, H, device=dev, dtype=torch.bfloat16)
 lse2 = torch.zeros(B, A, S, device=dev)
 keep = torch.zeros(B, A, S, 12, dtype=torch.int32, device=dev)
 st = torch.cuda.current_stream().cuda_stream
-lib.bqa_attention_backward.argtypes = [vp] * 8 + [ctypes.c_int32] * 3 + [ctypes.c_float, ctypes.c_uint64, ctypes.c_uint32, vp]
+lib.bqa_attention_backward.argtypes = [vp] * 8 + [ctypes.c_int32] * 3 + [ctypes.c_float, ctypes.c_uint64, ctypes.c_uint32, vp, vp]
 dctx = torch.randn(B, S, H, device=dev).to(torch.bfloat16)
 dqkv = torch.zeros(B, S, 3 * H, device=dev, dtype=torch.bfloat16)
 dsum = torch.zeros(B, A, S, device=dev)
@@ -43,7 +43,7 @@ for p in (0.1, 0.0):
     rc = lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep.data_ptr(), None, B, S, A, p, 7, 5, st)
     # backward = dsum kernel, dq kernel, dkv kernel on one stream: the trace holds the LAST kernel (dkv)
     rc = lib.bqa_attention_backward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep.data_ptr(), dctx.data_ptr(),
-                                    dqkv.data_ptr(), dsum.data_ptr(), None, B, S, A, p, 7, 5, st)
+                                    dqkv.data_ptr(), dsum.data_ptr(), None, B, S, A, p, 7, 5, None, st)
     assert rc == 0
     report(f"dkv kernel, dropout {p}", ["start", "ctrl_loads_issued", "kv_landed", None, "S0_ready", "chunk1_start", "chunks_done", "out_ready", "stored", "end"])
 for p in (0.1, 0.0):

@@ -7,7 +7,7 @@ lib = ctypes.CDLL(os.path.join(ROOT, "tools/_trace/libbqa_trace" + (sys.argv[1] 
 vp = ctypes.c_void_p
 lib.bqa_attention_forward.argtypes = [vp, vp, vp, vp, vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_float,
                                       ctypes.c_uint64, ctypes.c_uint32, vp]
-lib.bqa_attention_backward.argtypes = [vp] * 8 + [ctypes.c_int32] * 3 + [ctypes.c_float, ctypes.c_uint64, ctypes.c_uint32, vp]
+lib.bqa_attention_backward.argtypes = [vp] * 8 + [ctypes.c_int32] * 3 + [ctypes.c_float, ctypes.c_uint64, ctypes.c_uint32, vp, vp]
 lib.bqa_attention_keep_words.argtypes = [ctypes.c_int32]
 lib.bqa_trace_read.argtypes = [vp]
 B, S, A = 32, 384, 12
@@ -25,9 +25,9 @@ names = {1: "wait scores", 2: "tmem load", 3: "math", 4: "wait operand buffers",
          7: "tile prologue", 8: "other"}
 for p in (0.1, 0.0):
     for _ in range(2):
-        assert lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep.data_ptr(), None, B, S, A, p, 7, 5, st) == 0
+        assert lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep.data_ptr(), None, B, S, A, p, 7, 5, None, st) == 0
         assert lib.bqa_attention_backward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep.data_ptr(), dctx.data_ptr(),
-                                          dqkv.data_ptr(), dsum.data_ptr(), None, B, S, A, p, 7, 5, st) == 0
+                                          dqkv.data_ptr(), dsum.data_ptr(), None, B, S, A, p, 7, 5, None, st) == 0
     torch.cuda.synchronize()
     buf = np.zeros(4096 * 16, dtype=np.uint64)
     assert lib.bqa_trace_read(buf.ctypes.data) == 0
