@@ -112,9 +112,11 @@ def test_step_matches_oracle(pkg, shape, B, S, p_drop, use_mask):
 
 # Measured on B200 (round 2, dropout off, B = 4, S = 384, BERT-base, perturbed LayerNorm weights and biases), CUDA
 # path (bf16 operands, fp32 accumulation) against the oracle in plain fp32 — i.e. against the arithmetic of the
-# reference's own PyTorch path: see FP32_BOUNDS below; the test asserts them with ~2x head room and writes the
-# measured values to gpurun_out/parity_fp32_base.json when that directory exists.
-FP32_BOUNDS = dict(outputs=5e-2, losses=1e-2, grad_global=6e-2, grad_tensor=0.15)
+# reference's own PyTorch path (profiles/r02_parity_fp32_base.json): outputs 0.9e-3 .. 1.6e-2 norm-wise (the span
+# logits are the worst), the six losses within 6.8e-4 relative, concatenated gradient 9.8e-3, worst single tensor
+# 8.5e-3 (token-type table).  The stated tolerance is ~2x that; the test writes the measured values to
+# gpurun_out/parity_fp32_base.json when that directory exists.
+FP32_BOUNDS = dict(outputs=3e-2, losses=2e-3, grad_global=2e-2, grad_tensor=2.5e-2)
 
 
 def test_step_within_stated_fp32_tolerance_at_bert_base(pkg):
