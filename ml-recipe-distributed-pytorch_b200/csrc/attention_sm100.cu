@@ -40,7 +40,7 @@ constexpr int BW_THREADS = BW_ROW_THREADS + 32;
 constexpr int BW_CTRL_WARP = BW_ROW_THREADS / 32;
 
 struct AttnArgs {
-  int B, S, A, H, nchunk, nchunk64, tmem_cols;
+  int B, S, A, H, nchunk, nchunk64, nchunk96, tmem_cols;
   float scale, scale_log2;
   const uint8_t* key_mask;
   bf16* ctx;
@@ -74,7 +74,19 @@ __device__ unsigned long long g_attn_trace[4096 * 16];
     if (bl < 4096)                                                                                          \
       for (int k_ = 1; k_ < 9; ++k_) g_attn_trace[bl * 16 + k_] = tacc_[k_];                                \
   } while (0)
+// SM id and wall-clock stamps of a CTA's life (slots 10-12): which CTAs were co-resident
+#define ATRACE_WHERE(slot)                                                                                  \
+  do {                                                                                                      \
+    const unsigned bl = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);                     \
+    unsigned smid_;                                                                                         \
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid_));                                                      \
+    if (bl < 4096) {                                                                                        \
+      g_attn_trace[bl * 16 + 10] = smid_;                                                                   \
+      g_attn_trace[bl * 16 + (slot)] = global_timer_ns();                                                   \
+    }                                                                                                       \
+  } while (0)
 #else
+#define ATRACE_WHERE(slot) do {} while (0)
 #define ATRACE(slot) do {} while (0)
 #define ATACC_DECL do {} while (0)
 #define ATACC(k) do {} while (0)
@@ -235,76 +247,86 @@ attn_keep_bits_kernel(uint32_t* __restrict__ keep, int BH, int S, int W, DropKey
 // =========================================================================================
 // forward
 // =========================================================================================
-// Persistent: each CTA walks a contiguous range of (batch, head, query-tile) tiles, so that K and V
-// stay in shared memory across the query tiles of one (batch, head), the next tile's Q (and K) load
-// and its S = Q K^T overlap the current tile's epilogue, and TMEM / barriers are set up once.
-// Barrier phases are derived from the per-CTA tile counter `it`, never from local toggles.
-// KB: whether the additive key bias (padding mask / ragged last chunk) is needed
+// Two CTAs per SM, each: 4 softmax warps (one thread per query row of a 128-query tile), one MMA-issuing warp, one
+// TMA warp.  A CTA walks a contiguous range of (batch, head, 128-query tile) tiles; per tile the keys stream
+// through in chunks of KC = 96 (K and V tiles in a 3-stage TMA ring), online softmax:
+//   S_g = Q K_g^T            tcgen05.mma into one of TWO score buffers in TMEM (96 fp32 columns each)
+//   softmax threads          read the 96 scores of their row, update the running maximum, exponentiate, and
+//                            write P_g as bf16 pairs IN PLACE over the first 48 columns of the same buffer
+//   O += P_g V_g             tcgen05.mma with the A operand (P) read from TMEM, V the MN-major smem operand
+// so scores and probabilities never touch shared memory, and the score MMA of chunk g+1 (other buffer) runs
+// while the threads work on chunk g.  TMEM per CTA: 2 x 96 score columns + 64 output columns = 256.
+// The running maximum is lazy (the output accumulator is rescaled only when the maximum grows by more than
+// 2^8, decided per warp), which keeps the result exact: the final normalisation uses the same maximum.
+// Barrier phases are derived from the per-CTA chunk / tile counters, never from local toggles.
+constexpr int KC = 96;                 // keys per chunk
+constexpr int KCB = KC * 128;          // bytes of one K or V chunk tile (96 rows x 128 B)
+constexpr int FW_SOFT = 128;           // softmax threads
+constexpr int FW_THREADS = FW_SOFT + 64;
+constexpr int FW_MMA_WARP = 4, FW_TMA_WARP = 5;
+constexpr int FW_RING = 3;             // K / V ring depth
+constexpr uint32_t FW_COL_O = 192;     // output accumulator columns [192, 256)
+constexpr float FW_RESCALE_LOG2 = 8.0f;
+
 template <bool KB>
-__global__ void __launch_bounds__(ATT_THREADS, 1)
-attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_ctx,
-                const AttnArgs a) {
+__global__ void __launch_bounds__(FW_THREADS, 2)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_kv96,
+                const __grid_constant__ CUtensorMap tm_ctx, const AttnArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
-  const int N = a.nchunk;
-  uint8_t* sQ = smem;
-  uint8_t* sK = sQ + CH;
-  uint8_t* sV = sK + N * CH;
-  uint8_t* sP = sV + N * CH;  // 2 buffers x (2 * CH)
-  float* kbias = reinterpret_cast<float*>(sP + 4 * CH);
-  float* xmax = kbias + 512;  // [4][128] row statistics exchanged between the four column quarters
-  float* xsum = xmax + 512;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(xsum + 512);
-  uint64_t* bar_q = bars + 0;
-  uint64_t* bar_k = bars + 1;
-  uint64_t* bar_v = bars + 2;
-  uint64_t* bar_s = bars + 3;
-  uint64_t* bar_o = bars + 4;
-  uint64_t* bar_ofree = bars + 5;
-  uint64_t* bar_p = bars + 6;      // [2]
-  uint64_t* bar_pfree = bars + 8;  // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
-  uint32_t* kvalid = reinterpret_cast<uint32_t*>(bars + 16);  // [16] bit k of word w: key 32 w + k is attended
+  uint8_t* sQ = smem;                    // 2 x CH; a finished tile's buffer stages its output tile
+  uint8_t* sK = sQ + 2 * CH;             // FW_RING x KCB
+  uint8_t* sV = sK + FW_RING * KCB;      // FW_RING x KCB
+  float* kbias = reinterpret_cast<float*>(sV + FW_RING * KCB);  // [6 * 96]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(kbias + 6 * KC);
+  uint64_t* q_full = bars + 0;    // [2]
+  uint64_t* q_free = bars + 2;    // [2] last score MMA of the tile done + output store has read the buffer
+  uint64_t* k_full = bars + 4;    // [3]
+  uint64_t* k_free = bars + 7;    // [3]
+  uint64_t* v_full = bars + 10;   // [3]
+  uint64_t* v_free = bars + 13;   // [3]
+  uint64_t* s_full = bars + 16;   // [2]
+  uint64_t* p_full = bars + 18;   // [2]
+  uint64_t* pv_done = bars + 20;  // [2]
+  uint64_t* o_full = bars + 22;
+  uint64_t* o_free = bars + 23;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
+  uint32_t* kvalid = tmem_slot + 2;  // [18] bit k of word w: key 32 w + k is attended
 
-  const int tid = threadIdx.x, warp = tid >> 5;
-  const int S = a.S, Sp = N * 128;
-  const int tiles = a.B * a.A * N;
+  const int tid = threadIdx.x;
+  const int warp = uniform_warp_idx();
+  const int S = a.S, NQ = a.nchunk, NC = a.nchunk96;
+  const int tiles = a.B * a.A * NQ;
   const int t0 = static_cast<int>(static_cast<long long>(blockIdx.x) * tiles / gridDim.x);
   const int t1 = static_cast<int>(static_cast<long long>(blockIdx.x + 1) * tiles / gridDim.x);
-  // O accumulator: beside the scores when they leave 64 columns free, else aliased onto columns [0, 64)
-  const bool alias = Sp > 448;
-  const uint32_t o_col = alias ? 0u : static_cast<uint32_t>(Sp);
-  const int cnt0 = (N + 1) >> 1, cnt1 = N >> 1;  // uses of P buffer 0 / 1 per tile
   if (tid == 0) ATRACE(0);
 
-  if (tid == ROW_THREADS) {
-    tma_prefetch_desc(&tm_qkv);
-    mbar_init(bar_q, 1);
-    mbar_init(bar_k, 1);
-    mbar_init(bar_v, 1);
-    mbar_init(bar_s, 1);
-    mbar_init(bar_o, 1);
-    mbar_init(bar_ofree, ROW_THREADS);
+  if (tid == 0) {
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&bar_p[i], ROW_THREADS);
-      mbar_init(&bar_pfree[i], 1);
+      mbar_init(&q_full[i], 1);
+      mbar_init(&q_free[i], 2);
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_full[i], FW_SOFT);
+      mbar_init(&pv_done[i], 1);
     }
+    for (int i = 0; i < FW_RING; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&k_free[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&v_free[i], 1);
+    }
+    mbar_init(o_full, 1);
+    mbar_init(o_free, FW_SOFT);
     fence_mbar_init();
-    // operand loads need nothing but the barriers: start them before the rest of the prologue
-    tma_prefetch_desc(&tm_ctx);
-    if (t0 < t1) {
-      const int bh = t0 / N, qt = t0 - bh * N, b = bh / a.A, h = bh - b * a.A;
-      mbar_arrive_expect_tx(bar_q, CH);
-      tma_load_3d(sQ, &tm_qkv, h * 64, qt * 128, b, bar_q);
-      mbar_arrive_expect_tx(bar_k, N * CH);
-      for (int c = 0; c < N; ++c) tma_load_3d(sK + c * CH, &tm_qkv, a.H + h * 64, c * 128, b, bar_k);
-      mbar_arrive_expect_tx(bar_v, N * CH);
-      for (int c = 0; c < N; ++c) tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + h * 64, c * 128, b, bar_v);
-    }
   }
-  if (warp == CTRL_WARP) {
-    tmem_alloc(tmem_slot, a.tmem_cols);
+  if (warp == FW_MMA_WARP) {
+    tmem_alloc(tmem_slot, 256);
     tmem_relinquish();
+  }
+  if (tid == FW_TMA_WARP * 32) {
+    tma_prefetch_desc(&tm_qkv);
+    tma_prefetch_desc(&tm_kv96);
+    tma_prefetch_desc(&tm_ctx);
   }
   tc_fence_before();
   __syncthreads();
@@ -312,173 +334,277 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   const uint32_t tmem = *tmem_slot;
   pdl_trigger();  // the next kernel may start its prologue; it waits for this grid before reading
 
-  if (tid == ROW_THREADS) {
-    // ---------------- control thread: TMA + MMA issue ----------------
-    constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
-    constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
-    uint32_t kv_loads = 0;  // K/V loads waited so far
-    int prev_bh = -1;
+  if (warp == FW_TMA_WARP) {
+    // ---------------- TMA producer: Q per tile (double-buffered), K / V chunks through the ring ----------------
+    const bool leader = elect_one();
+    uint32_t g = 0, slot = 0, round = 0;  // chunk counter, g % FW_RING, g / FW_RING
     for (int t = t0, it = 0; t < t1; ++t, ++it) {
-      const int bh = t / N;
-      const bool fresh = bh != prev_bh;
-      prev_bh = bh;
-      const bool has_next = t + 1 < t1;
-      const int nbh = (t + 1) / N, nqt = (t + 1) - nbh * N, nb = nbh / a.A, nh = nbh - nb * a.A;
-      const bool next_fresh = has_next && nbh != bh;
-      mbar_wait(bar_q, it & 1);
-      if (fresh) mbar_wait(bar_k, kv_loads & 1);
-      if (alias && it > 0) mbar_wait(bar_ofree, (it - 1) & 1);
-      tc_fence_after();
-      for (int c = 0; c < N; ++c) mma_k64(tmem + c * 128, smem_u32(sQ), smem_u32(sK + c * CH), idesc_s);
-      umma_commit(bar_s);
-      // Q (and K when the head changes) are free once the score MMAs have completed
-      mbar_wait(bar_s, it & 1);
-      if (has_next) {
-        mbar_arrive_expect_tx(bar_q, CH);
-        tma_load_3d(sQ, &tm_qkv, nh * 64, nqt * 128, nb, bar_q);
-        if (next_fresh) {
-          mbar_arrive_expect_tx(bar_k, N * CH);
-          for (int c = 0; c < N; ++c) tma_load_3d(sK + c * CH, &tm_qkv, a.H + nh * 64, c * 128, nb, bar_k);
+      const int bh = t / NQ, qt = t - bh * NQ, b = bh / a.A, h = bh - b * a.A;
+      const int qb = it & 1;
+      if (it >= 2) mbar_wait(&q_free[qb], ((it >> 1) - 1) & 1);
+      if (leader) {
+        mbar_arrive_expect_tx(&q_full[qb], CH);
+        tma_load_3d(sQ + qb * CH, &tm_qkv, h * 64, qt * 128, b, &q_full[qb]);
+      }
+      __syncwarp();
+      for (int j = 0; j < NC; ++j, ++g) {
+        if (round > 0) mbar_wait(&k_free[slot], (round - 1) & 1);
+        if (leader) {
+          mbar_arrive_expect_tx(&k_full[slot], KCB);
+          tma_load_3d(sK + slot * KCB, &tm_kv96, a.H + h * 64, j * KC, b, &k_full[slot]);
+        }
+        __syncwarp();
+        if (round > 0) mbar_wait(&v_free[slot], (round - 1) & 1);
+        if (leader) {
+          mbar_arrive_expect_tx(&v_full[slot], KCB);
+          tma_load_3d(sV + slot * KCB, &tm_kv96, 2 * a.H + h * 64, j * KC, b, &v_full[slot]);
+        }
+        __syncwarp();
+        if (++slot == FW_RING) {
+          slot = 0;
+          ++round;
         }
       }
-      if (fresh) {
-        mbar_wait(bar_v, kv_loads & 1);
-        ++kv_loads;
+    }
+  } else if (warp == FW_MMA_WARP) {
+    // ---------------- MMA issuer ----------------
+    constexpr uint32_t idesc_s = umma_idesc_bf16(128, KC, 0, 0);
+    constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+    const bool leader = elect_one();
+    // O += P V for chunk gp (the jp-th chunk of this CTA's itp-th tile, ring slot sp of round rp)
+    auto issue_pv = [&](uint32_t gp, int itp, int jp, uint32_t sp, uint32_t rp) {
+      const uint32_t bp = gp & 1u;
+      mbar_wait(&p_full[bp], (gp >> 1) & 1u);
+      mbar_wait(&v_full[sp], rp & 1u);
+      if (jp == 0 && itp > 0) mbar_wait(o_free, (itp - 1) & 1);  // the previous tile's output has been read
+      tc_fence_after();
+      if (leader) {
+        const uint32_t v_addr = smem_u32(sV + sp * KCB);
+#pragma unroll
+        for (int k = 0; k < KC / 16; ++k)
+          umma_bf16_ts(tmem + FW_COL_O, tmem + bp * KC + k * 8, umma_desc_mnmajor(v_addr + k * 2048, KCB), idesc_o,
+                       (jp > 0 || k > 0) ? 1u : 0u);
+        umma_commit(&pv_done[bp]);
+        umma_commit(&v_free[sp]);
+        if (jp == NC - 1) umma_commit(o_full);
       }
-      for (int j = 0; j < N; ++j) {
-        const uint32_t idx = static_cast<uint32_t>(it) * ((j & 1) ? cnt1 : cnt0) + (j >> 1);
-        mbar_wait(&bar_p[j & 1], idx & 1);
+      __syncwarp();
+    };
+    uint32_t g = 0, slot = 0, round = 0;
+    int p_it = 0, p_j = 0;        // tile / chunk position of chunk g - 1
+    uint32_t p_slot = 0, p_round = 0;
+    for (int t = t0, it = 0; t < t1; ++t, ++it) {
+      const int qb = it & 1;
+      for (int j = 0; j < NC; ++j, ++g) {
+        const uint32_t bsel = g & 1u;
+        // a new tile's first score MMA must not delay the previous tile's last P V
+        if (j == 0 && g > 0) issue_pv(g - 1, p_it, p_j, p_slot, p_round);
+        if (j == 0) mbar_wait(&q_full[qb], (it >> 1) & 1);
+        if (g >= 2) mbar_wait(&pv_done[bsel], ((g >> 1) - 1u) & 1u);  // P of chunk g - 2 consumed: buffer free
+        mbar_wait(&k_full[slot], round & 1u);
         tc_fence_after();
-        mma_k128_mn(tmem + o_col, smem_u32(sP + (j & 1) * 2 * CH), smem_u32(sV + j * CH), idesc_o, j > 0);
-        umma_commit(&bar_pfree[j & 1]);
-      }
-      umma_commit(bar_o);
-      if (next_fresh) {
-        mbar_wait(bar_o, it & 1);  // V is still being read by the P V MMAs until then
-        mbar_arrive_expect_tx(bar_v, N * CH);
-        for (int c = 0; c < N; ++c) tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + nh * 64, c * 128, nb, bar_v);
+        if (leader) {
+          const uint32_t q_addr = smem_u32(sQ + qb * CH), k_addr = smem_u32(sK + slot * KCB);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_bf16(tmem + bsel * KC, umma_desc_kmajor(q_addr + k * 32), umma_desc_kmajor(k_addr + k * 32), idesc_s,
+                      k > 0 ? 1u : 0u);
+          umma_commit(&s_full[bsel]);
+          umma_commit(&k_free[slot]);
+          if (j == NC - 1) umma_commit(&q_free[qb]);
+        }
+        __syncwarp();
+        if (j > 0) issue_pv(g - 1, p_it, p_j, p_slot, p_round);
+        p_it = it;
+        p_j = j;
+        p_slot = slot;
+        p_round = round;
+        if (++slot == FW_RING) {
+          slot = 0;
+          ++round;
+        }
       }
     }
-  } else if (tid < ROW_THREADS) {
-    // ---- softmax threads: thread (r, qd) owns columns [32 qd, 32 qd + 32) of every 128-key chunk of row r
-    const int r = tid & 127, qd = tid >> 7;
-    const uint32_t lane_base = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
-    const uint32_t lane_addr = lane_base + qd * 32;
+    if (g > 0) issue_pv(g - 1, p_it, p_j, p_slot, p_round);
+  } else {
+    // ---------------- softmax threads: thread r owns query row r of the tile ----------------
+    const int r = tid;
+    const uint32_t lane_base = tmem + (static_cast<uint32_t>(warp * 32) << 16);
     const float sl2 = a.scale_log2;
+    const bool dropping = a.drop.thresh != 0u;
+    const int keep_words = 8 * NQ;  // per (batch, head, query) row; the first 4 NQ are query-major
     int prev_b = -1;
+    int pending_qb = -1;  // thread 0: output store whose staging buffer has not been released yet
+    uint32_t g = 0;
+    ATACC_DECL;
+    if (tid == 0) ATRACE_WHERE(11);
     for (int t = t0, it = 0; t < t1; ++t, ++it) {
-      const int bh = t / N, qt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
+      const int bh = t / NQ, qt = t - bh * NQ, b = bh / a.A, h = bh - b * a.A;
       const int q = qt * 128 + r;
+      const int qb = it & 1;
       if (KB && b != prev_b) {
-        // every thread is past the previous tile's second pass (it has been through the xsum barrier)
-        fill_key_bias(kbias, kvalid, a.key_mask, b, S, Sp, tid);
-        named_bar_sync(1, ROW_THREADS);
+        named_bar_sync(1, FW_SOFT);  // nobody still reads the previous batch row's bias
+        for (int base = 0; base < NC * KC; base += FW_SOFT) {
+          const int key = base + tid;
+          const bool ok = key < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + key] != 0);
+          if (key < NC * KC) kbias[key] = ok ? 0.0f : -INFINITY;
+          const uint32_t w = __ballot_sync(0xffffffffu, ok);
+          if ((tid & 31) == 0 && key < NC * KC) kvalid[key >> 5] = w;
+        }
+        named_bar_sync(1, FW_SOFT);
         prev_b = b;
       }
       const uint32_t* keep_row =
-          a.keep + ((static_cast<size_t>(b) * a.A + h) * S + (q < S ? q : 0)) * (8 * N) + qd;
-      uint32_t kw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-      if (a.drop.thresh != 0u) {
+          a.keep + ((static_cast<size_t>(b) * a.A + h) * S + (q < S ? q : 0)) * keep_words;
+      float m_run = -INFINITY, l = 0.0f;
+      // keep bits of the row over the keys of one chunk (3 words), fetched one chunk ahead of their use
+      auto fetch_keep = [&](int j, uint32_t (&w)[3]) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (j < N) kw[j] = __ldg(keep_row + j * 4);  // written by attn_keep_bits_kernel
-      }
-      mbar_wait(bar_s, it & 1);
-      if (tid == 0) ATRACE(4);
-      tc_fence_after();
-      // 32-key groups without a masked key (all of them unless KB) take the path without the bias
-      float mx = -INFINITY, mraw = -INFINITY;
-      for (int j = 0; j < N; ++j) {
-        uint32_t v[32];
-        tmem_ld_32x32(lane_addr + j * 128, v);
+        for (int k = 0; k < 3; ++k)
+          w[k] = (dropping && j < NC && 3 * j + k < 4 * NQ) ? ldg_issue_u32(keep_row + 3 * j + k) : 0xffffffffu;
+      };
+      uint32_t kw_next[3];
+      fetch_keep(0, kw_next);
+      for (int j = 0; j < NC; ++j, ++g) {
+        const uint32_t bsel = g & 1u;
+        const uint32_t s_addr = lane_base + bsel * KC;
+        const uint32_t kw[3] = {kw_next[0], kw_next[1], kw_next[2]};
+        fetch_keep(j + 1, kw_next);
+        ATACC(8);
+        mbar_wait(&s_full[bsel], (g >> 1) & 1u);
+        ATACC(1);
+        tc_fence_after();
+        uint32_t v[3][32];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) tmem_ld_32x32(s_addr + k * 32, v[k]);
         tmem_wait_ld();
-        if (KB && kvalid[j * 4 + qd] != 0xffffffffu) {
-          const float* kb = kbias + j * 128 + qd * 32;
+        // chunk maximum of the scaled (and, where a key is masked, biased) scores
+        float cmax = -INFINITY;
 #pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaf(__uint_as_float(v[i]), sl2, kb[i]));
-        } else {
+        for (int k = 0; k < 3; ++k) {
+          if (KB && kvalid[3 * j + k] != 0xffffffffu) {
+            const float* kb = kbias + j * KC + k * 32;
 #pragma unroll
-          for (int i = 0; i < 32; ++i) mraw = fmaxf(mraw, __uint_as_float(v[i]));
+            for (int i = 0; i < 32; ++i) cmax = fmaxf(cmax, fmaf(__uint_as_float(v[k][i]), sl2, kb[i]));
+          } else {
+            float raw = -INFINITY;
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) raw = fmax3(raw, __uint_as_float(v[k][i]), __uint_as_float(v[k][i + 1]));
+            cmax = fmaxf(cmax, raw * sl2);
+          }
+        }
+        ATACC(2);
+        const float m_new = fmaxf(m_run, cmax);
+        const bool grow = m_new > m_run + FW_RESCALE_LOG2;  // also true for the first finite maximum
+        if (j == 0) {
+          m_run = m_new;
+        } else if (__any_sync(0xffffffffu, grow)) {
+          // rescale the running sum and the output accumulator (whole warp: TMEM accesses are warp-wide)
+          const float alpha = grow ? fast_exp2(m_run - m_new) : 1.0f;
+          if (grow) m_run = m_new;
+          l *= alpha;
+          mbar_wait(&pv_done[(g - 1) & 1u], ((g - 1) >> 1) & 1u);  // P V of the previous chunk has landed
+          tc_fence_after();
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            uint32_t o[32];
+            tmem_ld_32x32(lane_base + FW_COL_O + c * 32, o);
+            tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st_32x32(lane_base + FW_COL_O + c * 32, o);
+          }
+          tmem_wait_st();
+        }
+        ATACC(3);
+        const float m_use = m_run == -INFINITY ? 0.0f : m_run;
+        // P is stored unscaled; the dropout scale 1 / (1 - p) is applied with the final 1 / rowsum
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const uint32_t bits = kw[k];
+          uint32_t pk[16];
+          auto piece = [&](auto biased) {
+            const float* kb = kbias + j * KC + k * 32;
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              const float off0 = decltype(biased)::value ? kb[i] - m_use : -m_use;
+              const float off1 = decltype(biased)::value ? kb[i + 1] - m_use : -m_use;
+              const float p0 = fast_exp2(fmaf(__uint_as_float(v[k][i]), sl2, off0));
+              const float p1 = fast_exp2(fmaf(__uint_as_float(v[k][i + 1]), sl2, off1));
+              l += p0 + p1;
+              pk[i >> 1] = pack_bf16x2(((bits >> i) & 1u) ? p0 : 0.0f, ((bits >> (i + 1)) & 1u) ? p1 : 0.0f);
+            }
+          };
+          if (KB && kvalid[3 * j + k] != 0xffffffffu) piece(std::true_type{}); else piece(std::false_type{});
+          tmem_st_32x16(s_addr + k * 16, pk);
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        mbar_arrive(&p_full[bsel]);
+        ATACC(4);
+        if (tid == 0 && pending_qb >= 0) {
+          // the previous tile's output store has long finished reading its staging buffer: release it
+          tma_wait_group_read<0>();
+          mbar_arrive(&q_free[pending_qb]);
+          pending_qb = -1;
         }
       }
-      mx = fmaxf(mx, mraw * sl2);
-      xmax[qd * 128 + r] = mx;
-      named_bar_sync(1, ROW_THREADS);
-      mx = fmaxf(fmaxf(xmax[r], xmax[128 + r]), fmaxf(xmax[256 + r], xmax[384 + r]));
-      if (mx == -INFINITY) mx = 0.0f;
-      if (tid == 0) ATRACE(5);
-      float l = 0.0f;
-      for (int j = 0; j < N; ++j) {
-        uint8_t* tile = sP + (j & 1) * 2 * CH;
-        uint32_t v[32];
-        tmem_ld_32x32(lane_addr + j * 128, v);
-        tmem_wait_ld();
-        const int key0 = j * 128 + qd * 32;
-        const uint32_t bits = kw[j & 3];
-        const uint32_t idx = static_cast<uint32_t>(it) * ((j & 1) ? cnt1 : cnt0) + (j >> 1);
-        if (idx > 0) mbar_wait(&bar_pfree[j & 1], (idx - 1) & 1);
-        // P is stored unscaled; the dropout scale 1 / (1 - p) is applied with the final 1 / rowsum
-        auto chunk = [&](auto biased) {
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            float p[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const float off = decltype(biased)::value ? kbias[key0 + g * 8 + e] - mx : -mx;
-              const float pv = fast_exp2(fmaf(__uint_as_float(v[g * 8 + e]), sl2, off));
-              l += pv;
-              p[e] = ((bits >> (g * 8 + e)) & 1u) ? pv : 0.0f;
-            }
-            st_tile16(tile, r, qd * 4 + g, p);
-          }
-        };
-        if (KB && kvalid[j * 4 + qd] != 0xffffffffu) chunk(std::true_type{}); else chunk(std::false_type{});
-        fence_proxy_async_smem();
-        tc_fence_before();
-        mbar_arrive(&bar_p[j & 1]);
-      }
-      if (tid == 0) ATRACE(6);
-      xsum[qd * 128 + r] = l;
-      named_bar_sync(1, ROW_THREADS);
-      l = (xsum[r] + xsum[128 + r]) + (xsum[256 + r] + xsum[384 + r]);
-      mbar_wait(bar_o, it & 1);
-      if (tid == 0) ATRACE(7);
+      // ---- tile epilogue: O * (dropout scale / rowsum) -> bf16 -> swizzled smem (this tile's Q buffer: every
+      // MMA of the tile has completed) -> one TMA store, which also clips the rows beyond S
+      ATACC(5);
+      mbar_wait(o_full, it & 1);
+      ATACC(6);
       tc_fence_after();
       const float inv = l > 0.0f ? a.drop.scale / l : 0.0f;
-      {
-        // O tile -> swizzled smem (P buffer 0 is free: every MMA of this tile has completed) -> one TMA
-        // store, which also clips the rows beyond S.  The next tile writes P only after its row-max
-        // barrier, which thread 0 joins after the store has finished reading.
-        uint32_t v[16];
-        tmem_ld_32x16(lane_base + o_col + qd * 16, v);
-        tmem_wait_ld();
-        tc_fence_before();
-        mbar_arrive(bar_ofree);
-        float f[16];
+      uint8_t* stage = sQ + qb * CH;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]) * inv;
-        st_out16(sP, r, qd, f);
-        fence_proxy_async_smem();
-        named_bar_sync(1, ROW_THREADS);
-        if (tid == 0) {
-          tma_store_3d(&tm_ctx, sP, h * 64, qt * 128, b);
-          tma_commit_group();
-          tma_wait_group_read<0>();
+      for (int c = 0; c < 2; ++c) {
+        uint32_t o[32];
+        tmem_ld_32x32(lane_base + FW_COL_O + c * 32, o);
+        tmem_wait_ld();
+        if (c == 1) {
+          tc_fence_before();
+          mbar_arrive(o_free);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          uint4 w;
+          w.x = pack_bf16x2(__uint_as_float(o[8 * u]) * inv, __uint_as_float(o[8 * u + 1]) * inv);
+          w.y = pack_bf16x2(__uint_as_float(o[8 * u + 2]) * inv, __uint_as_float(o[8 * u + 3]) * inv);
+          w.z = pack_bf16x2(__uint_as_float(o[8 * u + 4]) * inv, __uint_as_float(o[8 * u + 5]) * inv);
+          w.w = pack_bf16x2(__uint_as_float(o[8 * u + 6]) * inv, __uint_as_float(o[8 * u + 7]) * inv);
+          *reinterpret_cast<uint4*>(stage + r * 128 + (((c * 4 + u) ^ (r & 7)) << 4)) = w;
         }
       }
+      fence_proxy_async_smem();
+      named_bar_sync(2, FW_SOFT);
+      if (tid == 0) {
+        tma_store_3d(&tm_ctx, stage, h * 64, qt * 128, b);
+        tma_commit_group();
+        pending_qb = qb;
+      }
       // a row whose keys are all masked has l == 0: store +inf so that the backward recomputes P = 0
-      if (q < S && qd == 0)
-        a.lse2[(static_cast<size_t>(b) * a.A + h) * S + q] = l > 0.0f ? mx + log2f(l) : INFINITY;
-      if (tid == 0) ATRACE(8);
+      if (q < S) a.lse2[(static_cast<size_t>(b) * a.A + h) * S + q] = l > 0.0f ? m_run + log2f(l) : INFINITY;
+      ATACC(7);
     }
-    if (tid == 0) tma_wait_group<0>();
+    if (tid == 0) {
+      ATACC_WRITE();
+      ATRACE_WHERE(12);
+    }
+    if (tid == 0) {
+      if (pending_qb >= 0) {
+        tma_wait_group_read<0>();
+        mbar_arrive(&q_free[pending_qb]);
+      }
+      tma_wait_group<0>();
+    }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == CTRL_WARP) {
+  if (warp == FW_MMA_WARP) {
     tc_fence_after();
-    tmem_dealloc(tmem, a.tmem_cols);
+    tmem_dealloc(tmem, 256);
   }
   if (tid == 0) ATRACE(9);
 }
@@ -515,181 +641,221 @@ attn_dsum_kernel(const bf16* __restrict__ ctx, const bf16* __restrict__ dctx, fl
 // =========================================================================================
 // backward, dQ
 // =========================================================================================
-// Persistent like the forward: contiguous (batch, head, query-tile) ranges per CTA, K and V kept in
-// shared memory across the query tiles of a (batch, head), the next tile's Q / dO loaded as soon as the
-// last score MMAs of the current tile have completed.  Chunk-level barriers are indexed by the running
-// chunk counter g = it * N + j.
+// Same organisation as the forward: two CTAs per SM, each with 8 row warps (thread (r, hq) = query row r of a
+// 128-query tile, half hq of the chunk's key columns), one MMA-issuing warp and one TMA warp; contiguous
+// (batch, head, query-tile) ranges per CTA.  Keys stream through in chunks of 64 (K ring of 3 because the dQ
+// MMA reads K again, V ring of 2); Q / dO tiles are double-buffered across tiles.  Per chunk g:
+//   S = Q K_g^T, dP = dO V_g^T     tcgen05.mma into TMEM (64 + 64 fp32 columns, single-buffered: the row threads
+//                                  pull them into registers and hand the columns back at once)
+//   dS = P (keep dP c - D scale)   in registers; written as bf16 pairs into 32 further TMEM columns
+//   dQ += dS K_g                   tcgen05.mma with the A operand (dS) read from TMEM, K the MN-major operand
+// The score MMAs of chunk g + 1 are issued before the dQ MMA of chunk g is waited for.
+constexpr int DQ_ROW = 256;
+constexpr int DQ_THREADS = DQ_ROW + 64;
+constexpr int DQ_MMA_WARP = 8, DQ_TMA_WARP = 9;
+constexpr int DQ_KRING = 3, DQ_VRING = 2;
+constexpr uint32_t DQ_COL_S = 0, DQ_COL_DP = 64, DQ_COL_DS = 128, DQ_COL_DQ = 192;
+
 template <bool KB>
-__global__ void __launch_bounds__(ATT_THREADS, 1)
-attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_dctx,
-                   const __grid_constant__ CUtensorMap tm_dqkv, const AttnArgs a) {
+__global__ void __launch_bounds__(DQ_THREADS, 2)
+attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_kv64,
+                   const __grid_constant__ CUtensorMap tm_dctx, const __grid_constant__ CUtensorMap tm_dqkv,
+                   const AttnArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
-  const int N = a.nchunk;
-  uint8_t* sQ = smem;
-  uint8_t* sdO = sQ + CH;
-  uint8_t* sOut = sdO + CH;  // dQ tile staged for the TMA store
-  uint8_t* sK = sOut + CH;
-  uint8_t* sV = sK + N * CH;
-  uint8_t* sdS = sV + N * CH;  // 2 * CH
-  float* kbias = reinterpret_cast<float*>(sdS + 2 * CH);
-  float* s_red = kbias + 512;  // [8][64] partial column sums of the drained tile
+  uint8_t* sQ = smem;                      // 2 x CH; a finished tile's buffer stages its dQ tile
+  uint8_t* sdO = sQ + 2 * CH;              // 2 x CH
+  uint8_t* sK = sdO + 2 * CH;              // DQ_KRING x HC
+  uint8_t* sV = sK + DQ_KRING * HC;        // DQ_VRING x HC
+  float* kbias = reinterpret_cast<float*>(sV + DQ_VRING * HC);  // [512]
+  float* s_red = kbias + 512;              // [8][64] partial column sums of the drained tile
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_red + 512);
-  uint64_t* bar_qo = bars + 0;
-  uint64_t* bar_kv = bars + 1;
-  uint64_t* bar_s = bars + 2;
-  uint64_t* bar_sfree = bars + 3;
-  uint64_t* bar_ds = bars + 4;
-  uint64_t* bar_dsfree = bars + 5;
-  uint64_t* bar_dq = bars + 6;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 7);
-  uint32_t* kvalid = reinterpret_cast<uint32_t*>(bars + 16);  // [16] bit k of word w: key 32 w + k is attended
+  uint64_t* qdo_full = bars + 0;   // [2]
+  uint64_t* qdo_free = bars + 2;   // [2] last score MMAs of the tile done + dQ store has read the staging buffer
+  uint64_t* k_full = bars + 4;     // [3]
+  uint64_t* k_free = bars + 7;     // [3]
+  uint64_t* v_full = bars + 10;    // [2]
+  uint64_t* v_free = bars + 12;    // [2]
+  uint64_t* s_full = bars + 14;
+  uint64_t* s_free = bars + 15;
+  uint64_t* ds_full = bars + 16;
+  uint64_t* dq_done = bars + 17;   // dQ MMA of a chunk complete: dS columns free
+  uint64_t* dq_full = bars + 18;   // tile's accumulator complete
+  uint64_t* dq_free = bars + 19;   // accumulator drained
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
+  uint32_t* kvalid = tmem_slot + 2;  // [16]
 
-  const int tid = threadIdx.x, warp = tid >> 5;
-  const int S = a.S, Sp = N * 128;
-  const int tiles = a.B * a.A * N;
+  const int tid = threadIdx.x;
+  const int warp = uniform_warp_idx();
+  const int S = a.S, NQ = a.nchunk, NC = a.nchunk64;
+  const int tiles = a.B * a.A * NQ;
   const int t0 = static_cast<int>(static_cast<long long>(blockIdx.x) * tiles / gridDim.x);
   const int t1 = static_cast<int>(static_cast<long long>(blockIdx.x + 1) * tiles / gridDim.x);
   if (tid == 0) ATRACE(0);
 
-  if (tid == ROW_THREADS) {
-    tma_prefetch_desc(&tm_qkv);
-    tma_prefetch_desc(&tm_dctx);
-    mbar_init(bar_qo, 1);
-    mbar_init(bar_kv, 1);
-    mbar_init(bar_s, 1);
-    mbar_init(bar_sfree, ROW_THREADS);
-    mbar_init(bar_ds, ROW_THREADS);
-    mbar_init(bar_dsfree, 1);
-    mbar_init(bar_dq, 1);
-    fence_mbar_init();
-    tma_prefetch_desc(&tm_dqkv);
-    if (t0 < t1) {
-      const int bh = t0 / N, qt = t0 - bh * N, b = bh / a.A, h = bh - b * a.A;
-      mbar_arrive_expect_tx(bar_qo, 2 * CH);
-      tma_load_3d(sQ, &tm_qkv, h * 64, qt * 128, b, bar_qo);
-      tma_load_3d(sdO, &tm_dctx, h * 64, qt * 128, b, bar_qo);
-      mbar_arrive_expect_tx(bar_kv, 2 * N * CH);
-      for (int c = 0; c < N; ++c) {
-        tma_load_3d(sK + c * CH, &tm_qkv, a.H + h * 64, c * 128, b, bar_kv);
-        tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + h * 64, c * 128, b, bar_kv);
-      }
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&qdo_full[i], 1);
+      mbar_init(&qdo_free[i], 2);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&v_free[i], 1);
     }
+    for (int i = 0; i < DQ_KRING; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&k_free[i], 1);
+    }
+    mbar_init(s_full, 1);
+    mbar_init(s_free, DQ_ROW);
+    mbar_init(ds_full, DQ_ROW);
+    mbar_init(dq_done, 1);
+    mbar_init(dq_full, 1);
+    mbar_init(dq_free, DQ_ROW);
+    fence_mbar_init();
   }
-  if (warp == CTRL_WARP) {
-    tmem_alloc(tmem_slot, 512);
+  if (warp == DQ_MMA_WARP) {
+    tmem_alloc(tmem_slot, 256);
     tmem_relinquish();
+  }
+  if (tid == DQ_TMA_WARP * 32) {
+    tma_prefetch_desc(&tm_qkv);
+    tma_prefetch_desc(&tm_kv64);
+    tma_prefetch_desc(&tm_dctx);
+    tma_prefetch_desc(&tm_dqkv);
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   pdl_trigger();  // the next kernel may start its prologue; it waits for this grid before reading
-  constexpr uint32_t COL_S = 0, COL_DP = 128, COL_DQ = 256;
 
-  if (tid == ROW_THREADS) {
-    constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
-    constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
-    uint32_t kv_loads = 0;
-    int prev_bh = -1;
+  if (warp == DQ_TMA_WARP) {
+    // ---------------- TMA producer ----------------
+    const bool leader = elect_one();
+    uint32_t ks = 0, kr = 0, vs = 0, vr = 0;  // ring slots and rounds
     for (int t = t0, it = 0; t < t1; ++t, ++it) {
-      const int bh = t / N;
-      const bool fresh = bh != prev_bh;
-      prev_bh = bh;
-      const bool has_next = t + 1 < t1;
-      const int nbh = (t + 1) / N, nqt = (t + 1) - nbh * N, nb = nbh / a.A, nh = nbh - nb * a.A;
-      const bool next_fresh = has_next && nbh != bh;
-      const uint32_t g0 = static_cast<uint32_t>(it) * N;
-      mbar_wait(bar_qo, it & 1);
-      if (fresh) {
-        mbar_wait(bar_kv, kv_loads & 1);
-        ++kv_loads;
+      const int bh = t / NQ, qt = t - bh * NQ, b = bh / a.A, h = bh - b * a.A;
+      const int qb = it & 1;
+      if (it >= 2) mbar_wait(&qdo_free[qb], ((it >> 1) - 1) & 1);
+      if (leader) {
+        mbar_arrive_expect_tx(&qdo_full[qb], 2 * CH);
+        tma_load_3d(sQ + qb * CH, &tm_qkv, h * 64, qt * 128, b, &qdo_full[qb]);
+        tma_load_3d(sdO + qb * CH, &tm_dctx, h * 64, qt * 128, b, &qdo_full[qb]);
       }
-      if (it > 0) mbar_wait(bar_sfree, (g0 - 1) & 1);  // previous tile's last scores are in registers
-      tc_fence_after();
-      mma_k64(tmem + COL_S, smem_u32(sQ), smem_u32(sK), idesc_s);
-      mma_k64(tmem + COL_DP, smem_u32(sdO), smem_u32(sV), idesc_s);
-      umma_commit(bar_s);
-      for (int j = 0; j < N; ++j) {
-        const uint32_t g = g0 + j;
-        if (j + 1 < N) {
-          mbar_wait(bar_sfree, g & 1);
-          tc_fence_after();
-          mma_k64(tmem + COL_S, smem_u32(sQ), smem_u32(sK + (j + 1) * CH), idesc_s);
-          mma_k64(tmem + COL_DP, smem_u32(sdO), smem_u32(sV + (j + 1) * CH), idesc_s);
-          umma_commit(bar_s);
-        } else if (has_next) {
-          // the tile's last score MMAs have completed: Q and dO can be replaced
-          mbar_wait(bar_s, g & 1);
-          mbar_arrive_expect_tx(bar_qo, 2 * CH);
-          tma_load_3d(sQ, &tm_qkv, nh * 64, nqt * 128, nb, bar_qo);
-          tma_load_3d(sdO, &tm_dctx, nh * 64, nqt * 128, nb, bar_qo);
+      __syncwarp();
+      for (int j = 0; j < NC; ++j) {
+        if (kr > 0) mbar_wait(&k_free[ks], (kr - 1) & 1);
+        if (leader) {
+          mbar_arrive_expect_tx(&k_full[ks], HC);
+          tma_load_3d(sK + ks * HC, &tm_kv64, a.H + h * 64, j * 64, b, &k_full[ks]);
         }
-        mbar_wait(bar_ds, g & 1);
-        tc_fence_after();
-        mma_k128_mn(tmem + COL_DQ + (it & 1) * 64, smem_u32(sdS), smem_u32(sK + j * CH), idesc_o, j > 0);
-        umma_commit(bar_dsfree);
-      }
-      umma_commit(bar_dq);
-      if (next_fresh) {
-        mbar_wait(bar_dq, it & 1);  // K is read by the dQ MMAs until then
-        mbar_arrive_expect_tx(bar_kv, 2 * N * CH);
-        for (int c = 0; c < N; ++c) {
-          tma_load_3d(sK + c * CH, &tm_qkv, a.H + nh * 64, c * 128, nb, bar_kv);
-          tma_load_3d(sV + c * CH, &tm_qkv, 2 * a.H + nh * 64, c * 128, nb, bar_kv);
+        __syncwarp();
+        if (vr > 0) mbar_wait(&v_free[vs], (vr - 1) & 1);
+        if (leader) {
+          mbar_arrive_expect_tx(&v_full[vs], HC);
+          tma_load_3d(sV + vs * HC, &tm_kv64, 2 * a.H + h * 64, j * 64, b, &v_full[vs]);
+        }
+        __syncwarp();
+        if (++ks == DQ_KRING) {
+          ks = 0;
+          ++kr;
+        }
+        if (++vs == DQ_VRING) {
+          vs = 0;
+          ++vr;
         }
       }
     }
-  } else if (tid < ROW_THREADS) {
-    const int r = tid & 127, qd = tid >> 7;
+  } else if (warp == DQ_MMA_WARP) {
+    // ---------------- MMA issuer ----------------
+    constexpr uint32_t idesc_s = umma_idesc_bf16(128, 64, 0, 0);
+    constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+    const bool leader = elect_one();
+    // dQ += dS K for chunk gp (the jp-th chunk of tile itp, K ring slot sp of round rp)
+    auto issue_dq = [&](uint32_t gp, int itp, int jp, uint32_t sp) {
+      mbar_wait(ds_full, gp & 1u);
+      if (jp == 0 && itp > 0) mbar_wait(dq_free, (itp - 1) & 1);  // the previous tile's accumulator has been drained
+      tc_fence_after();
+      if (leader) {
+        const uint32_t k_addr = smem_u32(sK + sp * HC);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          umma_bf16_ts(tmem + DQ_COL_DQ, tmem + DQ_COL_DS + k * 8, umma_desc_mnmajor(k_addr + k * 2048, HC), idesc_o,
+                       (jp > 0 || k > 0) ? 1u : 0u);
+        umma_commit(dq_done);
+        umma_commit(&k_free[sp]);
+        if (jp == NC - 1) umma_commit(dq_full);
+      }
+      __syncwarp();
+    };
+    uint32_t g = 0, ks = 0, kr = 0, vs = 0, vr = 0;
+    int p_it = 0, p_j = 0;
+    uint32_t p_ks = 0;
+    for (int t = t0, it = 0; t < t1; ++t, ++it) {
+      const int qb = it & 1;
+      for (int j = 0; j < NC; ++j, ++g) {
+        // a new tile's first score MMAs must not delay the previous tile's last dQ MMA
+        if (j == 0 && g > 0) issue_dq(g - 1, p_it, p_j, p_ks);
+        if (j == 0) mbar_wait(&qdo_full[qb], (it >> 1) & 1);
+        mbar_wait(&k_full[ks], kr & 1u);
+        mbar_wait(&v_full[vs], vr & 1u);
+        if (g > 0) mbar_wait(s_free, (g - 1) & 1u);  // the previous chunk's scores are in registers
+        tc_fence_after();
+        if (leader) {
+          const uint32_t q_addr = smem_u32(sQ + qb * CH), do_addr = smem_u32(sdO + qb * CH);
+          const uint32_t k_addr = smem_u32(sK + ks * HC), v_addr = smem_u32(sV + vs * HC);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_bf16(tmem + DQ_COL_S, umma_desc_kmajor(q_addr + k * 32), umma_desc_kmajor(k_addr + k * 32), idesc_s,
+                      k > 0 ? 1u : 0u);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_bf16(tmem + DQ_COL_DP, umma_desc_kmajor(do_addr + k * 32), umma_desc_kmajor(v_addr + k * 32), idesc_s,
+                      k > 0 ? 1u : 0u);
+          umma_commit(s_full);
+          umma_commit(&v_free[vs]);
+          if (j == NC - 1) umma_commit(&qdo_free[qb]);
+        }
+        __syncwarp();
+        if (j > 0) issue_dq(g - 1, p_it, p_j, p_ks);
+        p_it = it;
+        p_j = j;
+        p_ks = ks;
+        if (++ks == DQ_KRING) {
+          ks = 0;
+          ++kr;
+        }
+        if (++vs == DQ_VRING) {
+          vs = 0;
+          ++vr;
+        }
+      }
+    }
+    if (g > 0) issue_dq(g - 1, p_it, p_j, p_ks);
+  } else {
+    // ---------------- row threads ----------------
+    const int r = tid & 127, hq = tid >> 7;
     const uint32_t lane_base = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     const float sl2 = a.scale_log2;
     const bool dropping = a.drop.thresh != 0u;
-    // dQ of this CTA's tile `it` (accumulator buffer it & 1) -> bf16 -> swizzled smem -> TMA store
-    auto drain = [&](int it) {
-      const int t = t0 + it;
-      const int bh = t / N, qt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
-      mbar_wait(bar_dq, it & 1);
-      tc_fence_after();
-      uint32_t v[16];
-      tmem_ld_32x16(lane_base + COL_DQ + (it & 1) * 64 + qd * 16, v);
-      tmem_wait_ld();
-      tc_fence_before();
-      float f[16];
-#pragma unroll
-      for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-      // the previous store must have finished reading the staging buffer
-      if (tid == 0) tma_wait_group_read<0>();
-      named_bar_sync(1, ROW_THREADS);
-      st_out16(sOut, r, qd, f);
-      fence_proxy_async_smem();
-      named_bar_sync(1, ROW_THREADS);
-      if (tid == 0) {
-        tma_store_3d(&tm_dqkv, sOut, h * 64, qt * 128, b);  // Q slab of dqkv; rows beyond S are clipped
-        tma_commit_group();
-      }
-      if (a.dbias != nullptr) {
-        // gradient of the query bias: column sums of the staged tile (rows beyond S are exact zeros),
-        // 8 row groups -> shared memory -> 64 atomics per tile
-        s_red[(tid >> 6) * 64 + (tid & 63)] = staged_colsum(sOut, (tid >> 6) * 16, 16, tid & 63);
-        named_bar_sync(1, ROW_THREADS);
-        if (tid < 64) {
-          float sum = 0.0f;
-#pragma unroll
-          for (int g8 = 0; g8 < 8; ++g8) sum += s_red[g8 * 64 + tid];
-          atomicAdd(a.dbias + h * 64 + tid, sum);
-        }
-      }
-    };
+    const float c1 = a.drop.scale * a.scale;
+    const int keep_words = 8 * NQ;
     int prev_b = -1;
+    int pending_qb = -1;  // thread 0: dQ store whose staging buffer has not been released yet
+    uint32_t g = 0;
     for (int t = t0, it = 0; t < t1; ++t, ++it) {
-      const int bh = t / N, qt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
+      const int bh = t / NQ, qt = t - bh * NQ, b = bh / a.A, h = bh - b * a.A;
       const int q = qt * 128 + r;
-      const uint32_t g0 = static_cast<uint32_t>(it) * N;
+      const int qb = it & 1;
       if (KB && b != prev_b) {
-        named_bar_sync(1, ROW_THREADS);  // nobody still reads the previous batch row's bias
-        fill_key_bias(kbias, kvalid, a.key_mask, b, S, Sp, tid);
-        named_bar_sync(1, ROW_THREADS);
+        named_bar_sync(1, DQ_ROW);  // nobody still reads the previous batch row's bias
+        for (int base = 0; base < NC * 64; base += DQ_ROW) {
+          const int key = base + tid;
+          const bool ok = key < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + key] != 0);
+          if (key < NC * 64) kbias[key] = ok ? 0.0f : -INFINITY;
+          const uint32_t w = __ballot_sync(0xffffffffu, ok);
+          if ((tid & 31) == 0 && key < NC * 64) kvalid[key >> 5] = w;
+        }
+        named_bar_sync(1, DQ_ROW);
         prev_b = b;
       }
       const bool q_ok = q < S;
@@ -697,67 +863,107 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
       // ds = p * (keep ? dp : 0) * c1 - p * D * scale with p = exp2(s * sl2 - lse)
       const float nlse = q_ok ? -a.lse2[stat] : -INFINITY;
       const float nds = q_ok ? -a.dsum[stat] * a.scale : 0.0f;
-      const float c1 = a.drop.scale * a.scale;
-      uint32_t kw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-      if (dropping) {
-        const uint32_t* keep_row = a.keep + stat * (8 * N) + qd;
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (j < N) kw[j] = __ldg(keep_row + j * 4);
-      }
-      for (int j = 0; j < N; ++j) {
-        const uint32_t g = g0 + j;
-        mbar_wait(bar_s, g & 1);
-        if (tid == 0 && j == 0) ATRACE(4);
+      const uint32_t* keep_row = a.keep + stat * keep_words + hq;
+      auto fetch_keep = [&](int j) -> uint32_t {
+        return (dropping && j < NC && 2 * j + hq < 4 * NQ) ? ldg_issue_u32(keep_row + 2 * j) : 0xffffffffu;
+      };
+      uint32_t kw_next = fetch_keep(0);
+      for (int j = 0; j < NC; ++j, ++g) {
+        const uint32_t bits = kw_next;
+        kw_next = fetch_keep(j + 1);
+        mbar_wait(s_full, g & 1u);
         tc_fence_after();
         uint32_t vs[32], vd[32];
-        tmem_ld_32x32(lane_base + COL_S + qd * 32, vs);
-        tmem_ld_32x32(lane_base + COL_DP + qd * 32, vd);
+        tmem_ld_32x32(lane_base + DQ_COL_S + hq * 32, vs);
+        tmem_ld_32x32(lane_base + DQ_COL_DP + hq * 32, vd);
         tmem_wait_ld();
         tc_fence_before();
-        mbar_arrive(bar_sfree);
-        const int key0 = j * 128 + qd * 32;
-        const uint32_t bits = kw[j & 3];
-        uint4 pk[4];
+        mbar_arrive(s_free);
+        const int key0 = j * 64 + hq * 32;
+        uint32_t pk[16];
         auto chunk = [&](auto biased) {
 #pragma unroll
-          for (int gq = 0; gq < 4; ++gq) {
-            float ds[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const float off = decltype(biased)::value ? kbias[key0 + gq * 8 + e] + nlse : nlse;
-              const float p = fast_exp2(fmaf(__uint_as_float(vs[gq * 8 + e]), sl2, off));
-              const float dp = ((bits >> (gq * 8 + e)) & 1u) ? __uint_as_float(vd[gq * 8 + e]) : 0.0f;
-              ds[e] = p * fmaf(dp, c1, nds);
-            }
-            pk[gq] = make_uint4(pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]), pack_bf16x2(ds[4], ds[5]),
-                                pack_bf16x2(ds[6], ds[7]));
+          for (int i = 0; i < 32; i += 2) {
+            const float off0 = decltype(biased)::value ? kbias[key0 + i] + nlse : nlse;
+            const float off1 = decltype(biased)::value ? kbias[key0 + i + 1] + nlse : nlse;
+            const float p0 = fast_exp2(fmaf(__uint_as_float(vs[i]), sl2, off0));
+            const float p1 = fast_exp2(fmaf(__uint_as_float(vs[i + 1]), sl2, off1));
+            const float dp0 = ((bits >> i) & 1u) ? __uint_as_float(vd[i]) : 0.0f;
+            const float dp1 = ((bits >> (i + 1)) & 1u) ? __uint_as_float(vd[i + 1]) : 0.0f;
+            pk[i >> 1] = pack_bf16x2(p0 * fmaf(dp0, c1, nds), p1 * fmaf(dp1, c1, nds));
           }
         };
         // 32-key groups without a masked key (all of them unless KB) take the path without the bias
-        if (KB && kvalid[j * 4 + qd] != 0xffffffffu) chunk(std::true_type{}); else chunk(std::false_type{});
-        // the dS buffer is needed only now: the previous chunk's dQ MMA has had the whole computation to finish
-        if (g >= 1) mbar_wait(bar_dsfree, (g - 1) & 1);
-        if (tid == 0 && j == 1) ATRACE(5);
-#pragma unroll
-        for (int gq = 0; gq < 4; ++gq) st_tile16p(sdS, r, qd * 4 + gq, pk[gq]);
-        fence_proxy_async_smem();
+        if (KB && kvalid[j * 2 + hq] != 0xffffffffu) chunk(std::true_type{}); else chunk(std::false_type{});
+        // the dS columns are needed only now: the previous chunk's dQ MMA has had the whole computation to finish
+        if (g > 0) mbar_wait(dq_done, (g - 1) & 1u);
+        tc_fence_after();
+        tmem_st_32x16(lane_base + DQ_COL_DS + hq * 16, pk);
+        tmem_wait_st();
         tc_fence_before();
-        mbar_arrive(bar_ds);
-        // the previous tile's accumulator (the other TMEM buffer) is drained here, after this tile's first
-        // chunk, so that nobody idles while that tile's last MMA completes
-        if (j == 0 && it > 0) drain(it - 1);
+        mbar_arrive(ds_full);
+        if (tid == 0 && pending_qb >= 0) {
+          // the previous tile's dQ store has long finished reading its staging buffer: release it
+          tma_wait_group_read<0>();
+          mbar_arrive(&qdo_free[pending_qb]);
+          pending_qb = -1;
+        }
+      }
+      // ---- drain: dQ tile -> bf16 -> swizzled smem (this tile's Q buffer: every MMA of the tile has completed)
+      // -> one TMA store into the Q slab of dqkv (rows beyond S are clipped)
+      mbar_wait(dq_full, it & 1);
+      tc_fence_after();
+      uint8_t* stage = sQ + qb * CH;
+      {
+        uint32_t o[32];
+        tmem_ld_32x32(lane_base + DQ_COL_DQ + hq * 32, o);
+        tmem_wait_ld();
+        tc_fence_before();
+        mbar_arrive(dq_free);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          uint4 w;
+          w.x = pack_bf16x2(__uint_as_float(o[8 * u]), __uint_as_float(o[8 * u + 1]));
+          w.y = pack_bf16x2(__uint_as_float(o[8 * u + 2]), __uint_as_float(o[8 * u + 3]));
+          w.z = pack_bf16x2(__uint_as_float(o[8 * u + 4]), __uint_as_float(o[8 * u + 5]));
+          w.w = pack_bf16x2(__uint_as_float(o[8 * u + 6]), __uint_as_float(o[8 * u + 7]));
+          *reinterpret_cast<uint4*>(stage + r * 128 + (((hq * 4 + u) ^ (r & 7)) << 4)) = w;
+        }
+      }
+      fence_proxy_async_smem();
+      named_bar_sync(2, DQ_ROW);
+      if (tid == 0) {
+        tma_store_3d(&tm_dqkv, stage, h * 64, qt * 128, b);
+        tma_commit_group();
+        pending_qb = qb;
+      }
+      if (a.dbias != nullptr) {
+        // gradient of the query bias: column sums of the staged tile (rows beyond S are exact zeros),
+        // 4 row groups of 32 -> shared memory -> 64 atomics per tile
+        s_red[(tid >> 6) * 64 + (tid & 63)] = staged_colsum(stage, (tid >> 6) * 32, 32, tid & 63);
+        named_bar_sync(2, DQ_ROW);
+        if (tid < 64) {
+          float sum = 0.0f;
+#pragma unroll
+          for (int g4 = 0; g4 < 4; ++g4) sum += s_red[g4 * 64 + tid];
+          atomicAdd(a.dbias + h * 64 + tid, sum);
+        }
       }
     }
-    if (t1 > t0) drain(t1 - t0 - 1);
-    if (tid == 0) tma_wait_group_read<0>();
+    if (tid == 0) {
+      if (pending_qb >= 0) {
+        tma_wait_group_read<0>();
+        mbar_arrive(&qdo_free[pending_qb]);
+      }
+      tma_wait_group<0>();
+    }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == CTRL_WARP) {
+  if (warp == DQ_MMA_WARP) {
     tc_fence_after();
-    tmem_dealloc(tmem, 512);
+    tmem_dealloc(tmem, 256);
   }
   if (tid == 0) ATRACE(9);
 }
@@ -1068,8 +1274,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
   if (tid == 0) ATRACE(9);
 }
 
-int fwd_smem_bytes(int n) { return CH * (5 + 2 * n) + 2048 + 4096 + 256 + 1024; }
-int dq_smem_bytes(int n) { return CH * (5 + 2 * n) + 2048 + 2048 + 256 + 1024; }
+int fwd_smem_bytes() { return 2 * CH + 2 * FW_RING * KCB + 6 * KC * 4 + 512 + 1024; }
+int dq_smem_bytes() { return 4 * CH + (DQ_KRING + DQ_VRING) * HC + 2048 + 2048 + 512 + 1024; }
 int dkv_smem_bytes() { return CH * 4 + HC * 4 + 4096 + 256 + 1024; }
 
 AttnArgs make_args(const AttnPlan& p, const uint8_t* key_mask, DropKey drop) {
@@ -1080,6 +1286,7 @@ AttnArgs make_args(const AttnPlan& p, const uint8_t* key_mask, DropKey drop) {
   a.H = p.shape.H;
   a.nchunk = p.nchunk;
   a.nchunk64 = (p.shape.S + 63) / 64;
+  a.nchunk96 = (p.shape.S + KC - 1) / KC;
   a.tmem_cols = p.tmem_cols;
   a.scale = 0.125f;  // 1 / sqrt(64)
   a.scale_log2 = 0.125f * 1.4426950408889634f;
@@ -1131,6 +1338,9 @@ int attn_plan(AttnPlan* plan, const AttnShape& s, const void* qkv, void* ctx, fl
   if (dqkv != nullptr &&
       encode_tmap_3d(&plan->tm_dqkv32, dqkv, 2, 3 * H, s.S, s.B, 3 * H, static_cast<uint64_t>(s.S) * 3 * H, 64, 32, 1))
     return 1;
+  if (qkv != nullptr &&
+      encode_tmap_3d(&plan->tm_kv96, qkv, 2, 3 * H, s.S, s.B, 3 * H, static_cast<uint64_t>(s.S) * 3 * H, 64, KC, 1))
+    return 1;
   if (ctx != nullptr &&
       encode_tmap_3d(&plan->tm_ctx, ctx, 2, H, s.S, s.B, H, static_cast<uint64_t>(s.S) * H, 64, 128, 1))
     return 1;
@@ -1157,11 +1367,15 @@ int attn_make_keep_bits(const AttnPlan& plan, DropKey drop, cudaStream_t st) {
 
 int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cudaStream_t st, bool bits_ready) {
   static PerDeviceOnce once;
-  int once_dev; if (once.needs_setup(&once_dev)) {
+  int once_dev;
+  if (once.needs_setup(&once_dev)) {
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        fwd_smem_bytes(4)));
+                                        fwd_smem_bytes()));
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        fwd_smem_bytes(4)));
+                                        fwd_smem_bytes()));
+    // two CTAs per SM need the whole shared-memory carve-out
+    BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     once.mark_done(once_dev);
   }
   const AttnArgs a = make_args(plan, key_mask, drop);
@@ -1169,12 +1383,12 @@ int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cu
   int sms = 0;
   if (device_sm_count(&sms)) return 1;
   const int tiles = plan.nchunk * plan.shape.A * plan.shape.B;
-  const int grid = tiles < sms ? tiles : sms;  // persistent: contiguous tile ranges per CTA
-  const bool kb = key_mask != nullptr || (plan.shape.S % 128) != 0;
+  const int grid = tiles < 2 * sms ? tiles : 2 * sms;  // persistent, two co-resident CTAs per SM
+  const bool kb = key_mask != nullptr || (plan.shape.S % KC) != 0;
   if (kb)
-    attn_fwd_kernel<true><<<grid, ATT_THREADS, fwd_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_ctx, a);
+    attn_fwd_kernel<true><<<grid, FW_THREADS, fwd_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_kv96, plan.tm_ctx, a);
   else
-    attn_fwd_kernel<false><<<grid, ATT_THREADS, fwd_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_ctx, a);
+    attn_fwd_kernel<false><<<grid, FW_THREADS, fwd_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_kv96, plan.tm_ctx, a);
   return check_launch("attn_fwd");
 }
 
@@ -1183,9 +1397,11 @@ int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, c
   static PerDeviceOnce once;
   int once_dev; if (once.needs_setup(&once_dev)) {
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        dq_smem_bytes(4)));
+                                        dq_smem_bytes()));
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        dq_smem_bytes(4)));
+                                        dq_smem_bytes()));
+    BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dkv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         dkv_smem_bytes()));
     once.mark_done(once_dev);
@@ -1205,16 +1421,16 @@ int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, c
   int sms = 0;
   if (device_sm_count(&sms)) return 1;
   const int tiles = plan.nchunk * plan.shape.A * plan.shape.B;
-  const int grid = tiles < sms ? tiles : sms;  // persistent: contiguous tile ranges per CTA
-  const bool kb = key_mask != nullptr || (plan.shape.S % 128) != 0;
+  const int grid = tiles < 2 * sms ? tiles : 2 * sms;  // persistent, two co-resident CTAs per SM
+  const bool kb = key_mask != nullptr || (plan.shape.S % 64) != 0;
   if (kb)
-    attn_bwd_dq_kernel<true><<<grid, ATT_THREADS, dq_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_dctx,
-                                                                                     plan.tm_dqkv, a);
+    attn_bwd_dq_kernel<true><<<grid, DQ_THREADS, dq_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_q64, plan.tm_dctx,
+                                                                         plan.tm_dqkv, a);
   else
-    attn_bwd_dq_kernel<false><<<grid, ATT_THREADS, dq_smem_bytes(plan.nchunk), st>>>(plan.tm_qkv, plan.tm_dctx,
-                                                                                      plan.tm_dqkv, a);
+    attn_bwd_dq_kernel<false><<<grid, DQ_THREADS, dq_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_q64, plan.tm_dctx,
+                                                                          plan.tm_dqkv, a);
   if (check_launch("attn_bwd_dq")) return 1;
-  const int grid_kv = tiles < 2 * sms ? tiles : 2 * sms;  // two co-resident CTAs per SM
+  const int grid_kv = grid;  // two co-resident CTAs per SM as well
   attn_bwd_dkv_kernel<<<grid_kv, BW_THREADS, dkv_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_q64, plan.tm_do64,
                                                                      plan.tm_dqkv32, a);
   return check_launch("attn_bwd_dkv");

@@ -15,6 +15,7 @@ struct AttnShape {
 
 struct AttnPlan {
   CUtensorMap tm_qkv;   // [B][S][3H] bf16, box {64,128,1}
+  CUtensorMap tm_kv96;  // qkv with box {64,96,1}: K / V chunks of the forward kernel
   CUtensorMap tm_dctx;  // [B][S][H]  bf16, box {64,128,1}
   CUtensorMap tm_q64;   // qkv with box {64,64,1}: 64-row Q chunks of the dK/dV kernel
   CUtensorMap tm_do64;  // dctx with box {64,64,1}

@@ -138,58 +138,76 @@ __device__ __forceinline__ void ln_apply(RowVec& r, const RowVec& g, const RowVe
   }
 }
 
-// NV = 16-byte vectors per lane (H <= 256 NV); gamma/beta are read at use (L1-resident) so that only the
-// row itself lives in registers and many rows are in flight per SM.
+// NV = 16-byte vectors per lane (H <= 256 NV).  Persistent grid (every block resident, 8 per SM): rows are dealt
+// round-robin to the warps, so every SM streams the same number of rows and there is no partial last wave; the
+// loads of a warp's next row are issued before the current row is reduced.  gamma / beta are read at use
+// (L1-resident) so that only the rows themselves live in registers.
+constexpr int LN_FWD_BLOCKS_PER_SM = 8;
 template <int NV>
-__global__ void __launch_bounds__(ROW_WARPS * 32)
+__global__ void __launch_bounds__(ROW_WARPS * 32, LN_FWD_BLOCKS_PER_SM)
 ln_fwd_kernel(const bf16* __restrict__ z, const float* __restrict__ gamma, const float* __restrict__ beta,
               bf16* __restrict__ y, int T, int H, float eps) {
   pdl_trigger();  // the next kernel (a GEMM) may start its prologue now; it waits for this grid before reading
   const int lane = threadIdx.x & 31;
-  const int row = blockIdx.x * ROW_WARPS + (threadIdx.x >> 5);
+  const int row_stride = gridDim.x * ROW_WARPS;
+  int row = blockIdx.x * ROW_WARPS + (threadIdx.x >> 5);
   if (row >= T) return;
-  float x[NV][8];
-  const bf16* zr = z + static_cast<size_t>(row) * H;
+  const float invH = 1.0f / static_cast<float>(H);
+  uint4 nraw[NV];
 #pragma unroll
   for (int j = 0; j < NV; ++j) {
     const int c = (j * 32 + lane) * 8;
-    const uint4 u = c < H ? __ldg(reinterpret_cast<const uint4*>(zr + c)) : make_uint4(0, 0, 0, 0);
-    const float2 a0 = unpack_bf16x2(u.x), a1 = unpack_bf16x2(u.y), a2 = unpack_bf16x2(u.z), a3 = unpack_bf16x2(u.w);
-    x[j][0] = a0.x; x[j][1] = a0.y; x[j][2] = a1.x; x[j][3] = a1.y;
-    x[j][4] = a2.x; x[j][5] = a2.y; x[j][6] = a3.x; x[j][7] = a3.y;
+    nraw[j] = c < H ? __ldg(reinterpret_cast<const uint4*>(z + static_cast<size_t>(row) * H + c)) : make_uint4(0, 0, 0, 0);
   }
-  const float invH = 1.0f / static_cast<float>(H);
-  float s = 0.0f;
+  for (; row < T; row += row_stride) {
+    float x[NV][8];
 #pragma unroll
-  for (int j = 0; j < NV; ++j)
+    for (int j = 0; j < NV; ++j) {
+      const uint4 u = nraw[j];
+      const float2 a0 = unpack_bf16x2(u.x), a1 = unpack_bf16x2(u.y), a2 = unpack_bf16x2(u.z), a3 = unpack_bf16x2(u.w);
+      x[j][0] = a0.x; x[j][1] = a0.y; x[j][2] = a1.x; x[j][3] = a1.y;
+      x[j][4] = a2.x; x[j][5] = a2.y; x[j][6] = a3.x; x[j][7] = a3.y;
+    }
+    const int nrow = row + row_stride;
+    if (nrow < T) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) s += x[j][i];
-  const float mean = warp_sum(s) * invH;
-  float qv = 0.0f;
-#pragma unroll
-  for (int j = 0; j < NV; ++j) {
-    if ((j * 32 + lane) * 8 < H) {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float t = x[j][i] - mean;
-        qv += t * t;
+      for (int j = 0; j < NV; ++j) {
+        const int c = (j * 32 + lane) * 8;
+        if (c < H) nraw[j] = __ldg(reinterpret_cast<const uint4*>(z + static_cast<size_t>(nrow) * H + c));
       }
     }
-  }
-  const float rstd = rsqrtf(warp_sum(qv) * invH + eps);
-  bf16* yr = y + static_cast<size_t>(row) * H;
+    float s = 0.0f;
 #pragma unroll
-  for (int j = 0; j < NV; ++j) {
-    const int c = (j * 32 + lane) * 8;
-    if (c < H) {
-      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c + 4));
-      const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + c)), b1 = __ldg(reinterpret_cast<const float4*>(beta + c + 4));
-      uint4 o;
-      o.x = pack_bf16x2((x[j][0] - mean) * rstd * g0.x + b0.x, (x[j][1] - mean) * rstd * g0.y + b0.y);
-      o.y = pack_bf16x2((x[j][2] - mean) * rstd * g0.z + b0.z, (x[j][3] - mean) * rstd * g0.w + b0.w);
-      o.z = pack_bf16x2((x[j][4] - mean) * rstd * g1.x + b1.x, (x[j][5] - mean) * rstd * g1.y + b1.y);
-      o.w = pack_bf16x2((x[j][6] - mean) * rstd * g1.z + b1.z, (x[j][7] - mean) * rstd * g1.w + b1.w);
-      *reinterpret_cast<uint4*>(yr + c) = o;
+    for (int j = 0; j < NV; ++j)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s += x[j][i];
+    const float mean = warp_sum(s) * invH;
+    float qv = 0.0f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      if ((j * 32 + lane) * 8 < H) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float t = x[j][i] - mean;
+          qv = fmaf(t, t, qv);
+        }
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(qv) * invH + eps);
+    bf16* yr = y + static_cast<size_t>(row) * H;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int c = (j * 32 + lane) * 8;
+      if (c < H) {
+        const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c + 4));
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + c)), b1 = __ldg(reinterpret_cast<const float4*>(beta + c + 4));
+        uint4 o;
+        o.x = pack_bf16x2((x[j][0] - mean) * rstd * g0.x + b0.x, (x[j][1] - mean) * rstd * g0.y + b0.y);
+        o.y = pack_bf16x2((x[j][2] - mean) * rstd * g0.z + b0.z, (x[j][3] - mean) * rstd * g0.w + b0.w);
+        o.z = pack_bf16x2((x[j][4] - mean) * rstd * g1.x + b1.x, (x[j][5] - mean) * rstd * g1.y + b1.y);
+        o.w = pack_bf16x2((x[j][6] - mean) * rstd * g1.z + b1.z, (x[j][7] - mean) * rstd * g1.w + b1.w);
+        *reinterpret_cast<uint4*>(yr + c) = o;
+      }
     }
   }
 }
@@ -245,13 +263,14 @@ embed_ln_fwd_kernel(const int64_t* __restrict__ ids, const int64_t* __restrict__
 //   drop_in : dy is first multiplied by the keep mask of a dropout applied AFTER this LN (embeddings)
 //   drop_out: additionally emits dz * keep-mask (gradient of the GEMM output that was dropped
 //             BEFORE the residual add) and accumulates its column sums into dbias
-// Rows are distributed round-robin over a persistent grid.  NV = 16-byte vectors per lane
-// (H <= 256 NV).  To keep the register count low enough for ~20 resident warps per SM the
-// per-warp column partials and gamma live in shared memory; the loads of the next row are issued
-// before the current row is reduced (software pipeline), partials are reduced once per block and
-// once per grid (atomicAdd).
+// Rows are distributed round-robin over a persistent grid, one warp per row, NV = 16-byte vectors per lane
+// (H <= 256 NV).  The kernel is bound by instruction issue, not by HBM, unless the per-element work is small:
+// a lane always meets the same columns, so the three column partials (dgamma, dbeta, dbias) live in registers
+// for the whole kernel (no shared-memory read-modify-write per row), xhat and the output come from fused
+// multiply-adds with per-row constants, and the next row's loads are issued before the current row is reduced.
+// Partials are combined once per block (shared memory) and once per grid (atomicAdd).
 template <int NV>
-__global__ void __launch_bounds__(ROW_WARPS * 32)
+__global__ void __launch_bounds__(ROW_WARPS * 32, NV <= 3 ? 3 : 2)
 ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const float* __restrict__ gamma,
               bf16* __restrict__ dz, bf16* __restrict__ dz_masked, float* __restrict__ dgamma,
               float* __restrict__ dbeta, float* __restrict__ dbias, int T, int H, float eps, DropKey drop_in,
@@ -260,16 +279,20 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
   extern __shared__ float ln_smem[];
   constexpr int W = NV * 256;           // padded row width
   float* s_gamma = ln_smem;             // [W]
-  float* s_acc = ln_smem + W;           // [ROW_WARPS][3][W]
+  float* s_acc = ln_smem + W;           // [ROW_WARPS][W], reused for the three reductions at the end
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   for (int c = threadIdx.x; c < W; c += blockDim.x) s_gamma[c] = c < H ? gamma[c] : 0.0f;
-  for (int c = threadIdx.x; c < ROW_WARPS * 3 * W; c += blockDim.x) s_acc[c] = 0.0f;
   __syncthreads();
-  float* acc_g = s_acc + (warp * 3 + 0) * W;
-  float* acc_b = s_acc + (warp * 3 + 1) * W;
-  float* acc_m = s_acc + (warp * 3 + 2) * W;
   const float invH = 1.0f / static_cast<float>(H);
+  const bool masking = dz_masked != nullptr;
+  const bool want_dbias = dbias != nullptr;
+
+  float ag[NV][8], ab[NV][8], am[NV][8];
+#pragma unroll
+  for (int j = 0; j < NV; ++j)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) ag[j][i] = ab[j][i] = am[j][i] = 0.0f;
 
   const int row_stride = gridDim.x * ROW_WARPS;
   int row = blockIdx.x * ROW_WARPS + warp;
@@ -319,47 +342,47 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const float t = x[j][i] - mean;
-          qv += t * t;
+          qv = fmaf(t, t, qv);
         }
       }
     }
     const float rstd = rsqrtf(warp_sum(qv) * invH + eps);
+    const float nmr = -mean * rstd;  // xhat = x * rstd + nmr
     float s1 = 0.0f, s2 = 0.0f;
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
       const int c = (j * 32 + lane) * 8;
       if (c < H) {
-        float4 g0 = *reinterpret_cast<const float4*>(s_gamma + c), g1 = *reinterpret_cast<const float4*>(s_gamma + c + 4);
+        const float4 g0 = *reinterpret_cast<const float4*>(s_gamma + c), g1 = *reinterpret_cast<const float4*>(s_gamma + c + 4);
         const float gv[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-        float4 ag0 = *reinterpret_cast<float4*>(acc_g + c), ag1 = *reinterpret_cast<float4*>(acc_g + c + 4);
-        float4 ab0 = *reinterpret_cast<float4*>(acc_b + c), ab1 = *reinterpret_cast<float4*>(acc_b + c + 4);
-        float* ag = reinterpret_cast<float*>(&ag0);
-        float* ab = reinterpret_cast<float*>(&ab0);
-        float agv[8] = {ag0.x, ag0.y, ag0.z, ag0.w, ag1.x, ag1.y, ag1.z, ag1.w};
-        float abv[8] = {ab0.x, ab0.y, ab0.z, ab0.w, ab1.x, ab1.y, ab1.z, ab1.w};
-        (void)ag; (void)ab;
+        if (drop_in.thresh != 0u) {
+          const uint32_t base = static_cast<uint32_t>(row) * H + c;  // even
+#pragma unroll
+          for (int i = 0; i < 8; i += 2) {
+            bool k0, k1;
+            drop_keep2(drop_in, base + i, k0, k1);
+            d[j][i] = k0 ? d[j][i] * drop_in.scale : 0.0f;
+            d[j][i + 1] = k1 ? d[j][i + 1] * drop_in.scale : 0.0f;
+          }
+        }
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          float dyv = d[j][i];
-          if (drop_in.thresh != 0u)
-            dyv = drop_keep(drop_in, static_cast<uint32_t>(row) * H + c + i) ? dyv * drop_in.scale : 0.0f;
-          const float xhat = (x[j][i] - mean) * rstd;
+          const float dyv = d[j][i];
+          const float xhat = fmaf(x[j][i], rstd, nmr);
           const float dxhat = dyv * gv[i];
-          agv[i] += dyv * xhat;
-          abv[i] += dyv;
+          ag[j][i] = fmaf(dyv, xhat, ag[j][i]);
+          ab[j][i] += dyv;
           s1 += dxhat;
-          s2 += dxhat * xhat;
+          s2 = fmaf(dxhat, xhat, s2);
           x[j][i] = xhat;
           d[j][i] = dxhat;
         }
-        *reinterpret_cast<float4*>(acc_g + c) = make_float4(agv[0], agv[1], agv[2], agv[3]);
-        *reinterpret_cast<float4*>(acc_g + c + 4) = make_float4(agv[4], agv[5], agv[6], agv[7]);
-        *reinterpret_cast<float4*>(acc_b + c) = make_float4(abv[0], abv[1], abv[2], abv[3]);
-        *reinterpret_cast<float4*>(acc_b + c + 4) = make_float4(abv[4], abv[5], abv[6], abv[7]);
       }
     }
     s1 = warp_sum(s1) * invH;
     s2 = warp_sum(s2) * invH;
+    // dz = rstd * (dxhat - s1 - xhat * s2) = dxhat * rstd + (xhat * k2 + k1)
+    const float k1 = -s1 * rstd, k2 = -s2 * rstd;
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
       const int c = (j * 32 + lane) * 8;
@@ -367,60 +390,66 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
         uint32_t pk[4];
 #pragma unroll
         for (int i = 0; i < 8; i += 2) {
-          const float v0 = rstd * (d[j][i] - s1 - x[j][i] * s2);
-          const float v1 = rstd * (d[j][i + 1] - s1 - x[j][i + 1] * s2);
+          const float v0 = fmaf(d[j][i], rstd, fmaf(x[j][i], k2, k1));
+          const float v1 = fmaf(d[j][i + 1], rstd, fmaf(x[j][i + 1], k2, k1));
           pk[i >> 1] = pack_bf16x2(v0, v1);
-          // consumers on the GEMM side read the bf16-rounded value
-          const float2 rr = unpack_bf16x2(pk[i >> 1]);
-          d[j][i] = rr.x;
-          d[j][i + 1] = rr.y;
         }
         *reinterpret_cast<uint4*>(dz + static_cast<size_t>(row) * H + c) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-        if (dz_masked != nullptr) {
-          if (drop_out.thresh != 0u) {
-            const uint32_t base = static_cast<uint32_t>(row) * H + c;  // even: H and c are multiples of 8
-#pragma unroll
-            for (int i = 0; i < 8; i += 2) {
-              bool k0, k1;
-              drop_keep2(drop_out, base + i, k0, k1);
-              d[j][i] = k0 ? d[j][i] * drop_out.scale : 0.0f;
-              d[j][i + 1] = k1 ? d[j][i + 1] * drop_out.scale : 0.0f;
-            }
-          }
+        if (masking) {
+          // consumers on the GEMM side read the bf16-rounded value: mask and scale THAT value
           uint32_t pm[4];
+          const uint32_t base = static_cast<uint32_t>(row) * H + c;  // even: H and c are multiples of 8
 #pragma unroll
           for (int i = 0; i < 8; i += 2) {
-            pm[i >> 1] = pack_bf16x2(d[j][i], d[j][i + 1]);
-            const float2 rr = unpack_bf16x2(pm[i >> 1]);
-            d[j][i] = rr.x;
-            d[j][i + 1] = rr.y;
+            const float2 rr = unpack_bf16x2(pk[i >> 1]);
+            float m0 = rr.x, m1 = rr.y;
+            if (drop_out.thresh != 0u) {
+              bool k0, k1b;
+              drop_keep2(drop_out, base + i, k0, k1b);
+              m0 = k0 ? m0 * drop_out.scale : 0.0f;
+              m1 = k1b ? m1 * drop_out.scale : 0.0f;
+            }
+            pm[i >> 1] = pack_bf16x2(m0, m1);
+            if (want_dbias) {
+              const float2 mr = unpack_bf16x2(pm[i >> 1]);
+              am[j][i] += mr.x;
+              am[j][i + 1] += mr.y;
+            }
           }
           if (dz_masked != dz)
             *reinterpret_cast<uint4*>(dz_masked + static_cast<size_t>(row) * H + c) = make_uint4(pm[0], pm[1], pm[2], pm[3]);
-        }
-        if (dbias != nullptr) {
-          float4 am0 = *reinterpret_cast<float4*>(acc_m + c), am1 = *reinterpret_cast<float4*>(acc_m + c + 4);
-          am0.x += d[j][0]; am0.y += d[j][1]; am0.z += d[j][2]; am0.w += d[j][3];
-          am1.x += d[j][4]; am1.y += d[j][5]; am1.z += d[j][6]; am1.w += d[j][7];
-          *reinterpret_cast<float4*>(acc_m + c) = am0;
-          *reinterpret_cast<float4*>(acc_m + c + 4) = am1;
+        } else if (want_dbias) {
+#pragma unroll
+          for (int i = 0; i < 8; i += 2) {
+            const float2 rr = unpack_bf16x2(pk[i >> 1]);
+            am[j][i] += rr.x;
+            am[j][i + 1] += rr.y;
+          }
         }
       }
     }
   }
-  __syncthreads();
-  for (int c = threadIdx.x; c < H; c += blockDim.x) {
-    float sg = 0.0f, sb = 0.0f, sm = 0.0f;
+  // block reduction of the three column partials, one after the other through the same buffer
+  auto reduce_out = [&](float (&acc)[NV][8], float* out) {
+    if (out == nullptr) return;  // uniform
+    __syncthreads();
 #pragma unroll
-    for (int w = 0; w < ROW_WARPS; ++w) {
-      sg += s_acc[(w * 3 + 0) * W + c];
-      sb += s_acc[(w * 3 + 1) * W + c];
-      sm += s_acc[(w * 3 + 2) * W + c];
+    for (int j = 0; j < NV; ++j) {
+      const int c = (j * 32 + lane) * 8;
+      *reinterpret_cast<float4*>(s_acc + warp * W + c) = make_float4(acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
+      *reinterpret_cast<float4*>(s_acc + warp * W + c + 4) = make_float4(acc[j][4], acc[j][5], acc[j][6], acc[j][7]);
     }
-    if (dgamma != nullptr) atomicAdd(dgamma + c, sg);
-    if (dbeta != nullptr) atomicAdd(dbeta + c, sb);
-    if (dbias != nullptr) atomicAdd(dbias + c, sm);
-  }
+    __syncthreads();
+    for (int c = threadIdx.x; c < H; c += blockDim.x) {
+      float t = 0.0f;
+#pragma unroll
+      for (int w = 0; w < ROW_WARPS; ++w) t += s_acc[w * W + c];
+      atomicAdd(out + c, t);
+    }
+  };
+  reduce_out(ag, dgamma);
+  reduce_out(ab, dbeta);
+  reduce_out(am, dbias);
 }
 
 // out[n] += sum_t X[t][n]  (bias gradients of the fused QKV and intermediate projections)
@@ -591,11 +620,15 @@ int launch_ln_fwd(const bf16* z, const float* gamma, const float* beta, bf16* y,
     set_error("layernorm: H=%d must be a multiple of 8 and <= %d", H, MAXV * 256);
     return 1;
   }
+  int sms = 0;
+  if (device_sm_count(&sms)) return 1;
+  int grid = sms * LN_FWD_BLOCKS_PER_SM;
+  if (grid > row_blocks(T)) grid = row_blocks(T);
   switch ((H + 255) / 256) {
-    case 1: ln_fwd_kernel<1><<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
-    case 2: ln_fwd_kernel<2><<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
-    case 3: ln_fwd_kernel<3><<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
-    default: ln_fwd_kernel<4><<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
+    case 1: ln_fwd_kernel<1><<<grid, ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
+    case 2: ln_fwd_kernel<2><<<grid, ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
+    case 3: ln_fwd_kernel<3><<<grid, ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
+    default: ln_fwd_kernel<4><<<grid, ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
   }
   return check_launch("ln_fwd");
 }
@@ -622,8 +655,8 @@ int launch_ln_bwd(const bf16* dy, const bf16* z, const float* gamma, bf16* dz, b
     return 1;
   }
   const int nv = (H + 255) / 256;
-  const size_t smem = static_cast<size_t>(nv) * 256 * (1 + 3 * ROW_WARPS) * sizeof(float);
-  int grid = num_sms * 4;
+  const size_t smem = static_cast<size_t>(nv) * 256 * (1 + ROW_WARPS) * sizeof(float);
+  int grid = num_sms * (nv <= 3 ? 3 : 2);  // every block resident: see __launch_bounds__ of the kernel
   if (grid > row_blocks(T)) grid = row_blocks(T);
 #define BQA_LN_BWD(NV)                                                                                         \
   {                                                                                                            \

@@ -25,7 +25,7 @@ names = {1: "wait scores", 2: "tmem load", 3: "math", 4: "wait operand buffers",
          7: "tile prologue", 8: "other"}
 for p in (0.1, 0.0):
     for _ in range(2):
-        assert lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep.data_ptr(), None, B, S, A, p, 7, 5, None, st) == 0
+        assert lib.bqa_attention_forward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep.data_ptr(), None, B, S, A, p, 7, 5, st) == 0
         assert lib.bqa_attention_backward(qkv.data_ptr(), ctx.data_ptr(), lse2.data_ptr(), keep.data_ptr(), dctx.data_ptr(),
                                           dqkv.data_ptr(), dsum.data_ptr(), None, B, S, A, p, 7, 5, None, st) == 0
     torch.cuda.synchronize()
