@@ -275,10 +275,13 @@ BQA_API int bqa_set_output_grads(bqa_handle* h, const float* d_start, const floa
 BQA_API int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* stream);
 BQA_API int bqa_num_backward_phases(const bqa_handle* h);
 BQA_API int64_t bqa_phase_grad_begin(const bqa_handle* h, int32_t phase);
-/* Per-launch device timing of the tensor-core kernels (CUDA events on the launch stream around
- * every GEMM / attention launch between begin and end).  end() synchronises and fills HOST
- * arrays of 5 entries: 0 GEMM forward, 1 dgrad, 2 wgrad, 3 attention forward, 4 attention
- * backward (milliseconds, algorithmic matmul FLOPs, launches).  Measurement aid for bench.py. */
+/* Per-launch device timing of the step's kernels (CUDA events on the launch stream around every
+ * GEMM / attention / row-kernel launch between begin and end).  end() synchronises and fills HOST
+ * arrays of BQA_PROFILE_KINDS entries (milliseconds, algorithmic work, launches): 0 GEMM forward,
+ * 1 dgrad, 2 wgrad, 3 attention forward, 4 attention backward — work = matmul FLOPs; 5 LayerNorm
+ * forward, 6 LayerNorm backward, 7 embeddings + LayerNorm forward, 8 embedding backward — work =
+ * algorithmic HBM bytes.  Measurement aid for bench.py. */
+#define BQA_PROFILE_KINDS 9
 BQA_API int bqa_profile_begin(bqa_handle* h);
 BQA_API int bqa_profile_end(bqa_handle* h, double* host_ms, double* host_flops, int64_t* host_count);
 /* Number of kernels launched by this handle since creation (bench.py's gpu_launches). */

@@ -85,7 +85,24 @@ __device__ unsigned long long g_attn_trace[4096 * 16];
       g_attn_trace[bl * 16 + (slot)] = global_timer_ns();                                                   \
     }                                                                                                       \
   } while (0)
+// MMA-warp buckets (slots 13..15), same accumulate-since-last-call scheme
+#define MTACC_DECL long long macc_[3] = {0, 0, 0}; long long mprev_ = clock64()
+#define MTACC(k)                                                                                             \
+  do {                                                                                                      \
+    const long long now_ = clock64();                                                                       \
+    macc_[k] += now_ - mprev_;                                                                              \
+    mprev_ = now_;                                                                                          \
+  } while (0)
+#define MTACC_WRITE()                                                                                        \
+  do {                                                                                                      \
+    const unsigned bl = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);                     \
+    if (bl < 4096 && (threadIdx.x & 31) == 0)                                                               \
+      for (int k_ = 0; k_ < 3; ++k_) g_attn_trace[bl * 16 + 13 + k_] = macc_[k_];                           \
+  } while (0)
 #else
+#define MTACC_DECL do {} while (0)
+#define MTACC(k) do {} while (0)
+#define MTACC_WRITE() do {} while (0)
 #define ATRACE_WHERE(slot) do {} while (0)
 #define ATRACE(slot) do {} while (0)
 #define ATACC_DECL do {} while (0)
@@ -971,218 +988,334 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
 // =========================================================================================
 // backward, dK and dV (rows = keys)
 // =========================================================================================
-// Two CTAs per SM (288 threads, half of TMEM and of shared memory each), so that one CTA's TMEM loads,
-// operand stores and barrier waits overlap the other's arithmetic.  Persistent: contiguous (batch, head,
-// key-tile) ranges per CTA.  The Q / dO rows stream through a 2-stage ring in chunks of 64 queries that
-// keeps running across tile boundaries (chunk counter g = it * M + i, M = ceil(S / 64)); the next tile's
-// K / V are fetched once the current tile's last score MMAs have completed.
-__global__ void __launch_bounds__(BW_THREADS, 2)
-attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_q64,
-                    const __grid_constant__ CUtensorMap tm_do64, const __grid_constant__ CUtensorMap tm_dqkv,
-                    const AttnArgs a) {
+// The transposed problem (rows of the score tile are keys).  One CTA per SM with the whole tensor memory: 16 row
+// warps (thread (r, qd) = key row r of a 128-key tile, quarter qd of a chunk's query columns), two MMA-issuing
+// warps (score MMAs / gradient MMAs, on two scheduler partitions), one TMA warp; contiguous (batch, head, key-tile)
+// ranges per CTA.  The queries stream through in chunks of 128 (Q / dO tiles in a 4-stage ring); K / V tiles are
+// double-buffered across tiles and a finished tile's buffers stage its dK / dV output.  Per chunk g:
+//   S^T = K Q_g^T, dP^T = V dO_g^T   tcgen05.mma into 128 + 128 fp32 columns; the row threads pull them into
+//                                    registers and hand the columns back at once, so the score MMAs of chunk
+//                                    g + 1 run while chunk g is still being computed
+//   P^T, dS^T                        computed in registers, written as bf16 pairs into 64 + 64 further columns:
+//                                    no shared-memory round trip, no proxy fence
+//   dV += P^T dO_g, dK += dS^T Q_g   tcgen05.mma with the A operands read from TMEM
+// TMEM: S 128, dP 128, P^T 64, dS^T 64, dV 64, dK 64 = 512 columns.  A tile's accumulators are drained lazily,
+// after the next tile's first chunk (warps 0-7 take dV, warps 8-15 dK), so that nobody idles on the last MMAs.
+constexpr int KV_ROW = 512;
+constexpr int KV_THREADS = KV_ROW + 96;
+constexpr int KV_MMA_WARP = 16, KV_MMA2_WARP = 17, KV_TMA_WARP = 18;
+constexpr int KV_RING = 4;  // a stage lives from its load to the chunk's gradient MMAs: ~2 chunk periods + the load latency
+constexpr uint32_t KV_COL_S = 0, KV_COL_DP = 128, KV_COL_PT = 256, KV_COL_DST = 320, KV_COL_DV = 384, KV_COL_DK = 448;
+
+__global__ void __launch_bounds__(KV_THREADS, 1)
+attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_dctx,
+                    const __grid_constant__ CUtensorMap tm_dqkv, const AttnArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
-  const int N = a.nchunk, M = a.nchunk64;
-  uint8_t* sK = smem;
-  uint8_t* sV = sK + CH;
-  uint8_t* sQ = sV + CH;       // 2 stages of 64 queries
-  uint8_t* sdO = sQ + 2 * HC;  // 2 stages
-  uint8_t* sPt = sdO + 2 * HC;  // [128 keys][64 queries] bf16; staging of the dV tile at the end of a tile
-  uint8_t* sdSt = sPt + CH;     // same for dS^T / dK
-  float* s_lse = reinterpret_cast<float*>(sdSt + CH);
-  float* s_dsum = s_lse + 512;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_dsum + 512);
-  uint64_t* bar_kv = bars + 0;
-  uint64_t* bar_ld = bars + 1;  // [2]
-  uint64_t* bar_s = bars + 3;
-  uint64_t* bar_sfree = bars + 4;
-  uint64_t* bar_pt = bars + 5;
-  uint64_t* bar_ptfree = bars + 6;
-  uint64_t* bar_out = bars + 7;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  const int N = a.nchunk;  // key tiles per (batch, head) = query chunks per tile
+  uint8_t* sK = smem;                 // 2 x CH; a finished tile's buffer stages its dK tile
+  uint8_t* sV = sK + 2 * CH;          // 2 x CH; ... its dV tile
+  uint8_t* sQ = sV + 2 * CH;          // KV_RING stages of 128 queries
+  uint8_t* sdO = sQ + KV_RING * CH;   // KV_RING stages
+  float* s_stat = reinterpret_cast<float*>(sdO + KV_RING * CH);  // [2 buffers][-lse2 | -D * scale][512]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_stat + 2 * 2 * 512);
+  uint64_t* kv_full = bars + 0;    // [2]
+  uint64_t* kv_free = bars + 2;    // [2] last score MMAs of the tile done + the eight output stores have read the buffers
+  uint64_t* ld_full = bars + 4;    // [KV_RING]
+  uint64_t* ld_free = bars + 8;    // [KV_RING] score MMAs + gradient MMAs of the chunk
+  uint64_t* s_full = bars + 12;
+  uint64_t* s_free = bars + 13;
+  uint64_t* pt_full = bars + 14;
+  uint64_t* pt_free = bars + 15;
+  uint64_t* out_full = bars + 16;
+  uint64_t* out_free = bars + 17;
+  uint64_t* st_full = bars + 18;   // [2] per-query statistics of a (batch, head) staged by the TMA warp
+  uint64_t* st_free = bars + 20;   // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 22);
 
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x;
+  const int warp = uniform_warp_idx();
   const int S = a.S;
   const int tiles = a.B * a.A * N;
   const int t0 = static_cast<int>(static_cast<long long>(blockIdx.x) * tiles / gridDim.x);
   const int t1 = static_cast<int>(static_cast<long long>(blockIdx.x + 1) * tiles / gridDim.x);
-  const uint32_t chunks = static_cast<uint32_t>(t1 - t0) * M;  // Q / dO chunks this CTA streams
+  const uint32_t chunks = static_cast<uint32_t>(t1 - t0) * N;  // Q / dO chunks this CTA streams
   if (tid == 0) ATRACE(0);
 
-  // chunk g of this CTA's stream -> TMA coordinates of its Q / dO rows
-  auto load_chunk = [&](uint32_t g) {
-    const int t = t0 + static_cast<int>(g) / M, i = static_cast<int>(g) % M;
-    const int bh = t / N, b = bh / a.A, h = bh - b * a.A;
-    const int st = g & 1;
-    mbar_arrive_expect_tx(&bar_ld[st], 2 * HC);
-    tma_load_3d(sQ + st * HC, &tm_q64, h * 64, i * 64, b, &bar_ld[st]);
-    tma_load_3d(sdO + st * HC, &tm_do64, h * 64, i * 64, b, &bar_ld[st]);
-  };
-  auto load_kv = [&](int t) {
-    const int bh = t / N, kt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
-    mbar_arrive_expect_tx(bar_kv, 2 * CH);
-    tma_load_3d(sK, &tm_qkv, a.H + h * 64, kt * 128, b, bar_kv);
-    tma_load_3d(sV, &tm_qkv, 2 * a.H + h * 64, kt * 128, b, bar_kv);
-  };
-
-  if (tid == BW_ROW_THREADS) {
-    tma_prefetch_desc(&tm_qkv);
-    tma_prefetch_desc(&tm_q64);
-    tma_prefetch_desc(&tm_do64);
-    mbar_init(bar_kv, 1);
-    mbar_init(&bar_ld[0], 1);
-    mbar_init(&bar_ld[1], 1);
-    mbar_init(bar_s, 1);
-    mbar_init(bar_sfree, BW_ROW_THREADS);
-    mbar_init(bar_pt, BW_ROW_THREADS);
-    mbar_init(bar_ptfree, 1);
-    mbar_init(bar_out, 1);
-    fence_mbar_init();
-    tma_prefetch_desc(&tm_dqkv);
-    if (t0 < t1) {
-      load_kv(t0);
-      for (uint32_t g = 0; g < 2 && g < chunks; ++g) load_chunk(g);
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&kv_full[i], 1);
+      mbar_init(&kv_free[i], 9);
+      mbar_init(&st_full[i], 1);
+      mbar_init(&st_free[i], KV_ROW);
     }
+    for (int i = 0; i < KV_RING; ++i) {
+      mbar_init(&ld_full[i], 1);
+      mbar_init(&ld_free[i], 2);
+    }
+    mbar_init(s_full, 1);
+    mbar_init(s_free, KV_ROW);
+    mbar_init(pt_full, KV_ROW);
+    mbar_init(pt_free, 1);
+    mbar_init(out_full, 1);
+    mbar_init(out_free, KV_ROW);
+    fence_mbar_init();
   }
-  if (warp == BW_CTRL_WARP) {
-    tmem_alloc(tmem_slot, 256);
+  if (warp == KV_MMA_WARP) {
+    tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
+  }
+  if (tid == KV_TMA_WARP * 32) {
+    tma_prefetch_desc(&tm_qkv);
+    tma_prefetch_desc(&tm_dctx);
+    tma_prefetch_desc(&tm_dqkv);
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   pdl_trigger();  // the next kernel may start its prologue; it waits for this grid before reading
-  constexpr uint32_t COL_S = 0, COL_DP = 64, COL_DV = 128, COL_DK = 192;
 
-  if (uniform_warp_idx() == BW_CTRL_WARP) {
-    // The whole control warp walks the loop (warp-uniform control flow and operands); one elected lane
-    // issues the MMAs and TMA loads.  i and t follow the chunk counter without divisions.
-    constexpr uint32_t idesc_s = umma_idesc_bf16(128, 64, 0, 0);
-    constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+  if (warp == KV_TMA_WARP) {
+    // ---------------- TMA producer ----------------
     const bool leader = elect_one();
-    // score MMAs of chunk g (first chunk of a tile if `first`): S^T = K Q^T and dP^T = V dO^T into the
-    // single-buffered TMEM columns
-    auto issue_scores = [&](uint32_t g, bool first, uint32_t tile_it) {
-      const int st = g & 1;
-      if (first) mbar_wait(bar_kv, tile_it & 1);
-      mbar_wait(&bar_ld[st], (g >> 1) & 1);
-      if (g > 0) mbar_wait(bar_sfree, (g - 1) & 1);
-      tc_fence_after();
+    const int lane = tid & 31;
+    uint32_t g = 0;
+    int prev_bh = -1, nbh = 0;
+    for (int t = t0, it = 0; t < t1; ++t, ++it) {
+      const int bh = t / N, kt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
+      const int kvb = it & 1;
+      if (it >= 2) mbar_wait(&kv_free[kvb], ((it >> 1) - 1) & 1);
       if (leader) {
-        mma_k64(tmem + COL_S, smem_u32(sK), smem_u32(sQ + st * HC), idesc_s);
-        mma_k64(tmem + COL_DP, smem_u32(sV), smem_u32(sdO + st * HC), idesc_s);
-        umma_commit(bar_s);
+        mbar_arrive_expect_tx(&kv_full[kvb], 2 * CH);
+        tma_load_3d(sK + kvb * CH, &tm_qkv, a.H + h * 64, kt * 128, b, &kv_full[kvb]);
+        tma_load_3d(sV + kvb * CH, &tm_qkv, 2 * a.H + h * 64, kt * 128, b, &kv_full[kvb]);
       }
       __syncwarp();
-    };
-    if (chunks > 0) issue_scores(0, true, 0);
-    int i = 0, t = t0;
-    uint32_t it = 0;
-    for (uint32_t g = 0; g < chunks; ++g) {
-      const int st = g & 1;
-      const bool last = i == M - 1;
-      if (last && t + 1 < t1) {
-        // the tile's last score MMAs have completed: K and V can be replaced
-        mbar_wait(bar_s, g & 1);
-        if (leader) load_kv(t + 1);
+      if (bh != prev_bh) {
+        // per-query statistics of the (batch, head), staged for the row threads: -lse2 (p = exp2(s * sl2 - lse2)) and
+        // -D * scale (ds = p * (dp * c1 - D * scale)); queries beyond S get p = 0.  Double-buffered: the row threads
+        // never wait for each other at a (batch, head) boundary, only for this warp.
+        const int sb = nbh & 1;
+        if (nbh >= 2) mbar_wait(&st_free[sb], ((nbh >> 1) - 1) & 1);
+        float* dst = s_stat + sb * 1024;
+        const size_t stat = static_cast<size_t>(bh) * S;
+#pragma unroll 4
+        for (int q = lane; q < 512; q += 32) {
+          dst[q] = q < S ? -__ldg(a.lse2 + stat + q) : -INFINITY;
+          dst[512 + q] = q < S ? -__ldg(a.dsum + stat + q) * a.scale : 0.0f;
+        }
         __syncwarp();
+        if (lane == 0) mbar_arrive(&st_full[sb]);
+        prev_bh = bh;
+        ++nbh;
       }
-      // the next chunk's scores are issued before this chunk's P^T / dS^T are waited for, so that they
-      // run while the row threads are still busy with this chunk
-      if (g + 1 < chunks) issue_scores(g + 1, last, it + 1);
-      mbar_wait(bar_pt, g & 1);
-      tc_fence_after();
-      if (leader) {
-        mma_k64_mn(tmem + COL_DV, smem_u32(sPt), smem_u32(sdO + st * HC), idesc_o, i > 0);
-        mma_k64_mn(tmem + COL_DK, smem_u32(sdSt), smem_u32(sQ + st * HC), idesc_o, i > 0);
-        umma_commit(bar_ptfree);
-        if (last) umma_commit(bar_out);
-      }
-      __syncwarp();
-      if (g + 2 < chunks) {
-        // stage `st` is re-filled only after every MMA that reads it has completed
-        mbar_wait(bar_ptfree, g & 1);
-        if (leader) load_chunk(g + 2);
+      for (int i = 0; i < N; ++i, ++g) {
+        const uint32_t st = g % KV_RING;  // KV_RING is a power of two
+        if (g >= KV_RING) mbar_wait(&ld_free[st], ((g / KV_RING) - 1u) & 1u);
+        if (leader) {
+          mbar_arrive_expect_tx(&ld_full[st], 2 * CH);
+          tma_load_3d(sQ + st * CH, &tm_qkv, h * 64, i * 128, b, &ld_full[st]);
+          tma_load_3d(sdO + st * CH, &tm_dctx, h * 64, i * 128, b, &ld_full[st]);
+        }
         __syncwarp();
-      }
-      if (last) {
-        i = 0;
-        ++t;
-        ++it;
-      } else {
-        ++i;
       }
     }
-  } else if (tid < BW_ROW_THREADS) {
-    // thread (r, hq): key row r of the tile, queries [32 hq, 32 hq + 32) of every 64-query chunk
-    const int r = tid & 127, hq = tid >> 7, ew = warp & 3;
+  } else if (warp == KV_MMA_WARP) {
+    // ---------------- MMA issuer 1: score MMAs (S^T, dP^T of chunk g) ----------------
+    // Two issuing warps on two scheduler partitions: the issue slots of a partition are shared with four row warps,
+    // and a single warp doing all the waiting and issuing was the critical path of the kernel.  The two chains need
+    // no mutual ordering beyond the barriers below.  Positions are tracked by counters (no divisions in the loop).
+    constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
+    const bool leader = elect_one();
+    int it = 0, i = 0;
+    uint32_t st = 0, round = 0;
+    MTACC_DECL;
+    for (uint32_t g = 0; g < chunks; ++g) {
+      const int kvb = it & 1;
+      if (i == 0) mbar_wait(&kv_full[kvb], (it >> 1) & 1);
+      mbar_wait(&ld_full[st], round & 1u);
+      MTACC(0);
+      if (g >= 1) mbar_wait(s_free, (g - 1u) & 1u);  // the previous chunk's scores are in registers
+      MTACC(1);
+      tc_fence_after();
+      if (leader) {
+        const uint32_t k_addr = smem_u32(sK + kvb * CH), v_addr = smem_u32(sV + kvb * CH);
+        const uint32_t q_addr = smem_u32(sQ + st * CH), do_addr = smem_u32(sdO + st * CH);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          umma_bf16(tmem + KV_COL_S, umma_desc_kmajor(k_addr + k * 32), umma_desc_kmajor(q_addr + k * 32), idesc_s,
+                    k > 0 ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          umma_bf16(tmem + KV_COL_DP, umma_desc_kmajor(v_addr + k * 32), umma_desc_kmajor(do_addr + k * 32), idesc_s,
+                    k > 0 ? 1u : 0u);
+        umma_commit(s_full);
+        umma_commit(&ld_free[st]);  // one of the two arrivals (the gradient MMAs read the stage too)
+        if (i == N - 1) umma_commit(&kv_free[kvb]);
+      }
+      __syncwarp();
+      MTACC(2);
+      if (++st == KV_RING) {
+        st = 0;
+        ++round;
+      }
+      if (++i == N) {
+        i = 0;
+        ++it;
+      }
+    }
+    MTACC_WRITE();
+  } else if (warp == KV_MMA2_WARP) {
+    // ---------------- MMA issuer 2: dV += P^T dO_g, dK += dS^T Q_g, A operands from TMEM ----------------
+    constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+    const bool leader = elect_one();
+    int it = 0, i = 0;
+    uint32_t st = 0, round = 0;
+    for (uint32_t g = 0; g < chunks; ++g) {
+      mbar_wait(pt_full, g & 1u);
+      mbar_wait(&ld_full[st], round & 1u);  // long complete (the score MMAs read the same stage); orders this warp too
+      if (i == 0 && it > 0) mbar_wait(out_free, (it - 1) & 1);  // the previous tile's accumulators have been drained
+      tc_fence_after();
+      if (leader) {
+        const uint32_t q_addr = smem_u32(sQ + st * CH), do_addr = smem_u32(sdO + st * CH);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          umma_bf16_ts(tmem + KV_COL_DV, tmem + KV_COL_PT + k * 8, umma_desc_mnmajor(do_addr + k * 2048, CH), idesc_o,
+                       (i > 0 || k > 0) ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          umma_bf16_ts(tmem + KV_COL_DK, tmem + KV_COL_DST + k * 8, umma_desc_mnmajor(q_addr + k * 2048, CH), idesc_o,
+                       (i > 0 || k > 0) ? 1u : 0u);
+        umma_commit(pt_free);
+        umma_commit(&ld_free[st]);
+        if (i == N - 1) umma_commit(out_full);
+      }
+      __syncwarp();
+      if (++st == KV_RING) {
+        st = 0;
+        ++round;
+      }
+      if (++i == N) {
+        i = 0;
+        ++it;
+      }
+    }
+  } else {
+    // ---------------- row threads ----------------
+    // thread (r, qd): key row r of the tile, queries [32 qd, 32 qd + 32) of every 128-query chunk
+    const int r = tid & 127, qd = tid >> 7, ew = warp & 3;
     const uint32_t lane_base = tmem + (static_cast<uint32_t>(ew * 32) << 16);
     const float sl2 = a.scale_log2;
     const bool dropping = a.drop.thresh != 0u;
     const float c1 = a.drop.scale * a.scale;
     ATACC_DECL;
     // Inputs are fetched ahead of their use so that their global-memory latency hides behind the arithmetic:
-    // the key's keep decisions over the chunk's queries (key-major layout, word 2 i + hq) one chunk ahead,
-    // and the row statistics -lse2 and -D * scale of queries tid, tid + 256 one (batch, head) ahead.
+    // the key's keep decisions over the chunk's queries (key-major layout, word 4 i + qd) one chunk ahead.
     auto fetch_keep = [&](uint32_t g) -> uint32_t {
       if (!dropping || g >= chunks) return 0xffffffffu;
-      const int t = t0 + static_cast<int>(g / M), i = static_cast<int>(g % M);
+      const int t = t0 + static_cast<int>(g / N), i = static_cast<int>(g % N);
       const int bh = t / N, kt = t - bh * N;
       const int key = kt * 128 + r;
       if (key >= S) return 0xffffffffu;
-      return ldg_issue_u32(a.keep + (static_cast<size_t>(bh) * S + key) * (8 * N) + 4 * N + 2 * i + hq);
-    };
-    float nlse_next[2] = {-INFINITY, -INFINITY}, nds_next[2] = {0.0f, 0.0f};
-    auto fetch_stats = [&](int t) {
-      const size_t stat = static_cast<size_t>(t / N) * S;
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        const int q = tid + u * BW_ROW_THREADS;
-        nlse_next[u] = q < S ? -ldg_issue_f32(a.lse2 + stat + q) : -INFINITY;
-        nds_next[u] = q < S ? -ldg_issue_f32(a.dsum + stat + q) * a.scale : 0.0f;
-      }
+      return ldg_issue_u32(a.keep + (static_cast<size_t>(bh) * S + key) * (8 * N) + 4 * N + 4 * i + qd);
     };
     uint32_t keep_next = fetch_keep(0);
-    if (t0 < t1) fetch_stats(t0);
-    int prev_bh = -1;
-    for (int t = t0, it = 0; t < t1; ++t, ++it) {
+    int prev_bh = -1, nbh = 0;
+    const float* s_lse = s_stat;
+    const float* s_dsum = s_stat + 512;
+    const int half = tid >> 8;                    // 0: drains dV, 1: drains dK
+    const int hq = (tid >> 7) & 1;                // column half of the drained accumulator
+    const bool storer = (tid & 255) == ew * 32;   // one storing thread per (half, lane quarter)
+    int release_kvb = -1;  // storing threads: K / V buffer whose output store has not been waited for yet
+    // Storing threads: hand a staged K / V buffer back to the producer once its output store has read it.  Called
+    // before every wait that could depend on the producer (the store itself depends on nothing), one chunk or more
+    // after the store was issued, so that it practically never blocks.
+    auto release_staged = [&]() {
+      if (storer && release_kvb >= 0) {
+        tma_wait_group_read<0>();
+        mbar_arrive(&kv_free[release_kvb]);
+        release_kvb = -1;
+      }
+    };
+    // ---- drain of tile it_d: accumulator -> bf16 -> swizzled smem (the tile's V / K buffer: its score MMAs have
+    // completed) -> TMA stores, per (half, TMEM lane quarter): 2 warps, named barrier, box of 32 rows.  Rows of
+    // masked keys hold garbage (their probabilities are not forced to zero in the loop): they get exact zeros.
+    // P^T was accumulated without the dropout scale: dV takes it here.
+    auto drain = [&](int it_d) {
+      const int t = t0 + it_d;
       const int bh = t / N, kt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
-      const uint32_t g0 = static_cast<uint32_t>(it) * M;
-      if (bh != prev_bh) {
-        // p = exp2(s * sl2 + nlse) and ds = p * (dp * c1 + nds); nobody may still read the old statistics
-        if (it > 0) named_bar_sync(1, BW_ROW_THREADS);
+      const int kvb = it_d & 1;
+      const int key = kt * 128 + r;
+      const bool key_ok = key < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + key] != 0);
+      uint8_t* stage = (half == 0 ? sV : sK) + kvb * CH;
+      const float mul = half == 0 ? a.drop.scale : 1.0f;
+      release_staged();
+      mbar_wait(out_full, it_d & 1);
+      tc_fence_after();
+      uint32_t v[32];
+      tmem_ld_32x32(lane_base + (half == 0 ? KV_COL_DV : KV_COL_DK) + hq * 32, v);
+      tmem_wait_ld();
+      tc_fence_before();
+      mbar_arrive(out_free);
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
-          s_lse[tid + u * BW_ROW_THREADS] = nlse_next[u];
-          s_dsum[tid + u * BW_ROW_THREADS] = nds_next[u];
-        }
-        named_bar_sync(1, BW_ROW_THREADS);
+      for (int q4 = 0; q4 < 4; ++q4) {
+        float f[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = key_ok ? __uint_as_float(v[q4 * 8 + e]) * mul : 0.0f;
+        st_tile16(stage, r, hq * 4 + q4, f);
+      }
+      fence_proxy_async_smem();
+      const uint32_t bar_id = 2 + half * 4 + ew;  // the two warps of (half, lane quarter)
+      named_bar_sync(bar_id, 64);
+      // V block is the third H-wide slab of dqkv, K the second; rows beyond S are clipped by the map
+      const int slab = half == 0 ? 2 * a.H : a.H;
+      if (storer) {
+        tma_store_3d(&tm_dqkv, stage + ew * 4096, slab + h * 64, kt * 128 + ew * 32, b);
+        tma_commit_group();
+        release_kvb = kvb;  // the buffer goes back to the producer once the store has read it (checked lazily)
+      }
+      if (a.dbias != nullptr) {
+        // gradients of the value / key biases: column sums of the quarter's 32 staged rows (rows of masked or
+        // out-of-range keys are exact zeros)
+        const int col = (r & 31) + 32 * hq;
+        atomicAdd(a.dbias + slab + h * 64 + col, staged_colsum(stage, ew * 32, 32, col));
+        named_bar_sync(bar_id, 64);  // the quarter's column sums have been read before the buffer can be released
+      }
+      ATACC(6);
+    };
+    int pending = -1;  // tile whose accumulators have not been drained yet
+    uint32_t g = 0;
+    for (int t = t0, it = 0; t < t1; ++t, ++it) {
+      const int bh = t / N;
+      if (bh != prev_bh) {
+        if (prev_bh >= 0) mbar_arrive(&st_free[(nbh - 1) & 1]);  // done with the previous (batch, head)'s statistics
+        release_staged();  // (the producer stages the statistics after it has got this tile's K / V buffers back)
+        mbar_wait(&st_full[nbh & 1], (nbh >> 1) & 1);
+        s_lse = s_stat + (nbh & 1) * 1024;
+        s_dsum = s_lse + 512;
         prev_bh = bh;
-        // the next (batch, head) this CTA will meet, if any
-        const int tn = (bh + 1) * N;
-        if (tn < t1) fetch_stats(tn);
+        ++nbh;
       }
       ATACC(7);
-      for (int i = 0; i < M; ++i) {
-        const uint32_t g = g0 + i;
+      for (int i = 0; i < N; ++i, ++g) {
         const uint32_t bits = keep_next;
         keep_next = fetch_keep(g + 1);
-        mbar_wait(bar_s, g & 1);
+        release_staged();
+        mbar_wait(s_full, g & 1u);
         ATACC(1);
         tc_fence_after();
         uint32_t vs[32], vd[32];
-        tmem_ld_32x32(lane_base + COL_S + hq * 32, vs);
-        tmem_ld_32x32(lane_base + COL_DP + hq * 32, vd);
+        tmem_ld_32x32(lane_base + KV_COL_S + qd * 32, vs);
+        tmem_ld_32x32(lane_base + KV_COL_DP + qd * 32, vd);
         tmem_wait_ld();
         tc_fence_before();
-        mbar_arrive(bar_sfree);
+        mbar_arrive(s_free);
         ATACC(2);
-        const int q0 = i * 64 + hq * 32;
-        uint4 ppk[4], dpk[4];
+        const int q0 = i * 128 + qd * 32;
+        uint32_t ppk[16], dpk[16];
 #pragma unroll
         for (int gq = 0; gq < 4; ++gq) {
-          float pt[8], ds[8];
           const float4 l0 = *reinterpret_cast<const float4*>(s_lse + q0 + gq * 8);
           const float4 l1 = *reinterpret_cast<const float4*>(s_lse + q0 + gq * 8 + 4);
           const float4 d0 = *reinterpret_cast<const float4*>(s_dsum + q0 + gq * 8);
@@ -1190,93 +1323,56 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
           const float nlse[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w};
           const float nds[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const bool keep = (bits >> (gq * 8 + e)) & 1u;
-            const float p = fast_exp2(fmaf(__uint_as_float(vs[gq * 8 + e]), sl2, nlse[e]));
-            const float dp = keep ? __uint_as_float(vd[gq * 8 + e]) : 0.0f;
-            pt[e] = keep ? p : 0.0f;
-            ds[e] = p * fmaf(dp, c1, nds[e]);
+          for (int e = 0; e < 8; e += 2) {
+            const int c = gq * 8 + e;
+            const bool keep0 = (bits >> c) & 1u, keep1 = (bits >> (c + 1)) & 1u;
+            const float p0 = fast_exp2(fmaf(__uint_as_float(vs[c]), sl2, nlse[e]));
+            const float p1 = fast_exp2(fmaf(__uint_as_float(vs[c + 1]), sl2, nlse[e + 1]));
+            const float dp0 = keep0 ? __uint_as_float(vd[c]) : 0.0f;
+            const float dp1 = keep1 ? __uint_as_float(vd[c + 1]) : 0.0f;
+            ppk[c >> 1] = pack_bf16x2(keep0 ? p0 : 0.0f, keep1 ? p1 : 0.0f);
+            dpk[c >> 1] = pack_bf16x2(p0 * fmaf(dp0, c1, nds[e]), p1 * fmaf(dp1, c1, nds[e + 1]));
           }
-          ppk[gq] = make_uint4(pack_bf16x2(pt[0], pt[1]), pack_bf16x2(pt[2], pt[3]), pack_bf16x2(pt[4], pt[5]),
-                               pack_bf16x2(pt[6], pt[7]));
-          dpk[gq] = make_uint4(pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]), pack_bf16x2(ds[4], ds[5]),
-                               pack_bf16x2(ds[6], ds[7]));
         }
         ATACC(3);
-        // the operand buffers are needed only now: the previous chunk's dV / dK MMAs have had the whole
+        // the operand columns are needed only now: the previous chunk's gradient MMAs have had the whole
         // computation to finish
-        if (g >= 1) mbar_wait(bar_ptfree, (g - 1) & 1);
+        if (g >= 1) mbar_wait(pt_free, (g - 1u) & 1u);
         ATACC(4);
-#pragma unroll
-        for (int gq = 0; gq < 4; ++gq) {
-          st_tile16p(sPt, r, hq * 4 + gq, ppk[gq]);
-          st_tile16p(sdSt, r, hq * 4 + gq, dpk[gq]);
-        }
-        fence_proxy_async_smem();
-        tc_fence_before();
-        mbar_arrive(bar_pt);
-        ATACC(5);
-      }
-      // ---- drain: dV and dK of the tile -> bf16 -> swizzled smem (the operand buffers: every MMA of the
-      // tile has completed) -> TMA stores, per TMEM lane quarter (2 warps, named barrier 2 + ew, box of 32
-      // rows).  Rows of masked keys hold garbage (their probabilities are not forced to zero in the loop):
-      // they get exact zeros.  P^T was accumulated without the dropout scale: dV takes it here.
-      {
-        const int key = kt * 128 + r;
-        const bool key_ok = key < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + key] != 0);
-        mbar_wait(bar_out, it & 1);
         tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {  // c = 0: dV, c = 1: dK; 32 columns per thread
-          uint32_t v[32];
-          tmem_ld_32x32(lane_base + COL_DV + c * 64 + hq * 32, v);
-          tmem_wait_ld();
-          const float mul = c == 0 ? a.drop.scale : 1.0f;
-          uint8_t* tile = c == 0 ? sPt : sdSt;
-#pragma unroll
-          for (int q4 = 0; q4 < 4; ++q4) {
-            float f[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e) f[e] = key_ok ? __uint_as_float(v[q4 * 8 + e]) * mul : 0.0f;
-            st_tile16(tile, r, hq * 4 + q4, f);
-          }
-        }
+        tmem_st_32x16(lane_base + KV_COL_PT + qd * 16, ppk);
+        tmem_st_32x16(lane_base + KV_COL_DST + qd * 16, dpk);
+        tmem_wait_st();
         tc_fence_before();
-        fence_proxy_async_smem();
-        named_bar_sync(2 + ew, 64);
-        if (tid == ew * 32) {
-          // V block is the third H-wide slab of dqkv, K the second; rows beyond S are clipped by the map
-          tma_store_3d(&tm_dqkv, sPt + ew * 4096, 2 * a.H + h * 64, kt * 128 + ew * 32, b);
-          tma_store_3d(&tm_dqkv, sdSt + ew * 4096, a.H + h * 64, kt * 128 + ew * 32, b);
-          tma_commit_group();
+        mbar_arrive(pt_full);
+        ATACC(5);
+        // The previous tile is drained AFTER this tile's first chunk: by then its last gradient MMAs have certainly
+        // completed, so nobody idles on them.
+        if (pending >= 0) {
+          drain(pending);
+          pending = -1;
         }
-        if (a.dbias != nullptr) {
-          // gradients of the value and key biases: column sums of the quarter's 32 staged rows (rows of
-          // masked or out-of-range keys are exact zeros)
-          const int col = (r & 31) + 32 * hq;
-          atomicAdd(a.dbias + 2 * a.H + h * 64 + col, staged_colsum(sPt, ew * 32, 32, col));
-          atomicAdd(a.dbias + a.H + h * 64 + col, staged_colsum(sdSt, ew * 32, 32, col));
-        }
-        if (tid == ew * 32) tma_wait_group_read<0>();  // the next tile's first chunk overwrites these rows
-        named_bar_sync(2 + ew, 64);
-        ATACC(6);
       }
+      pending = it;
     }
+    if (pending >= 0) drain(pending);
+    release_staged();
     if (tid == 0) ATACC_WRITE();
+    if ((tid & 255) < 128 && (tid & 31) == 0) tma_wait_group<0>();  // the eight storing threads
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == BW_CTRL_WARP) {
+  if (warp == KV_MMA_WARP) {
     tc_fence_after();
-    tmem_dealloc(tmem, 256);
+    tmem_dealloc(tmem, 512);
   }
   if (tid == 0) ATRACE(9);
 }
 
 int fwd_smem_bytes() { return 2 * CH + 2 * FW_RING * KCB + 6 * KC * 4 + 512 + 1024; }
 int dq_smem_bytes() { return 4 * CH + (DQ_KRING + DQ_VRING) * HC + 2048 + 2048 + 512 + 1024; }
-int dkv_smem_bytes() { return CH * 4 + HC * 4 + 4096 + 256 + 1024; }
+int dkv_smem_bytes() { return 4 * CH + 2 * KV_RING * CH + 8192 + 256 + 1024; }
 
 AttnArgs make_args(const AttnPlan& p, const uint8_t* key_mask, DropKey drop) {
   AttnArgs a;
@@ -1404,6 +1500,7 @@ int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, c
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dkv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         dkv_smem_bytes()));
+    BQA_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dkv_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     once.mark_done(once_dev);
   }
   AttnArgs a = make_args(plan, key_mask, drop);
@@ -1430,9 +1527,8 @@ int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, c
     attn_bwd_dq_kernel<false><<<grid, DQ_THREADS, dq_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_q64, plan.tm_dctx,
                                                                           plan.tm_dqkv, a);
   if (check_launch("attn_bwd_dq")) return 1;
-  const int grid_kv = grid;  // two co-resident CTAs per SM as well
-  attn_bwd_dkv_kernel<<<grid_kv, BW_THREADS, dkv_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_q64, plan.tm_do64,
-                                                                     plan.tm_dqkv32, a);
+  const int grid_kv = tiles < sms ? tiles : sms;  // one CTA per SM (it owns the whole tensor memory)
+  attn_bwd_dkv_kernel<<<grid_kv, KV_THREADS, dkv_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_dctx, plan.tm_dqkv32, a);
   return check_launch("attn_bwd_dkv");
 }
 

@@ -217,7 +217,10 @@ struct bqa_handle {
   struct Timed {
     cudaEvent_t a, b;
     double flops;
-    int kind;  // 0 = GEMM forward, 1 = dgrad, 2 = wgrad, 3 = attention forward, 4 = attention backward
+    // 0 = GEMM forward, 1 = dgrad, 2 = wgrad, 3 = attention forward, 4 = attention backward (flops = matmul FLOPs);
+    // 5 = LayerNorm forward, 6 = LayerNorm backward, 7 = embeddings + LayerNorm forward, 8 = embedding backward
+    // (flops = algorithmic HBM bytes)
+    int kind;
   };
   // side stream on which the attention-dropout keep bits of all layers are generated while the main
   // stream runs the embeddings and the first GEMMs (the decisions depend only on the step's keys)
@@ -513,7 +516,7 @@ int bqa_profile_end(bqa_handle* h, double* host_ms, double* host_flops, int64_t*
     return 1;
   }
   h->profiling = false;
-  for (int k = 0; k < 5; ++k) {
+  for (int k = 0; k < BQA_PROFILE_KINDS; ++k) {
     host_ms[k] = 0.0;
     host_flops[k] = 0.0;
     host_count[k] = 0;
@@ -617,10 +620,13 @@ int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_ty
     }
   }
   h->bits_ahead = false;
+  // algorithmic bytes: three fp32 table rows in, two bf16 rows out per token
+  h->time_begin(7, static_cast<double>(T) * H * (3 * 4 + 2 * 2), st);
   if (launch_embed_ln_fwd(input_ids, token_type_ids, attention_mask, h->P(Y.word_emb), h->P(Y.pos_emb),
                           h->P(Y.type_emb), h->P(Y.emb_ln_g), h->P(Y.emb_ln_b), w.z0, w.x0, w.ids, w.tt, w.mask, T, S,
                           H, c.vocab, c.type_vocab, c.ln_eps, h->key(site_embed(), c.hidden_dropout), w.err_flag, st))
     return 1;
+  h->time_end(st);
   h->launches += 1;
   const int slots = static_cast<int>(w.layer.size());
   const DropKey nodrop = make_drop_key(0, 0, 0.0f);
@@ -634,10 +640,15 @@ int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_ty
     if (attn_forward(lp.attn, mask, h->key(site_attn(l), c.attn_dropout), st, /*bits_ready=*/true)) return 1;
     h->time_end(st);
     if (launch_gemm(h, lp.ao, h->key(site_ao(l), c.hidden_dropout), st)) return 1;
+    const double ln_fwd_bytes = static_cast<double>(T) * H * 2 * 2;  // one bf16 row in, one out
+    h->time_begin(5, ln_fwd_bytes, st);
     if (launch_ln_fwd(act.z1, h->P(lo + Y.ln1_g), h->P(lo + Y.ln1_b), act.a, T, H, c.ln_eps, st)) return 1;
+    h->time_end(st);
     if (launch_gemm(h, lp.ffn1, nodrop, st)) return 1;
     if (launch_gemm(h, lp.ffn2, h->key(site_ffn(l), c.hidden_dropout), st)) return 1;
+    h->time_begin(5, ln_fwd_bytes, st);
     if (launch_ln_fwd(act.z2, h->P(lo + Y.ln2_g), h->P(lo + Y.ln2_b), act.x_out, T, H, c.ln_eps, st)) return 1;
+    h->time_end(st);
     h->launches += 3;
   }
   const bf16* y = w.layer[(c.num_layers - 1) % slots].x_out;
@@ -797,19 +808,24 @@ int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* s
       const bf16* dy_in = ((l + 1) & 1) ? w.dy1 : w.dy0;  // gradient w.r.t. this layer's output
       const bool hd = c.hidden_dropout > 0.0f;
       // LN2 backward: dres = d z2 (residual branch), dgm = d (ffn2 GEMM output) = dres * keep-mask
+      const double ln_bwd_bytes = static_cast<double>(T) * H * 2 * (hd ? 4 : 3);  // dy, z in; dz (+ masked dz) out
+      h->time_begin(6, ln_bwd_bytes, st);
       if (launch_ln_bwd(dy_in, act.z2, h->P(lo + Y.ln2_g), w.dres, hd ? w.dgm : w.dres, h->G(lo + Y.ln2_g),
                         h->G(lo + Y.ln2_b), h->G(lo + Y.o_b), T, H, c.ln_eps, nodrop,
                         h->key(site_ffn(l), c.hidden_dropout), h->num_sms, st))
         return 1;
+      h->time_end(st);
       if (launch_gemm(h, lp.w_ffn2, nodrop, st)) return 1;
       if (launch_gemm(h, lp.d_ffn2, nodrop, st)) return 1;  // du = (dgm . W2) * gelu'(u)
       if (launch_gemm(h, lp.w_ffn1, nodrop, st)) return 1;
       if (launch_gemm(h, lp.d_ffn1, nodrop, st)) return 1;  // da = du . W1 + dres   (into the dctx slab)
       // LN1 backward on da
+      h->time_begin(6, ln_bwd_bytes, st);
       if (launch_ln_bwd(w.dctx, act.z1, h->P(lo + Y.ln1_g), w.dres, hd ? w.dgm : w.dres, h->G(lo + Y.ln1_g),
                         h->G(lo + Y.ln1_b), h->G(lo + Y.ao_b), T, H, c.ln_eps, nodrop,
                         h->key(site_ao(l), c.hidden_dropout), h->num_sms, st))
         return 1;
+      h->time_end(st);
       if (launch_gemm(h, lp.w_ao, nodrop, st)) return 1;
       if (launch_gemm(h, lp.d_ao, nodrop, st)) return 1;  // dctx = dgm . Wo
       h->time_begin(4, attn_flops(h, B, S, true), st);
@@ -823,12 +839,17 @@ int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* s
     } else {
       // embeddings: x0 = dropout(LN(z0)); dz0 scattered into the three tables
       const bf16* dy_in = w.dy0;  // layer 0 wrote its input gradient into dy[0 & 1]
+      h->time_begin(6, static_cast<double>(T) * H * 2 * 3, st);
       if (launch_ln_bwd(dy_in, w.z0, h->P(Y.emb_ln_g), w.dres, nullptr, h->G(Y.emb_ln_g), h->G(Y.emb_ln_b), nullptr,
                         T, H, c.ln_eps, h->key(site_embed(), c.hidden_dropout), nodrop, h->num_sms, st))
         return 1;
+      h->time_end(st);
+      // one bf16 row in per token for each of the two kernels; one fp32 table row read-modify-written per token
+      h->time_begin(8, static_cast<double>(T) * H * (2 * 2 + 2 * 4), st);
       if (launch_embed_bwd(w.dres, w.ids, w.tt, h->G(Y.word_emb), h->G(Y.pos_emb), h->G(Y.type_emb), T, S, H,
                            c.vocab, c.type_vocab, /*pad_token_id (BertConfig default)=*/0, st))
         return 1;
+      h->time_end(st);
       h->launches += 2;
     }
   }

@@ -203,10 +203,13 @@ class Engine:
         L.check(L.lib.bqa_profile_begin(self.handle), "bqa_profile_begin")
 
     def profile_end(self):
-        """-> {kind: (ms, flops, launches)} for the tensor-core kernels launched since profile_begin."""
-        ms, fl, n = (ctypes.c_double * 5)(), (ctypes.c_double * 5)(), (L.c_i64 * 5)()
+        """-> {kind: (ms, work, launches)} for the kernels launched since profile_begin; work = matmul FLOPs for
+        the GEMM / attention kinds, algorithmic HBM bytes for the row kernels (include/bqa.h)."""
+        K = 9  # BQA_PROFILE_KINDS
+        ms, fl, n = (ctypes.c_double * K)(), (ctypes.c_double * K)(), (L.c_i64 * K)()
         L.check(L.lib.bqa_profile_end(self.handle, ms, fl, n), "bqa_profile_end")
-        names = ("gemm_fwd", "gemm_dgrad", "gemm_wgrad", "attn_fwd", "attn_bwd")
+        names = ("gemm_fwd", "gemm_dgrad", "gemm_wgrad", "attn_fwd", "attn_bwd", "ln_fwd", "ln_bwd", "embed_fwd",
+                 "embed_bwd")
         return {k: (ms[i], fl[i], int(n[i])) for i, k in enumerate(names)}
 
     def launch_count(self):

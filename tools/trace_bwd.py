@@ -37,3 +37,6 @@ for p in (0.1, 0.0):
     print(f"--- dkv kernel (last launched), dropout {p}: cycles per CTA {total.mean():.0f}; per chunk {total.mean() / chunks:.0f}")
     for k in range(1, 9):
         print(f"  {names[k]:>22s}: {t[:, k].mean():9.0f} per CTA  {t[:, k].mean() / chunks:8.0f} per chunk  {t[:, k].mean() / total.mean() * 100:5.1f}%")
+    allchunks = 1152 * 3 / 148
+    for k, nm in ((13, "score-MMA warp: wait operands (TMA)"), (14, "score-MMA warp: wait S/dP columns free"), (15, "score-MMA warp: issue + commits")):
+        print(f"  {nm:>44s}: {t[:, k].mean() / allchunks:8.0f} per chunk (all chunks)  {t[:, k].mean() / total.mean() * 100:5.1f}%")
