@@ -6,6 +6,7 @@ and runs torch.max / softmax there (predictor.py:111-120); here bqa_decode produ
 indices, class ids and scores on the device and only those ~7 small vectors are copied.  The
 per-document candidate selection (predictor.py:63-87) is unchanged host logic.
 """
+import dataclasses
 import logging
 from collections import defaultdict
 from dataclasses import dataclass
@@ -24,6 +25,47 @@ class PredictorCandidate:
     start_reg: float
     end_reg: float
     label: int
+
+
+class DocumentShard:
+    """Every `world`-th document of a chunk dataset, starting at `rank`.  A dataset item is ALL chunks of one
+    document (validation_dataset.py:42-319), so every chunk of a document is scored on the same rank and the
+    per-document best-candidate rule of the Predictor (predictor.py:63-87) needs no communication; only the
+    per-document winners are gathered at the end (`gather_predictions`)."""
+
+    def __init__(self, dataset, rank, world):
+        self.dataset = dataset
+        self.indices = list(range(rank, len(dataset), world))
+
+    def __len__(self):
+        return len(self.indices)
+
+    def __getitem__(self, i):
+        return self.dataset[self.indices[i]]
+
+
+def gather_predictions(predictor, dst=0, group=None):
+    """Data-parallel validation: merges the per-document winners of every rank's Predictor into rank `dst`'s
+    `scores` / `candidates` / `items` (documents are disjoint across ranks under DocumentShard; should an item_id
+    appear twice, the higher score wins, which is the Predictor's own rule).  Returns the number of documents on
+    `dst`, 0 elsewhere.  No-op without an initialised process group."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return len(predictor.candidates)
+    payload = {k: (predictor.scores[k], dataclasses.astuple(predictor.candidates[k]), predictor.items.get(k))
+               for k in predictor.candidates}
+    gathered = [None] * dist.get_world_size(group)
+    dist.all_gather_object(gathered, payload, group=group)
+    if dist.get_rank(group) != dst:
+        return 0
+    for part in gathered:
+        for k, (score, cand, item) in part.items():
+            if k in predictor.candidates and predictor.scores[k] >= score:
+                continue
+            predictor.scores[k] = score
+            predictor.candidates[k] = PredictorCandidate(*cand)
+            predictor.items[k] = item
+    return len(predictor.candidates)
 
 
 class Predictor:

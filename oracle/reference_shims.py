@@ -1,8 +1,9 @@
 """Makes the UNMODIFIED reference importable in this authoring container.  TEST INFRASTRUCTURE ONLY.
 
-Used by oracle/make_golden.py (golden-vector generation) and by tests that are skipped when
-/root/reference is absent (it does not exist on the GPU box).  Nothing is copied from the
-reference: its modules are imported from where they lie, after installing the stand-ins that
+Used by oracle/make_golden.py (golden-vector generation), oracle/ref_runner.py (the timed CPU arm of
+bench.py) and by tests that are skipped when no reference tree is available.  The reference's modules
+are imported unmodified — from /root/reference where that exists, else from the staged copy
+oracle/_ref (oracle/stage_ref.py; git-ignored) — after installing the stand-ins that
 SURVEY.md §8c lists for dependencies this image lacks:
   nltk            -> empty module (only used for sentence splitting of real data)
   configargparse  -> the argparse-based shim of the product package (-c files, key=value lines)
@@ -13,7 +14,18 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = os.environ.get("BQA_REFERENCE_ROOT", "/root/reference")
+def _find_reference_root():
+    """/root/reference in the authoring container; on the GPU box the unmodified copy that
+    oracle/stage_ref.py put under oracle/_ref (git-ignored, travels with the snapshot)."""
+    env = os.environ.get("BQA_REFERENCE_ROOT")
+    if env:
+        return env
+    if os.path.isdir("/root/reference/modules"):
+        return "/root/reference"
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+REFERENCE_ROOT = _find_reference_root()
 REFERENCE_MODULES = os.path.join(REFERENCE_ROOT, "modules")
 
 

@@ -144,6 +144,48 @@ def test_gradient_allreduce_mean_gloo_world2(tmp_path):
     assert torch.equal(f0, f1)
 
 
+def _shard_worker(rank, world, port, tmp):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from __graft_entry__ import load_package
+    load_package()
+    Pm = importlib.import_module("bqa_b200.modules.model.inference.predictor")
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    docs = [[f"doc{d}-chunk{c}" for c in range(1 + d % 3)] for d in range(7)]
+    shard = Pm.DocumentShard(docs, rank, world)
+    mine = [shard[i] for i in range(len(shard))]
+    # a Predictor-shaped holder of this rank's per-document winners (no model needed for the merge logic)
+    pred = Pm.Predictor.__new__(Pm.Predictor)
+    from collections import defaultdict
+    pred.scores, pred.candidates, pred.items = defaultdict(int), {}, {}
+    for chunks in mine:
+        doc = chunks[0].split("-")[0]
+        pred.scores[doc] = float(len(chunks)) + rank
+        pred.candidates[doc] = Pm.PredictorCandidate(start_id=len(chunks), end_id=len(chunks) + 1, start_reg=0.5,
+                                                     end_reg=0.75, label=rank)
+        pred.items[doc] = chunks[-1]
+    n = Pm.gather_predictions(pred)
+    torch.save((mine, n, dict(pred.scores), {k: (v.start_id, v.label) for k, v in pred.candidates.items()},
+                dict(pred.items)), os.path.join(tmp, f"s{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_document_sharded_prediction_merge_gloo_world2(tmp_path):
+    """BASELINE configs[4] on N ranks: documents (not chunks) are dealt to the ranks, every rank keeps the best
+    candidate of ITS documents (predictor.py:63-87), rank 0 ends up with all of them."""
+    import torch.multiprocessing as mp
+    port = 31500 + os.getpid() % 2000
+    mp.spawn(_shard_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    (d0, n0, sc0, c0, it0), (d1, n1, sc1, c1, it1) = (torch.load(tmp_path / f"s{r}.pt") for r in range(2))
+    all_docs = sorted(ch[0].split("-")[0] for ch in d0 + d1)
+    assert all_docs == [f"doc{d}" for d in range(7)]                          # disjoint and complete
+    assert all(len({c.split("-")[0] for c in chunks}) == 1 for chunks in d0 + d1)  # a document never straddles ranks
+    assert n0 == 7 and n1 == 0 and sorted(c0) == all_docs
+    assert c0["doc1"] == (2, 1) and c0["doc2"] == (3, 0) and sc0["doc1"] == 3.0  # rank 1's winner reached rank 0
+    assert it0["doc4"] == "doc4-chunk1" and it0["doc5"] == "doc5-chunk2"
+    assert sorted(c1) == ["doc1", "doc3", "doc5"]                             # other ranks keep only their own
+
+
 def test_dropout_hash_is_deterministic_and_calibrated():
     from oracle.dropout_hash import drop_key, keep_mask
     a = keep_mask(1234, 7, 0.1, 200000)
