@@ -197,6 +197,13 @@ typedef struct bqa_config {
   int32_t num_layers, hidden, heads, intermediate;
   int32_t vocab, max_pos, type_vocab, num_labels;
   float ln_eps, hidden_dropout, attn_dropout;
+  /* Embedding conventions of the encoder family (ABI version 4).  pad_token_id: row of the word table that is
+   * nn.Embedding's padding_idx and receives no gradient (BERT 0, RoBERTa 1).  position_mode 0 (BERT,
+   * modeling_bert.py:72-112): position id = index in the sequence.  position_mode 1 (RoBERTa, the reference's
+   * second `--model` choice, model.py:9-10 -> RobertaModel; modeling_roberta.py create_position_ids_from_input_ids):
+   * position id = pad_token_id + (number of non-padding tokens up to and including this one) for non-padding
+   * tokens, pad_token_id for padding tokens; that row of the position table is a padding_idx too. */
+  int32_t pad_token_id, position_mode;
 } bqa_config;
 
 /* Element offsets of every parameter tensor inside the flat buffers (fp32 master, fp32

@@ -9,7 +9,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbqa.so")
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 EPI_LINEAR, EPI_GELU_FWD, EPI_GELU_BWD, EPI_F32_ADD = 0, 1, 2, 3
 CLS_SMOOTH, CLS_CE, CLS_FOCAL = 0, 1, 2
@@ -38,7 +38,8 @@ class GemmDesc(ctypes.Structure):
 class Config(ctypes.Structure):
     _fields_ = [("num_layers", c_i32), ("hidden", c_i32), ("heads", c_i32), ("intermediate", c_i32),
                 ("vocab", c_i32), ("max_pos", c_i32), ("type_vocab", c_i32), ("num_labels", c_i32),
-                ("ln_eps", c_f32), ("hidden_dropout", c_f32), ("attn_dropout", c_f32)]
+                ("ln_eps", c_f32), ("hidden_dropout", c_f32), ("attn_dropout", c_f32),
+                ("pad_token_id", c_i32), ("position_mode", c_i32)]
 
 
 LAYOUT_FIELDS = ["word_emb", "pos_emb", "type_emb", "emb_ln_g", "emb_ln_b", "layer0", "layer_stride",

@@ -12,7 +12,7 @@ extern "C" {
 
 const char* bqa_last_error(void) { return bqa::last_error(); }
 
-int bqa_abi_version(void) { return 3; }
+int bqa_abi_version(void) { return 4; }
 
 int bqa_gemm_bf16(const bqa_gemm_desc* d, void* stream) {
   if (d == nullptr) {

@@ -34,7 +34,8 @@ inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 int compute_layout(const bqa_config& c, bqa_layout* L) {
   if (c.num_layers < 1 || c.hidden < 64 || c.hidden % 64 != 0 || c.heads * 64 != c.hidden || c.hidden > 1024 ||
       c.intermediate % 64 != 0 || c.intermediate < 64 || c.vocab < 1 || c.max_pos < 1 || c.type_vocab < 1 ||
-      c.type_vocab > 2 || c.num_labels < 1 || c.num_labels > 32) {
+      c.type_vocab > 2 || c.num_labels < 1 || c.num_labels > 32 || c.pad_token_id < 0 || c.pad_token_id >= c.vocab ||
+      (c.position_mode != 0 && c.position_mode != 1)) {
     set_error("config: unsupported shape (L=%d H=%d A=%d I=%d V=%d P=%d TV=%d C=%d): need H = 64*A <= 1024, "
               "H and I multiples of 64, type_vocab <= 2",
               c.num_layers, c.hidden, c.heads, c.intermediate, c.vocab, c.max_pos, c.type_vocab, c.num_labels);
@@ -114,6 +115,7 @@ struct Workspace {
   float *loss_rows, *dpre, *dx0;
   uint8_t* mask;
   int64_t *ids, *tt;
+  int32_t* pos_ids;  // position ids of the forward (RoBERTa counts non-padding tokens)
   // backward temporaries
   bf16 *dy0, *dy1, *dres, *dgm, *du, *dctx, *dqkv;
   float* dsum;
@@ -149,6 +151,7 @@ void carve(Workspace* w, uint8_t* base, const bqa_config& c, int B, int S, bool 
   w->mask = b.take<uint8_t>(T);
   w->ids = b.take<int64_t>(T);
   w->tt = b.take<int64_t>(T);
+  w->pos_ids = b.take<int32_t>(T);
   w->err_flag = b.take<int>(1);
   w->loss_rows = b.take<float>(static_cast<uint64_t>(B) * 5);
   if (training) {
@@ -623,8 +626,9 @@ int bqa_forward(bqa_handle* h, const int64_t* input_ids, const int64_t* token_ty
   // algorithmic bytes: three fp32 table rows in, two bf16 rows out per token
   h->time_begin(7, static_cast<double>(T) * H * (3 * 4 + 2 * 2), st);
   if (launch_embed_ln_fwd(input_ids, token_type_ids, attention_mask, h->P(Y.word_emb), h->P(Y.pos_emb),
-                          h->P(Y.type_emb), h->P(Y.emb_ln_g), h->P(Y.emb_ln_b), w.z0, w.x0, w.ids, w.tt, w.mask, T, S,
-                          H, c.vocab, c.type_vocab, c.ln_eps, h->key(site_embed(), c.hidden_dropout), w.err_flag, st))
+                          h->P(Y.type_emb), h->P(Y.emb_ln_g), h->P(Y.emb_ln_b), w.z0, w.x0, w.ids, w.tt, w.mask,
+                          w.pos_ids, T, S, H, c.vocab, c.type_vocab, c.max_pos, c.position_mode, c.pad_token_id, c.ln_eps,
+                          h->key(site_embed(), c.hidden_dropout), w.err_flag, st))
     return 1;
   h->time_end(st);
   h->launches += 1;
@@ -846,8 +850,8 @@ int bqa_backward(bqa_handle* h, int32_t first_phase, int32_t last_phase, void* s
       h->time_end(st);
       // one bf16 row in per token for each of the two kernels; one fp32 table row read-modify-written per token
       h->time_begin(8, static_cast<double>(T) * H * (2 * 2 + 2 * 4), st);
-      if (launch_embed_bwd(w.dres, w.ids, w.tt, h->G(Y.word_emb), h->G(Y.pos_emb), h->G(Y.type_emb), T, S, H,
-                           c.vocab, c.type_vocab, /*pad_token_id (BertConfig default)=*/0, st))
+      if (launch_embed_bwd(w.dres, w.ids, w.tt, w.pos_ids, h->G(Y.word_emb), h->G(Y.pos_emb), h->G(Y.type_emb), T, S, H,
+                           c.vocab, c.type_vocab, c.max_pos, c.position_mode, c.pad_token_id, st))
         return 1;
       h->time_end(st);
       h->launches += 2;

@@ -25,16 +25,18 @@ int launch_ln_fwd(const bf16* z, const float* gamma, const float* beta, bf16* y,
 // ids_kept / tt_kept / mask_kept (each may be null): range-checked private copies of the inputs for the backward
 int launch_embed_ln_fwd(const int64_t* ids, const int64_t* token_type, const uint8_t* key_mask, const float* word,
                         const float* pos, const float* type, const float* gamma, const float* beta, bf16* z0,
-                        bf16* x0, int64_t* ids_kept, int64_t* tt_kept, uint8_t* mask_kept, int T, int S, int H, int V,
-                        int TV, float eps, DropKey drop, int* err_flag, cudaStream_t st);
+                        bf16* x0, int64_t* ids_kept, int64_t* tt_kept, uint8_t* mask_kept, int32_t* pos_kept, int T,
+                        int S, int H, int V, int TV, int P, int pos_mode, int pad_id, float eps, DropKey drop,
+                        int* err_flag, cudaStream_t st);
 int launch_ln_bwd(const bf16* dy, const bf16* z, const float* gamma, bf16* dz, bf16* dz_masked, float* dgamma,
                   float* dbeta, float* dbias, int T, int H, float eps, DropKey drop_in, DropKey drop_out,
                   int num_sms, cudaStream_t st);
 int launch_colsum(const bf16* X, int ld, float* out, int T, int N, int num_sms, cudaStream_t st);
 int launch_prepare_inputs(const int32_t* ids32, int64_t* ids, int64_t* token_type, uint8_t* mask, int B, int S,
                           int sep_id, int type_coef, int* missing_sep, cudaStream_t st);
-int launch_embed_bwd(const bf16* dz0, const int64_t* ids, const int64_t* token_type, float* dword, float* dpos,
-                     float* dtype, int T, int S, int H, int V, int TV, int pad_id, cudaStream_t st);
+int launch_embed_bwd(const bf16* dz0, const int64_t* ids, const int64_t* token_type, const int32_t* pos_ids,
+                     float* dword, float* dpos, float* dtype, int T, int S, int H, int V, int TV, int P, int pos_mode,
+                     int pad_id, cudaStream_t st);
 
 // ---- heads_loss.cu ----------------------------------------------------------------------
 struct HeadParams {  // fp32 master weights of the pooler and the four heads (+ their gradients)

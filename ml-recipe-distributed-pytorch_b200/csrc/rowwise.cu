@@ -220,7 +220,8 @@ embed_ln_fwd_kernel(const int64_t* __restrict__ ids, const int64_t* __restrict__
                     const float* __restrict__ pos, const float* __restrict__ type, const float* __restrict__ gamma,
                     const float* __restrict__ beta, bf16* __restrict__ z0, bf16* __restrict__ x0,
                     int64_t* __restrict__ ids_kept, int64_t* __restrict__ tt_kept, uint8_t* __restrict__ mask_kept,
-                    int T, int S, int H, int V, int TV, float eps, DropKey drop, int* __restrict__ err_flag) {
+                    int32_t* __restrict__ pos_kept, int T, int S, int H, int V, int TV, int P, int pos_mode, int pad_id,
+                    float eps, DropKey drop, int* __restrict__ err_flag) {
   pdl_trigger();  // the next kernel (a GEMM) may start its prologue now; it waits for this grid before reading
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * ROW_WARPS + (threadIdx.x >> 5);
@@ -239,7 +240,20 @@ embed_ln_fwd_kernel(const int64_t* __restrict__ ids, const int64_t* __restrict__
     if (tt_kept != nullptr) tt_kept[row] = tt;
     if (mask_kept != nullptr && key_mask != nullptr) mask_kept[row] = key_mask[row];
   }
-  const int s = row % S;
+  int s = row % S;
+  if (pos_mode != 0) {
+    // RoBERTa: pad_id + (non-padding tokens up to and including this one), pad_id for a padding token
+    const int64_t* seq = ids + static_cast<size_t>(row - s);
+    int cnt = 0;
+    for (int j = lane; j <= s; j += 32) cnt += seq[j] != pad_id ? 1 : 0;
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    s = ids[row] != pad_id ? cnt + pad_id : pad_id;
+  }
+  if (s >= P) {
+    if (lane == 0) atomicExch(err_flag, 1);  // beyond the position table: IndexError in the reference
+    s = 0;
+  }
+  if (lane == 0 && pos_kept != nullptr) pos_kept[row] = s;
   RowVec w, p, t, g, b;
   load_vec_f32(word + static_cast<size_t>(id) * H, H, lane, w);
   load_vec_f32(pos + static_cast<size_t>(s) * H, H, lane, p);
@@ -521,6 +535,29 @@ embed_word_bwd_kernel(const bf16* __restrict__ dz0, const int64_t* __restrict__ 
   }
 }
 
+// dpos[pos_ids[t]] += dz0[t] for position ids that are not the index in the sequence (RoBERTa); the padding
+// index of the position table receives no gradient.  One warp per token, 16-byte vector reductions.
+__global__ void __launch_bounds__(ROW_WARPS * 32)
+embed_pos_scatter_bwd_kernel(const bf16* __restrict__ dz0, const int32_t* __restrict__ pos_ids, float* __restrict__ dpos,
+                             int T, int H, int P, int pad_id) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * ROW_WARPS + (threadIdx.x >> 5);
+  if (row >= T) return;
+  const int pid = pos_ids[row];
+  if (pid == pad_id || pid < 0 || pid >= P) return;
+  RowVec d;
+  load_row_bf16(dz0 + static_cast<size_t>(row) * H, H, lane, d);
+  float* w = dpos + static_cast<size_t>(pid) * H;
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    const int c = (j * 32 + lane) * 8;
+    if (c < H) {
+      red_add_f32x4(w + c, d.v[j][0], d.v[j][1], d.v[j][2], d.v[j][3]);
+      red_add_f32x4(w + c + 4, d.v[j][4], d.v[j][5], d.v[j][6], d.v[j][7]);
+    }
+  }
+}
+
 // block = one position s: 128 column-vector threads x PT_GROUPS batch groups, combined through shared memory
 constexpr int PT_GROUPS = 4;
 __global__ void __launch_bounds__(128 * PT_GROUPS)
@@ -568,8 +605,10 @@ embed_pos_type_bwd_kernel(const bf16* __restrict__ dz0, const int64_t* __restric
       for (int i = 0; i < 8; ++i) acc[t][i] += s_acc[g][t][c + i];
     }
   }
+  if (dpos != nullptr) {
 #pragma unroll
-  for (int i = 0; i < 8; ++i) dpos[static_cast<size_t>(s) * H + c + i] += acc[0][i] + acc[1][i];
+    for (int i = 0; i < 8; ++i) dpos[static_cast<size_t>(s) * H + c + i] += acc[0][i] + acc[1][i];
+  }
 #pragma unroll
   for (int t = 0; t < 2; ++t)
     if (any[t]) {
@@ -635,15 +674,16 @@ int launch_ln_fwd(const bf16* z, const float* gamma, const float* beta, bf16* y,
 
 int launch_embed_ln_fwd(const int64_t* ids, const int64_t* token_type, const uint8_t* key_mask, const float* word,
                         const float* pos, const float* type, const float* gamma, const float* beta, bf16* z0,
-                        bf16* x0, int64_t* ids_kept, int64_t* tt_kept, uint8_t* mask_kept, int T, int S, int H, int V,
-                        int TV, float eps, DropKey drop, int* err_flag, cudaStream_t st) {
+                        bf16* x0, int64_t* ids_kept, int64_t* tt_kept, uint8_t* mask_kept, int32_t* pos_kept, int T,
+                        int S, int H, int V, int TV, int P, int pos_mode, int pad_id, float eps, DropKey drop,
+                        int* err_flag, cudaStream_t st) {
   if (H % 8 != 0 || H > MAXV * 256) {
     set_error("embeddings: H=%d must be a multiple of 8 and <= %d", H, MAXV * 256);
     return 1;
   }
   embed_ln_fwd_kernel<<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(ids, token_type, key_mask, word, pos, type, gamma,
-                                                              beta, z0, x0, ids_kept, tt_kept, mask_kept, T, S, H, V,
-                                                              TV, eps, drop, err_flag);
+                                                              beta, z0, x0, ids_kept, tt_kept, mask_kept, pos_kept, T,
+                                                              S, H, V, TV, P, pos_mode, pad_id, eps, drop, err_flag);
   return check_launch("embed_ln_fwd");
 }
 
@@ -693,16 +733,29 @@ int launch_colsum(const bf16* X, int ld, float* out, int T, int N, int num_sms, 
   return check_launch("colsum");
 }
 
-int launch_embed_bwd(const bf16* dz0, const int64_t* ids, const int64_t* token_type, float* dword, float* dpos,
-                     float* dtype, int T, int S, int H, int V, int TV, int pad_id, cudaStream_t st) {
+int launch_embed_bwd(const bf16* dz0, const int64_t* ids, const int64_t* token_type, const int32_t* pos_ids,
+                     float* dword, float* dpos, float* dtype, int T, int S, int H, int V, int TV, int P, int pos_mode,
+                     int pad_id, cudaStream_t st) {
   if (H % 8 != 0 || H > 1024) {
     set_error("embedding backward: H=%d must be a multiple of 8 and <= 1024", H);
     return 1;
   }
   embed_word_bwd_kernel<<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(dz0, ids, dword, T, H, V, pad_id);
   if (check_launch("embed_word_bwd")) return 1;
-  embed_pos_type_bwd_kernel<<<S, 128 * PT_GROUPS, 0, st>>>(dz0, token_type, dpos, dtype, T / S, S, H, TV);
-  return check_launch("embed_pos_type_bwd");
+  // BERT: the position id is the index in the sequence, one block per position owns its row of the table;
+  // RoBERTa: scatter by the position ids the forward kept, and only the type row comes out of the per-position kernel
+  embed_pos_type_bwd_kernel<<<S, 128 * PT_GROUPS, 0, st>>>(dz0, token_type, pos_mode == 0 ? dpos : nullptr, dtype, T / S,
+                                                          S, H, TV);
+  if (check_launch("embed_pos_type_bwd")) return 1;
+  if (pos_mode != 0) {
+    if (pos_ids == nullptr) {
+      set_error("embedding backward: position ids of the forward are missing");
+      return 1;
+    }
+    embed_pos_scatter_bwd_kernel<<<row_blocks(T), ROW_WARPS * 32, 0, st>>>(dz0, pos_ids, dpos, T, H, P, pad_id);
+    return check_launch("embed_pos_scatter_bwd");
+  }
+  return 0;
 }
 
 int launch_prepare_inputs(const int32_t* ids32, int64_t* ids, int64_t* token_type, uint8_t* mask, int B, int S,

@@ -17,6 +17,10 @@ MODEL_SHAPES = {
                               type_vocab=2),
     "bert-large-uncased": dict(num_layers=24, hidden=1024, heads=16, intermediate=4096, vocab=30522, max_pos=512,
                                type_vocab=2),
+    # the reference's second choice (model.py:9-10 -> RobertaModel): one token type, <pad> = 1, position ids counted
+    # over the non-padding tokens and offset by the padding index (514 = 512 + 2 rows)
+    "roberta-base": dict(num_layers=12, hidden=768, heads=12, intermediate=3072, vocab=50265, max_pos=514,
+                         type_vocab=1, pad_token_id=1, position_mode=1),
 }
 
 
@@ -26,6 +30,7 @@ def make_config(shape, *, num_labels=5, ln_eps=1e-12, hidden_dropout=0.1, attn_d
                                                        shape["intermediate"])
     c.vocab, c.max_pos, c.type_vocab, c.num_labels = shape["vocab"], shape["max_pos"], shape["type_vocab"], num_labels
     c.ln_eps, c.hidden_dropout, c.attn_dropout = ln_eps, hidden_dropout, attn_dropout
+    c.pad_token_id, c.position_mode = int(shape.get("pad_token_id", 0)), int(shape.get("position_mode", 0))
     return c
 
 

@@ -18,12 +18,15 @@ logger = logging.getLogger(__name__)
 
 class DummyTokenizer:
     """What DummyDataset and collate_fun need when no vocab file is shipped (the reference falls
-    back to downloading one, init.py:65-73, which is impossible offline): BERT's special ids."""
+    back to downloading one, init.py:65-73, which is impossible offline): the special ids of the
+    model family (BERT: [PAD] 0, [UNK] 100, [CLS] 101, [SEP] 102; RoBERTa: <s> 0, <pad> 1, </s> 2, <unk> 3)."""
     pad_token_id, unk_token_id, cls_token_id, sep_token_id = 0, 100, 101, 102
 
     def __init__(self, model_name='bert', vocab_size=30522):
         self.model_name = model_name
         self._n = vocab_size
+        if model_name == 'roberta':
+            self.pad_token_id, self.unk_token_id, self.cls_token_id, self.sep_token_id = 1, 3, 0, 2
 
     def __len__(self):
         return self._n
@@ -50,24 +53,34 @@ def init_loss(params, train_weights):
                          'cls': (class_loss, _wght('w_cls'))})
 
 
+# buffers that transformers registers on the embeddings (persistent in the reference's pinned 3.5.1): present in
+# checkpoints written by the reference, not parameters of the drop-in
+_EMBEDDING_BUFFERS = ('embeddings.position_ids', 'embeddings.token_type_ids')
+
+
+def strip_reference_buffers(model_state):
+    return {k: v for k, v in model_state.items() if not k.endswith(_EMBEDDING_BUFFERS)}
+
+
 def _load_checkpoint(model, checkpoint, *, device=torch.device('cpu')):
     if checkpoint is not None:
-        state_dict = torch.load(checkpoint, map_location=device)
+        # the recipe's own checkpoints (trainer.py:355-379): trusted pickles, as with the reference's torch 1.3
+        state_dict = torch.load(checkpoint, map_location=device, weights_only=False)
         model.load_state_dict(state_dict['model'], strict=False)
         logger.info(f'Model checkpoint was restored from {checkpoint}.')
 
 
 def init_model(model_params, *, checkpoint=None, device=torch.device('cpu'), bpe_dropout=None):
     model_params.model_name = model_params.model.split('-')[0]
-    if model_params.model_name != 'bert':
-        raise NotImplementedError(f'{model_params.model}: only BERT encoders have a B200 path')
+    if model_params.model_name not in ('bert', 'roberta'):
+        raise NotImplementedError(f'{model_params.model}: the reference knows bert and roberta encoders (model.py:9-10)')
     vocab_file = getattr(model_params, 'vocab_file', None)
     if vocab_file is not None and os.path.exists(vocab_file):
         with open(vocab_file) as f:
             vocab_size = sum(1 for _ in f)
     else:
         logger.warning('No vocab file: using the special-token stand-in tokenizer (dummy data only).')
-        vocab_size = 30522
+        vocab_size = 50265 if model_params.model_name == 'roberta' else 30522
     tokenizer = DummyTokenizer(model_params.model_name, vocab_size)
     model = BertForQuestionAnswering(model_params, num_labels=len(RawPreprocessor.labels2id))
     model.to(device)

@@ -106,8 +106,7 @@ class BertForQuestionAnswering(nn.Module):
         name = getattr(model_params, "model", "bert-base-uncased")
         shape = getattr(model_params, "model_shape", None) or _engine.MODEL_SHAPES.get(name)
         if shape is None:
-            raise NotImplementedError(f"model {name!r}: only {sorted(_engine.MODEL_SHAPES)} have a B200 path "
-                                      "(roberta-base of the reference's choice list is not implemented)")
+            raise NotImplementedError(f"model {name!r}: only {sorted(_engine.MODEL_SHAPES)} have a B200 path")
         self._shape = dict(shape)
         self._num_labels = num_labels
         self._hidden_dropout = float(getattr(model_params, "hidden_dropout_prob", 0.1))
@@ -119,6 +118,7 @@ class BertForQuestionAnswering(nn.Module):
             hidden_size=shape["hidden"], num_hidden_layers=shape["num_layers"], num_attention_heads=shape["heads"],
             intermediate_size=shape["intermediate"], vocab_size=shape["vocab"],
             max_position_embeddings=shape["max_pos"], type_vocab_size=shape["type_vocab"],
+            pad_token_id=shape.get("pad_token_id", 0),
             hidden_dropout_prob=self._hidden_dropout, attention_probs_dropout_prob=self._attn_dropout,
             layer_norm_eps=self._ln_eps, num_labels=num_labels)
         H = shape["hidden"]

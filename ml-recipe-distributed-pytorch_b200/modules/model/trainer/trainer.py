@@ -377,8 +377,10 @@ class Trainer:
         if not os.path.exists(path_):
             logger.warning(f'Checkpoint {path_} does not exist, so checkpoint was not loaded.')
             return
-        state = torch.load(path_, map_location=self.device)
-        self.model.load_state_dict(state['model'])
+        state = torch.load(path_, map_location=self.device, weights_only=False)  # the recipe's own, trusted pickles
+        # checkpoints written by the reference carry transformers' embedding buffers (position_ids): not parameters
+        self.model.load_state_dict({k: v for k, v in state['model'].items()
+                                    if not k.endswith(('embeddings.position_ids', 'embeddings.token_type_ids'))})
         self.global_step = state['global_step']
         logger.info(f'Model weights were loaded from {path_} checkpoint.')
         if not self.drop_optimizer:

@@ -52,6 +52,9 @@ class OracleConfig:
     ln_eps: float = 1e-12
     hidden_dropout: float = 0.1
     attn_dropout: float = 0.1
+    # embedding conventions of the encoder family: BERT (0, 0) / RoBERTa (1, 1), see forward()
+    pad_token_id: int = 0
+    position_mode: int = 0
 
 
 @dataclass
@@ -164,12 +167,22 @@ def forward(P: Dict[str, torch.Tensor], cfg: OracleConfig, input_ids, attention_
     wq = lambda name: _q(P[name], bf16)             # noqa: E731  GEMM weights live in bf16
     if token_type_ids is None:
         token_type_ids = torch.zeros_like(input_ids)
-    pos = torch.arange(S, device=input_ids.device)
     e = "transformer.embeddings."
-    # nn.Embedding(vocab, H, padding_idx=pad_token_id=0) in BertEmbeddings: row 0 receives no gradient
-    z0 = (F.embedding(input_ids, P[e + "word_embeddings.weight"], padding_idx=0)
+    pad = cfg.pad_token_id
+    if cfg.position_mode == 0:
+        # BertEmbeddings (modeling_bert.py:72-112): position id = index in the sequence
+        pos_emb = P[e + "position_embeddings.weight"][torch.arange(S, device=input_ids.device)][None]
+    else:
+        # RobertaEmbeddings (modeling_roberta.py: create_position_ids_from_input_ids): padding_idx + number of
+        # non-padding tokens up to and including this one, padding_idx for padding tokens; the position table has
+        # padding_idx = pad_token_id as well (that row receives no gradient)
+        nonpad = (input_ids != pad).long()
+        pos_ids = torch.cumsum(nonpad, dim=1) * nonpad + pad
+        pos_emb = F.embedding(pos_ids, P[e + "position_embeddings.weight"], padding_idx=pad)
+    # nn.Embedding(vocab, H, padding_idx=pad_token_id) in Bert/RobertaEmbeddings: that row receives no gradient
+    z0 = (F.embedding(input_ids, P[e + "word_embeddings.weight"], padding_idx=pad)
           + P[e + "token_type_embeddings.weight"][token_type_ids]) \
-        + P[e + "position_embeddings.weight"][pos][None]
+        + pos_emb
     z0 = q(z0)
     x = _layer_norm(z0, P[e + "LayerNorm.weight"], P[e + "LayerNorm.bias"], cfg.ln_eps)
     x = q(_drop(x, cfg.hidden_dropout, drop, 0))

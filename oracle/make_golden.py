@@ -200,6 +200,70 @@ def main():
         fx6[f"loss/{alpha}/{gamma}"] = val.detach().numpy()
         fx6[f"grad/{alpha}/{gamma}"] = g.numpy()
     np.savez_compressed(os.path.join(OUT, "ref_focal.npz"), **fx6)
+    # ---- (6) the reference's second encoder family: BertForQuestionAnswering over RobertaModel (model.py:9-10),
+    # one token type, <pad> = 1, position ids counted over the non-padding tokens.  Rows are padded with <pad>; the
+    # reference's collate_fun builds attention_mask = tokens > 0, i.e. RoBERTa padding is attended (kept as is).
+    torch.manual_seed(4321)
+    rshape = dict(num_hidden_layers=2, hidden_size=64, num_attention_heads=1, intermediate_size=128, vocab_size=200,
+                  max_position_embeddings=130, type_vocab_size=1, pad_token_id=1, bos_token_id=0, eos_token_id=2)
+    ref_r = import_reference(extra_shapes={"roberta-golden-tiny": rshape})
+    mp_r = types.SimpleNamespace(model="roberta-golden-tiny", model_name="roberta", hidden_dropout_prob=0.0,
+                                 attention_probs_dropout_prob=0.0, layer_norm_eps=1e-5)
+    model_r = ref_r.model.BertForQuestionAnswering(mp_r, num_labels=5)
+    g = torch.Generator().manual_seed(8)
+    with torch.no_grad():
+        for n, p in model_r.named_parameters():
+            if n.endswith("LayerNorm.weight"):
+                p.copy_(1.0 + 0.1 * torch.randn(p.shape, generator=g))
+            elif n.endswith(".bias") and n.startswith("transformer."):
+                p.copy_(0.05 * torch.randn(p.shape, generator=g))
+            elif "position_embeddings" in n or "word_embeddings" in n:
+                p.copy_(0.05 * torch.randn(p.shape, generator=g))  # incl. the padding rows: they must not matter twice
+    model_r.train()
+    tok_r = StubTokenizer(200)
+    tok_r.model_name = "roberta"
+    tok_r.pad_token_id, tok_r.unk_token_id, tok_r.cls_token_id, tok_r.sep_token_id = 1, 3, 0, 2
+    rng = np.random.RandomState(6)
+    items_r = []
+    for i, n_doc in enumerate((66, 30, 49)):
+        qq = rng.randint(4, 200, 10).tolist()
+        dd = rng.randint(4, 200, n_doc).tolist()
+        ids = [0] + qq + [2] + dd + [2]
+        if i == 1:
+            ids[5] = 1  # a <pad> id in the middle of a row: it does not advance the position count
+        items_r.append(ref_r.dataset.DatasetItem(example_id=str(i), input_ids=ids, start_id=[14, -1, 21][i],
+                                                 end_id=[19, -1, 30][i], label_id=[1, 3, 0][i],
+                                                 start_position=[0.2, 0.0, 0.5][i], end_position=[0.3, 0.0, 0.8][i]))
+    inputs_r, labels_r = ref_r.dataset.collate_fun(items_r, tok_r)
+    loss_r = ref_r.init.init_loss(trainer_params(), defaultdict(lambda: None))
+    out_r = model_r(**inputs_r)
+    meters_r = {}
+    total_r = loss_r(out_r, labels_r, avg_meters=meters_r)
+    total_r.backward()
+    fx7 = {}
+    fx7.update(np_dict({k: v for k, v in model_r.state_dict().items() if "position_ids" not in k and "token_type_ids" not in k},
+                       "param"))
+    fx7.update(np_dict(inputs_r, "input"))
+    fx7.update(np_dict(labels_r, "label"))
+    fx7.update(np_dict(out_r, "out"))
+    fx7.update({f"loss/{k}": np.float32(v) for k, v in meters_r.items()})
+    fx7.update({f"grad/{n}": p.grad.detach().numpy() for n, p in model_r.named_parameters()})
+    np.savez_compressed(os.path.join(OUT, "ref_roberta_forward_backward.npz"), **fx7)
+
+    # ---- (7) a checkpoint written by the reference's own Trainer.save_state_dict (trainer.py:355-379) after two
+    # optimizer steps on DummyDataset: model / optimizer / scheduler / global_step, the wire format the drop-in loads
+    torch.manual_seed(77)
+    np.random.seed(77)
+    model_c = ref.model.BertForQuestionAnswering(model_params(0.0), num_labels=5)
+    tp_c = trainer_params()
+    opt_c = ref.init.init_optimizer(tp_c, model_c)
+    ds_c = ref.dataset.DummyDataset(tok, max_seq_len=48, max_question_len=8, dataset_len=8)
+    tr_c = ref.trainer.Trainer(model=model_c, loss=ref.init.init_loss(tp_c, defaultdict(lambda: None)),
+                               collate_fun=lambda items_: ref.dataset.collate_fun(items_, tok), optimizer=opt_c,
+                               train_dataset=ds_c, test_dataset=None, device=torch.device("cpu"), n_epochs=1,
+                               train_batch_size=4, batch_split=1, n_jobs=0, warmup_coef=0.5, max_grad_norm=0.5)
+    tr_c.train()
+    tr_c.save_state_dict(os.path.join(OUT, "ref_checkpoint.ch"))
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -89,6 +89,18 @@ class _OfflineBert:
         return BertModel(cfg)
 
 
+class _OfflineRoberta:
+    """Stand-in for MODELS['roberta']: from_pretrained(name, **kw) -> randomly initialised RobertaModel."""
+    shapes = {}
+
+    @classmethod
+    def from_pretrained(cls, name, **kw):
+        from transformers import RobertaConfig, RobertaModel
+        shape = dict(cls.shapes.get(name, {}))
+        cfg = RobertaConfig(attn_implementation="eager", **shape, **dict(kw))
+        return RobertaModel(cfg)
+
+
 class StubTokenizer:
     """What DummyDataset / collate_fun need from a tokenizer (dummy_dataset.py:21-23,39)."""
     model_name = "bert"
@@ -119,7 +131,9 @@ def import_reference(extra_shapes=None):
     import model.trainer.trainer as ref_trainer_mod
     if extra_shapes:
         _OfflineBert.shapes.update(extra_shapes)
+        _OfflineRoberta.shapes.update(extra_shapes)
     ref_model_mod.MODELS["bert"] = _OfflineBert
+    ref_model_mod.MODELS["roberta"] = _OfflineRoberta
     import transformers
     sys.modules["transformers"].AdamW = HFAdamW
     transformers.AdamW = HFAdamW

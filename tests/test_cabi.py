@@ -41,7 +41,7 @@ def test_binding_covers_header(pkg):
 def test_struct_layouts_match_header(pkg):
     L = pkg._lib
     assert ctypes.sizeof(L.AdamWChunk) == 24
-    assert ctypes.sizeof(L.Config) == 44
+    assert ctypes.sizeof(L.Config) == 52  # 8 shape ints, 3 floats, pad_token_id, position_mode
     assert ctypes.sizeof(L.Layout) == 8 * len(L.LAYOUT_FIELDS)
     assert ctypes.sizeof(L.GemmDesc) % 8 == 0
 

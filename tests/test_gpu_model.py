@@ -179,6 +179,93 @@ def test_step_matches_reference_golden(pkg):
     assert eng.grad_views()["transformer.embeddings.word_embeddings.weight"][0].abs().max().item() == 0.0
 
 
+ROBERTA_GOLD = dict(num_layers=2, hidden=64, heads=1, intermediate=128, vocab=200, max_pos=130, type_vocab=1,
+                    pad_token_id=1, position_mode=1)
+
+
+def test_roberta_step_matches_reference_golden(pkg):
+    """The reference's second `--model` choice (model.py:9-10, RobertaModel): one token type, <pad> = 1, position ids
+    counted over the non-padding tokens on the device, padding rows of the word and position tables without
+    gradient.  Inputs, weights, outputs, losses and gradients come from the reference's own class (fp32)."""
+    E = pkg.engine
+    fx = load_npz("ref_roberta_forward_backward.npz")
+    grp = lambda p: {k[len(p) + 1:]: torch.from_numpy(np.asarray(v)).to(DEV) for k, v in fx.items()  # noqa: E731
+                     if k.startswith(p + "/")}
+    P, inp, lab, out_ref, grad_ref = (grp(p) for p in ("param", "input", "label", "out", "grad"))
+    eng = E.Engine(E.make_config(ROBERTA_GOLD, ln_eps=1e-5, hidden_dropout=0.0, attn_dropout=0.0), DEV)
+    for k, v in eng.param_views().items():
+        v.copy_(P[k])
+    eng.sync_weights()
+    outs = eng.forward(inp["input_ids"], inp["token_type_ids"], inp["attention_mask"], training=True, seed=1, step=1)
+    losses = eng.loss(outs, lab, E.make_loss_config(), with_grad=True).clone()
+    eng.backward()
+    torch.cuda.synchronize()
+    eng.check_inputs()
+    valid = inp["attention_mask"]
+    for k, t in zip(OUT_KEYS, outs):
+        a, b = (t[valid], out_ref[k][valid]) if t.dim() == 2 and t.shape == valid.shape else (t, out_ref[k])
+        assert rel(a, b) < 3e-2, k
+    ref_l = [float(fx[f"loss/{k}"]) for k in ("start_class", "end_class", "start_reg", "end_reg", "cls", "loss")]
+    for a, b in zip(losses.tolist(), ref_l):
+        assert abs(a - b) <= 1e-2 * max(1.0, abs(b))
+    check_grads(eng, grad_ref, glob_tol=6e-2, tensor_tol=0.15)
+    gv = eng.grad_views()
+    assert gv["transformer.embeddings.word_embeddings.weight"][1].abs().max().item() == 0.0
+    assert gv["transformer.embeddings.position_embeddings.weight"][1].abs().max().item() == 0.0
+    assert gv["transformer.embeddings.position_embeddings.weight"][0].abs().max().item() == 0.0  # never indexed
+
+
+def test_checkpoint_written_by_the_reference_loads(pkg, tmp_path):
+    """tests/golden/ref_checkpoint.ch was written by the reference's own Trainer.save_state_dict after two
+    optimizer steps (oracle/make_golden.py).  Trainer.load_state_dict restores weights, AdamW moments, scheduler
+    and global_step from it; init_model(checkpoint=...) restores the weights alone (init.py:43-48, strict=False)."""
+    import os
+    from conftest import GOLDEN
+    I = importlib.import_module("bqa_b200.modules.init")
+    T = importlib.import_module("bqa_b200.modules.model.trainer.trainer")
+    D = importlib.import_module("bqa_b200.modules.model.dataset")
+    path = os.path.join(GOLDEN, "ref_checkpoint.ch")
+    ck = torch.load(path, map_location="cpu", weights_only=False)
+    model = _model(pkg, GOLD)
+    hp = types.SimpleNamespace(lr=1e-3, weight_decay=1e-2, optimizer="adam", finetune=False, apex_level=None)
+    opt = I.init_optimizer(hp, model)
+    tok = I.DummyTokenizer(vocab_size=200)
+    ds = D.DummyDataset(tok, max_seq_len=48, max_question_len=8, dataset_len=8)
+    tr = T.Trainer(model=model, loss=_loss_obj(), collate_fun=I.init_collate_fun(tok), optimizer=opt, train_dataset=ds,
+                   device=torch.device(DEV), n_epochs=1, train_batch_size=4, batch_split=1, n_jobs=0, warmup_coef=0.5,
+                   max_grad_norm=0.5)
+    tr.load_state_dict(path)
+    assert tr.global_step == 2
+    sd = model.state_dict()
+    for k in sd:
+        assert torch.equal(sd[k].cpu(), ck["model"][k]), k
+    eng = model.engine
+    for i, (p, key) in enumerate(opt._keys):
+        saved = ck["optimizer"]["state"][i]
+        assert torch.equal(eng.view(opt._m, key).cpu(), saved["exp_avg"]), key
+        assert torch.equal(eng.view(opt._v, key).cpu(), saved["exp_avg_sq"]), key
+        assert opt.state[p]["step"] == saved["step"] == 2
+    assert tr.scheduler.state_dict()["last_epoch"] == ck["scheduler"]["last_epoch"]
+    # training goes on from the restored state (the restored schedule has reached its end, lr = 0: set one)
+    assert opt.param_groups[0]["lr"] == 0.0
+    for g_ in opt.param_groups:
+        g_["lr"] = 1e-3
+    opt.zero_grad()
+    tr.set_train()
+    inputs, labels = O.dummy_batch(4, 48, vocab=200, max_question_len=8, device=DEV)
+    tr.train_micro_batch(inputs, labels, last_of_step=True)
+    tr.optimizer_step()
+    torch.cuda.synchronize()
+    assert torch.isfinite(eng.params).all() and not torch.equal(model.state_dict()["classifier.1.weight"].cpu(),
+                                                               ck["model"]["classifier.1.weight"])
+    # weights-only restore of init_model
+    mp = types.SimpleNamespace(model="bert-base-uncased", model_shape=GOLD, hidden_dropout_prob=0.0,
+                               attention_probs_dropout_prob=0.0, layer_norm_eps=1e-12, vocab_file=None)
+    model2, _ = I.init_model(mp, checkpoint=path, device=torch.device(DEV))
+    for k, v in model2.state_dict().items():
+        assert torch.equal(v.cpu(), ck["model"][k]), k
+
+
 def test_ce_loss_with_label_weights_matches_reference_golden(pkg):
     E = pkg.engine
     L = pkg._lib

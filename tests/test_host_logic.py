@@ -209,9 +209,15 @@ def test_unsupported_options_fail_loudly(mods):
     I = mods["init"]
     with pytest.raises(NotImplementedError):
         I.init_loss(types.SimpleNamespace(loss="hinge", smooth_alpha=0.01), {})
-    mp = types.SimpleNamespace(model="roberta-base", vocab_file=None)
+    mp = types.SimpleNamespace(model="xlnet-base-cased", vocab_file=None)
     with pytest.raises(NotImplementedError):
         I.init_model(mp)
+    # both of the reference's --model choices are known (model.py:9-10); RoBERTa's special ids and conventions
+    tok = I.DummyTokenizer("roberta", 50265)
+    assert (tok.cls_token_id, tok.pad_token_id, tok.sep_token_id, tok.unk_token_id) == (0, 1, 2, 3)
+    shape = importlib.import_module("bqa_b200.engine").MODEL_SHAPES["roberta-base"]
+    assert (shape["vocab"], shape["max_pos"], shape["type_vocab"], shape["pad_token_id"], shape["position_mode"]) == \
+        (50265, 514, 1, 1, 1)
     # loss=focal and optimizer=adamod are configuration holders on the host (kernels: tests -m gpu)
     wl = I.init_loss(types.SimpleNamespace(loss="focal", focal_alpha=0.5, focal_gamma=3, smooth_alpha=0.01), {})
     assert type(wl._losses['cls'][0]).__name__ == "FocalLossWithLogits"

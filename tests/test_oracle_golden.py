@@ -29,6 +29,56 @@ def test_forward_loss_backward_match_reference():
         torch.testing.assert_close(grads[k], g, rtol=2e-4, atol=2e-7, msg=lambda m, k=k: f"{k}: {m}")
 
 
+ROBERTA_TINY = O.OracleConfig(num_layers=2, hidden=64, heads=1, intermediate=128, vocab=200, max_pos=130, type_vocab=1,
+                              hidden_dropout=0.0, attn_dropout=0.0, ln_eps=1e-5, pad_token_id=1, position_mode=1)
+
+
+def test_roberta_forward_loss_backward_match_reference():
+    """The reference's class over RobertaModel (model.py:9-10): one token type, <pad> = 1, position ids =
+    padding_idx + running count of non-padding tokens (a <pad> in the middle of a row does not advance it), padding
+    rows of the word AND position tables without gradient, attention_mask = tokens > 0 from the reference collate
+    (which masks <s> = 0 and attends <pad> = 1: kept as the reference does it)."""
+    fx = load_npz("ref_roberta_forward_backward.npz")
+    P, inp, lab, out_ref, grad_ref = (_group(fx, p) for p in ("param", "input", "label", "out", "grad"))
+    # (the installed transformers registers RoBERTa's token-type table before its position table; the reference's
+    # pinned 3.5.1 uses BERT's order, which is also the engine's: compare as sets)
+    assert sorted(P.keys()) == sorted(O.param_names(ROBERTA_TINY))
+    # the reference's collate masks ids == 0: with RoBERTa that is <s>, while the <pad> = 1 positions are attended
+    assert bool((inp["input_ids"] == 1).any()) and torch.equal(inp["attention_mask"], inp["input_ids"] > 0)
+    assert int(inp["token_type_ids"].max()) == 0
+    total, parts, grads, out = O.loss_and_grads(P, ROBERTA_TINY, inp, lab, O.LossConfig())
+    for k in out_ref:
+        torch.testing.assert_close(out[k], out_ref[k], rtol=2e-5, atol=2e-6)
+    assert abs(total.item() - float(fx["loss/loss"])) < 1e-5
+    for k, g in grad_ref.items():
+        torch.testing.assert_close(grads[k], g, rtol=2e-4, atol=2e-7, msg=lambda m, k=k: f"{k}: {m}")
+    assert float(grads["transformer.embeddings.position_embeddings.weight"][1].abs().max()) == 0.0
+    assert float(grads["transformer.embeddings.word_embeddings.weight"][1].abs().max()) == 0.0
+
+
+def test_reference_checkpoint_wire_format(pkg):
+    """A checkpoint written by the reference's own Trainer.save_state_dict (trainer.py:355-379): the drop-in's
+    state_dict has exactly its model keys and shapes, and its optimizer section has the per-parameter
+    {step, exp_avg, exp_avg_sq} layout that FusedAdamW.load_state_dict consumes (GPU side: tests/test_gpu_model.py)."""
+    import importlib
+    import os
+    import types
+    from conftest import GOLDEN
+    ck = torch.load(os.path.join(GOLDEN, "ref_checkpoint.ch"), map_location="cpu", weights_only=False)
+    assert set(ck) == {"model", "optimizer", "scheduler", "global_step"} and ck["global_step"] == 2
+    M = importlib.import_module("bqa_b200.modules.model.model")
+    shape = dict(num_layers=2, hidden=64, heads=1, intermediate=128, vocab=200, max_pos=128, type_vocab=2)
+    mp = types.SimpleNamespace(model="bert-base-uncased", model_shape=shape, hidden_dropout_prob=0.0,
+                               attention_probs_dropout_prob=0.0, layer_norm_eps=1e-12)
+    sd = M.BertForQuestionAnswering(mp, 5).state_dict()
+    ref_keys = [k for k in ck["model"] if not k.endswith("position_ids") and not k.endswith("embeddings.token_type_ids")]
+    assert list(sd.keys()) == ref_keys
+    assert all(tuple(sd[k].shape) == tuple(ck["model"][k].shape) for k in sd)
+    st = ck["optimizer"]["state"]
+    assert len(ck["optimizer"]["param_groups"]) == 2 and len(st) == len(sd)
+    assert all(set(v) == {"step", "exp_avg", "exp_avg_sq"} for v in st.values())
+
+
 def test_ce_class_loss_with_label_weights():
     fx = load_npz("ref_forward_backward.npz")
     out, lab = _group(fx, "out"), _group(fx, "label")
