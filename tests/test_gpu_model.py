@@ -28,6 +28,8 @@ GOLD = dict(num_layers=2, hidden=64, heads=1, intermediate=128, vocab=200, max_p
 BASE = dict(num_layers=12, hidden=768, heads=12, intermediate=3072, vocab=30522, max_pos=512, type_vocab=2)
 # two layers at the BERT-large widths (BASELINE configs[3]: S = 512, 16 heads, H = 1024, I = 4096)
 LARGE2 = dict(num_layers=2, hidden=1024, heads=16, intermediate=4096, vocab=2000, max_pos=512, type_vocab=2)
+# BASELINE configs[3] at full depth: bert-large-uncased
+LARGE24 = dict(num_layers=24, hidden=1024, heads=16, intermediate=4096, vocab=30522, max_pos=512, type_vocab=2)
 OUT_KEYS = ("start_class", "end_class", "cls", "start_reg", "end_reg")
 
 
@@ -75,7 +77,9 @@ def check_grads(eng, grads, glob_tol=2e-2, tensor_tol=5e-2):
                                                        # m-tiles through the cluster-launch-control scheduler, and the
                                                        # fused side outputs (row-dot D, GELU-backward column sums,
                                                        # attention bias gradients) run at full size
-                                                       (BASE, 32, 384, 0.1, False)])
+                                                       (BASE, 32, 384, 0.1, False),
+                                                       # BASELINE configs[3] exactly: 24 layers, B = 16, S = 512
+                                                       (LARGE24, 16, 512, 0.1, True)])
 def test_step_matches_oracle(pkg, shape, B, S, p_drop, use_mask):
     E = pkg.engine
     cfgo = O.OracleConfig(hidden_dropout=p_drop, attn_dropout=p_drop, **shape)
@@ -99,7 +103,8 @@ def test_step_matches_oracle(pkg, shape, B, S, p_drop, use_mask):
     drop = O.DropSpec(seed, step) if p_drop > 0 else None
     total, parts, grads, oout = O.loss_and_grads(P, cfgo, inputs, labels, O.LossConfig(), drop=drop, bf16=True)
     for k, t in zip(OUT_KEYS, outs):
-        assert rel(t, oout[k]) < (2.5e-2 if shape is BASE else 1e-2), k
+        # rounding accumulates with depth: 1e-2 at 2 layers, 2.5e-2 at 12, 4e-2 at 24
+        assert rel(t, oout[k]) < (4e-2 if shape is LARGE24 else 2.5e-2 if shape is BASE else 1e-2), k
     ref_l = [parts[k].item() for k in ("start_class", "end_class", "start_reg", "end_reg", "cls")] + [total.item()]
     for a, b in zip(losses.tolist(), ref_l):
         assert abs(a - b) <= 3e-3 * max(1.0, abs(b))
