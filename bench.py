@@ -351,7 +351,7 @@ def run_train(args, wl):
     if rank == 0 and world == 1 and not args.no_cpu_baseline and wl["kind"] == "train" and wl["model"] == "bert-base-uncased":
         out["cpu_baseline"] = cpu_baseline(steps=2, warmup=1, batch=8, seq=S)
     if rank == 0:
-        print(json.dumps(out), flush=True)
+        emit(out)
     if world > 1:
         dist.destroy_process_group()
 
@@ -464,7 +464,7 @@ def run_decode(args, wl):
                         "step_model_tflops": round(model_tflops, 1), "step_model_frac": round(model_tflops / sustained, 4),
                         "step_model_frac_burst": round(model_tflops / burst, 4)}}
     if rank == 0:
-        print(json.dumps(out), flush=True)
+        emit(out)
     if world > 1:
         dist.destroy_process_group()
 
@@ -523,10 +523,36 @@ def run_reference(args):
                       "global_batch": 8, "seq_len": seq, "parallelism": "cpu"},
            "cpu_baseline": cb,
            "e2e": {"value": cb["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(out), flush=True)
+    emit(out)
+
+
+class JsonLineOnly:
+    """Everything that libraries write to file descriptor 1 while the benchmark runs (NCCL prints its version there)
+    goes to stderr; the one JSON line is written to the real stdout at the end."""
+
+    def __init__(self):
+        sys.stdout.flush()
+        self.real = os.dup(1)
+        os.dup2(2, 1)
+
+    def emit(self, obj):
+        sys.stdout.flush()
+        os.write(self.real, (json.dumps(obj) + "\n").encode())
+
+
+OUT = None
+
+
+def emit(obj):
+    if OUT is not None:
+        OUT.emit(obj)
+    else:
+        print(json.dumps(obj), flush=True)
 
 
 def main():
+    global OUT
+    OUT = JsonLineOnly()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=40)
