@@ -349,6 +349,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  pdl_wait();     // launched with programmatic serialization: barrier set-up and TMEM allocation above overlapped the
+                  // previous kernel's tail; its results are complete from here on
   pdl_trigger();  // the next kernel may start its prologue; it waits for this grid before reading
 
   if (warp == FW_TMA_WARP) {
@@ -743,6 +745,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  pdl_wait();     // launched with programmatic serialization: barrier set-up and TMEM allocation above overlapped the
+                  // previous kernel's tail; its results are complete from here on
   pdl_trigger();  // the next kernel may start its prologue; it waits for this grid before reading
 
   if (warp == DQ_TMA_WARP) {
@@ -1074,6 +1078,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  pdl_wait();     // launched with programmatic serialization: barrier set-up and TMEM allocation above overlapped the
+                  // previous kernel's tail; its results are complete from here on
   pdl_trigger();  // the next kernel may start its prologue; it waits for this grid before reading
 
   if (warp == KV_TMA_WARP) {
@@ -1482,9 +1488,9 @@ int attn_forward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, cu
   const int grid = tiles < 2 * sms ? tiles : 2 * sms;  // persistent, two co-resident CTAs per SM
   const bool kb = key_mask != nullptr || (plan.shape.S % KC) != 0;
   if (kb)
-    attn_fwd_kernel<true><<<grid, FW_THREADS, fwd_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_kv96, plan.tm_ctx, a);
+    launch_pdl(attn_fwd_kernel<true>, grid, FW_THREADS, fwd_smem_bytes(), st, plan.tm_qkv, plan.tm_kv96, plan.tm_ctx, a);
   else
-    attn_fwd_kernel<false><<<grid, FW_THREADS, fwd_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_kv96, plan.tm_ctx, a);
+    launch_pdl(attn_fwd_kernel<false>, grid, FW_THREADS, fwd_smem_bytes(), st, plan.tm_qkv, plan.tm_kv96, plan.tm_ctx, a);
   return check_launch("attn_fwd");
 }
 
@@ -1521,14 +1527,14 @@ int attn_backward(const AttnPlan& plan, const uint8_t* key_mask, DropKey drop, c
   const int grid = tiles < 2 * sms ? tiles : 2 * sms;  // persistent, two co-resident CTAs per SM
   const bool kb = key_mask != nullptr || (plan.shape.S % 64) != 0;
   if (kb)
-    attn_bwd_dq_kernel<true><<<grid, DQ_THREADS, dq_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_q64, plan.tm_dctx,
-                                                                         plan.tm_dqkv, a);
+    launch_pdl(attn_bwd_dq_kernel<true>, grid, DQ_THREADS, dq_smem_bytes(), st, plan.tm_qkv, plan.tm_q64, plan.tm_dctx,
+               plan.tm_dqkv, a);
   else
-    attn_bwd_dq_kernel<false><<<grid, DQ_THREADS, dq_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_q64, plan.tm_dctx,
-                                                                          plan.tm_dqkv, a);
+    launch_pdl(attn_bwd_dq_kernel<false>, grid, DQ_THREADS, dq_smem_bytes(), st, plan.tm_qkv, plan.tm_q64, plan.tm_dctx,
+               plan.tm_dqkv, a);
   if (check_launch("attn_bwd_dq")) return 1;
   const int grid_kv = tiles < sms ? tiles : sms;  // one CTA per SM (it owns the whole tensor memory)
-  attn_bwd_dkv_kernel<<<grid_kv, KV_THREADS, dkv_smem_bytes(), st>>>(plan.tm_qkv, plan.tm_dctx, plan.tm_dqkv32, a);
+  launch_pdl(attn_bwd_dkv_kernel, grid_kv, KV_THREADS, dkv_smem_bytes(), st, plan.tm_qkv, plan.tm_dctx, plan.tm_dqkv32, a);
   return check_launch("attn_bwd_dkv");
 }
 

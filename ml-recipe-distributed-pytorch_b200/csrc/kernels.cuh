@@ -19,6 +19,26 @@ inline int check_launch(const char* what) {
   return 0;
 }
 
+// Launch with programmatic stream serialization: the grid may be scheduled while its predecessor in the stream is
+// still draining (launch latency and the kernel's own prologue overlap the predecessor's tail).  The kernel must call
+// pdl_wait() before it touches anything the predecessor may read or write, and pdl_trigger() only after that wait
+// (so that completion stays transitive along a chain of such launches).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // ---- rowwise.cu -------------------------------------------------------------------------
 int launch_ln_fwd(const bf16* z, const float* gamma, const float* beta, bf16* y, int T, int H, float eps,
                   cudaStream_t st);

@@ -232,7 +232,8 @@ int launch_f32_to_bf16(const float* src, bf16* dst, size_t n, int num_sms, cudaS
 namespace {
 
 constexpr int kNoAllocPartials = 2048;                 // one float per thread block of the first pass
-constexpr uint64_t kNoAllocMaxElems = 1ull << 31;      // at most 2^20 elements behind each fp32 partial
+constexpr uint64_t kNoAllocMaxElems = 1ull << 31;      // keeps the elements behind one fp32 partial below ~2M: the grid
+                                                       // is 8 blocks per SM, capped at 2048 (1184 blocks on a B200)
 constexpr int kNoAllocMaxDevices = 64;
 
 static __device__ __align__(256) float g_noalloc_partials[kNoAllocPartials];

@@ -147,6 +147,7 @@ template <int NV>
 __global__ void __launch_bounds__(ROW_WARPS * 32, LN_FWD_BLOCKS_PER_SM)
 ln_fwd_kernel(const bf16* __restrict__ z, const float* __restrict__ gamma, const float* __restrict__ beta,
               bf16* __restrict__ y, int T, int H, float eps) {
+  pdl_wait();     // launched with programmatic serialization: the producer of z has completed from here on
   pdl_trigger();  // the next kernel (a GEMM) may start its prologue now; it waits for this grid before reading
   const int lane = threadIdx.x & 31;
   const int row_stride = gridDim.x * ROW_WARPS;
@@ -289,6 +290,7 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
               bf16* __restrict__ dz, bf16* __restrict__ dz_masked, float* __restrict__ dgamma,
               float* __restrict__ dbeta, float* __restrict__ dbias, int T, int H, float eps, DropKey drop_in,
               DropKey drop_out) {
+  pdl_wait();     // launched with programmatic serialization: the producers of dy / z have completed from here on
   pdl_trigger();  // the next kernel (a GEMM) may start its prologue now; it waits for this grid before reading
   extern __shared__ float ln_smem[];
   constexpr int W = NV * 256;           // padded row width
@@ -664,10 +666,10 @@ int launch_ln_fwd(const bf16* z, const float* gamma, const float* beta, bf16* y,
   int grid = sms * LN_FWD_BLOCKS_PER_SM;
   if (grid > row_blocks(T)) grid = row_blocks(T);
   switch ((H + 255) / 256) {
-    case 1: ln_fwd_kernel<1><<<grid, ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
-    case 2: ln_fwd_kernel<2><<<grid, ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
-    case 3: ln_fwd_kernel<3><<<grid, ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
-    default: ln_fwd_kernel<4><<<grid, ROW_WARPS * 32, 0, st>>>(z, gamma, beta, y, T, H, eps); break;
+    case 1: launch_pdl(ln_fwd_kernel<1>, grid, ROW_WARPS * 32, 0, st, z, gamma, beta, y, T, H, eps); break;
+    case 2: launch_pdl(ln_fwd_kernel<2>, grid, ROW_WARPS * 32, 0, st, z, gamma, beta, y, T, H, eps); break;
+    case 3: launch_pdl(ln_fwd_kernel<3>, grid, ROW_WARPS * 32, 0, st, z, gamma, beta, y, T, H, eps); break;
+    default: launch_pdl(ln_fwd_kernel<4>, grid, ROW_WARPS * 32, 0, st, z, gamma, beta, y, T, H, eps); break;
   }
   return check_launch("ln_fwd");
 }
@@ -706,8 +708,8 @@ int launch_ln_bwd(const bf16* dy, const bf16* z, const float* gamma, bf16* dz, b
                                           static_cast<int>(smem)));                                            \
       once.mark_done(once_dev);                                                                                        \
     }                                                                                                          \
-    ln_bwd_kernel<NV><<<grid, ROW_WARPS * 32, smem, st>>>(dy, z, gamma, dz, dz_masked, dgamma, dbeta, dbias, T, H, \
-                                                          eps, drop_in, drop_out);                             \
+    launch_pdl(ln_bwd_kernel<NV>, grid, ROW_WARPS * 32, smem, st, dy, z, gamma, dz, dz_masked, dgamma, dbeta, dbias, T, \
+               H, eps, drop_in, drop_out);                                                                     \
   }
   switch (nv) {
     case 1: BQA_LN_BWD(1) break;
