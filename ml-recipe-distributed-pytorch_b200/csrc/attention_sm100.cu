@@ -294,8 +294,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   uint8_t* sQ = smem;                    // 2 x CH; a finished tile's buffer stages its output tile
   uint8_t* sK = sQ + 2 * CH;             // FW_RING x KCB
   uint8_t* sV = sK + FW_RING * KCB;      // FW_RING x KCB
-  float* kbias = reinterpret_cast<float*>(sV + FW_RING * KCB);  // [6 * 96]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(kbias + 6 * KC);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + FW_RING * KCB);
   uint64_t* q_full = bars + 0;    // [2]
   uint64_t* q_free = bars + 2;    // [2] last score MMA of the tile done + output store has read the buffer
   uint64_t* k_full = bars + 4;    // [3]
@@ -389,6 +388,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     // ---------------- MMA issuer ----------------
     constexpr uint32_t idesc_s = umma_idesc_bf16(128, KC, 0, 0);
     constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+    // the last chunk of a row of keys may be partial: its score MMA computes only the columns that hold keys
+    // (rounded up to the MMA's granularity of 16) and its P V MMA only those k-steps
+    const int last_keys = S - (NC - 1) * KC;                  // 1 .. KC
+    const int last_ksteps = (last_keys + 15) >> 4;            // k-steps of 16 keys
+    const uint32_t idesc_s_last = umma_idesc_bf16(128, last_ksteps * 16, 0, 0);
     const bool leader = elect_one();
     // O += P V for chunk gp (the jp-th chunk of this CTA's itp-th tile, ring slot sp of round rp)
     auto issue_pv = [&](uint32_t gp, int itp, int jp, uint32_t sp, uint32_t rp) {
@@ -399,10 +403,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       tc_fence_after();
       if (leader) {
         const uint32_t v_addr = smem_u32(sV + sp * KCB);
+        const int ksteps = jp == NC - 1 ? last_ksteps : KC / 16;
 #pragma unroll
         for (int k = 0; k < KC / 16; ++k)
-          umma_bf16_ts(tmem + FW_COL_O, tmem + bp * KC + k * 8, umma_desc_mnmajor(v_addr + k * 2048, KCB), idesc_o,
-                       (jp > 0 || k > 0) ? 1u : 0u);
+          if (k < ksteps)
+            umma_bf16_ts(tmem + FW_COL_O, tmem + bp * KC + k * 8, umma_desc_mnmajor(v_addr + k * 2048, KCB), idesc_o,
+                         (jp > 0 || k > 0) ? 1u : 0u);
         umma_commit(&pv_done[bp]);
         umma_commit(&v_free[sp]);
         if (jp == NC - 1) umma_commit(o_full);
@@ -426,8 +432,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
           const uint32_t q_addr = smem_u32(sQ + qb * CH), k_addr = smem_u32(sK + slot * KCB);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            umma_bf16(tmem + bsel * KC, umma_desc_kmajor(q_addr + k * 32), umma_desc_kmajor(k_addr + k * 32), idesc_s,
-                      k > 0 ? 1u : 0u);
+            umma_bf16(tmem + bsel * KC, umma_desc_kmajor(q_addr + k * 32), umma_desc_kmajor(k_addr + k * 32),
+                      j == NC - 1 ? idesc_s_last : idesc_s, k > 0 ? 1u : 0u);
           umma_commit(&s_full[bsel]);
           umma_commit(&k_free[slot]);
           if (j == NC - 1) umma_commit(&q_free[qb]);
@@ -452,6 +458,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     const float sl2 = a.scale_log2;
     const bool dropping = a.drop.thresh != 0u;
     const int keep_words = 8 * NQ;  // per (batch, head, query) row; the first 4 NQ are query-major
+    const int last_keys = S - (NC - 1) * KC;  // keys in the (possibly partial) last chunk
     int prev_b = -1;
     int pending_qb = -1;  // thread 0: output store whose staging buffer has not been released yet
     uint32_t g = 0;
@@ -462,11 +469,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       const int q = qt * 128 + r;
       const int qb = it & 1;
       if (KB && b != prev_b) {
-        named_bar_sync(1, FW_SOFT);  // nobody still reads the previous batch row's bias
+        named_bar_sync(1, FW_SOFT);  // nobody still reads the previous batch row's key bits
         for (int base = 0; base < NC * KC; base += FW_SOFT) {
           const int key = base + tid;
           const bool ok = key < S && (a.key_mask == nullptr || a.key_mask[static_cast<size_t>(b) * S + key] != 0);
-          if (key < NC * KC) kbias[key] = ok ? 0.0f : -INFINITY;
           const uint32_t w = __ballot_sync(0xffffffffu, ok);
           if ((tid & 31) == 0 && key < NC * KC) kvalid[key >> 5] = w;
         }
@@ -493,24 +499,31 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         mbar_wait(&s_full[bsel], (g >> 1) & 1u);
         ATACC(1);
         tc_fence_after();
+        // 32-key pieces of this chunk that hold keys at all (a partial last chunk has fewer; the columns beyond
+        // them were not written by the score MMA and are neither read nor exponentiated)
+        const int pieces = (KB && j == NC - 1) ? (last_keys + 31) >> 5 : 3;  // (without KB, S is a multiple of KC)
         uint32_t v[3][32];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) tmem_ld_32x32(s_addr + k * 32, v[k]);
+        for (int k = 0; k < 3; ++k)
+          if (k < pieces) tmem_ld_32x32(s_addr + k * 32, v[k]);
         tmem_wait_ld();
-        // chunk maximum of the scaled (and, where a key is masked, biased) scores
+        // chunk maximum of the scaled scores over the keys that are attended.  Masked keys (padding, keys beyond S)
+        // are SELECTED away by their bit in kvalid, never added to: a column beyond the score MMA's width may hold
+        // anything.
         float cmax = -INFINITY;
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
+          if (k >= pieces) continue;
+          float raw = -INFINITY;
           if (KB && kvalid[3 * j + k] != 0xffffffffu) {
-            const float* kb = kbias + j * KC + k * 32;
+            const uint32_t vb = kvalid[3 * j + k];
 #pragma unroll
-            for (int i = 0; i < 32; ++i) cmax = fmaxf(cmax, fmaf(__uint_as_float(v[k][i]), sl2, kb[i]));
+            for (int i = 0; i < 32; ++i) raw = fmaxf(raw, ((vb >> i) & 1u) ? __uint_as_float(v[k][i]) : -INFINITY);
           } else {
-            float raw = -INFINITY;
 #pragma unroll
             for (int i = 0; i < 32; i += 2) raw = fmax3(raw, __uint_as_float(v[k][i]), __uint_as_float(v[k][i + 1]));
-            cmax = fmaxf(cmax, raw * sl2);
           }
+          cmax = fmaxf(cmax, raw * sl2);
         }
         ATACC(2);
         const float m_new = fmaxf(m_run, cmax);
@@ -540,16 +553,19 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         // P is stored unscaled; the dropout scale 1 / (1 - p) is applied with the final 1 / rowsum
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
+          if (k >= pieces) continue;
           const uint32_t bits = kw[k];
           uint32_t pk[16];
-          auto piece = [&](auto biased) {
-            const float* kb = kbias + j * KC + k * 32;
+          auto piece = [&](auto masked) {
+            const uint32_t vb = decltype(masked)::value ? kvalid[3 * j + k] : 0xffffffffu;
 #pragma unroll
             for (int i = 0; i < 32; i += 2) {
-              const float off0 = decltype(biased)::value ? kb[i] - m_use : -m_use;
-              const float off1 = decltype(biased)::value ? kb[i + 1] - m_use : -m_use;
-              const float p0 = fast_exp2(fmaf(__uint_as_float(v[k][i]), sl2, off0));
-              const float p1 = fast_exp2(fmaf(__uint_as_float(v[k][i + 1]), sl2, off1));
+              float p0 = fast_exp2(fmaf(__uint_as_float(v[k][i]), sl2, -m_use));
+              float p1 = fast_exp2(fmaf(__uint_as_float(v[k][i + 1]), sl2, -m_use));
+              if (decltype(masked)::value) {
+                p0 = ((vb >> i) & 1u) ? p0 : 0.0f;
+                p1 = ((vb >> (i + 1)) & 1u) ? p1 : 0.0f;
+              }
               l += p0 + p1;
               pk[i >> 1] = pack_bf16x2(((bits >> i) & 1u) ? p0 : 0.0f, ((bits >> (i + 1)) & 1u) ? p1 : 0.0f);
             }
@@ -1376,7 +1392,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
   if (tid == 0) ATRACE(9);
 }
 
-int fwd_smem_bytes() { return 2 * CH + 2 * FW_RING * KCB + 6 * KC * 4 + 512 + 1024; }
+int fwd_smem_bytes() { return 2 * CH + 2 * FW_RING * KCB + 512 + 1024; }
 int dq_smem_bytes() { return 4 * CH + (DQ_KRING + DQ_VRING) * HC + 2048 + 2048 + 512 + 1024; }
 int dkv_smem_bytes() { return 4 * CH + 2 * KV_RING * CH + 8192 + 256 + 1024; }
 

@@ -50,3 +50,28 @@ for name, fn in (("forward (keep bits + kernel), p=0.1", lambda: fwd(None, 0.1))
         ts.append(e0.elapsed_time(e1) * 1e3)
     ts.sort()
     print(f"  {name:40s} median {ts[12]:6.1f} us   min {ts[0]:6.1f} us")
+
+
+# S = 512 (BASELINE configs[3] / [4]): six 96-key chunks, the last one partial (32 keys)
+def S512():
+    B2, S2, A2 = 16, 512, 16
+    H2 = A2 * 64
+    qkv2 = torch.randn(B2, S2, 3 * H2, device=dev).to(torch.bfloat16)
+    ctx2 = torch.zeros(B2, S2, H2, device=dev, dtype=torch.bfloat16)
+    lse22 = torch.zeros(B2, A2, S2, device=dev)
+    keep2 = torch.zeros(B2, A2, S2, L.lib.bqa_attention_keep_words(S2), dtype=torch.int32, device=dev)
+    ts = []
+    for _ in range(20):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        L.check(L.lib.bqa_attention_forward(qkv2.data_ptr(), ctx2.data_ptr(), lse22.data_ptr(), keep2.data_ptr(), None, B2, S2, A2,
+                                            0.0, 7, 5, st), "fwd512")
+        e1.record(); torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1) * 1e3)
+    ts.sort()
+    fl = 4.0 * B2 * A2 * S2 * S2 * 64
+    print(f"  forward S=512 B=16 A=16, p=0           median {ts[10]:6.1f} us   {fl / ts[10] / 1e6:.0f} TFLOP/s")
+
+
+S512()
