@@ -37,6 +37,7 @@ class FusedAdamW(torch.optim.Optimizer):
         self._max_grad_norm = 0.0
         self._built_for = None
         self._grads_clean = False
+        self._sumsq_by_bucket = False
 
     # ---- flat state ------------------------------------------------------------------------
     def _build(self):
@@ -99,13 +100,30 @@ class FusedAdamW(torch.optim.Optimizer):
     # ---- step --------------------------------------------------------------------------------
     def prepare_clip(self, max_grad_norm):
         """Trainer._clip_grad_norm: launches the sum-of-squares pass; the coefficient is applied by
-        the following step() on the device (no host synchronisation)."""
+        the following step() on the device (no host synchronisation).  If the sum was already
+        accumulated bucket by bucket during the backward (begin_bucket_sumsq / add_bucket_sumsq), nothing
+        is launched here."""
         eng = self._build()
         self._max_grad_norm = float(max_grad_norm) if max_grad_norm else 0.0
-        if self._max_grad_norm > 0.0:
+        if self._max_grad_norm > 0.0 and not self._sumsq_by_bucket:
             self._sumsq.zero_()
             L.check(L.lib.bqa_grad_sumsq(eng.grads.data_ptr(), eng.total, self._sumsq.data_ptr(),
                                          self._scratch.data_ptr(), L.current_stream_ptr()), "bqa_grad_sumsq")
+        self._sumsq_by_bucket = False
+
+    def begin_bucket_sumsq(self):
+        """Start of an optimizer step's last backward: the sum of squares of the gradient will be accumulated
+        per bucket (add_bucket_sumsq) as the buckets become final, overlapped with the rest of the backward.
+        Call with the stream current on which add_bucket_sumsq will run."""
+        self._build()
+        self._sumsq.zero_()
+        self._sumsq_by_bucket = True
+
+    def add_bucket_sumsq(self, begin, end):
+        """*sumsq += sum(g[begin:end]^2) on the current stream (stream-ordered with the other buckets)."""
+        eng = self._build()
+        L.check(L.lib.bqa_grad_sumsq(eng.grads.data_ptr() + 4 * begin, end - begin, self._sumsq.data_ptr(),
+                                     self._scratch.data_ptr(), L.current_stream_ptr()), "bqa_grad_sumsq")
 
     def grad_norm(self):
         """Total gradient norm seen by the last prepare_clip (synchronises)."""

@@ -30,10 +30,14 @@ def bucket_plan(phase_begins, total, min_bucket_elems):
 
 
 class GradReducer:
-    def __init__(self, flat_grads, phase_begins, *, group=None, min_bucket_mb=25.0):
+    def __init__(self, flat_grads, phase_begins, *, group=None, min_bucket_mb=25.0, world=None):
         self.flat = flat_grads
         self.group = group
-        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        # world=1: bucket schedule and side stream only, no exchange (a single-rank Trainer, also inside a process
+        # that has a process group)
+        if world is None:
+            world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.world = world
         self.plan = bucket_plan(phase_begins, flat_grads.numel(), int(min_bucket_mb * (1 << 20) / 4))
         self.cuda = flat_grads.is_cuda
         self.stream = torch.cuda.Stream(device=flat_grads.device) if self.cuda else None
@@ -47,24 +51,35 @@ class GradReducer:
             first = last + 1
         return out
 
-    def reduce_bucket(self, i):
+    def reduce_bucket(self, i, then=None):
         """All-reduce (mean) bucket i; on CUDA it is enqueued on the side stream behind everything
-        issued so far on the current stream."""
-        if self.world == 1:
-            return
+        issued so far on the current stream.  `then(begin, end)` (optional) is called with the side
+        stream current right after the bucket's exchange has been enqueued: work on the final gradient
+        of the bucket that can overlap the rest of the backward (the optimizer's sum of squares).
+        With one rank there is no exchange, only `then`."""
         _, b, e = self.plan[i]
+        if self.world == 1 and then is None:
+            return
         t = self.flat[b:e]
         if self.cuda:
             ready = torch.cuda.Event()
             ready.record(torch.cuda.current_stream(self.flat.device))
             with torch.cuda.stream(self.stream):
                 self.stream.wait_event(ready)
-                dist.all_reduce(t, op=dist.ReduceOp.AVG, group=self.group)
+                if self.world > 1:
+                    dist.all_reduce(t, op=dist.ReduceOp.AVG, group=self.group)
+                if then is not None:
+                    then(b, e)
+            self._pending = True
         else:
-            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
-            t.div_(self.world)
+            if self.world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+                t.div_(self.world)
+            if then is not None:
+                then(b, e)
 
     def wait(self):
         """Make the current stream wait for every bucket enqueued so far."""
-        if self.cuda and self.world > 1:
+        if self.cuda and getattr(self, "_pending", False):
             torch.cuda.current_stream(self.flat.device).wait_stream(self.stream)
+            self._pending = False

@@ -151,14 +151,20 @@ class Trainer:
         logger.info(f'apex_level={self.apex_level} is accepted for compatibility; compute is bf16 with fp32 master '
                     f'weights, no loss scaling.')
 
+        # The backward of an optimizer step's last micro-batch runs bucket by bucket: as a bucket of the flat gradient
+        # becomes final it is all-reduced (N > 1 ranks) and its share of the global-norm sum of squares is taken, both
+        # on a side stream under the backward of the remaining layers.
         self.reducer = None
-        if self.local_rank != -1 and torch.distributed.is_initialized() and torch.distributed.get_world_size() > 1:
+        self.distributed = (self.local_rank != -1 and torch.distributed.is_initialized()
+                            and torch.distributed.get_world_size() > 1)
+        if self.optimizer is not None:
             eng = self.model.engine
             begins = [eng.phase_grad_begin(k) for k in range(eng.num_phases)]
-            self.reducer = GradReducer(eng.grads, begins)
-            # replicas must start identical (DDP broadcasts rank 0's parameters at wrap time)
-            torch.distributed.broadcast(eng.params, src=0)
-            eng.sync_weights()
+            self.reducer = GradReducer(eng.grads, begins, world=None if self.distributed else 1)
+            if self.distributed:
+                # replicas must start identical (DDP broadcasts rank 0's parameters at wrap time)
+                torch.distributed.broadcast(eng.params, src=0)
+                eng.sync_weights()
 
         self.global_step = 0
         self.writer = self._init_writer(self.local_rank, self.writer_dir)
@@ -271,9 +277,16 @@ class Trainer:
         else:
             _, losses = self.model.forward_loss_backward(inputs, labels, lc, last_phase=-1)
             eng = self.model.engine
+            then = None
+            if self.max_grad_norm and hasattr(self.optimizer, 'add_bucket_sumsq') and self.reducer.cuda:
+                main = torch.cuda.current_stream(self.device)
+                with torch.cuda.stream(self.reducer.stream):
+                    self.reducer.stream.wait_stream(main)  # the previous step() has read the old sum
+                    self.optimizer.begin_bucket_sumsq()
+                then = self.optimizer.add_bucket_sumsq
             for first, last, bucket in self.reducer.phases():
                 eng.backward(first, last)
-                self.reducer.reduce_bucket(bucket)
+                self.reducer.reduce_bucket(bucket, then=then)
             self.reducer.wait()
         return losses
 

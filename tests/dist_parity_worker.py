@@ -125,7 +125,7 @@ def main():
 
     if rank == 0:
         model1, opt1, tr1 = build(-1)
-        assert tr1.reducer is None
+        assert tr1.reducer.world == 1  # local_rank -1: no exchange, although this process has a process group
         assert torch.equal(model1.engine.params, w0), "replicas must start from rank 0's weights"
         for s in range(args.steps):
             inputs, labels = make_batch(world * b, args.seq, shape["vocab"], 100 + s, dev)
