@@ -308,6 +308,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   uint64_t* o_free = bars + 23;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
   uint32_t* kvalid = tmem_slot + 2;  // [18] bit k of word w: key 32 w + k is attended
+  // keep words of the softmax threads' rows: [2 buffers][3 words][FW_SOFT threads], filled by cp.async
+  uint32_t* kw_stage = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(bars) + 512);
 
   const int tid = threadIdx.x;
   const int warp = uniform_warp_idx();
@@ -479,22 +481,26 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         named_bar_sync(1, FW_SOFT);
         prev_b = b;
       }
-      const uint32_t* keep_row =
-          a.keep + ((static_cast<size_t>(b) * a.A + h) * S + (q < S ? q : 0)) * keep_words;
       float m_run = -INFINITY, l = 0.0f;
-      // keep bits of the row over the keys of one chunk (3 words), fetched one chunk ahead of their use
-      auto fetch_keep = [&](int j, uint32_t (&w)[3]) {
+      // Keep bits of the row over the keys of one chunk (3 words), fetched one chunk ahead of their use — across the
+      // tile boundary too — by cp.async into shared memory: a register prefetch was spilled by the compiler right
+      // after the load (168 registers), which exposed the whole load latency in every chunk.  A thread reads back
+      // only what it copied itself, so cp.async.wait_group is the only synchronisation.
+      auto fetch_keep = [&](int tt, int j, uint32_t buf) {
+        if (dropping && tt < t1) {
+          const int bh_ = tt / NQ, q_ = (tt - bh_ * NQ) * 128 + r;
+          const uint32_t* row = a.keep + (static_cast<size_t>(bh_) * S + (q_ < S ? q_ : 0)) * keep_words;
 #pragma unroll
-        for (int k = 0; k < 3; ++k)
-          w[k] = (dropping && j < NC && 3 * j + k < 4 * NQ) ? ldg_issue_u32(keep_row + 3 * j + k) : 0xffffffffu;
+          for (int k = 0; k < 3; ++k)
+            if (3 * j + k < 4 * NQ) cp_async_4(kw_stage + (buf * 3 + k) * FW_SOFT + tid, row + 3 * j + k);
+        }
+        cp_async_commit();  // always: the group count tracks the chunk count
       };
-      uint32_t kw_next[3];
-      fetch_keep(0, kw_next);
+      if (it == 0) fetch_keep(t, 0, g & 1u);
       for (int j = 0; j < NC; ++j, ++g) {
         const uint32_t bsel = g & 1u;
         const uint32_t s_addr = lane_base + bsel * KC;
-        const uint32_t kw[3] = {kw_next[0], kw_next[1], kw_next[2]};
-        fetch_keep(j + 1, kw_next);
+        if (j + 1 < NC) fetch_keep(t, j + 1, bsel ^ 1u); else fetch_keep(t + 1, 0, bsel ^ 1u);
         ATACC(8);
         mbar_wait(&s_full[bsel], (g >> 1) & 1u);
         ATACC(1);
@@ -550,11 +556,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         }
         ATACC(3);
         const float m_use = m_run == -INFINITY ? 0.0f : m_run;
+        cp_async_wait<1>();  // this chunk's keep words have landed (the next chunk's may still be in flight)
         // P is stored unscaled; the dropout scale 1 / (1 - p) is applied with the final 1 / rowsum
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
           if (k >= pieces) continue;
-          const uint32_t bits = kw[k];
+          const uint32_t bits = (dropping && 3 * j + k < 4 * NQ) ? kw_stage[(bsel * 3 + k) * FW_SOFT + tid] : 0xffffffffu;
           uint32_t pk[16];
           auto piece = [&](auto masked) {
             const uint32_t vb = decltype(masked)::value ? kvalid[3 * j + k] : 0xffffffffu;
@@ -1392,7 +1399,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
   if (tid == 0) ATRACE(9);
 }
 
-int fwd_smem_bytes() { return 2 * CH + 2 * FW_RING * KCB + 512 + 1024; }
+int fwd_smem_bytes() { return 2 * CH + 2 * FW_RING * KCB + 512 + 2 * 3 * FW_SOFT * 4 + 1024; }
 int dq_smem_bytes() { return 4 * CH + (DQ_KRING + DQ_VRING) * HC + 2048 + 2048 + 512 + 1024; }
 int dkv_smem_bytes() { return 4 * CH + 2 * KV_RING * CH + 8192 + 256 + 1024; }
 

@@ -92,6 +92,15 @@ __device__ __forceinline__ uint32_t ldg_issue_u32(const uint32_t* p) {
   asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(p));
   return v;
 }
+// 4-byte asynchronous global -> shared copy (LDGSTS): the value never occupies a register while in flight
+__device__ __forceinline__ void cp_async_4(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
 __device__ __forceinline__ float ldg_issue_f32(const float* p) {
   float v;
   asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
@@ -478,6 +487,59 @@ __device__ __forceinline__ void gelu_and_grad(float x, float& g, float& dg) {
   const float phi_cdf = 0.5f + copysignf(0.5f - h, x);
   g = x * phi_cdf;
   dg = fmaf(x * 0.39894228040143268f, e, phi_cdf);
+}
+
+// ---- packed fp32 pairs (FFMA2 / FMUL2 / FADD2 on sm_100): one issue slot for two lanes of fp32 work.  The epilogues
+// and row kernels here are bound by instruction issue, not by the fp32 pipe, so halving the issue count of their
+// multiply-adds is worth the explicit pairing.  A pair lives in a 64-bit register (lo = first element).
+__device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t f2_mul(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t f2_splat(float v) { return f2_pack(v, v); }
+
+// gelu_and_grad for two elements at once: the same operations in the same order as the scalar version (bit-identical
+// results), with the multiply-adds issued as packed pairs.
+__device__ __forceinline__ void gelu_and_grad2(float x0, float x1, float& g0, float& g1, float& dg0, float& dg1) {
+  const uint64_t x = f2_pack(x0, x1);
+  const uint64_t ax = f2_pack(fabsf(x0), fabsf(x1));
+  const uint64_t w = f2_mul(ax, f2_splat(0.84932180028801904f));
+  const uint64_t nw = f2_mul(ax, f2_splat(-0.84932180028801904f));
+  float a0, a1, u0, u1, e0, e1, t0, t1;
+  f2_unpack(f2_mul(nw, w), a0, a1);
+  f2_unpack(f2_fma(f2_splat(0.39169197f), w, f2_splat(1.0f)), u0, u1);
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(a0));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(a1));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(u0));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(u1));
+  const uint64_t t = f2_pack(t0, t1), e = f2_pack(e0, e1);
+  uint64_t poly = f2_fma(t, f2_splat(0.3739278f), f2_splat(-0.0479399f));
+  poly = f2_fma(t, poly, f2_splat(0.1740121f));
+  const uint64_t h = f2_mul(f2_mul(poly, t), e);
+  float d0, d1;
+  f2_unpack(f2_fma(h, f2_splat(-1.0f), f2_splat(0.5f)), d0, d1);  // 0.5 - h, one rounding like the scalar subtraction
+  const uint64_t phi = f2_add(f2_splat(0.5f), f2_pack(copysignf(d0, x0), copysignf(d1, x1)));
+  f2_unpack(f2_mul(x, phi), g0, g1);
+  f2_unpack(f2_fma(f2_mul(x, f2_splat(0.39894228040143268f)), e, phi), dg0, dg1);
 }
 
 __device__ __forceinline__ float gelu_erf(float x) {

@@ -437,10 +437,11 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
             for (int q = 0; q < 4; ++q) {
               float gv[8];
 #pragma unroll
-              for (int e = 0; e < 8; ++e) {
-                float dg;
-                gelu_and_grad(f[8 * q + e], gv[e], dg);
-                f[8 * q + e] = dg;
+              for (int e = 0; e < 8; e += 2) {
+                float dg0, dg1;
+                gelu_and_grad2(f[8 * q + e], f[8 * q + e + 1], gv[e], gv[e + 1], dg0, dg1);
+                f[8 * q + e] = dg0;
+                f[8 * q + e + 1] = dg1;
               }
               uint4 o;
               o.x = pack_bf16x2(gv[0], gv[1]);

@@ -160,7 +160,11 @@ class Trainer:
         if self.optimizer is not None:
             eng = self.model.engine
             begins = [eng.phase_grad_begin(k) for k in range(eng.num_phases)]
-            self.reducer = GradReducer(eng.grads, begins, world=None if self.distributed else 1)
+            # exchange dtype: the reference's DDP moves fp32 gradients under apex O0 / O1 and 16-bit ones under O2 / O3
+            # (trainer.py:128-142); BQA_GRAD_EXCHANGE=bf16|fp32 overrides
+            exch = os.environ.get('BQA_GRAD_EXCHANGE', 'bf16' if self.apex_level in ('O2', 'O3') else 'fp32')
+            self.reducer = GradReducer(eng.grads, begins, world=None if self.distributed else 1,
+                                       exchange_dtype=torch.bfloat16 if exch == 'bf16' else torch.float32)
             if self.distributed:
                 # replicas must start identical (DDP broadcasts rank 0's parameters at wrap time)
                 torch.distributed.broadcast(eng.params, src=0)

@@ -17,6 +17,10 @@ init = importlib.import_module("bqa_b200.modules.init")
 tm = importlib.import_module("bqa_b200.modules.model.trainer.trainer")
 B, S = 32, 384
 params, mp = bench.make_params(B, S)
+if 'STEP_HIDDEN_DROPOUT' in os.environ:
+    mp.hidden_dropout_prob = float(os.environ['STEP_HIDDEN_DROPOUT'])
+if 'STEP_ATTN_DROPOUT' in os.environ:
+    mp.attention_probs_dropout_prob = float(os.environ['STEP_ATTN_DROPOUT'])
 torch.manual_seed(1234)
 model, tok = init.init_model(mp, device=dev)
 opt = init.init_optimizer(params, model)
