@@ -1110,7 +1110,32 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
     const bool leader = elect_one();
     const int lane = tid & 31;
     uint32_t g = 0;
-    int prev_bh = -1, nbh = 0;
+    int nbh = 0;
+    // per-query statistics of a (batch, head), staged for the row threads: -lse2 (p = exp2(s * sl2 - lse2)) and
+    // -D * scale (ds = p * (dp * c1 - D * scale)); queries beyond S get p = 0.  Double-buffered: the row threads
+    // never wait for each other at a (batch, head) boundary, only for this warp.  All 32 loads of a lane are in
+    // flight together (one load latency per staging).
+    auto stage_stats = [&](int bh_) {
+      const int sb = nbh & 1;
+      if (nbh >= 2) mbar_wait(&st_free[sb], ((nbh >> 1) - 1) & 1);
+      float* dst = s_stat + sb * 1024;
+      const size_t stat = static_cast<size_t>(bh_) * S;
+      float vl[16], vd[16];
+#pragma unroll
+      for (int u = 0; u < 16; ++u) {
+        const int q = lane + 32 * u;
+        vl[u] = q < S ? ldg_issue_f32(a.lse2 + stat + q) : INFINITY;
+        vd[u] = q < S ? ldg_issue_f32(a.dsum + stat + q) : 0.0f;
+      }
+#pragma unroll
+      for (int u = 0; u < 16; ++u) {
+        dst[lane + 32 * u] = -vl[u];
+        dst[512 + lane + 32 * u] = -vd[u] * a.scale;
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&st_full[sb]);
+      ++nbh;
+    };
     for (int t = t0, it = 0; t < t1; ++t, ++it) {
       const int bh = t / N, kt = t - bh * N, b = bh / a.A, h = bh - b * a.A;
       const int kvb = it & 1;
@@ -1121,24 +1146,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
         tma_load_3d(sV + kvb * CH, &tm_qkv, 2 * a.H + h * 64, kt * 128, b, &kv_full[kvb]);
       }
       __syncwarp();
-      if (bh != prev_bh) {
-        // per-query statistics of the (batch, head), staged for the row threads: -lse2 (p = exp2(s * sl2 - lse2)) and
-        // -D * scale (ds = p * (dp * c1 - D * scale)); queries beyond S get p = 0.  Double-buffered: the row threads
-        // never wait for each other at a (batch, head) boundary, only for this warp.
-        const int sb = nbh & 1;
-        if (nbh >= 2) mbar_wait(&st_free[sb], ((nbh >> 1) - 1) & 1);
-        float* dst = s_stat + sb * 1024;
-        const size_t stat = static_cast<size_t>(bh) * S;
-#pragma unroll 4
-        for (int q = lane; q < 512; q += 32) {
-          dst[q] = q < S ? -__ldg(a.lse2 + stat + q) : -INFINITY;
-          dst[512 + q] = q < S ? -__ldg(a.dsum + stat + q) * a.scale : 0.0f;
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&st_full[sb]);
-        prev_bh = bh;
-        ++nbh;
-      }
+      if (it == 0) stage_stats(bh);
       for (int i = 0; i < N; ++i, ++g) {
         const uint32_t st = g % KV_RING;  // KV_RING is a power of two
         if (g >= KV_RING) mbar_wait(&ld_free[st], ((g / KV_RING) - 1u) & 1u);
@@ -1149,6 +1157,9 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
         }
         __syncwarp();
       }
+      // the next (batch, head)'s statistics are staged one tile early, while the ring is full and this warp would
+      // only wait: staging them at the tile boundary stalled the operand loads for several load latencies
+      if (kt == N - 1 && t + 1 < t1) stage_stats(bh + 1);
     }
   } else if (warp == KV_MMA_WARP) {
     // ---------------- MMA issuer 1: score MMAs (S^T, dP^T of chunk g) ----------------
