@@ -132,13 +132,16 @@ loss_rows_kernel(const float* __restrict__ start, const float* __restrict__ end,
   __shared__ float red[8];
   __shared__ float s_cnt[3];
   const int b = blockIdx.x;
-  // denominators of the three mean-reduced classification losses
-  if (threadIdx.x < 3) {
+  // grid (B, 3): blockIdx.y = 0 / 1: start / end cross entropy of row b; 2: the regressions and the class loss —
+  // three short dependent chains side by side instead of one long one (the kernel is pure latency)
+  const int part = blockIdx.y;
+  // denominator of the part's mean-reduced classification loss
+  if (threadIdx.x < 32) {
     float cnt = 0.0f;
-    for (int i = 0; i < B; ++i) {
-      if (threadIdx.x == 0) cnt += (y_start[i] != -1) ? 1.0f : 0.0f;
-      if (threadIdx.x == 1) cnt += (y_end[i] != -1) ? 1.0f : 0.0f;
-      if (threadIdx.x == 2) {
+    for (int i = threadIdx.x; i < B; i += 32) {
+      if (part == 0) cnt += (y_start[i] != -1) ? 1.0f : 0.0f;
+      if (part == 1) cnt += (y_end[i] != -1) ? 1.0f : 0.0f;
+      if (part == 2) {
         const long long yc = y_cls[i];
         if (lc.cls_kind == CLS_LOSS_FOCAL) {
           if (yc != -1) cnt += 1.0f;  // NLLLoss(ignore_index=-1)
@@ -148,12 +151,14 @@ loss_rows_kernel(const float* __restrict__ start, const float* __restrict__ end,
         }
       }
     }
-    s_cnt[threadIdx.x] = cnt;
+    cnt = warp_sum(cnt);
+    if (threadIdx.x == 0) s_cnt[part] = cnt;
   }
   __syncthreads();
 
   // ---- start / end : CrossEntropyLoss(ignore_index=-1) over the S positions (init.py:34-35)
-  for (int which = 0; which < 2; ++which) {
+  if (part < 2) {
+    const int which = part;
     const float* logit = (which == 0 ? start : end) + static_cast<size_t>(b) * S;
     float* dl = (which == 0 ? d_start : d_end) + static_cast<size_t>(b) * S;
     const long long y = (which == 0 ? y_start : y_end)[b];
@@ -180,6 +185,7 @@ loss_rows_kernel(const float* __restrict__ start, const float* __restrict__ end,
         dl[s] = gs * (p - ((valid && s == y) ? 1.0f : 0.0f));
       }
     }
+    return;
   }
 
   // ---- regressions : MSELoss on the sigmoid outputs (init.py:36-37)
@@ -366,10 +372,15 @@ pooler_wgrad_kernel(const float* __restrict__ dpre, const bf16* __restrict__ y, 
       s_d[e / PJ][e % PJ] = (b < B && j < H) ? dpre[static_cast<size_t>(b) * H + j] : 0.0f;
     }
     __syncthreads();
-    for (int b = 0; b < PB && b0 + b < B; ++b) {
-      const float x = i < H ? __bfloat162float(y[static_cast<size_t>(b0 + b) * S * H + i]) : 0.0f;
+    // all [CLS] elements of the pass first: the loads are independent, one latency instead of PB
+    float xs[PB];
 #pragma unroll
-      for (int j = 0; j < PJ; ++j) acc[j] += s_d[b][j] * x;
+    for (int b = 0; b < PB; ++b)
+      xs[b] = (i < H && b0 + b < B) ? __bfloat162float(y[static_cast<size_t>(b0 + b) * S * H + i]) : 0.0f;
+#pragma unroll
+    for (int b = 0; b < PB; ++b) {  // rows beyond B are zeros in s_d and xs
+#pragma unroll
+      for (int j = 0; j < PJ; ++j) acc[j] += s_d[b][j] * xs[b];
       if (blockIdx.x == 0 && threadIdx.x < PJ) bsum += s_d[b][threadIdx.x];
     }
   }
@@ -383,20 +394,45 @@ pooler_wgrad_kernel(const float* __restrict__ dpre, const bf16* __restrict__ y, 
 
 // dy[t][:] = ds[t] * Ws[0][:] + de[t] * Ws[1][:] (+ dx0[b][:] on the [CLS] row)   -> bf16
 // dWs[k][:] += sum_t d_k[t] * y[t][:], dbs[k] += sum_t d_k[t]     (persistent grid, register partials)
-__global__ void __launch_bounds__(128)
+constexpr int SPAN_WARPS = 8;
+__global__ void __launch_bounds__(SPAN_WARPS * 32)
 span_bwd_kernel(const bf16* __restrict__ y, const float* __restrict__ d_start, const float* __restrict__ d_end,
                 const float* __restrict__ Ws, const float* __restrict__ dx0, bf16* __restrict__ dy,
                 float* __restrict__ dWs, float* __restrict__ dbs, int T, int S, int H) {
-  __shared__ float red[4][2 * 1024 + 2];
+  // One warp per token row, rows round-robin over a persistent grid of one block per SM (the weight-gradient
+  // partials end in 2 H atomics per BLOCK: few blocks keep that cheap).  The next row's activations are loaded
+  // before the current row is processed.
+  __shared__ float red[2 * 1024 + 2];  // block partials, combined with shared-memory atomics
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int MV = 4;
+  for (int c = threadIdx.x; c < 2 * 1024 + 2; c += blockDim.x) red[c] = 0.0f;
+  __syncthreads();
   float acc0[MV][8], acc1[MV][8];
 #pragma unroll
   for (int j = 0; j < MV; ++j)
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc0[j][i] = acc1[j][i] = 0.0f;
   float sb0 = 0.0f, sb1 = 0.0f;
-  for (int t = blockIdx.x * 4 + warp; t < T; t += gridDim.x * 4) {
+  const int stride = gridDim.x * SPAN_WARPS;
+  int t = blockIdx.x * SPAN_WARPS + warp;
+  uint4 nxt[MV];
+#pragma unroll
+  for (int j = 0; j < MV; ++j) {
+    const int c = (j * 32 + lane) * 8;
+    nxt[j] = (t < T && c < H) ? __ldg(reinterpret_cast<const uint4*>(y + static_cast<size_t>(t) * H + c)) : make_uint4(0, 0, 0, 0);
+  }
+  for (; t < T; t += stride) {
+    uint4 cur[MV];
+#pragma unroll
+    for (int j = 0; j < MV; ++j) cur[j] = nxt[j];
+    const int tn = t + stride;
+    if (tn < T) {
+#pragma unroll
+      for (int j = 0; j < MV; ++j) {
+        const int c = (j * 32 + lane) * 8;
+        if (c < H) nxt[j] = __ldg(reinterpret_cast<const uint4*>(y + static_cast<size_t>(tn) * H + c));
+      }
+    }
     const float ds = d_start[t], de = d_end[t];
     sb0 += ds;
     sb1 += de;
@@ -406,17 +442,24 @@ span_bwd_kernel(const bf16* __restrict__ y, const float* __restrict__ d_start, c
     for (int j = 0; j < MV; ++j) {
       const int c = (j * 32 + lane) * 8;
       if (c < H) {
-        const uint4 u = __ldg(reinterpret_cast<const uint4*>(y + static_cast<size_t>(t) * H + c));
+        const uint4 u = cur[j];
         float yv[8];
         const float2 a = unpack_bf16x2(u.x), bb = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
         yv[0] = a.x; yv[1] = a.y; yv[2] = bb.x; yv[3] = bb.y; yv[4] = cc.x; yv[5] = cc.y; yv[6] = d.x; yv[7] = d.y;
+        const float4 w00 = __ldg(reinterpret_cast<const float4*>(Ws + c)), w01 = __ldg(reinterpret_cast<const float4*>(Ws + c + 4));
+        const float4 w10 = __ldg(reinterpret_cast<const float4*>(Ws + H + c)), w11 = __ldg(reinterpret_cast<const float4*>(Ws + H + c + 4));
+        const float ws0[8] = {w00.x, w00.y, w00.z, w00.w, w01.x, w01.y, w01.z, w01.w};
+        const float ws1[8] = {w10.x, w10.y, w10.z, w10.w, w11.x, w11.y, w11.z, w11.w};
         float o[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           acc0[j][i] += ds * yv[i];
           acc1[j][i] += de * yv[i];
-          o[i] = ds * __ldg(Ws + c + i) + de * __ldg(Ws + H + c + i);
-          if (is_cls) o[i] += dx0[static_cast<size_t>(b) * H + c + i];
+          o[i] = ds * ws0[i] + de * ws1[i];
+        }
+        if (is_cls) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) o[i] += dx0[static_cast<size_t>(b) * H + c + i];
         }
         uint4 w;
         w.x = pack_bf16x2(o[0], o[1]);
@@ -428,26 +471,27 @@ span_bwd_kernel(const bf16* __restrict__ y, const float* __restrict__ d_start, c
     }
   }
 #pragma unroll
-  for (int j = 0; j < MV; ++j)
+  for (int j = 0; j < MV; ++j) {
+    if ((j * 32 + lane) * 8 < H) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      red[warp][(j * 32 + lane) * 8 + i] = acc0[j][i];
-      red[warp][1024 + (j * 32 + lane) * 8 + i] = acc1[j][i];
+      for (int i = 0; i < 8; ++i) {
+        atomicAdd(&red[(j * 32 + lane) * 8 + i], acc0[j][i]);
+        atomicAdd(&red[1024 + (j * 32 + lane) * 8 + i], acc1[j][i]);
+      }
     }
+  }
   sb0 = warp_sum(sb0);
   sb1 = warp_sum(sb1);
   if (lane == 0) {
-    red[warp][2048] = sb0;
-    red[warp][2049] = sb1;
+    atomicAdd(&red[2048], sb0);
+    atomicAdd(&red[2049], sb1);
   }
   __syncthreads();
   for (int c = threadIdx.x; c < H; c += blockDim.x) {
-    atomicAdd(dWs + c, red[0][c] + red[1][c] + red[2][c] + red[3][c]);
-    atomicAdd(dWs + H + c, red[0][1024 + c] + red[1][1024 + c] + red[2][1024 + c] + red[3][1024 + c]);
+    atomicAdd(dWs + c, red[c]);
+    atomicAdd(dWs + H + c, red[1024 + c]);
   }
-  if (threadIdx.x < 2)
-    atomicAdd(dbs + threadIdx.x, red[0][2048 + threadIdx.x] + red[1][2048 + threadIdx.x] +
-                                     red[2][2048 + threadIdx.x] + red[3][2048 + threadIdx.x]);
+  if (threadIdx.x < 2) atomicAdd(dbs + threadIdx.x, red[2048 + threadIdx.x]);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -537,7 +581,7 @@ int launch_loss_fwd_bwd(const float* start, const float* end, const float* cls, 
                         const float* y_reg_s, const float* y_reg_e, float* d_start, float* d_end, float* d_cls,
                         float* d_reg_s, float* d_reg_e, float* row_scratch, float* losses_out, int B, int S,
                         int C, const LossConfig& lc, int with_grad, cudaStream_t st, const int* err_flag) {
-  loss_rows_kernel<<<B, 256, 0, st>>>(start, end, cls, reg_s, reg_e, y_start, y_end, y_cls, y_reg_s, y_reg_e,
+  loss_rows_kernel<<<dim3(B, 3), 256, 0, st>>>(start, end, cls, reg_s, reg_e, y_start, y_end, y_cls, y_reg_s, y_reg_e,
                                       d_start, d_end, d_cls, d_reg_s, d_reg_e, row_scratch, B, S, C, lc,
                                       with_grad);
   if (check_launch("loss_rows")) return 1;
@@ -564,9 +608,9 @@ int launch_heads_bwd(const bf16* y, const float* pooled, const float* reg_s, con
   pooler_wgrad_kernel<<<g2, 256, 0, st>>>(dpre_scratch, y, hg.pool_w, hg.pool_b, B, S, H);
   if (check_launch("pooler_wgrad")) return 1;
   const int T = B * S;
-  int grid = num_sms * 4;
-  if (grid > (T + 3) / 4) grid = (T + 3) / 4;
-  span_bwd_kernel<<<grid, 128, 0, st>>>(y, d_start, d_end, hp.span_w, dx0_scratch, dy, hg.span_w, hg.span_b, T, S,
+  int grid = num_sms;
+  if (grid > (T + SPAN_WARPS - 1) / SPAN_WARPS) grid = (T + SPAN_WARPS - 1) / SPAN_WARPS;
+  span_bwd_kernel<<<grid, SPAN_WARPS * 32, 0, st>>>(y, d_start, d_end, hp.span_w, dx0_scratch, dy, hg.span_w, hg.span_b, T, S,
                                         H);
   return check_launch("span_bwd");
 }
