@@ -39,7 +39,7 @@ constexpr int TMEM_COLS = 512;
 constexpr int NUM_THREADS = 384;
 constexpr int EPI_THREADS = 256;
 constexpr int W_STAGE_BYTES = 32 * 128;  // one epilogue warp's staging buffer: 32 rows x 128 B (64 bf16 or 32 fp32)
-constexpr int SMEM_BARRIER_BYTES = 256;
+constexpr int SMEM_BARRIER_BYTES = 320;
 constexpr int QD = 2;  // tile-scheduler response ring depth
 
 // NCTA = 1: one CTA computes a 128 x 256 tile.  NCTA = 2: a CTA pair (cluster of 2, cta_group::2)
@@ -51,11 +51,13 @@ struct Cfg {
   static constexpr int B_ROWS = BLOCK_N / NCTA;          // B rows staged by one CTA
   static constexpr int A_STAGE_BYTES = 128 * BLOCK_K * 2;
   static constexpr int B_STAGE_BYTES = B_ROWS * BLOCK_K * 2;
-  // per-warp epilogue staging: one 32 x 128 B buffer per output
-  static constexpr int WARP_STAGE_BYTES = W_STAGE_BYTES * (EPI == EPI_GELU_FWD ? 2 : 1);
+  // per-warp epilogue staging: two 32 x 128 B buffers for the bf16 epilogues (the two outputs of the GELU epilogue;
+  // otherwise the two 64-column blocks of the warp's slab, so that the side operand of both blocks can be fetched
+  // by TMA while the main loop runs and a block's store never waits for the other's), one for the fp32 reduce-add
+  static constexpr int WARP_STAGE_BYTES = W_STAGE_BYTES * (EPI == EPI_F32_ADD ? 1 : 2);
   static constexpr int C_BYTES = 8 * WARP_STAGE_BYTES;
   // TMA -> MMA ring depth: whatever the staging buffers leave of the 227 KiB
-  static constexpr int STAGES = (NCTA == 2 ? 6 : 4) - (EPI == EPI_GELU_FWD ? 1 : 0);
+  static constexpr int STAGES = (NCTA == 2 ? 6 : 4) - (EPI == EPI_F32_ADD ? 0 : 1);
   static constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + C_BYTES + SMEM_BARRIER_BYTES;
   static constexpr int SMEM_ALLOC = SMEM_BYTES + 1024;   // slack for manual 1024-byte alignment
   static_assert(SMEM_ALLOC <= 232448, "exceeds the 227 KiB per-CTA shared memory limit");
@@ -82,6 +84,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
   uint64_t* bar_qempty = bar_qfull + QD;  // [QD] on the even CTA: every consumer warp of the cluster has read it
   uint64_t* bar_qgo = bar_qempty + QD;    // on the even CTA: its producer has started another tile
   uint4* clc_resp = reinterpret_cast<uint4*>((reinterpret_cast<uintptr_t>(bar_qgo + 1) + 15) & ~uintptr_t(15));  // [QD]
+  uint64_t* bar_side = reinterpret_cast<uint64_t*>(clc_resp + QD);  // [8] side operand of an epilogue warp has landed
 
   const int warp = uniform_warp_idx();  // warp-uniform value: role branches below are uniform control flow
   const int lane = threadIdx.x & 31;
@@ -105,6 +108,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       mbar_init(&bar_qempty[i], NCTA * 9 + 1);  // producer + 8 epilogue warps per CTA, one MMA warp
     }
     mbar_init(bar_qgo, 1);
+    for (int i = 0; i < 8; ++i) mbar_init(&bar_side[i], 1);
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -292,19 +296,23 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       const uint32_t aphase = (it >> 1) & 1u;
       const int m = m0 + row;
       const bool row_ok = m < args.M;
-      // operand of the fused elementwise op (residual / gelu'): one piece ahead of its use, the first
-      // piece before the accumulator is waited for
-      const bf16* side_row = nullptr;
-      if (EPI == EPI_LINEAR && args.residual != nullptr && row_ok) side_row = args.residual + static_cast<size_t>(m) * args.ld_res;
+      // Operand of the fused elementwise op (residual, gelu', or the rows the output is dotted with): its 32 x 128
+      // block comes by TMA into the warp's two staging buffers — the exact places the output blocks are written to
+      // afterwards — while the main loop of this tile still runs.  (Per-thread global loads one piece ahead left
+      // a load latency exposed in each of the four pieces.)  Rows / columns outside the operand arrive as zeros.
       const bool dotting = EPI == EPI_LINEAR && args.dot_out != nullptr;  // side operand = dot_with, not added
-      if (dotting && row_ok) side_row = args.dot_with + static_cast<size_t>(m) * args.ld_dot;
+      const bool has_side = (EPI == EPI_LINEAR && (args.residual != nullptr || dotting)) || EPI == EPI_GELU_BWD;
       float dot_acc = 0.0f;
-      if (EPI == EPI_GELU_BWD && row_ok) side_row = args.aux + static_cast<size_t>(m) * args.ld_aux;
-      uint4 side[4];
-      bool side_ok = side_row != nullptr && n0 < args.N;
-      if (side_ok) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q) side[q] = __ldg(reinterpret_cast<const uint4*>(side_row + n0) + q);
+      if (EPI != EPI_F32_ADD && EPI != EPI_GELU_FWD) {
+        if (lane == 0) {
+          tma_wait_group_read<0>();  // the previous tile's stores have read both buffers
+          if (has_side) {
+            mbar_arrive_expect_tx(&bar_side[warp - 4], 2 * W_STAGE_BYTES);
+            tma_load_2d(stage0, &tmC2, n0, m0 + ew * 32, &bar_side[warp - 4]);
+            tma_load_2d(stage1, &tmC2, n0 + 64, m0 + ew * 32, &bar_side[warp - 4]);
+          }
+        }
+        __syncwarp();
       }
       mbar_wait(&bar_tfull[as], aphase);
       tc_fence_after();
@@ -313,15 +321,15 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         const int n = n0 + piece * 32;
         uint32_t v[32];
         tmem_ld_32x32(lane_base + as * BLOCK_N + cg * 128 + piece * 32, v);
-        uint4 nside[4];
-        bool nside_ok = false;
-        if (piece < 3) {
-          nside_ok = side_row != nullptr && n + 32 < args.N;
-          if (nside_ok) {
+        // staging row of this piece's 64-column block (the GELU epilogue has one buffer per output instead)
+        uint8_t* brow = (EPI == EPI_GELU_FWD || EPI == EPI_F32_ADD) ? srow : srow + (piece >> 1) * W_STAGE_BYTES;
+        uint4 side[4];
+        if (has_side) {
+          if (piece == 0) mbar_wait(&bar_side[warp - 4], it & 1u);
 #pragma unroll
-            for (int q = 0; q < 4; ++q) nside[q] = __ldg(reinterpret_cast<const uint4*>(side_row + n + 32) + q);
-          }
+          for (int q = 0; q < 4; ++q) side[q] = *reinterpret_cast<const uint4*>(brow + ((((piece & 1) * 4 + q) ^ sw) << 4));
         }
+        const bool side_ok = has_side;
         tmem_wait_ld();
         if (piece == 3) {
           // accumulator fully drained into registers: hand the TMEM stage back to the MMA warp
@@ -425,8 +433,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
             if (n + lane < args.N) atomicAdd(args.colsum_out + n + lane, v[0]);
           }
           // two pieces fill one 128-byte staging row; the buffer is reused once the previous store has
-          // finished reading it
-          if ((piece & 1) == 0) {
+          // finished reading it (the other epilogues alternate between two buffers, checked once per tile)
+          if (EPI == EPI_GELU_FWD && (piece & 1) == 0) {
             if (lane == 0) tma_wait_group_read<0>();
             __syncwarp();
           }
@@ -459,7 +467,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
             o.y = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
             o.z = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]);
             o.w = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
-            *reinterpret_cast<uint4*>(srow + ((((piece & 1) * 4 + q) ^ sw) << 4)) = o;
+            *reinterpret_cast<uint4*>(brow + ((((piece & 1) * 4 + q) ^ sw) << 4)) = o;
             if (dotting && side_ok) {
               // dot product of the values as stored (bf16) with the side operand, 64 columns = two pieces
               const uint4 r = side[q];
@@ -483,17 +491,12 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
             if (lane == 0) {
               const int nc = n - 32;
               if (nc < args.N) {
-                tma_store_2d(&tmC, stage0, nc, m0 + ew * 32);
+                tma_store_2d(&tmC, EPI == EPI_GELU_FWD ? stage0 : stage0 + (piece >> 1) * W_STAGE_BYTES, nc, m0 + ew * 32);
                 if (EPI == EPI_GELU_FWD) tma_store_2d(&tmC2, stage1, nc, m0 + ew * 32);
               }
               tma_commit_group();
             }
           }
-        }
-        if (piece < 3) {
-          side_ok = nside_ok;
-#pragma unroll
-          for (int q = 0; q < 4; ++q) side[q] = nside[q];
         }
       }
       if (!next_tile(tile)) break;
@@ -679,7 +682,17 @@ int gemm_plan(GemmPlan* plan, const GemmProblem& p, int num_sms) {
     }
     rc |= encode_tmap_2d(&plan->tmC2, p.C2, 2, p.N, p.M, p.ldc, 64, 32);
   } else {
-    plan->tmC2 = plan->tmC;
+    // the other bf16 epilogues fetch their side operand (residual / rows to dot with / gelu') through this map: same
+    // [M][N] shape and 64 x 32 boxes as the output
+    const void* side = nullptr;
+    int ld_side = 0;
+    if (p.epilogue == EPI_LINEAR && p.residual != nullptr) side = p.residual, ld_side = p.ld_res;
+    if (p.epilogue == EPI_LINEAR && p.dot_out != nullptr) side = p.dot_with, ld_side = p.ld_dot;
+    if (p.epilogue == EPI_GELU_BWD) side = p.aux, ld_side = p.ld_aux;
+    if (side != nullptr)
+      rc |= encode_tmap_2d(&plan->tmC2, side, 2, p.N, p.M, ld_side, 64, 32);
+    else
+      plan->tmC2 = plan->tmC;
   }
   if (rc) return 1;
 

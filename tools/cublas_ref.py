@@ -6,7 +6,8 @@ dev = "cuda"
 T, H, I = 12288, 768, 3072
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 cases = [("qkv fwd   [T,H]x[H,3H]", T, 3 * H, H), ("ao fwd    [T,H]x[H,H]", T, H, H), ("ffn1 fwd  [T,H]x[H,I]", T, I, H),
-         ("ffn2 fwd  [T,I]x[I,H]", T, H, I), ("ffn1 wgrad [I,T]x[T,H]", I, H, T), ("qkv wgrad [3H,T]x[T,H]", 3 * H, H, T)]
+         ("ffn2 fwd  [T,I]x[I,H]", T, H, I), ("ffn1 wgrad [I,T]x[T,H]", I, H, T), ("qkv wgrad [3H,T]x[T,H]", 3 * H, H, T),
+         ("ao wgrad  [H,T]x[T,H]", H, H, T), ("ffn2 dgrad [T,H]x[H,I]", T, I, H), ("qkv dgrad [T,3H]x[3H,H]", T, H, 3 * H)]
 for name, M, N, K in cases:
     a = torch.randn(M, K, device=dev).to(torch.bfloat16)
     b = torch.randn(K, N, device=dev).to(torch.bfloat16)
