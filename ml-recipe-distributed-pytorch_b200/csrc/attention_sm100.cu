@@ -205,23 +205,6 @@ __device__ __forceinline__ void fill_key_bias(float* kbias, uint32_t* kvalid, co
   if ((tid & 31) == 0) kvalid[tid >> 5] = w;
 }
 
-// keep decisions for the 32 consecutive elements starting at `idx`, one bit each
-__device__ __forceinline__ uint32_t keep_bits32(const DropKey& dk, uint32_t idx) {
-  uint32_t bits = 0;
-  if ((idx & 1u) == 0u) {
-#pragma unroll
-    for (int e = 0; e < 32; e += 2) {
-      const uint32_t h = drop_hash(dk, (idx + e) >> 1);
-      bits |= ((h & 0xffffu) >= dk.thresh ? 1u : 0u) << e;
-      bits |= ((h >> 16) >= dk.thresh ? 1u : 0u) << (e + 1);
-    }
-  } else {
-#pragma unroll
-    for (int e = 0; e < 32; ++e) bits |= (drop_keep(dk, idx + e) ? 1u : 0u) << e;
-  }
-  return bits;
-}
-
 // =========================================================================================
 // dropout keep bits of one attention call, in two layouts per (batch, head) row r (W = 4 * nchunk words):
 //   keep[(bh * S + r) * 2 W + w]      bit k : (query r, key 32 w + k)      forward, dQ kernel

@@ -589,6 +589,23 @@ __device__ __forceinline__ void drop_keep2(const DropKey& dk, uint32_t idx_even,
   keep1 = (h >> 16) >= dk.thresh;
 }
 
+// keep decisions for the 32 consecutive elements starting at `idx`, one bit each
+__device__ __forceinline__ uint32_t keep_bits32(const DropKey& dk, uint32_t idx) {
+  uint32_t bits = 0;
+  if ((idx & 1u) == 0u) {
+#pragma unroll
+    for (int e = 0; e < 32; e += 2) {
+      const uint32_t h = drop_hash(dk, (idx + e) >> 1);
+      bits |= ((h & 0xffffu) >= dk.thresh ? 1u : 0u) << e;
+      bits |= ((h >> 16) >= dk.thresh ? 1u : 0u) << (e + 1);
+    }
+  } else {
+#pragma unroll
+    for (int e = 0; e < 32; ++e) bits |= (drop_keep(dk, idx + e) ? 1u : 0u) << e;
+  }
+  return bits;
+}
+
 // three-input maximum (one FMNMX3 on sm_100)
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
   float d;

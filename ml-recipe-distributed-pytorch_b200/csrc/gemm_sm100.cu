@@ -314,6 +314,14 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         }
         __syncwarp();
       }
+      // the dropout decisions of the thread's 128 elements depend only on their indices: hashed while the main loop
+      // still runs instead of on the critical path after it
+      uint32_t kbits[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+      if (EPI == EPI_LINEAR && args.drop.thresh != 0u) {
+        const uint32_t base_idx = static_cast<uint32_t>(m) * static_cast<uint32_t>(args.N) + static_cast<uint32_t>(n0);
+#pragma unroll
+        for (int piece = 0; piece < 4; ++piece) kbits[piece] = keep_bits32(args.drop, base_idx + piece * 32);  // even index
+      }
       mbar_wait(&bar_tfull[as], aphase);
       tc_fence_after();
 #pragma unroll
@@ -367,15 +375,9 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           }
           if (EPI == EPI_LINEAR) {
             if (args.drop.thresh != 0u) {
-              const uint32_t base_idx = static_cast<uint32_t>(m) * static_cast<uint32_t>(args.N) +
-                                        static_cast<uint32_t>(n);  // even: N and n are even
+              const uint32_t kb = kbits[piece];
 #pragma unroll
-              for (int i = 0; i < 32; i += 2) {
-                bool k0, k1;
-                drop_keep2(args.drop, base_idx + i, k0, k1);
-                f[i] = k0 ? f[i] * args.drop.scale : 0.0f;
-                f[i + 1] = k1 ? f[i + 1] * args.drop.scale : 0.0f;
-              }
+              for (int i = 0; i < 32; ++i) f[i] = ((kb >> i) & 1u) ? f[i] * args.drop.scale : 0.0f;
             }
             if (side_ok && !dotting) {
 #pragma unroll
