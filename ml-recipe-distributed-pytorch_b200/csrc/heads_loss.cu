@@ -358,7 +358,7 @@ pooler_dx_kernel(const float* __restrict__ dpre, const float* __restrict__ Wp, f
 __global__ void __launch_bounds__(256)
 pooler_wgrad_kernel(const float* __restrict__ dpre, const bf16* __restrict__ y, float* __restrict__ dWp,
                     float* __restrict__ dbp, int B, int S, int H) {
-  __shared__ float s_d[PB][PJ];
+  __shared__ __align__(16) float s_d[PB][PJ];
   const int i = blockIdx.x * 256 + threadIdx.x;
   const int j0 = blockIdx.y * PJ;
   float acc[PJ];
@@ -380,7 +380,13 @@ pooler_wgrad_kernel(const float* __restrict__ dpre, const bf16* __restrict__ y, 
 #pragma unroll
     for (int b = 0; b < PB; ++b) {  // rows beyond B are zeros in s_d and xs
 #pragma unroll
-      for (int j = 0; j < PJ; ++j) acc[j] += s_d[b][j] * xs[b];
+      for (int j = 0; j < PJ; j += 4) {  // 16-byte broadcast reads: the loop is bound by shared-memory instructions
+        const float4 d4 = *reinterpret_cast<const float4*>(&s_d[b][j]);
+        acc[j] += d4.x * xs[b];
+        acc[j + 1] += d4.y * xs[b];
+        acc[j + 2] += d4.z * xs[b];
+        acc[j + 3] += d4.w * xs[b];
+      }
       if (blockIdx.x == 0 && threadIdx.x < PJ) bsum += s_d[b][threadIdx.x];
     }
   }
