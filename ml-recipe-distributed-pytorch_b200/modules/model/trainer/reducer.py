@@ -18,6 +18,14 @@ BERT-base, the compute dtype of this implementation.  fp32 stays available (`exc
 import torch
 import torch.distributed as dist
 
+# Bucket size.  Every all-reduce issued beside the backward costs ~0.1-0.2 ms of step time whatever its size: its CTAs take
+# SMs as soon as a GEMM of the backward lets go of them and then spin until the peers' CTAs have been scheduled too
+# (every rank is in the middle of a different GEMM).  Over NVLink 5 / NVSwitch the bytes themselves are cheap (438 MB in
+# ~0.7 ms at 8 GPUs), so few large buckets beat many small ones.  Measured on B200s, BERT-base, ms per step at 25 / 60 /
+# 120 / 160 / 220 MB: 8 GPUs 10.50 / 10.41 / 10.24 / 10.20 / 10.01, 2 GPUs 10.05 / - / - / 10.03 / 9.93
+# (profiles/r02_bucket_sweep.json).  220 MB = two buckets for BERT-base (heads + layers 11..4 | layers 3..0 + embeddings).
+DEFAULT_BUCKET_MB = 220.0
+
 
 def bucket_plan(phase_begins, total, min_bucket_elems):
     """phase_begins[k] = first flat element that is final after backward phase k (decreasing, last
@@ -35,7 +43,7 @@ def bucket_plan(phase_begins, total, min_bucket_elems):
 
 
 class GradReducer:
-    def __init__(self, flat_grads, phase_begins, *, group=None, min_bucket_mb=25.0, world=None,
+    def __init__(self, flat_grads, phase_begins, *, group=None, min_bucket_mb=DEFAULT_BUCKET_MB, world=None,
                  exchange_dtype=torch.float32):
         self.flat = flat_grads
         self.group = group

@@ -30,7 +30,7 @@ from torch.utils.data import DataLoader, DistributedSampler, RandomSampler, Weig
 from ..dataset import expand_compact_inputs
 from .callback import TestCallback
 from .meters import AverageMeter
-from .reducer import GradReducer
+from .reducer import DEFAULT_BUCKET_MB, GradReducer
 
 logger = logging.getLogger(__file__)
 
@@ -160,11 +160,14 @@ class Trainer:
         if self.optimizer is not None:
             eng = self.model.engine
             begins = [eng.phase_grad_begin(k) for k in range(eng.num_phases)]
+            # bucket size: few large buckets when they are exchanged (reducer.DEFAULT_BUCKET_MB); a single rank only
+            # overlaps the sum of squares with the backward, where one bucket per layer is best
             # exchange dtype: the reference's DDP moves fp32 gradients under apex O0 / O1 and 16-bit ones under O2 / O3
             # (trainer.py:128-142); BQA_GRAD_EXCHANGE=bf16|fp32 overrides
             exch = os.environ.get('BQA_GRAD_EXCHANGE', 'bf16' if self.apex_level in ('O2', 'O3') else 'fp32')
             self.reducer = GradReducer(eng.grads, begins, world=None if self.distributed else 1,
-                                       exchange_dtype=torch.bfloat16 if exch == 'bf16' else torch.float32)
+                                       exchange_dtype=torch.bfloat16 if exch == 'bf16' else torch.float32,
+                                       min_bucket_mb=float(os.environ.get('BQA_BUCKET_MB', DEFAULT_BUCKET_MB if self.distributed else 25.0)))
             if self.distributed:
                 # replicas must start identical (DDP broadcasts rank 0's parameters at wrap time)
                 torch.distributed.broadcast(eng.params, src=0)

@@ -98,7 +98,7 @@ def main():
         return model, opt, tr
 
     model, opt, tr = build(rank)
-    assert tr.reducer is not None and len(tr.reducer.plan) >= (3 if args.shape == "base" else 1)
+    assert tr.reducer is not None and len(tr.reducer.plan) >= (2 if args.shape == "base" else 1)
     w0 = model.engine.params.clone()
     b = args.per_rank
     report = {"world": world, "shape": args.shape, "per_rank": b, "seq": args.seq, "steps": args.steps,
