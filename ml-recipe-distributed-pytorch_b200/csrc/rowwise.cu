@@ -284,7 +284,10 @@ embed_ln_fwd_kernel(const int64_t* __restrict__ ids, const int64_t* __restrict__
 // for the whole kernel (no shared-memory read-modify-write per row), xhat and the output come from fused
 // multiply-adds with per-row constants, and the next row's loads are issued before the current row is reduced.
 // Partials are combined once per block (shared memory) and once per grid (atomicAdd).
-template <int NV>
+// FAST: the encoder layers' case fixed at compile time (H == NV * 256, no dropout after this LayerNorm, masked copy
+// with dropout and its column sums wanted, dz_masked != dz): the uniform branches around every 8-element group cost 8 %
+// of the kernel's instructions.
+template <int NV, bool FAST>
 __global__ void __launch_bounds__(ROW_WARPS * 32, NV <= 3 ? 3 : 2)
 ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const float* __restrict__ gamma,
               bf16* __restrict__ dz, bf16* __restrict__ dz_masked, float* __restrict__ dgamma,
@@ -301,8 +304,8 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
   for (int c = threadIdx.x; c < W; c += blockDim.x) s_gamma[c] = c < H ? gamma[c] : 0.0f;
   __syncthreads();
   const float invH = 1.0f / static_cast<float>(H);
-  const bool masking = dz_masked != nullptr;
-  const bool want_dbias = dbias != nullptr;
+  const bool masking = FAST || dz_masked != nullptr;
+  const bool want_dbias = FAST || dbias != nullptr;
 
   float ag[NV][8], ab[NV][8], am[NV][8];
 #pragma unroll
@@ -316,7 +319,7 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
 #pragma unroll
   for (int j = 0; j < NV; ++j) {
     const int c = (j * 32 + lane) * 8;
-    const bool ok = row < T && c < H;
+    const bool ok = row < T && (FAST || c < H);
     nz[j] = ok ? __ldg(reinterpret_cast<const uint4*>(z + static_cast<size_t>(row) * H + c)) : make_uint4(0, 0, 0, 0);
     nd[j] = ok ? __ldg(reinterpret_cast<const uint4*>(dy + static_cast<size_t>(row) * H + c)) : make_uint4(0, 0, 0, 0);
   }
@@ -338,40 +341,48 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
 #pragma unroll
       for (int j = 0; j < NV; ++j) {
         const int c = (j * 32 + lane) * 8;
-        if (c < H) {
+        if (FAST || c < H) {
           nz[j] = __ldg(reinterpret_cast<const uint4*>(z + static_cast<size_t>(nrow) * H + c));
           nd[j] = __ldg(reinterpret_cast<const uint4*>(dy + static_cast<size_t>(nrow) * H + c));
         }
       }
     }
+    // The arithmetic below runs on packed fp32 pairs (FFMA2 / FMUL2 / FADD2: one issue slot for two elements; the
+    // kernel is bound by instruction issue).  Each element sees the same operations as in scalar form.
     // row statistics (biased two-pass variance, as torch)
-    float s = 0.0f;
+    uint64_t sp = f2_splat(0.0f);
 #pragma unroll
     for (int j = 0; j < NV; ++j)
 #pragma unroll
-      for (int i = 0; i < 8; ++i) s += x[j][i];
-    const float mean = warp_sum(s) * invH;
-    float qv = 0.0f;
+      for (int i = 0; i < 8; i += 2) sp = f2_add(sp, f2_pack(x[j][i], x[j][i + 1]));
+    float s_lo, s_hi;
+    f2_unpack(sp, s_lo, s_hi);
+    const float mean = warp_sum(s_lo + s_hi) * invH;
+    const uint64_t nmean2 = f2_splat(-mean);
+    uint64_t qp = f2_splat(0.0f);
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
-      if ((j * 32 + lane) * 8 < H) {
+      if (FAST || (j * 32 + lane) * 8 < H) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float t = x[j][i] - mean;
-          qv = fmaf(t, t, qv);
+        for (int i = 0; i < 8; i += 2) {
+          const uint64_t t2 = f2_add(f2_pack(x[j][i], x[j][i + 1]), nmean2);
+          qp = f2_fma(t2, t2, qp);
         }
       }
     }
-    const float rstd = rsqrtf(warp_sum(qv) * invH + eps);
+    float q_lo, q_hi;
+    f2_unpack(qp, q_lo, q_hi);
+    const float rstd = rsqrtf(warp_sum(q_lo + q_hi) * invH + eps);
     const float nmr = -mean * rstd;  // xhat = x * rstd + nmr
-    float s1 = 0.0f, s2 = 0.0f;
+    const uint64_t rstd2 = f2_splat(rstd), nmr2 = f2_splat(nmr);
+    uint64_t s1p = f2_splat(0.0f), s2p = f2_splat(0.0f);
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
       const int c = (j * 32 + lane) * 8;
-      if (c < H) {
+      if (FAST || c < H) {
         const float4 g0 = *reinterpret_cast<const float4*>(s_gamma + c), g1 = *reinterpret_cast<const float4*>(s_gamma + c + 4);
         const float gv[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-        if (drop_in.thresh != 0u) {
+        if (!FAST && drop_in.thresh != 0u) {
           const uint32_t base = static_cast<uint32_t>(row) * H + c;  // even
 #pragma unroll
           for (int i = 0; i < 8; i += 2) {
@@ -382,32 +393,35 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
           }
         }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float dyv = d[j][i];
-          const float xhat = fmaf(x[j][i], rstd, nmr);
-          const float dxhat = dyv * gv[i];
-          ag[j][i] = fmaf(dyv, xhat, ag[j][i]);
-          ab[j][i] += dyv;
-          s1 += dxhat;
-          s2 = fmaf(dxhat, xhat, s2);
-          x[j][i] = xhat;
-          d[j][i] = dxhat;
+        for (int i = 0; i < 8; i += 2) {
+          const uint64_t dy2 = f2_pack(d[j][i], d[j][i + 1]);
+          const uint64_t xhat2 = f2_fma(f2_pack(x[j][i], x[j][i + 1]), rstd2, nmr2);
+          const uint64_t dxhat2 = f2_mul(dy2, f2_pack(gv[i], gv[i + 1]));
+          f2_unpack(f2_fma(dy2, xhat2, f2_pack(ag[j][i], ag[j][i + 1])), ag[j][i], ag[j][i + 1]);
+          f2_unpack(f2_add(f2_pack(ab[j][i], ab[j][i + 1]), dy2), ab[j][i], ab[j][i + 1]);
+          s1p = f2_add(s1p, dxhat2);
+          s2p = f2_fma(dxhat2, xhat2, s2p);
+          f2_unpack(xhat2, x[j][i], x[j][i + 1]);
+          f2_unpack(dxhat2, d[j][i], d[j][i + 1]);
         }
       }
     }
-    s1 = warp_sum(s1) * invH;
-    s2 = warp_sum(s2) * invH;
+    float s1_lo, s1_hi, s2_lo, s2_hi;
+    f2_unpack(s1p, s1_lo, s1_hi);
+    f2_unpack(s2p, s2_lo, s2_hi);
+    const float s1 = warp_sum(s1_lo + s1_hi) * invH;
+    const float s2 = warp_sum(s2_lo + s2_hi) * invH;
     // dz = rstd * (dxhat - s1 - xhat * s2) = dxhat * rstd + (xhat * k2 + k1)
-    const float k1 = -s1 * rstd, k2 = -s2 * rstd;
+    const uint64_t k1p = f2_splat(-s1 * rstd), k2p = f2_splat(-s2 * rstd);
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
       const int c = (j * 32 + lane) * 8;
-      if (c < H) {
+      if (FAST || c < H) {
         uint32_t pk[4];
 #pragma unroll
         for (int i = 0; i < 8; i += 2) {
-          const float v0 = fmaf(d[j][i], rstd, fmaf(x[j][i], k2, k1));
-          const float v1 = fmaf(d[j][i + 1], rstd, fmaf(x[j][i + 1], k2, k1));
+          float v0, v1;
+          f2_unpack(f2_fma(f2_pack(d[j][i], d[j][i + 1]), rstd2, f2_fma(f2_pack(x[j][i], x[j][i + 1]), k2p, k1p)), v0, v1);
           pk[i >> 1] = pack_bf16x2(v0, v1);
         }
         *reinterpret_cast<uint4*>(dz + static_cast<size_t>(row) * H + c) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
@@ -419,20 +433,18 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
           for (int i = 0; i < 8; i += 2) {
             const float2 rr = unpack_bf16x2(pk[i >> 1]);
             float m0 = rr.x, m1 = rr.y;
-            if (drop_out.thresh != 0u) {
+            if (FAST || drop_out.thresh != 0u) {
               bool k0, k1b;
               drop_keep2(drop_out, base + i, k0, k1b);
-              m0 = k0 ? m0 * drop_out.scale : 0.0f;
-              m1 = k1b ? m1 * drop_out.scale : 0.0f;
+              f2_unpack(f2_mul(f2_pack(m0, m1), f2_pack(k0 ? drop_out.scale : 0.0f, k1b ? drop_out.scale : 0.0f)), m0, m1);
             }
             pm[i >> 1] = pack_bf16x2(m0, m1);
             if (want_dbias) {
               const float2 mr = unpack_bf16x2(pm[i >> 1]);
-              am[j][i] += mr.x;
-              am[j][i + 1] += mr.y;
+              f2_unpack(f2_add(f2_pack(am[j][i], am[j][i + 1]), f2_pack(mr.x, mr.y)), am[j][i], am[j][i + 1]);
             }
           }
-          if (dz_masked != dz)
+          if (FAST || dz_masked != dz)
             *reinterpret_cast<uint4*>(dz_masked + static_cast<size_t>(row) * H + c) = make_uint4(pm[0], pm[1], pm[2], pm[3]);
         } else if (want_dbias) {
 #pragma unroll
@@ -699,17 +711,25 @@ int launch_ln_bwd(const bf16* dy, const bf16* z, const float* gamma, bf16* dz, b
   const int nv = (H + 255) / 256;
   const size_t smem = static_cast<size_t>(nv) * 256 * (1 + ROW_WARPS) * sizeof(float);
   int grid = num_sms * (nv <= 3 ? 3 : 2);  // every block resident: see __launch_bounds__ of the kernel
+  const bool fast = H == nv * 256 && drop_in.thresh == 0u && drop_out.thresh != 0u && dz_masked != nullptr &&
+                    dz_masked != dz && dbias != nullptr;
   if (grid > row_blocks(T)) grid = row_blocks(T);
 #define BQA_LN_BWD(NV)                                                                                         \
   {                                                                                                            \
     static PerDeviceOnce once;                                                                                 \
     int once_dev; if (once.needs_setup(&once_dev)) {                                                                                  \
-      BQA_CUDA_CHECK(cudaFuncSetAttribute(ln_bwd_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
+      BQA_CUDA_CHECK(cudaFuncSetAttribute(ln_bwd_kernel<NV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                          static_cast<int>(smem)));                                            \
+      BQA_CUDA_CHECK(cudaFuncSetAttribute(ln_bwd_kernel<NV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                           static_cast<int>(smem)));                                            \
       once.mark_done(once_dev);                                                                                        \
     }                                                                                                          \
-    launch_pdl(ln_bwd_kernel<NV>, grid, ROW_WARPS * 32, smem, st, dy, z, gamma, dz, dz_masked, dgamma, dbeta, dbias, T, \
-               H, eps, drop_in, drop_out);                                                                     \
+    if (fast)                                                                                                  \
+      launch_pdl(ln_bwd_kernel<NV, true>, grid, ROW_WARPS * 32, smem, st, dy, z, gamma, dz, dz_masked, dgamma, dbeta, \
+                 dbias, T, H, eps, drop_in, drop_out);                                                         \
+    else                                                                                                       \
+      launch_pdl(ln_bwd_kernel<NV, false>, grid, ROW_WARPS * 32, smem, st, dy, z, gamma, dz, dz_masked, dgamma, dbeta, \
+                 dbias, T, H, eps, drop_in, drop_out);                                                         \
   }
   switch (nv) {
     case 1: BQA_LN_BWD(1) break;
