@@ -908,16 +908,20 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
         mbar_arrive(s_free);
         const int key0 = j * 64 + hq * 32;
         uint32_t pk[16];
+        const uint64_t sl2p = f2_splat(sl2), c1p = f2_splat(c1), ndsp = f2_splat(nds);
         auto chunk = [&](auto biased) {
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
             const float off0 = decltype(biased)::value ? kbias[key0 + i] + nlse : nlse;
             const float off1 = decltype(biased)::value ? kbias[key0 + i + 1] + nlse : nlse;
-            const float p0 = fast_exp2(fmaf(__uint_as_float(vs[i]), sl2, off0));
-            const float p1 = fast_exp2(fmaf(__uint_as_float(vs[i + 1]), sl2, off1));
+            // packed fp32 pairs: one issue slot for the two elements' multiply-adds (same operations per element)
+            float a0, a1, ds0, ds1;
+            f2_unpack(f2_fma(f2_pack(__uint_as_float(vs[i]), __uint_as_float(vs[i + 1])), sl2p, f2_pack(off0, off1)), a0, a1);
+            const float p0 = fast_exp2(a0), p1 = fast_exp2(a1);
             const float dp0 = ((bits >> i) & 1u) ? __uint_as_float(vd[i]) : 0.0f;
             const float dp1 = ((bits >> (i + 1)) & 1u) ? __uint_as_float(vd[i + 1]) : 0.0f;
-            pk[i >> 1] = pack_bf16x2(p0 * fmaf(dp0, c1, nds), p1 * fmaf(dp1, c1, nds));
+            f2_unpack(f2_mul(f2_pack(p0, p1), f2_fma(f2_pack(dp0, dp1), c1p, ndsp)), ds0, ds1);
+            pk[i >> 1] = pack_bf16x2(ds0, ds1);
           }
         };
         // 32-key groups without a masked key (all of them unless KB) take the path without the bias
@@ -1337,6 +1341,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
         ATACC(2);
         const int q0 = i * 128 + qd * 32;
         uint32_t ppk[16], dpk[16];
+        const uint64_t sl2p = f2_splat(sl2), c1p = f2_splat(c1);
 #pragma unroll
         for (int gq = 0; gq < 4; ++gq) {
           const float4 l0 = *reinterpret_cast<const float4*>(s_lse + q0 + gq * 8);
@@ -1349,12 +1354,15 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_con
           for (int e = 0; e < 8; e += 2) {
             const int c = gq * 8 + e;
             const bool keep0 = (bits >> c) & 1u, keep1 = (bits >> (c + 1)) & 1u;
-            const float p0 = fast_exp2(fmaf(__uint_as_float(vs[c]), sl2, nlse[e]));
-            const float p1 = fast_exp2(fmaf(__uint_as_float(vs[c + 1]), sl2, nlse[e + 1]));
+            // packed fp32 pairs: one issue slot for the two elements' multiply-adds (same operations per element)
+            float a0, a1, ds0, ds1;
+            f2_unpack(f2_fma(f2_pack(__uint_as_float(vs[c]), __uint_as_float(vs[c + 1])), sl2p, f2_pack(nlse[e], nlse[e + 1])), a0, a1);
+            const float p0 = fast_exp2(a0), p1 = fast_exp2(a1);
             const float dp0 = keep0 ? __uint_as_float(vd[c]) : 0.0f;
             const float dp1 = keep1 ? __uint_as_float(vd[c + 1]) : 0.0f;
             ppk[c >> 1] = pack_bf16x2(keep0 ? p0 : 0.0f, keep1 ? p1 : 0.0f);
-            dpk[c >> 1] = pack_bf16x2(p0 * fmaf(dp0, c1, nds[e]), p1 * fmaf(dp1, c1, nds[e + 1]));
+            f2_unpack(f2_mul(f2_pack(p0, p1), f2_fma(f2_pack(dp0, dp1), c1p, f2_pack(nds[e], nds[e + 1]))), ds0, ds1);
+            dpk[c >> 1] = pack_bf16x2(ds0, ds1);
           }
         }
         ATACC(3);
