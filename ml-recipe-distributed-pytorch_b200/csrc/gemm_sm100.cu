@@ -362,37 +362,38 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
             tma_commit_group();
           }
         } else {
+          // bias, dropout and residual on packed fp32 pairs (one issue slot per two elements; the same operations and
+          // roundings per element as in scalar form; a dropped element is multiplied by zero, as torch's dropout does)
           if (EPI != EPI_GELU_BWD && args.bias != nullptr && n < args.N) {
             const float4* bp = reinterpret_cast<const float4*>(args.bias + n);
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
               const float4 b = __ldg(bp + q);
-              f[4 * q] += b.x;
-              f[4 * q + 1] += b.y;
-              f[4 * q + 2] += b.z;
-              f[4 * q + 3] += b.w;
+              f2_unpack(f2_add(f2_pack(f[4 * q], f[4 * q + 1]), f2_pack(b.x, b.y)), f[4 * q], f[4 * q + 1]);
+              f2_unpack(f2_add(f2_pack(f[4 * q + 2], f[4 * q + 3]), f2_pack(b.z, b.w)), f[4 * q + 2], f[4 * q + 3]);
             }
           }
           if (EPI == EPI_LINEAR) {
             if (args.drop.thresh != 0u) {
               const uint32_t kb = kbits[piece];
+              const float sc = args.drop.scale;
 #pragma unroll
-              for (int i = 0; i < 32; ++i) f[i] = ((kb >> i) & 1u) ? f[i] * args.drop.scale : 0.0f;
+              for (int i = 0; i < 32; i += 2)
+                f2_unpack(f2_mul(f2_pack(f[i], f[i + 1]),
+                                 f2_pack(((kb >> i) & 1u) ? sc : 0.0f, ((kb >> (i + 1)) & 1u) ? sc : 0.0f)),
+                          f[i], f[i + 1]);
             }
             if (side_ok && !dotting) {
 #pragma unroll
               for (int q = 0; q < 4; ++q) {
                 const uint4 r = side[q];
-                const float2 r0 = unpack_bf16x2(r.x), r1 = unpack_bf16x2(r.y);
-                const float2 r2 = unpack_bf16x2(r.z), r3 = unpack_bf16x2(r.w);
-                f[8 * q] += r0.x;
-                f[8 * q + 1] += r0.y;
-                f[8 * q + 2] += r1.x;
-                f[8 * q + 3] += r1.y;
-                f[8 * q + 4] += r2.x;
-                f[8 * q + 5] += r2.y;
-                f[8 * q + 6] += r3.x;
-                f[8 * q + 7] += r3.y;
+                const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const float2 rv = unpack_bf16x2(rw[e]);
+                  f2_unpack(f2_add(f2_pack(f[8 * q + 2 * e], f[8 * q + 2 * e + 1]), f2_pack(rv.x, rv.y)), f[8 * q + 2 * e],
+                            f[8 * q + 2 * e + 1]);
+                }
               }
             }
           }
