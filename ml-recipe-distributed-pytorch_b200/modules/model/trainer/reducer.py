@@ -100,6 +100,8 @@ class GradReducer:
     def _all_reduce_bf16(self, t):
         """fp32 bucket -> bf16 (library kernel) -> all-reduce (mean) of half the bytes -> back into the fp32 bucket.
         Runs on the side stream; consecutive buckets share one staging buffer (stream-ordered)."""
+        if not t.is_cuda:
+            raise RuntimeError('the bf16 gradient exchange packs with a CUDA kernel (bqa_f32_to_bf16): there is no CPU path')
         from .... import _lib as L
         if self._pack is None:
             n_max = max(e - b for _, b, e in self.plan)

@@ -144,6 +144,28 @@ def test_gradient_allreduce_mean_gloo_world2(tmp_path):
     assert torch.equal(f0, f1)
 
 
+def test_default_bucket_plan_is_two_buckets_for_bert_base(pkg):
+    """reducer.DEFAULT_BUCKET_MB (220 MB): heads + layers 11..4 | layers 3..0 + embeddings for BERT-base-sized phases
+    (every overlapped all-reduce costs 0.1-0.2 ms whatever its size)."""
+    R = importlib.import_module("bqa_b200.modules.model.trainer.reducer")
+    mb = lambda x: int(x * (1 << 20) / 4)
+    sizes = [mb(2.4)] + [mb(28.3)] * 12 + [mb(95.0)]   # heads, layers 11..0, embeddings (elements)
+    total = sum(sizes)
+    begins, left = [], total
+    for n in sizes:
+        left -= n
+        begins.append(left)
+    plan = R.bucket_plan(begins, total, mb(R.DEFAULT_BUCKET_MB))
+    assert len(plan) == 2 and plan[0][0] == 8 and plan[1][0] == 13          # last phase of each bucket
+    assert plan[0][2] == total and plan[1][1] == 0 and plan[0][1] == plan[1][2]
+    per_layer = R.bucket_plan(begins, total, mb(25.0))
+    assert len(per_layer) == 13
+    # the bf16 exchange has no CPU path: it must say so instead of silently exchanging fp32
+    red = R.GradReducer(torch.zeros(16), [8, 0], world=2, exchange_dtype=torch.bfloat16, min_bucket_mb=0.0)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        red._all_reduce_bf16(red.flat[:8])
+
+
 def _shard_worker(rank, world, port, tmp):
     sys.path.insert(0, ROOT)
     import torch.distributed as dist
