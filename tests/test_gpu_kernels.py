@@ -35,6 +35,11 @@ GEMM_CASES = [
     (768, 768, 1000, "nt", {"k_splits": 3}),                               # ragged K, split-K reduce-add
     (3072, 768, 12288, "nt", {"k_splits": 8}),                             # wgrad at the BASELINE size
     (12288, 2304, 768, "tn", {"bias": True}),                              # fused QKV at the BASELINE size
+    # side operand by TMA with blocks partly / wholly outside the operand, in the one-CTA kernel (M <= 128) and the pair one
+    (100, 320, 128, "tn", {"bias": True, "residual": True, "dropout": 0.1}),
+    (300, 192, 64, "nn", {"residual": True}),
+    (200, 192, 64, "nn_gelu_bwd", {}),
+    (96, 64, 64, "nn_gelu_bwd", {}),
 ]
 
 
