@@ -1,5 +1,6 @@
+"""Attention-output projection (M = 12288, N = K = 768: two waves of tiles) with each part of its epilogue switched on in\nturn, cold (L2 flushed) and back to back: shows what bias / dropout / residual cost when the last epilogue is exposed."""
 import os, sys
-ROOT = "/root/repo"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, ROOT + "/tools")
 import torch
 from __graft_entry__ import load_package
