@@ -1,4 +1,5 @@
-"""Attention-output projection (M = 12288, N = K = 768: two waves of tiles) with each part of its epilogue switched on in\nturn, cold (L2 flushed) and back to back: shows what bias / dropout / residual cost when the last epilogue is exposed."""
+"""Attention-output projection (M = 12288, N = K = 768: two waves of tiles) with each part of its epilogue switched on in
+turn, cold (L2 flushed) and back to back: shows what bias / dropout / residual cost when the last epilogue is exposed."""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, ROOT + "/tools")
