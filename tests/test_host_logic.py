@@ -135,13 +135,16 @@ def _gloo_worker(rank, world, port, tmp):
     dist.destroy_process_group()
 
 
-def test_gradient_allreduce_mean_gloo_world2(tmp_path):
+@pytest.mark.parametrize("world", [2, 3])
+def test_gradient_allreduce_mean_gloo(tmp_path, world):
     import torch.multiprocessing as mp
-    port = 29500 + os.getpid() % 2000
-    mp.spawn(_gloo_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
-    (m0, f0), (m1, f1) = (torch.load(tmp_path / f"r{r}.pt") for r in range(2))
-    torch.testing.assert_close(f0, (m0 + m1) / 2)   # reference semantic: DDP averages over ranks
-    assert torch.equal(f0, f1)
+    port = 29500 + os.getpid() % 2000 + 7 * world
+    mp.spawn(_gloo_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    loaded = [torch.load(tmp_path / f"r{r}.pt") for r in range(world)]
+    mean = sum(m for m, _ in loaded) / world
+    for _, f in loaded:
+        torch.testing.assert_close(f, mean)          # reference semantic: DDP averages over ranks
+        assert torch.equal(f, loaded[0][1])          # and every rank holds the same result
 
 
 def test_default_bucket_plan_is_two_buckets_for_bert_base(pkg):
